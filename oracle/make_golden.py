@@ -1,0 +1,177 @@
+"""TEST INFRASTRUCTURE ONLY -- generate `tests/golden/*` from the UNMODIFIED reference.
+
+Run in the build container (where /root/reference is mounted):
+
+    python oracle/make_golden.py
+
+Writes, for each case in `CASES`, `tests/golden/<name>.npz` holding the reference
+output for a seeded input and a seeded randomised state_dict (the generator
+`oracle.hat_oracle.randomized_state_dict` is ours, so the weights can be rebuilt
+on the GPU box without the reference), plus integer fixtures:
+`index_tables.npz` (relative position indices straight from the reference's
+buffers), `tile_rects.json` (tile geometry recovered by running the reference's
+`HATModel.tile_process` with a probe network) and `state_dict_manifest.json`
+(key -> shape/dtype for the five published variants).
+"""
+import json
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import hat_oracle as O          # noqa: E402
+from oracle import load_ref                # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+BASE = dict(in_chans=3, img_size=64, window_size=16, conv_scale=0.01, overlap_ratio=0.5,
+            img_range=1., mlp_ratio=2, upsampler="pixelshuffle", resi_connection="1conv")
+
+
+def variant(name):
+    v = dict(BASE)
+    if name == "HAT-S_x4":
+        v.update(embed_dim=144, depths=[6] * 6, num_heads=[6] * 6, compress_ratio=24, squeeze_factor=24, upscale=4)
+    elif name in ("HAT_x2", "HAT_x3", "HAT_x4"):
+        v.update(embed_dim=180, depths=[6] * 6, num_heads=[6] * 6, compress_ratio=3, squeeze_factor=30,
+                 upscale=int(name[-1]))
+    elif name == "HAT-L_x4":
+        v.update(embed_dim=180, depths=[6] * 12, num_heads=[6] * 12, compress_ratio=3, squeeze_factor=30, upscale=4)
+    else:
+        raise KeyError(name)
+    return v
+
+
+def mini(**over):
+    v = dict(BASE)
+    v.update(embed_dim=48, depths=[2, 2], num_heads=[6, 6], compress_ratio=3, squeeze_factor=30, upscale=4)
+    v.update(over)
+    return v
+
+
+# name -> (cfg, state_dict seed, input seed, input shape)
+CASES = {
+    "mini_x4_32x32":       (mini(), 1, 11, (1, 3, 32, 32)),
+    "mini_x2_32x48":       (mini(upscale=2), 2, 12, (1, 3, 32, 48)),
+    "mini_x3_48x32":       (mini(upscale=3), 3, 13, (1, 3, 48, 32)),
+    "mini_x4_16x16":       (mini(), 4, 14, (1, 3, 16, 16)),
+    "mini_x4_b3_32x32":    (mini(), 5, 15, (3, 3, 32, 32)),
+    "mini_x2_ocabesc":     (mini(upscale=2, ocab_esc_enable=True), 6, 16, (2, 3, 32, 32)),
+    "mini_x2_identity":    (mini(upscale=2, resi_connection="identity"), 7, 17, (1, 3, 32, 32)),
+    "mini_x4_range255":    (mini(img_range=255.), 8, 18, (1, 3, 32, 32)),
+    "hats_dims_x4_32x32":  (dict(BASE, embed_dim=144, depths=[2], num_heads=[6], compress_ratio=24,
+                                 squeeze_factor=24, upscale=4), 9, 19, (1, 3, 32, 32)),
+    "hat_dims_x4_32x32":   (dict(BASE, embed_dim=180, depths=[2], num_heads=[6], compress_ratio=3,
+                                 squeeze_factor=30, upscale=4), 10, 20, (2, 3, 32, 32)),
+    "hat_full_x4_64x64":   (variant("HAT_x4"), 21, 31, (1, 3, 64, 64)),
+}
+
+
+def gen_forward_cases():
+    for name, (cfg, sd_seed, x_seed, shape) in CASES.items():
+        torch.manual_seed(0)
+        net = load_ref.build_reference(cfg)
+        sd = O.randomized_state_dict(net.state_dict(), sd_seed)
+        net.load_state_dict(sd, strict=True)
+        x = torch.rand(shape, generator=torch.Generator().manual_seed(x_seed), dtype=torch.float32)
+        y = load_ref.reference_forward(net, x)
+        # restatement must agree before we commit the fixture
+        y2 = O.hat_forward(x, sd, cfg)
+        err = (y - y2).abs().max().item()
+        print(f"{name}: out {tuple(y.shape)} |y|max {y.abs().max():.3f}  oracle-vs-reference max-abs {err:.2e}")
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"),
+                            cfg=json.dumps(cfg), sd_seed=sd_seed, x_seed=x_seed,
+                            x_shape=np.array(shape), y=y.numpy(), torch_version=torch.__version__)
+
+
+def gen_index_tables():
+    torch.manual_seed(0)
+    net = load_ref.build_reference(mini())
+    np.savez_compressed(os.path.join(GOLD, "index_tables.npz"),
+                        rpi_sa=net.relative_position_index_SA.numpy(),
+                        rpi_oca=net.relative_position_index_OCA.numpy(),
+                        mask_32x48=net.calculate_mask((32, 48)).numpy())
+
+
+def gen_manifest():
+    man = {}
+    for name in ("HAT-S_x4", "HAT_x2", "HAT_x3", "HAT_x4", "HAT-L_x4"):
+        torch.manual_seed(0)
+        net = load_ref.build_reference(variant(name))
+        man[name] = {"cfg": variant(name),
+                     "params": sum(p.numel() for p in net.parameters()),
+                     "keys": {k: [list(v.shape), str(v.dtype)] for k, v in net.state_dict().items()}}
+    torch.manual_seed(0)
+    net = load_ref.build_reference(mini(upscale=2, ocab_esc_enable=True))
+    man["mini_x2_ocabesc"] = {"cfg": mini(upscale=2, ocab_esc_enable=True),
+                              "params": sum(p.numel() for p in net.parameters()),
+                              "keys": {k: [list(v.shape), str(v.dtype)] for k, v in net.state_dict().items()}}
+    with open(os.path.join(GOLD, "state_dict_manifest.json"), "w") as f:
+        json.dump(man, f)
+
+
+def gen_tile_rects():
+    """Drive the reference's HATModel.tile_process with a probe network whose output
+    encodes (call number, local y, local x); the input is an index image."""
+    load_ref.load_reference_hat()
+    import importlib.util
+    path = os.path.join(load_ref.REF_ROOT, "HAT", "hat", "models", "hat_model.py")
+    spec = importlib.util.spec_from_file_location("hat.models.hat_model", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = {}
+    for (h, w, ts, pad, scale) in [(1024, 1024, 256, 32, 4), (544, 960, 256, 32, 4), (96, 80, 32, 16, 2),
+                                   (64, 64, 64, 8, 3), (48, 112, 48, 16, 4)]:
+        calls = []
+
+        class Probe(torch.nn.Module):
+            def forward(self, t):
+                b, c, th, tw = t.shape
+                calls.append([int(t[0, 0, 0, 0]), int(t[0, 0, -1, -1]), th, tw])
+                o = torch.zeros(b, 3, th * scale, tw * scale)
+                o[:, 0] = len(calls) - 1
+                o[:, 1] = torch.arange(th * scale, dtype=torch.float32)[:, None]
+                o[:, 2] = torch.arange(tw * scale, dtype=torch.float32)[None, :]
+                return o
+
+        fake = types.SimpleNamespace()
+        fake.opt = {"tile": {"tile_size": ts, "tile_pad": pad}, "scale": scale}
+        fake.scale = scale
+        fake.net_g = Probe()
+        idx = torch.arange(h * w, dtype=torch.float32).view(1, 1, h, w).repeat(1, 3, 1, 1)
+        fake.img = idx
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            mod.HATModel.tile_process(fake)
+        o = fake.output[0].to(torch.int64).numpy()
+        rects = []
+        for i, (first, last, th, tw) in enumerate(calls):
+            ys, xs = np.nonzero(o[0] == i)
+            y0, x0 = divmod(first, w)
+            y1, x1 = divmod(last, w)
+            rects.append(dict(idx=i, in_x0=x0, in_x1=x1 + 1, in_y0=y0, in_y1=y1 + 1,
+                              out_x0=int(xs.min()), out_x1=int(xs.max()) + 1,
+                              out_y0=int(ys.min()), out_y1=int(ys.max()) + 1,
+                              crop_x0=int(o[2][ys.min(), xs.min()]), crop_x1=int(o[2][ys.max(), xs.max()]) + 1,
+                              crop_y0=int(o[1][ys.min(), xs.min()]), crop_y1=int(o[1][ys.max(), xs.max()]) + 1))
+            assert len(ys) == (rects[-1]["out_x1"] - rects[-1]["out_x0"]) * (rects[-1]["out_y1"] - rects[-1]["out_y0"])
+        out[f"{h}x{w}_ts{ts}_pad{pad}_s{scale}"] = rects
+        print(f"tile_rects {h}x{w} ts{ts} pad{pad}: {len(rects)} tiles")
+    with open(os.path.join(GOLD, "tile_rects.json"), "w") as f:
+        json.dump(out, f)
+
+
+if __name__ == "__main__":
+    if not load_ref.reference_available():
+        sys.exit("reference not mounted; goldens can only be generated in the build container")
+    os.makedirs(GOLD, exist_ok=True)
+    torch.set_num_threads(os.cpu_count())
+    gen_index_tables()
+    gen_tile_rects()
+    gen_manifest()
+    gen_forward_cases()
