@@ -1,0 +1,155 @@
+/* hatb200.h -- C ABI of the B200-native HAT forward (libhatb200.so).
+ *
+ * The reference has no native interface for this path: its boundary is the Python
+ * class `HAT(nn.Module)` (reference HAT/hat/archs/hat_arch.py:607-859) built by
+ * `build_network` (HAT/ESC/basicsr/archs/__init__.py:18-24) and called as
+ * `net(img)` (HAT/hat/models/hat_model.py:28-38, :80-88).  This header is the
+ * contract a host binds instead; each entry cites the reference
+ * lines it replaces.  Plain C: pointers, sizes, a CUDA stream passed as void*.
+ *
+ * Conventions: every function returns 0 on success and a negative
+ * HATB200_E* code otherwise (never aborts); `hatb200_last_error()` gives a
+ * thread-local message.  The caller owns all tensors and the workspace; the
+ * handle owns only packed weight copies.  All work is enqueued on the given
+ * stream, no hidden synchronisation.  A handle is bound to the CUDA device that
+ * was current at `hatb200_create`; it is not thread-safe, distinct handles are.
+ * There is no CPU path: without a CUDA device every compute entry fails.
+ */
+#ifndef HATB200_H
+#define HATB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HATB200_VERSION 100
+#define HATB200_MAX_LAYERS 32
+
+enum { HATB200_F32 = 0, HATB200_BF16 = 1, HATB200_F16 = 2, HATB200_I64 = 3 };
+
+enum {
+  HATB200_OK = 0,
+  HATB200_EINVAL = -1,   /* bad argument / shape (reference: RuntimeError from .view) */
+  HATB200_ECUDA = -2,    /* CUDA runtime error */
+  HATB200_EPARAM = -3,   /* missing / mis-shaped state_dict entry */
+  HATB200_ENOMEM = -4,   /* workspace too small */
+  HATB200_EUNSUPPORTED = -5
+};
+
+/* Mirrors the constructor arguments of the reference HAT (hat_arch.py:610-644)
+ * after the host has resolved derived sizes. */
+typedef struct hatb200_config {
+  int32_t struct_size;            /* sizeof(hatb200_config), ABI guard */
+  int32_t in_chans;               /* 1..4 */
+  int32_t embed_dim;              /* C */
+  int32_t num_layers;             /* len(depths) */
+  int32_t depths[HATB200_MAX_LAYERS];
+  int32_t num_heads[HATB200_MAX_LAYERS];
+  int32_t window_size;            /* ws */
+  int32_t overlap_win_size;       /* int(ws*overlap_ratio)+ws, hat_arch.py:289 */
+  int32_t cab_mid;                /* C // compress_ratio, hat_arch.py:84 */
+  int32_t ffn_hidden;             /* int(C*mlp_ratio), hat_arch.py:98 */
+  int32_t esc_pdim, esc_kernel;   /* hat_arch.py:638-639 */
+  int32_t ocab_esc_enable, ocab_esc_pdim, ocab_esc_kernel; /* hat_arch.py:641-643 */
+  int32_t upscale;                /* 2^n or 3, hat_arch.py:593-605 */
+  int32_t upsampler;              /* 1 = 'pixelshuffle', 0 = none (hat_arch.py:852) */
+  int32_t resi_conv;              /* 1 = '1conv', 0 = 'identity' (hat_arch.py:543-548) */
+  int32_t patch_norm;             /* hat_arch.py:683-688 */
+  int32_t qkv_bias;
+  float conv_scale;               /* hat_arch.py:236 */
+  float img_range;                /* hat_arch.py:850 */
+  float qk_scale;                 /* <=0: head_dim^-0.5 (hat_arch.py:288) */
+  float mean[4];                  /* hat_arch.py:658-662 */
+} hatb200_config;
+
+typedef struct hatb200_handle hatb200_handle;
+
+int hatb200_version(void);
+const char* hatb200_last_error(void);
+
+/* HAT.__init__ (hat_arch.py:610-759): validates the configuration. */
+int hatb200_create(const hatb200_config* cfg, hatb200_handle** out);
+void hatb200_destroy(hatb200_handle* h);
+
+/* load_state_dict (basicsr base_model.py:289-315): borrow one tensor of the
+ * reference state_dict layout by its key.  `dev_ptr` must stay valid until the
+ * next hatb200_pack().  Unknown keys -> HATB200_EPARAM. */
+int hatb200_set_param(hatb200_handle* h, const char* key, const void* dev_ptr, int dtype,
+                      const int64_t* shape, int ndim);
+/* Number / names of the state_dict entries this configuration expects. */
+int hatb200_num_params(hatb200_handle* h);
+const char* hatb200_param_key(hatb200_handle* h, int i);
+/* Build the packed device copies (allocates; call outside stream capture). */
+int hatb200_pack(hatb200_handle* h, void* stream);
+
+/* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1). */
+int hatb200_set_option(hatb200_handle* h, const char* name, int value);
+
+/* Bytes of scratch needed by hatb200_forward for (B,H,W) in the given compute
+ * dtype (HATB200_F32 or HATB200_BF16). */
+int hatb200_workspace_bytes(hatb200_handle* h, int B, int H, int W, int compute_dtype, size_t* out);
+
+/* HAT.forward (hat_arch.py:848-859).  x: (B,in_chans,H,W) NCHW contiguous,
+ * y: (B,in_chans,H*s,W*s) NCHW; x_dtype selects the arithmetic: F32 -> fp32
+ * CUDA-core path (parity mode), BF16 -> bf16 tensor-core path (fp32
+ * accumulate).  H and W must be multiples of window_size (the reference raises
+ * from calculate_mask -> window_partition, hat_arch.py:124-128, :831). */
+int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W,
+                    void* y, int y_dtype, void* workspace, size_t ws_bytes, void* stream);
+/* Number of kernels launched by the last hatb200_forward on this handle. */
+int hatb200_last_launch_count(hatb200_handle* h);
+
+/* HATModel.tile_process geometry (hat_model.py:52-108).  Fills up to `cap`
+ * rectangles of 12 ints each {in_x0,in_x1,in_y0,in_y1,out_x0,out_x1,out_y0,out_y1,
+ * crop_x0,crop_x1,crop_y0,crop_y1} in the reference's tile order; returns the
+ * number of tiles (host-only, no CUDA). */
+int hatb200_tile_plan(int height, int width, int tile_size, int tile_pad, int scale,
+                      int32_t* rects, int cap);
+/* dst[:, :, out rect] = src[:, :, crop rect] for NCHW images on device
+ * (hat_model.py:106-108). */
+int hatb200_crop_place(const void* src, int dtype, int B, int C, int src_h, int src_w,
+                       int crop_y0, int crop_x0, void* dst, int dst_h, int dst_w,
+                       int out_y0, int out_x0, int rh, int rw, void* stream);
+/* F.pad(img, (0,pw,0,ph), 'reflect') of HATModel.pre_process (hat_model.py:16-26). */
+int hatb200_reflect_pad(const void* src, int dtype, int B, int C, int h, int w,
+                        void* dst, int ph, int pw, void* stream);
+
+/* ---- single-kernel entry points (unit tests, ncu) ------------------------ */
+
+/* nn.LayerNorm(C), eps 1e-5 (hat_arch.py:222,:237,:331,:392,:844).
+ * x fp32 (M,C) -> out (M,out_pitch) of out_dtype; optional compact copy of the
+ * first `head_c` channels to out_head (M,head_c). */
+int hatb200_layernorm(const float* x, int M, int C, const float* gamma, const float* beta,
+                      void* out, int out_dtype, int out_pitch, void* out_head, int head_c,
+                      void* stream);
+
+/* Dense conv KHxKW (stride 1, zero pad K/2) / Linear (1x1) over channels-last
+ * tokens: out[m,n] = sum_tap sum_c in[pix(m)+tap, coff+c] * w[n,c,tap] + bias[n].
+ * `w` is the PyTorch OIHW fp32 weight (packed internally per call: test entry).
+ * act: 0 none, 1 exact GELU, 2 LeakyReLU(0.01).  use_tc=1 runs the tcgen05
+ * kernel (dtype must be BF16). */
+int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, int Cin,
+                        int B, int H, int W, const float* w, const float* bias, int N,
+                        int KH, int KW, int act, void* out, int out_pitch, int use_tc,
+                        void* stream);
+
+/* OCAB attention core (hat_arch.py:354-388): qkv (M, pitch) holding q (already
+ * scaled) at channel 0, k at C, v at 2C; bias_table (heads, (ws+ows-1)^2)
+ * compact relative-position table indexed by (ky-qy+ws-1, kx-qx+ws-1);
+ * out (M,out_pitch).  Keys outside the image are zero vectors, not masked. */
+int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, int W, int C,
+                           int heads, int ws, int ows, const float* bias_table,
+                           void* out, int out_pitch, int use_tc, void* stream);
+
+/* GatedDconvFFN middle (hat_arch.py:112-116): depthwise 3x3 (+bias) over 2*hid
+ * channels, then proj * SiLU(gate).  in (M,in_pitch) -> out (M,out_pitch). */
+int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, int W, int hid,
+                        const float* dw_w /* (2hid,1,3,3) */, const float* dw_b,
+                        void* out, int out_pitch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HATB200_H */

@@ -1,0 +1,113 @@
+// common.cuh -- shared device/host helpers for libhatb200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/hatb200.h"
+
+typedef __nv_bfloat16 bf16;
+
+namespace hb {
+
+// ---- error plumbing (thread-local message, negative codes; never abort) ----
+void set_error(const char* fmt, ...);
+extern thread_local int g_launches;   // kernels launched since last reset
+
+#define HB_CHECK_CUDA(expr)                                                        \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) {                                                       \
+      hb::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+      return HATB200_ECUDA;                                                        \
+    }                                                                              \
+  } while (0)
+
+#define HB_CHECK_LAUNCH()                                                          \
+  do {                                                                             \
+    hb::g_launches++;                                                              \
+    cudaError_t _e = cudaPeekAtLastError();                                        \
+    if (_e != cudaSuccess) {                                                       \
+      hb::set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return HATB200_ECUDA;                                                        \
+    }                                                                              \
+  } while (0)
+
+#define HB_REQUIRE(cond, code, ...)                                                \
+  do {                                                                             \
+    if (!(cond)) {                                                                 \
+      hb::set_error(__VA_ARGS__);                                                  \
+      return (code);                                                               \
+    }                                                                              \
+  } while (0)
+
+#define HB_TRY(expr)                                                               \
+  do {                                                                             \
+    int _r = (expr);                                                               \
+    if (_r != 0) return _r;                                                        \
+  } while (0)
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline int round_up(int a, int b) { return cdiv(a, b) * b; }
+
+// ---- storage-type helpers: arithmetic is always fp32 ----
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f(__half v) { return __half2float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f<__half>(float v) { return __float2half_rn(v); }
+
+// exact GELU (approximate='none'), SiLU, LeakyReLU(0.01)
+__device__ __forceinline__ float gelu_f(float v) { return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f)); }
+__device__ __forceinline__ float silu_f(float v) { return v / (1.0f + expf(-v)); }
+__device__ __forceinline__ float lrelu_f(float v) { return v > 0.f ? v : 0.01f * v; }
+__device__ __forceinline__ float sigmoid_f(float v) { return 1.0f / (1.0f + expf(-v)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_LRELU = 2 };
+
+// Epilogue shared by the CUDA-core and tcgen05 conv/GEMM kernels.
+// value order:  v = acc + bias[n]; v += dyn-depthwise term; v *= scale (n < scale_ncols);
+//               v = act(v); v += eca_coef * eca_scale[b,n] * U[m,n]; v += resid[m,n]
+struct Epilogue {
+  const float* bias = nullptr;       // [N]
+  int act = ACT_NONE;
+  float out_scale = 1.f;             // applied to columns n < scale_ncols
+  int scale_ncols = 0;
+  const float* resid = nullptr;      // fp32 (M, resid_pitch)
+  int resid_pitch = 0;
+  const void* eca_u = nullptr;       // T (M, eca_pitch): CAB conv2 output
+  int eca_pitch = 0;
+  const float* eca_scale = nullptr;  // (B, N) sigmoid gate
+  float eca_coef = 0.f;              // conv_scale
+  const void* dyn_x = nullptr;       // T (M, dyn_pitch) compact first-pdim channels of the conv input
+  int dyn_pitch = 0;
+  const float* dyn_k = nullptr;      // (B, pdim, 9) per-sample depthwise 3x3 kernels
+  float* out_f32 = nullptr;          // fp32 (M, out_f32_pitch) residual-stream output
+  int out_f32_pitch = 0;
+  void* out_t = nullptr;             // T (M', out_t_pitch) activation output at channel offset out_t_coff
+  int out_t_pitch = 0;
+  int out_t_coff = 0;
+  int out_t_zero_to = 0;             // columns [N, out_t_zero_to) are written as zero (K padding of the consumer)
+  int shuffle_r = 1;                 // PixelShuffle factor folded into the store (hat_arch.py:593-605)
+  // fused LayerNorm of the fp32 result row (tcgen05 kernel only; the CUDA-core path runs layernorm separately)
+  const float* ln_gamma = nullptr;
+  const float* ln_beta = nullptr;
+  void* ln_out = nullptr;            // T (M, ln_pitch)
+  int ln_pitch = 0;
+  void* ln_head = nullptr;           // T (M, ln_head_c) compact copy of the first channels
+  int ln_head_c = 0;
+  float* ln_head_colsum = nullptr;   // fp32 (num_m_tiles, ln_head_c) per-tile column sums of the LN head
+  float* colsum = nullptr;           // fp32 (num_m_tiles, N) per-tile column sums of v (GAP partials)
+};
+
+}  // namespace hb

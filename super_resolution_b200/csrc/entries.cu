@@ -1,0 +1,125 @@
+// entries.cu -- tile-mode helpers and single-kernel C entry points (unit tests, ncu).
+#include <math.h>
+
+#include "model.cuh"
+
+using namespace hb;
+
+namespace {
+struct TmpPool {   // test entry points pack weights per call; freed after a sync
+  std::vector<void*> ptrs;
+  ~TmpPool() { for (void* p : ptrs) cudaFree(p); }
+  int alloc(void** out, size_t bytes, cudaStream_t st) {
+    HB_CHECK_CUDA(cudaMalloc(out, bytes ? bytes : 16));
+    ptrs.push_back(*out);
+    HB_CHECK_CUDA(cudaMemsetAsync(*out, 0, bytes ? bytes : 16, st));
+    return 0;
+  }
+};
+}  // namespace
+
+extern "C" {
+
+// HATModel.tile_process geometry, hat_model.py:52-108 (integer bookkeeping, bit-exact).
+int hatb200_tile_plan(int height, int width, int tile_size, int tile_pad, int scale, int32_t* rects, int cap) {
+  HB_REQUIRE(height > 0 && width > 0 && tile_size > 0 && tile_pad >= 0 && scale > 0, HATB200_EINVAL,
+             "tile_plan: bad arguments");
+  int tiles_x = (width + tile_size - 1) / tile_size;
+  int tiles_y = (height + tile_size - 1) / tile_size;
+  int n = 0;
+  for (int y = 0; y < tiles_y; y++) {
+    for (int x = 0; x < tiles_x; x++, n++) {
+      if (!rects || n >= cap) continue;
+      int x0 = x * tile_size, y0 = y * tile_size;
+      int x1 = x0 + tile_size < width ? x0 + tile_size : width;
+      int y1 = y0 + tile_size < height ? y0 + tile_size : height;
+      int x0p = x0 - tile_pad > 0 ? x0 - tile_pad : 0, x1p = x1 + tile_pad < width ? x1 + tile_pad : width;
+      int y0p = y0 - tile_pad > 0 ? y0 - tile_pad : 0, y1p = y1 + tile_pad < height ? y1 + tile_pad : height;
+      int32_t* r = rects + (size_t)n * 12;
+      r[0] = x0p; r[1] = x1p; r[2] = y0p; r[3] = y1p;
+      r[4] = x0 * scale; r[5] = x1 * scale; r[6] = y0 * scale; r[7] = y1 * scale;
+      r[8] = (x0 - x0p) * scale; r[9] = r[8] + (x1 - x0) * scale;
+      r[10] = (y0 - y0p) * scale; r[11] = r[10] + (y1 - y0) * scale;
+    }
+  }
+  return n;
+}
+
+int hatb200_crop_place(const void* src, int dtype, int B, int C, int src_h, int src_w, int crop_y0, int crop_x0,
+                       void* dst, int dst_h, int dst_w, int out_y0, int out_x0, int rh, int rw, void* stream) {
+  HB_REQUIRE(src && dst, HATB200_EINVAL, "crop_place: null tensor");
+  return launch_crop_place(src, dtype, B, C, src_h, src_w, crop_y0, crop_x0, dst, dst_h, dst_w, out_y0, out_x0, rh, rw,
+                           (cudaStream_t)stream);
+}
+
+int hatb200_reflect_pad(const void* src, int dtype, int B, int C, int h, int w, void* dst, int ph, int pw,
+                        void* stream) {
+  HB_REQUIRE(src && dst, HATB200_EINVAL, "reflect_pad: null tensor");
+  return launch_reflect_pad(src, dtype, B, C, h, w, dst, ph, pw, (cudaStream_t)stream);
+}
+
+int hatb200_layernorm(const float* x, int M, int C, const float* gamma, const float* beta, void* out, int out_dtype,
+                      int out_pitch, void* out_head, int head_c, void* stream) {
+  HB_REQUIRE(x && gamma && beta && out && out_pitch >= C, HATB200_EINVAL, "layernorm: bad arguments");
+  return launch_layernorm(x, M, C, gamma, beta, out, out_dtype, out_pitch, out_pitch, out_head, head_c,
+                          (cudaStream_t)stream);
+}
+
+int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, int Cin, int B, int H, int W,
+                        const float* w, const float* bias, int N, int KH, int KW, int act, void* out, int out_pitch,
+                        int use_tc, void* stream) {
+  HB_REQUIRE(in && w && out && N >= 1 && Cin >= 1, HATB200_EINVAL, "conv_tokens: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  TmpPool pool;
+  ConvArgs a{in, in_pitch, in_coff, Cin, B, H, W, KH, KW, N};
+  Epilogue ep;
+  ep.bias = bias; ep.act = act; ep.out_t = out; ep.out_t_pitch = out_pitch;
+  int taps = KH * KW, r;
+  if (use_tc) {
+    HB_REQUIRE(dtype == HATB200_BF16, HATB200_EINVAL, "conv_tokens: the tcgen05 kernel needs bf16 activations");
+    int Npad = round_up(N, 16), Kpad = Cin <= 16 ? 16 : (Cin <= 32 ? 32 : round_up(Cin, 64));
+    bf16* w16;
+    HB_TRY(pool.alloc((void**)&w16, (size_t)taps * Npad * Kpad * sizeof(bf16), st));
+    HB_TRY(launch_pack_w_bf16(w, HATB200_F32, N, Cin, taps, w16, Npad, Kpad, 0, Cin, st));
+    HB_REQUIRE(tapconv_tc_supported(a, Npad, Kpad, ep), HATB200_EUNSUPPORTED,
+               "conv_tokens: shape not supported by the tcgen05 kernel");
+    r = launch_tapconv_tc(a, w16, Npad, Kpad, ep, st);
+  } else {
+    int Np = round_up(N, 64);
+    float* w32;
+    HB_TRY(pool.alloc((void**)&w32, (size_t)taps * Cin * Np * sizeof(float), st));
+    HB_TRY(launch_pack_w_f32(w, HATB200_F32, N, Cin, taps, w32, Np, Np, st));
+    r = launch_tapconv_simt(dtype, a, w32, Np, ep, st);
+  }
+  cudaError_t e = cudaStreamSynchronize(st);   // test entry: the packed copy dies with this call
+  if (r == 0 && e != cudaSuccess) { set_error("conv_tokens: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
+  return r;
+}
+
+int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, int W, int C, int heads, int ws,
+                           int ows, const float* bias_table, void* out, int out_pitch, int use_tc, void* stream) {
+  HB_REQUIRE(qkv && bias_table && out, HATB200_EINVAL, "ocab_attention: null tensor");
+  AttnArgs a{qkv, pitch, B, H, W, C, heads, ws, ows, bias_table, out, out_pitch, 0};
+  if (use_tc) {
+    HB_REQUIRE(dtype == HATB200_BF16 && attn_tc_supported(a), HATB200_EUNSUPPORTED,
+               "ocab_attention: shape/dtype not supported by the tcgen05 kernel");
+    return launch_attn_tc(a, (cudaStream_t)stream);
+  }
+  return launch_attn_simt(dtype, a, (cudaStream_t)stream);
+}
+
+int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, int W, int hid, const float* dw_w,
+                        const float* dw_b, void* out, int out_pitch, void* stream) {
+  HB_REQUIRE(in && dw_w && dw_b && out, HATB200_EINVAL, "dwconv_gate: null tensor");
+  cudaStream_t st = (cudaStream_t)stream;
+  TmpPool pool;
+  float* wt;
+  HB_TRY(pool.alloc((void**)&wt, (size_t)9 * 2 * hid * sizeof(float), st));
+  HB_TRY(launch_pack_w_f32(dw_w, HATB200_F32, 2 * hid, 1, 9, wt, 2 * hid, 2 * hid, st));
+  int r = launch_dwgate(in, dtype, in_pitch, B, H, W, hid, wt, dw_b, out, out_pitch, hid, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (r == 0 && e != cudaSuccess) { set_error("dwconv_gate: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
+  return r;
+}
+
+}  // extern "C"

@@ -1,0 +1,344 @@
+// forward.cu -- hatb200_forward: the HAT forward (hat_arch.py:848-859) as one stream of
+// kernel launches over a single channels-last token layout.  No layout copies
+// (reference: 691 copy_ calls per forward), no attention mask
+// (dead in the reference, hat_arch.py:831), no unfold / softmax materialisation.
+//
+// Data layout in HBM (M = B*H*W tokens in (b, y, x) order):
+//   residual stream  fp32 (M, C)      -- S (conv_first out, long skip), XA (group input), XB (running)
+//   activations      T    (M, pitch)  -- T = bf16 (tensor-core path) or fp32 (parity path); pitch = C rounded
+//                                        up to 64, pad columns are written as zero (K padding of the consumer)
+#include "model.cuh"
+
+namespace hb {
+
+struct Dims {
+  int B, H, W, M, C, Cp, mid, midp, hid, hp2, hp4, qkvp, h1p, pdim, opdim;
+  int dt;      // storage dtype of activations
+  size_t es;   // element size of T
+};
+
+static Dims make_dims(const hatb200_config& c, int B, int H, int W, int dt) {
+  Dims d;
+  d.B = B; d.H = H; d.W = W; d.M = B * H * W;
+  d.C = c.embed_dim; d.Cp = round_up(d.C, 64);
+  d.mid = c.cab_mid; d.midp = round_up(d.mid, 64);
+  d.hid = c.ffn_hidden; d.hp2 = round_up(d.hid, 64); d.hp4 = round_up(2 * d.hid, 64);
+  d.qkvp = round_up(3 * d.C, 64);
+  d.h1p = d.hp4 > d.qkvp ? d.hp4 : d.qkvp;
+  d.pdim = c.esc_pdim; d.opdim = c.ocab_esc_enable ? c.ocab_esc_pdim : 0;
+  d.dt = dt; d.es = dt == HATB200_F32 ? 4 : 2;
+  return d;
+}
+
+static void plan(const hatb200_config& c, const Dims& d, char* base, Workspace& w) {
+  size_t off = 0;
+  auto take = [&](size_t bytes) -> void* {
+    void* p = base ? base + off : nullptr;
+    off += (bytes + 255) & ~(size_t)255;
+    return p;
+  };
+  size_t M = (size_t)d.M;
+  w.S = (float*)take(M * d.C * 4);
+  w.XA = (float*)take(M * d.C * 4);
+  w.XB = (float*)take(M * d.C * 4);
+  w.XN = take(M * d.Cp * d.es);
+  w.XN2 = take(M * d.Cp * d.es);
+  w.U = take(M * d.Cp * d.es);
+  int pd = d.pdim > d.opdim ? d.pdim : d.opdim;
+  w.X16 = take(M * pd * d.es);
+  w.T1 = take(M * d.midp * d.es);
+  w.H1 = take(M * d.h1p * d.es);
+  size_t gp = d.hp2 > d.Cp ? d.hp2 : d.Cp;
+  w.G = take(M * gp * d.es);
+  if (c.upsampler == 1) {
+    int s = c.upscale;
+    w.F64 = take(M * 64 * d.es);
+    if (s == 3) w.UP1 = take(M * 9 * 64 * d.es);
+    if (s == 2 || s == 4) w.UP1 = take(M * 4 * 64 * d.es);
+    if (s == 4) w.UP2 = take(M * 16 * 64 * d.es);
+  }
+  int nchunk = colsum_chunks(d.H * d.W);
+  w.part = (float*)take((size_t)d.B * nchunk * d.C * 4);
+  w.part16 = (float*)take((size_t)d.B * nchunk * 64 * 4);
+  w.eca_s = (float*)take((size_t)d.B * d.C * 4);
+  w.dyn = (float*)take((size_t)d.B * 64 * 9 * 4);
+  w.bytes = off;
+}
+
+struct Fwd {
+  hatb200_handle* h;
+  Dims d;
+  Workspace w;
+  cudaStream_t st;
+
+  bool tc() const { return h->use_tc && d.dt == HATB200_BF16; }
+
+  int dbg(const char* what) {
+    if (!h->sync_debug) return 0;
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+      set_error("forward: '%s' failed: %s", what, cudaGetErrorString(e));
+      return HATB200_ECUDA;
+    }
+    return 0;
+  }
+
+  // dense conv / linear over tokens; tensor cores when available for this shape
+  int conv(const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
+    ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
+    if (!ep.bias) ep.bias = cw.bias;
+    if (tc() && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
+      HB_TRY(launch_tapconv_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
+      return dbg("tapconv_tc");
+    }
+    // CUDA-core path: LayerNorm / column sums are separate kernels
+    Epilogue e2 = ep;
+    e2.ln_gamma = e2.ln_beta = nullptr; e2.ln_out = e2.ln_head = nullptr;
+    e2.ln_head_colsum = nullptr; e2.colsum = nullptr;
+    HB_TRY(launch_tapconv_simt(d.dt, a, cw.w32, cw.Np, e2, st));
+    HB_TRY(dbg("tapconv_simt"));
+    int hw = H * W;
+    if (ep.ln_out) {
+      HB_REQUIRE(ep.out_f32 != nullptr, HATB200_EINVAL, "conv: fused LN needs the fp32 stream output");
+      HB_TRY(launch_layernorm(ep.out_f32, d.B * hw, cw.O, ep.ln_gamma, ep.ln_beta, ep.ln_out, d.dt, ep.ln_pitch,
+                              ep.ln_pitch, ep.ln_head, ep.ln_head_c, st));
+      if (ep.ln_head_colsum)
+        HB_TRY(launch_colsum(ep.ln_head, d.dt, ep.ln_head_c, d.B, hw, ep.ln_head_c, ep.ln_head_colsum, st));
+    }
+    if (ep.colsum) HB_TRY(launch_colsum(ep.out_t, d.dt, ep.out_t_pitch, d.B, hw, cw.O, ep.colsum, st));
+    return dbg("conv tail");
+  }
+
+  // standalone LayerNorm of the fp32 stream (+ compact head and its column sums)
+  int ln(const float* x, const LNW& n, void* out, int head_c) {
+    HB_TRY(launch_layernorm(x, d.M, d.C, n.g, n.b, out, d.dt, d.Cp, d.Cp, head_c ? w.X16 : nullptr, head_c, st));
+    if (head_c) HB_TRY(launch_colsum(w.X16, d.dt, head_c, d.B, d.H * d.W, head_c, w.part16, st));
+    return dbg("layernorm");
+  }
+
+  void set_ln(Epilogue& ep, const LNW* n, void* out, int head_c) {
+    if (!n) return;
+    ep.ln_gamma = n->g; ep.ln_beta = n->b; ep.ln_out = out; ep.ln_pitch = d.Cp;
+    if (head_c) { ep.ln_head = w.X16; ep.ln_head_c = head_c; ep.ln_head_colsum = w.part16; }
+  }
+
+  // ESC ConvAttn core on xn (esc_arch.py:119-123): writes the mixed first-pdim channels into
+  // dst[:, :pdim] (dst already holds xn elsewhere).  Needs X16 + part16 from the preceding LN.
+  int esc_mix(const EscW& e, void* dst) {
+    int nchunk = colsum_chunks(d.H * d.W);
+    HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
+    Epilogue ep;
+    ep.dyn_x = w.X16; ep.dyn_pitch = e.pdim; ep.dyn_k = w.dyn;
+    ep.out_t = dst; ep.out_t_pitch = d.Cp; ep.out_t_coff = 0;
+    return conv(e.plk, w.X16, e.pdim, 0, d.H, d.W, ep);
+  }
+
+  // HAB.forward (hat_arch.py:217-238).  Entry: XN = norm1(src) (+X16, part16).  Exit: dst = block output
+  // and XN = next_ln(dst) (+X16) when next_ln is given.
+  int hab(const HabW& b, const float* src, float* dst, const LNW* next_ln, int next_head) {
+    const hatb200_config& c = h->cfg;
+    int nchunk = colsum_chunks(d.H * d.W);
+    {  // CAB conv1 + GELU
+      Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.T1; ep.out_t_pitch = d.midp; ep.out_t_zero_to = d.midp;
+      HB_TRY(conv(b.cab0, w.XN, d.Cp, 0, d.H, d.W, ep));
+    }
+    {  // CAB conv2 -> U, with GAP partials for ECA
+      Epilogue ep; ep.out_t = w.U; ep.out_t_pitch = d.Cp; ep.colsum = w.part;
+      HB_TRY(conv(b.cab2, w.T1, d.midp, 0, d.H, d.W, ep));
+      HB_TRY(launch_eca_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, st));
+    }
+    HB_TRY(esc_mix(b.esc, w.XN));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
+    {  // aggr 1x1 + HAB combine (hat_arch.py:236) [+ norm2]
+      Epilogue ep;
+      ep.eca_u = w.U; ep.eca_pitch = d.Cp; ep.eca_scale = w.eca_s; ep.eca_coef = c.conv_scale;
+      ep.resid = src; ep.resid_pitch = d.C; ep.out_f32 = dst; ep.out_f32_pitch = d.C;
+      set_ln(ep, &b.n2, w.XN2, 0);
+      HB_TRY(conv(b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
+    }
+    {  // GatedDconvFFN (hat_arch.py:107-119)
+      Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.hp4;
+      HB_TRY(conv(b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(launch_dwgate(w.H1, d.dt, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, w.G, d.hp2, d.hp2, st));
+      HB_TRY(dbg("dwgate"));
+      Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
+      set_ln(e2, next_ln, w.XN, next_head);
+      HB_TRY(conv(b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
+    }
+    return 0;
+  }
+
+  // OCAB.forward (hat_arch.py:326-393).  Entry: XN = norm1(x) (+X16 when esc).  x updated in place.
+  // Exit: XN2 = T copy of x (input of the RHAG conv; XN receives that conv's fused LN) when want_copy.
+  int ocab(const OcabW& o, float* x, bool want_copy) {
+    const hatb200_config& c = h->cfg;
+    int dh = d.C / o.heads;
+    float scale = c.qk_scale > 0.f ? c.qk_scale : 1.0f / sqrtf((float)dh);
+    if (c.ocab_esc_enable) {   // K/V from y = ConvAttnWrapper(xn) (hat_arch.py:336-344)
+      HB_CHECK_CUDA(cudaMemcpyAsync(w.XN2, w.XN, (size_t)d.M * d.Cp * d.es, cudaMemcpyDeviceToDevice, st));
+      HB_TRY(esc_mix(o.esc, w.XN2));
+      Epilogue ey; ey.out_t = w.U; ey.out_t_pitch = d.Cp; ey.out_t_zero_to = d.Cp;
+      HB_TRY(conv(o.esc.aggr, w.XN2, d.Cp, 0, d.H, d.W, ey));
+      Epilogue eq; eq.out_scale = scale; eq.scale_ncols = d.C; eq.out_t = w.H1; eq.out_t_pitch = d.qkvp;
+      HB_TRY(conv(o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
+      Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = d.qkvp; ek.out_t_coff = d.C;
+      HB_TRY(conv(o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
+    } else {
+      Epilogue ep; ep.out_scale = scale; ep.scale_ncols = d.C; ep.out_t = w.H1; ep.out_t_pitch = d.qkvp;
+      HB_TRY(conv(o.qkv, w.XN, d.Cp, 0, d.H, d.W, ep));
+    }
+    AttnArgs a{w.H1, d.qkvp, d.B, d.H, d.W, d.C, o.heads, c.window_size, c.overlap_win_size, o.bias_compact,
+               w.G, d.Cp, d.Cp};
+    if (tc() && attn_tc_supported(a)) HB_TRY(launch_attn_tc(a, st));
+    else HB_TRY(launch_attn_simt(d.dt, a, st));
+    HB_TRY(dbg("attention"));
+    {  // proj + shortcut, norm2
+      Epilogue ep; ep.resid = x; ep.resid_pitch = d.C; ep.out_f32 = x; ep.out_f32_pitch = d.C;
+      set_ln(ep, &o.n2, w.XN2, 0);
+      HB_TRY(conv(o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
+    }
+    {  // MLP (hat_arch.py:309-313)
+      Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.H1; ep.out_t_pitch = d.hp2; ep.out_t_zero_to = d.hp2;
+      HB_TRY(conv(o.mlp0, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      Epilogue e2; e2.resid = x; e2.resid_pitch = d.C; e2.out_f32 = x; e2.out_f32_pitch = d.C;
+      if (want_copy) { e2.out_t = w.XN2; e2.out_t_pitch = d.Cp; e2.out_t_zero_to = d.Cp; }
+      HB_TRY(conv(o.mlp2, w.H1, d.hp2, 0, d.H, d.W, e2));
+    }
+    return 0;
+  }
+
+  int run(const void* x, int x_dt, void* y, int y_dt) {
+    const hatb200_config& c = h->cfg;
+    if (c.upsampler != 1)   // hat_arch.py:852: no tail -> only the (de)normalisation remains
+      return launch_affine_roundtrip(x, x_dt, d.B, c.in_chans, d.H * d.W, c.mean, c.img_range, y, y_dt, st);
+    HB_TRY(launch_conv_first(x, x_dt, d.B, c.in_chans, d.H, d.W, h->conv_first_w, h->conv_first_b, d.C, c.mean,
+                             c.img_range, w.S, st));
+    HB_TRY(dbg("conv_first"));
+    // patch_embed (+norm) -> XA: the running stream at the first group input (hat_arch.py:836)
+    if (c.patch_norm) {
+      HB_TRY(launch_layernorm(w.S, d.M, d.C, h->pe_norm.g, h->pe_norm.b, w.XA, HATB200_F32, d.C, d.C, nullptr, 0, st));
+    } else {
+      HB_CHECK_CUDA(cudaMemcpyAsync(w.XA, w.S, (size_t)d.M * d.C * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    // first LN of the first block
+    auto first_ln_of = [&](int L) -> const LNW* {
+      const LayerW& lw = h->layers[L];
+      return lw.habs.empty() ? &lw.ocab.n1 : &lw.habs[0].n1;
+    };
+    auto first_head_of = [&](int L) -> int {
+      const LayerW& lw = h->layers[L];
+      return lw.habs.empty() ? d.opdim : d.pdim;
+    };
+    HB_TRY(ln(w.XA, *first_ln_of(0), w.XN, first_head_of(0)));
+    for (int L = 0; L < c.num_layers; L++) {
+      const LayerW& lw = h->layers[L];
+      int nb = (int)lw.habs.size();
+      const float* src = w.XA;       // RHAG input stays in XA; blocks run in XB
+      for (int i = 0; i < nb; i++) {
+        const LNW* nl = i + 1 < nb ? &lw.habs[i + 1].n1 : &lw.ocab.n1;
+        int nh = i + 1 < nb ? d.pdim : d.opdim;
+        HB_TRY(hab(lw.habs[i], src, w.XB, nl, nh));
+        src = w.XB;
+      }
+      if (nb == 0) HB_CHECK_CUDA(cudaMemcpyAsync(w.XB, w.XA, (size_t)d.M * d.C * 4, cudaMemcpyDeviceToDevice, st));
+      HB_TRY(ocab(lw.ocab, w.XB, c.resi_conv != 0));
+      // RHAG tail (hat_arch.py:555-556): XA = XA + conv(XB)  [+ next LN]
+      bool last = L + 1 == c.num_layers;
+      const LNW* nl = last ? &h->final_norm : first_ln_of(L + 1);
+      int nh = last ? 0 : first_head_of(L + 1);
+      if (c.resi_conv) {
+        Epilogue ep; ep.resid = w.XA; ep.resid_pitch = d.C; ep.out_f32 = w.XA; ep.out_f32_pitch = d.C;
+        set_ln(ep, nl, w.XN, nh);
+        HB_TRY(conv(lw.conv, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      } else {
+        HB_TRY(launch_add_convert(w.XA, w.XB, d.M, d.C, w.XA, nullptr, d.dt, 0, 0, st));
+        HB_TRY(ln(w.XA, *nl, w.XN, nh));
+      }
+    }
+    // XN = norm(x) (hat_arch.py:844); conv_after_body + long skip (hat_arch.py:854) -> XN2 (T)
+    if (c.resi_conv) {
+      Epilogue ep; ep.resid = w.S; ep.resid_pitch = d.C; ep.out_t = w.XN2; ep.out_t_pitch = d.Cp; ep.out_t_zero_to = d.Cp;
+      HB_TRY(conv(h->conv_after_body, w.XN, d.Cp, 0, d.H, d.W, ep));
+    } else {
+      HB_TRY(launch_layernorm(w.XA, d.M, d.C, h->final_norm.g, h->final_norm.b, w.XB, HATB200_F32, d.C, d.C, nullptr,
+                              0, st));
+      HB_TRY(launch_add_convert(w.XB, w.S, d.M, d.C, nullptr, w.XN2, d.dt, d.Cp, d.Cp, st));
+    }
+    {  // conv_before_upsample + LeakyReLU (hat_arch.py:855)
+      Epilogue ep; ep.act = ACT_LRELU; ep.out_t = w.F64; ep.out_t_pitch = 64;
+      HB_TRY(conv(h->conv_before_up, w.XN2, d.Cp, 0, d.H, d.W, ep));
+    }
+    // Upsample: conv + PixelShuffle folded into the store (hat_arch.py:593-605)
+    const void* hr = w.F64;
+    int hh = d.H, hw = d.W;
+    if (c.upscale == 3) {
+      Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 3;
+      HB_TRY(conv(h->up0, w.F64, 64, 0, hh, hw, ep));
+      hr = w.UP1; hh *= 3; hw *= 3;
+    } else {
+      if (c.upscale >= 2) {
+        Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 2;
+        HB_TRY(conv(h->up0, w.F64, 64, 0, hh, hw, ep));
+        hr = w.UP1; hh *= 2; hw *= 2;
+      }
+      if (c.upscale >= 4) {
+        Epilogue ep; ep.out_t = w.UP2; ep.out_t_pitch = 64; ep.shuffle_r = 2;
+        HB_TRY(conv(h->up1, w.UP1, 64, 0, hh, hw, ep));
+        hr = w.UP2; hh *= 2; hw *= 2;
+      }
+    }
+    HB_TRY(launch_conv_last(hr, d.dt, 64, 64, d.B, hh, hw, h->conv_last_w, h->conv_last_b, c.in_chans, c.mean,
+                            c.img_range, y, y_dt, st));
+    return dbg("conv_last");
+  }
+};
+
+static int check_geometry(hatb200_handle* h, int B, int H, int W) {
+  HB_REQUIRE(h, HATB200_EINVAL, "null handle");
+  int ws = h->cfg.window_size;
+  HB_REQUIRE(B >= 1 && H >= ws && W >= ws && H % ws == 0 && W % ws == 0, HATB200_EINVAL,
+             "input %dx%d (batch %d) must be a positive multiple of window_size %d in both dimensions", H, W, B, ws);
+  HB_REQUIRE((long long)B * H * W * 16 * 64 < (1ll << 31), HATB200_EUNSUPPORTED,
+             "input too large for 32-bit token indexing: use tile mode");
+  return 0;
+}
+
+}  // namespace hb
+
+using namespace hb;
+
+extern "C" int hatb200_workspace_bytes(hatb200_handle* h, int B, int H, int W, int compute_dtype, size_t* out) {
+  HB_TRY(check_geometry(h, B, H, W));
+  HB_REQUIRE(out, HATB200_EINVAL, "workspace_bytes: null out");
+  HB_REQUIRE(compute_dtype == HATB200_F32 || compute_dtype == HATB200_BF16, HATB200_EUNSUPPORTED,
+             "compute dtype %d: only F32 and BF16 are implemented", compute_dtype);
+  Dims d = make_dims(h->cfg, B, H, W, compute_dtype);
+  Workspace w;
+  plan(h->cfg, d, nullptr, w);
+  *out = w.bytes + 256;
+  return 0;
+}
+
+extern "C" int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W, void* y,
+                               int y_dtype, void* workspace, size_t ws_bytes, void* stream) {
+  HB_TRY(check_geometry(h, B, H, W));
+  HB_REQUIRE(x && y, HATB200_EINVAL, "forward: null tensor");
+  HB_REQUIRE(x_dtype == HATB200_F32 || x_dtype == HATB200_BF16, HATB200_EUNSUPPORTED,
+             "forward: input dtype %d (only F32 and BF16 are implemented)", x_dtype);
+  HB_REQUIRE(y_dtype == HATB200_F32 || y_dtype == HATB200_BF16, HATB200_EUNSUPPORTED, "forward: output dtype %d",
+             y_dtype);
+  HB_REQUIRE(h->packed, HATB200_EPARAM, "forward: weights are not packed (hatb200_set_param + hatb200_pack first)");
+  Fwd f;
+  f.h = h;
+  f.st = (cudaStream_t)stream;
+  f.d = make_dims(h->cfg, B, H, W, x_dtype);
+  plan(h->cfg, f.d, nullptr, f.w);
+  HB_REQUIRE(workspace != nullptr && ws_bytes >= f.w.bytes + 256, HATB200_ENOMEM,
+             "forward: workspace of %zu bytes is smaller than the %zu required", ws_bytes, f.w.bytes + 256);
+  char* base = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  plan(h->cfg, f.d, base, f.w);
+  g_launches = 0;
+  int r = f.run(x, x_dtype, y, y_dtype);
+  h->last_launches = g_launches;
+  return r;
+}

@@ -1,0 +1,77 @@
+// kernels.cuh -- host-side launchers of every kernel in libhatb200.
+// All launchers enqueue on `st`, never synchronise, and return HATB200_* codes.
+#pragma once
+#include "common.cuh"
+
+namespace hb {
+
+// ---- weight packing (pack.cu) ----
+// src: PyTorch (O, I, KH, KW) [Linear: (O, I)] of dtype `src_dt`.
+// fp32 layout for the CUDA-core kernels: dst[tap][i][n], n pitch = Np (zero padded).
+int launch_pack_w_f32(const void* src, int src_dt, int O, int I, int taps, float* dst, int Np, int ncols,
+                      cudaStream_t st);
+// bf16 K-major layout for tcgen05: dst[tap][n][k], n < Npad, k < Kpad (zero padded).
+int launch_pack_w_bf16(const void* src, int src_dt, int O, int I, int taps, bf16* dst, int Npad, int Kpad,
+                       int src_i_off, int src_i_total, cudaStream_t st);
+// any float dtype vector -> fp32
+int launch_to_f32(const void* src, int src_dt, float* dst, size_t n, cudaStream_t st);
+
+// ---- CUDA-core kernels (simt_kernels.cu) ----
+int launch_layernorm(const float* x, int M, int C, const float* gamma, const float* beta, void* out, int out_dt,
+                     int out_pitch, int zero_to, void* head, int head_c, cudaStream_t st);
+// conv_first (hat_arch.py:849-853): y[m, c] = conv3x3((x - mean) * range), x NCHW.
+int launch_conv_first(const void* x, int x_dt, int B, int IC, int H, int W, const float* w /*[9][IC][C]*/,
+                      const float* bias, int C, const float* mean, float range, float* out, cudaStream_t st);
+// conv_last + de-normalisation (hat_arch.py:856-858): in (B*H*W, pitch) tokens of `dt` -> y NCHW of y_dt.
+int launch_conv_last(const void* in, int dt, int pitch, int Cin, int B, int H, int W, const float* w /*[9][Cin][OC]*/,
+                     const float* bias, int OC, const float* mean, float range, void* y, int y_dt, cudaStream_t st);
+// no-upsampler path (hat_arch.py:849-858 with upsampler ''): y = ((x-mean)*range)/range + mean
+int launch_affine_roundtrip(const void* x, int x_dt, int B, int IC, int HW, const float* mean, float range, void* y,
+                            int y_dt, cudaStream_t st);
+// deterministic per-sample column sums: in (B*HW, pitch) channels [0,nc) -> partial (B, nchunk, nc)
+int colsum_chunks(int HW);
+int launch_colsum(const void* in, int dt, int pitch, int B, int HW, int nc, float* partial, cudaStream_t st);
+// ECA gate (hat_arch.py:72-77): mean over HW -> conv1d(k=5, pad 2) across channels -> sigmoid. partial (B,nchunk,C)
+int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
+                      cudaStream_t st);
+// ESC dynamic kernel (esc_arch.py:95-100,:121): GAP(pdim) -> 1x1 (pdim->pdim/2) -> GELU -> 1x1 (->pdim*9)
+int launch_dyn_finish(const float* partial, int nchunk, int B, int pdim, int HW, const float* w1, const float* b1,
+                      const float* w2, const float* b2, float* dyn /*(B,pdim,9)*/, cudaStream_t st);
+// GatedDconvFFN middle (hat_arch.py:112-116)
+int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w /*(2hid,9)*/,
+                  const float* b, void* out, int out_pitch, int zero_to, cudaStream_t st);
+// out_t[m, c] = a[m, c] + b[m, c] (b optional), fp32 in (M, C); optional fp32 copy to out_f32 (may alias a)
+int launch_add_convert(const float* a, const float* b, int M, int C, float* out_f32, void* out_t, int dt, int out_pitch,
+                       int zero_to, cudaStream_t st);
+int launch_crop_place(const void* src, int dt, int B, int C, int sh, int sw, int cy, int cx, void* dst, int dh, int dw,
+                      int oy, int ox, int rh, int rw, cudaStream_t st);
+int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void* dst, int ph, int pw, cudaStream_t st);
+
+// ---- dense conv / GEMM over channels-last tokens ----
+struct ConvArgs {
+  const void* A; int a_pitch; int a_coff; int Cin;   // input tokens (B*H*W, a_pitch), channels [a_coff, a_coff+Cin)
+  int B, H, W, KH, KW;                               // stride 1, zero pad K/2
+  int N;                                             // output channels
+};
+// CUDA-core path, fp32 math, storage dtype `dt` (F32 or BF16); w: fp32 [taps][Cin][Np]
+int launch_tapconv_simt(int dt, const ConvArgs& a, const float* w, int Np, const Epilogue& ep, cudaStream_t st);
+// tcgen05 path (bf16 storage, fp32 accumulate in TMEM); w: bf16 [taps][Npad][Kpad]
+int launch_tapconv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
+bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
+
+// ---- OCAB attention core (hat_arch.py:354-388) ----
+struct AttnArgs {
+  const void* qkv; int pitch;        // (M, pitch): q at 0 (pre-scaled), k at C, v at 2C
+  int B, H, W, C, heads, ws, ows;
+  const float* bias;                 // (heads, (ws+ows-1)^2) compact table, see pack_ocab_bias
+  void* out; int out_pitch; int out_zero_to;
+};
+int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st);
+int launch_attn_tc(const AttnArgs& a, cudaStream_t st);
+bool attn_tc_supported(const AttnArgs& a);
+// compact[h][(dy+ws-1)*(ws+ows-1) + dx+ws-1] = table[wrap(rpi[q][k])][h]; also verifies on device that
+// the index buffer is translation invariant (err_flag != 0 otherwise).
+int launch_pack_ocab_bias(const void* table, int table_dt, const int64_t* rpi, int heads, int ws, int ows,
+                          float* compact, int* err_flag, cudaStream_t st);
+
+}  // namespace hb

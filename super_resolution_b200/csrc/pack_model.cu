@@ -1,0 +1,202 @@
+// pack_model.cu -- hatb200_pack: build the device-resident packed copies of the
+// borrowed state_dict tensors (both kernel layouts), once per load_state_dict.
+#include "model.cuh"
+
+namespace hb {
+
+struct Packer {
+  hatb200_handle* h;
+  cudaStream_t st;
+
+  int alloc(void** out, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    HB_CHECK_CUDA(cudaMalloc(out, bytes));
+    h->allocs.push_back(*out);
+    HB_CHECK_CUDA(cudaMemsetAsync(*out, 0, bytes, st));
+    return 0;
+  }
+  int get(const std::string& key, const ParamRef** out) {
+    auto it = h->index.find(key);
+    HB_REQUIRE(it != h->index.end(), HATB200_EPARAM, "pack: key '%s' is not part of this configuration", key.c_str());
+    const ParamRef& p = h->params[it->second];
+    HB_REQUIRE(p.ptr != nullptr, HATB200_EPARAM, "pack: missing key '%s' (call hatb200_set_param first)", key.c_str());
+    *out = &p;
+    return 0;
+  }
+  bool has(const std::string& key) { return h->index.count(key) != 0; }
+
+  int vec(const std::string& key, float** out) {
+    const ParamRef* p;
+    HB_TRY(get(key, &p));
+    HB_TRY(alloc((void**)out, p->numel() * sizeof(float)));
+    return launch_to_f32(p->ptr, p->dtype, *out, p->numel(), st);
+  }
+  int ln(const std::string& prefix, LNW& w) {
+    HB_TRY(vec(prefix + ".weight", &w.g));
+    return vec(prefix + ".bias", &w.b);
+  }
+  static int kpad_of(int I) { return I <= 16 ? 16 : (I <= 32 ? 32 : round_up(I, 64)); }
+
+  // weight tensor `wkey` (O, I, KH, KW) [+ bias `bkey`]
+  int conv(const std::string& wkey, const std::string& bkey, ConvW& w, int O, int I, int KH, int KW) {
+    const ParamRef* p;
+    HB_TRY(get(wkey, &p));
+    HB_REQUIRE(p->numel() == (size_t)O * I * KH * KW, HATB200_EPARAM, "pack: %s has %zu elements, expected %d",
+               wkey.c_str(), p->numel(), O * I * KH * KW);
+    w.O = O; w.I = I; w.KH = KH; w.KW = KW;
+    int taps = KH * KW;
+    w.Np = round_up(O, 64);
+    HB_TRY(alloc((void**)&w.w32, (size_t)taps * I * w.Np * sizeof(float)));
+    HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, O, I, taps, w.w32, w.Np, w.Np, st));
+    w.Npad = round_up(O, 16);
+    w.Kpad = kpad_of(I);
+    HB_TRY(alloc((void**)&w.w16, (size_t)taps * w.Npad * w.Kpad * sizeof(bf16)));
+    HB_TRY(launch_pack_w_bf16(p->ptr, p->dtype, O, I, taps, w.w16, w.Npad, w.Kpad, 0, I, st));
+    HB_TRY(alloc((void**)&w.bias, (size_t)O * sizeof(float)));
+    if (!bkey.empty() && has(bkey)) {
+      const ParamRef* b;
+      HB_TRY(get(bkey, &b));
+      HB_TRY(launch_to_f32(b->ptr, b->dtype, w.bias, (size_t)O, st));
+    }
+    return 0;
+  }
+  int conv(const std::string& prefix, ConvW& w, int O, int I, int KH, int KW) {
+    return conv(prefix + ".weight", prefix + ".bias", w, O, I, KH, KW);
+  }
+
+  int esc(const std::string& core, const std::string& plk_key, EscW& e, int C, int pdim, int k) {
+    e.pdim = pdim;
+    HB_TRY(conv(plk_key, "", e.plk, pdim, pdim, k, k));
+    HB_TRY(vec(core + ".plk.dwc_proj.1.weight", &e.w1));
+    HB_TRY(vec(core + ".plk.dwc_proj.1.bias", &e.b1));
+    HB_TRY(vec(core + ".plk.dwc_proj.3.weight", &e.w2));
+    HB_TRY(vec(core + ".plk.dwc_proj.3.bias", &e.b2));
+    return conv(core + ".aggr", e.aggr, C, C, 1, 1);
+  }
+
+  // q_proj and kv_proj concatenated along the output axis (one GEMM, N = 3C)
+  int qkv(const std::string& op, ConvW& w, int C) {
+    const ParamRef *q, *kv;
+    HB_TRY(get(op + ".q_proj.weight", &q));
+    HB_TRY(get(op + ".kv_proj.weight", &kv));
+    w.O = 3 * C; w.I = C; w.KH = w.KW = 1;
+    w.Np = round_up(3 * C, 64);
+    HB_TRY(alloc((void**)&w.w32, (size_t)C * w.Np * sizeof(float)));
+    HB_TRY(launch_pack_w_f32(q->ptr, q->dtype, C, C, 1, w.w32, w.Np, C, st));
+    HB_TRY(launch_pack_w_f32(kv->ptr, kv->dtype, 2 * C, C, 1, w.w32 + C, w.Np, w.Np - C, st));
+    w.Npad = round_up(3 * C, 16);
+    w.Kpad = kpad_of(C);
+    HB_TRY(alloc((void**)&w.w16, (size_t)w.Npad * w.Kpad * sizeof(bf16)));
+    HB_TRY(launch_pack_w_bf16(q->ptr, q->dtype, C, C, 1, w.w16, C, w.Kpad, 0, C, st));
+    HB_TRY(launch_pack_w_bf16(kv->ptr, kv->dtype, 2 * C, C, 1, w.w16 + (size_t)C * w.Kpad, w.Npad - C, w.Kpad, 0, C, st));
+    HB_TRY(alloc((void**)&w.bias, (size_t)3 * C * sizeof(float)));
+    if (has(op + ".q_proj.bias")) {
+      const ParamRef *qb, *kvb;
+      HB_TRY(get(op + ".q_proj.bias", &qb));
+      HB_TRY(get(op + ".kv_proj.bias", &kvb));
+      HB_TRY(launch_to_f32(qb->ptr, qb->dtype, w.bias, (size_t)C, st));
+      HB_TRY(launch_to_f32(kvb->ptr, kvb->dtype, w.bias + C, (size_t)2 * C, st));
+    }
+    return 0;
+  }
+
+  int run() {
+    const hatb200_config& c = h->cfg;
+    const int C = c.embed_dim, hid = c.ffn_hidden, ws = c.window_size, ows = c.overlap_win_size;
+    HB_TRY(alloc((void**)&h->err_flag, sizeof(int)));
+    HB_TRY(alloc((void**)&h->mean_dev, 4 * sizeof(float)));
+    HB_CHECK_CUDA(cudaMemcpyAsync(h->mean_dev, c.mean, 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+    const ParamRef* p;
+    {  // conv_first: (C, IC, 3, 3) -> [9][IC][C]
+      HB_TRY(get("conv_first.weight", &p));
+      HB_TRY(alloc((void**)&h->conv_first_w, (size_t)9 * c.in_chans * C * sizeof(float)));
+      HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, C, c.in_chans, 9, h->conv_first_w, C, C, st));
+      HB_TRY(vec("conv_first.bias", &h->conv_first_b));
+    }
+    if (c.patch_norm) HB_TRY(ln("patch_embed.norm", h->pe_norm));
+    const ParamRef* rpi;
+    HB_TRY(get("relative_position_index_OCA", &rpi));
+    h->layers.resize(c.num_layers);
+    for (int L = 0; L < c.num_layers; L++) {
+      LayerW& lw = h->layers[L];
+      std::string lp = "layers." + std::to_string(L);
+      lw.habs.resize(c.depths[L]);
+      for (int i = 0; i < c.depths[L]; i++) {
+        HabW& b = lw.habs[i];
+        std::string bp = lp + ".residual_group.blocks." + std::to_string(i);
+        HB_TRY(ln(bp + ".norm1", b.n1));
+        HB_TRY(ln(bp + ".norm2", b.n2));
+        HB_TRY(esc(bp + ".esc_attn.core", bp + ".esc_attn.plk_filter", b.esc, C, c.esc_pdim, c.esc_kernel));
+        HB_TRY(conv(bp + ".conv_block.cab.0", b.cab0, c.cab_mid, C, 3, 3));
+        HB_TRY(conv(bp + ".conv_block.cab.2", b.cab2, C, c.cab_mid, 3, 3));
+        HB_TRY(vec(bp + ".conv_block.cab.3.conv.weight", &b.eca_w5));
+        HB_TRY(conv(bp + ".mlp.fc1", b.fc1, 2 * hid, C, 1, 1));
+        HB_TRY(conv(bp + ".mlp.fc2", b.fc2, C, hid, 1, 1));
+        HB_TRY(get(bp + ".mlp.dw.weight", &p));
+        HB_TRY(alloc((void**)&b.dw_w, (size_t)9 * 2 * hid * sizeof(float)));
+        HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, 2 * hid, 1, 9, b.dw_w, 2 * hid, 2 * hid, st));
+        HB_TRY(vec(bp + ".mlp.dw.bias", &b.dw_b));
+      }
+      OcabW& o = lw.ocab;
+      std::string op = lp + ".residual_group.overlap_attn";
+      o.heads = c.num_heads[L];
+      HB_TRY(ln(op + ".norm1", o.n1));
+      HB_TRY(ln(op + ".norm2", o.n2));
+      HB_TRY(qkv(op, o.qkv, C));
+      if (c.ocab_esc_enable) {
+        HB_TRY(conv(op + ".q_proj", o.q, C, C, 1, 1));
+        HB_TRY(conv(op + ".kv_proj", o.kv, 2 * C, C, 1, 1));
+        HB_TRY(esc(op + ".esc_core", op + ".esc_plk", o.esc, C, c.ocab_esc_pdim, c.ocab_esc_kernel));
+      }
+      HB_TRY(conv(op + ".proj", o.proj, C, C, 1, 1));
+      HB_TRY(conv(op + ".mlp.0", o.mlp0, hid, C, 1, 1));
+      HB_TRY(conv(op + ".mlp.2", o.mlp2, C, hid, 1, 1));
+      int T = ws + ows - 1;
+      HB_TRY(get(op + ".relative_position_bias_table", &p));
+      HB_TRY(alloc((void**)&o.bias_compact, (size_t)o.heads * T * T * sizeof(float)));
+      HB_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
+                                   h->err_flag, st));
+      if (c.resi_conv) HB_TRY(conv(lp + ".conv", lw.conv, C, C, 3, 3));
+    }
+    HB_TRY(ln("norm", h->final_norm));
+    if (c.resi_conv) HB_TRY(conv("conv_after_body", h->conv_after_body, C, C, 3, 3));
+    if (c.upsampler == 1) {
+      HB_TRY(conv("conv_before_upsample.0", h->conv_before_up, 64, C, 3, 3));
+      if (c.upscale == 3) {
+        HB_TRY(conv("upsample.0", h->up0, 576, 64, 3, 3));
+      } else {
+        if (c.upscale >= 2) HB_TRY(conv("upsample.0", h->up0, 256, 64, 3, 3));
+        if (c.upscale >= 4) HB_TRY(conv("upsample.2", h->up1, 256, 64, 3, 3));
+        HB_REQUIRE(c.upscale <= 4, HATB200_EUNSUPPORTED, "upscale=%d: only 1, 2, 3, 4 are implemented", c.upscale);
+      }
+      HB_TRY(get("conv_last.weight", &p));
+      HB_TRY(alloc((void**)&h->conv_last_w, (size_t)9 * 64 * c.in_chans * sizeof(float)));
+      HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, c.in_chans, 64, 9, h->conv_last_w, c.in_chans, c.in_chans, st));
+      HB_TRY(vec("conv_last.bias", &h->conv_last_b));
+    }
+    int flag = 0;
+    HB_CHECK_CUDA(cudaMemcpyAsync(&flag, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HB_CHECK_CUDA(cudaStreamSynchronize(st));
+    HB_REQUIRE(flag == 0, HATB200_EUNSUPPORTED,
+               flag == 2 ? "pack: relative_position_index_OCA holds an index outside the bias table"
+                         : "pack: relative_position_index_OCA is not translation invariant (not produced by "
+                           "calculate_rpi_oca); the compact bias table cannot represent it");
+    return 0;
+  }
+};
+
+}  // namespace hb
+
+extern "C" int hatb200_pack(hatb200_handle* h, void* stream) {
+  HB_REQUIRE(h, HATB200_EINVAL, "pack: null handle");
+  HB_CHECK_CUDA(cudaSetDevice(h->device));
+  for (void* p : h->allocs) cudaFree(p);
+  h->allocs.clear();
+  h->layers.clear();
+  h->packed = false;
+  hb::Packer pk{h, (cudaStream_t)stream};
+  int r = pk.run();
+  if (r != 0) return r;
+  h->packed = true;
+  return 0;
+}

@@ -1,0 +1,435 @@
+// simt_kernels.cu -- CUDA-core kernels of the HAT forward: the HBM-bound ops of the
+// bf16 path and every small op of both paths.  fp32 arithmetic, storage type T.
+#include "kernels.cuh"
+
+namespace hb {
+
+#define HB_DISPATCH_T(dt, T, ...)                                          \
+  switch (dt) {                                                            \
+    case HATB200_F32: { using T = float; __VA_ARGS__; break; }             \
+    case HATB200_BF16: { using T = bf16; __VA_ARGS__; break; }             \
+    case HATB200_F16: { using T = __half; __VA_ARGS__; break; }            \
+    default: set_error("unsupported dtype %d", dt); return HATB200_EINVAL; \
+  }
+
+// ---------------------------------------------------------------------------
+// LayerNorm over C, one warp per token (reference: nn.LayerNorm, eps 1e-5;
+// hat_arch.py:222,:237,:331,:392,:575,:844).  fp32 statistics, two-pass.
+// ---------------------------------------------------------------------------
+template <typename T, int PER_LANE>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int M, int C,
+                                                        const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, T* __restrict__ out,
+                                                        int out_pitch, int zero_to, T* __restrict__ head, int head_c) {
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (warp >= M) return;
+  const float* row = x + (size_t)warp * C;
+  float v[PER_LANE];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < PER_LANE; i++) {
+    int c = lane + i * 32;
+    v[i] = c < C ? row[c] : 0.f;
+    s += v[i];
+  }
+  float mean = warp_sum(s) / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < PER_LANE; i++) {
+    int c = lane + i * 32;
+    float d = c < C ? v[i] - mean : 0.f;
+    q += d * d;
+  }
+  float rstd = rsqrtf(warp_sum(q) / (float)C + 1e-5f);
+  T* orow = out + (size_t)warp * out_pitch;
+#pragma unroll
+  for (int i = 0; i < PER_LANE; i++) {
+    int c = lane + i * 32;
+    if (c < C) {
+      float y = (v[i] - mean) * rstd * gamma[c] + beta[c];
+      orow[c] = from_f<T>(y);
+      if (head != nullptr && c < head_c) head[(size_t)warp * head_c + c] = from_f<T>(y);
+    } else if (c < zero_to) {
+      orow[c] = from_f<T>(0.f);
+    }
+  }
+}
+
+int launch_layernorm(const float* x, int M, int C, const float* gamma, const float* beta, void* out, int out_dt,
+                     int out_pitch, int zero_to, void* head, int head_c, cudaStream_t st) {
+  HB_REQUIRE(C <= 512 && zero_to <= 512, HATB200_EUNSUPPORTED, "layernorm: C=%d > 512", C);
+  int blocks = cdiv(M, 8);
+  HB_DISPATCH_T(out_dt, T, {
+    if (C <= 256 && zero_to <= 256)
+      layernorm_kernel<T, 8><<<blocks, 256, 0, st>>>(x, M, C, gamma, beta, (T*)out, out_pitch, zero_to, (T*)head, head_c);
+    else
+      layernorm_kernel<T, 16><<<blocks, 256, 0, st>>>(x, M, C, gamma, beta, (T*)out, out_pitch, zero_to, (T*)head, head_c);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// conv_first with the input normalisation folded in (hat_arch.py:849-853).
+// One thread per (token, channel); the 9*IC inputs are warp-broadcast loads.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) conv_first_kernel(const T* __restrict__ x, int B, int IC, int H, int W,
+                                                         const float* __restrict__ w, const float* __restrict__ bias,
+                                                         int C, float4 mean, float range, float* __restrict__ out) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)B * H * W * C;
+  if (idx >= total) return;
+  int c = (int)(idx % C);
+  size_t m = idx / C;
+  int px = (int)(m % W);
+  int py = (int)((m / W) % H);
+  int b = (int)(m / ((size_t)W * H));
+  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+  float acc = bias ? bias[c] : 0.f;
+  for (int ky = 0; ky < 3; ky++) {
+    int yy = py + ky - 1;
+    if (yy < 0 || yy >= H) continue;
+    for (int kx = 0; kx < 3; kx++) {
+      int xx = px + kx - 1;
+      if (xx < 0 || xx >= W) continue;
+      for (int i = 0; i < IC; i++) {
+        float v = (to_f(x[(((size_t)b * IC + i) * H + yy) * W + xx]) - mean_a[i]) * range;
+        acc = fmaf(v, w[((ky * 3 + kx) * IC + i) * C + c], acc);
+      }
+    }
+  }
+  out[idx] = acc;
+}
+
+int launch_conv_first(const void* x, int x_dt, int B, int IC, int H, int W, const float* w, const float* bias, int C,
+                      const float* mean, float range, float* out, cudaStream_t st) {
+  HB_REQUIRE(IC >= 1 && IC <= 4, HATB200_EUNSUPPORTED, "conv_first: in_chans=%d not in 1..4", IC);
+  size_t total = (size_t)B * H * W * C;
+  float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  HB_DISPATCH_T(x_dt, T, {
+    conv_first_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
+                                                                         range, out);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// conv_last (Cin -> OC<=4, 3x3) + "/ img_range + mean", NCHW store
+// (hat_arch.py:856-858).  HBM/L2-bound: one thread per HR pixel, weights in smem.
+// ---------------------------------------------------------------------------
+template <typename T, typename TY>
+__global__ void __launch_bounds__(256) conv_last_kernel(const T* __restrict__ in, int pitch, int Cin, int B, int H,
+                                                        int W, const float* __restrict__ w,
+                                                        const float* __restrict__ bias, int OC, float4 mean,
+                                                        float range, TY* __restrict__ y) {
+  extern __shared__ float sw[];  // [9][Cin][OC]
+  for (int i = threadIdx.x; i < 9 * Cin * OC; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  size_t m = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= (size_t)B * H * W) return;
+  int px = (int)(m % W);
+  int py = (int)((m / W) % H);
+  int b = (int)(m / ((size_t)W * H));
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int ky = 0; ky < 3; ky++) {
+    int yy = py + ky - 1;
+    if (yy < 0 || yy >= H) continue;
+    for (int kx = 0; kx < 3; kx++) {
+      int xx = px + kx - 1;
+      if (xx < 0 || xx >= W) continue;
+      const T* src = in + (((size_t)b * H + yy) * W + xx) * pitch;
+      const float* wt = sw + (ky * 3 + kx) * Cin * OC;
+      for (int c = 0; c < Cin; c++) {
+        float v = to_f(src[c]);
+        for (int o = 0; o < OC; o++) acc[o] = fmaf(v, wt[c * OC + o], acc[o]);
+      }
+    }
+  }
+  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+  for (int o = 0; o < OC; o++) {
+    float v = (acc[o] + (bias ? bias[o] : 0.f)) / range + mean_a[o];
+    y[(((size_t)b * OC + o) * H + py) * W + px] = from_f<TY>(v);
+  }
+}
+
+int launch_conv_last(const void* in, int dt, int pitch, int Cin, int B, int H, int W, const float* w,
+                     const float* bias, int OC, const float* mean, float range, void* y, int y_dt, cudaStream_t st) {
+  HB_REQUIRE(OC >= 1 && OC <= 4, HATB200_EUNSUPPORTED, "conv_last: out channels=%d not in 1..4", OC);
+  size_t total = (size_t)B * H * W;
+  float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  size_t smem = (size_t)9 * Cin * OC * sizeof(float);
+  unsigned blocks = (unsigned)((total + 255) / 256);
+  HB_DISPATCH_T(dt, T, {
+    HB_DISPATCH_T(y_dt, TY, {
+      conv_last_kernel<T, TY><<<blocks, 256, smem, st>>>((const T*)in, pitch, Cin, B, H, W, w, bias, OC, m4,
+                                                         range, (TY*)y);
+    });
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+template <typename T, typename TY>
+__global__ void affine_roundtrip_kernel(const T* __restrict__ x, int IC, int HW, size_t total, float4 mean,
+                                        float range, TY* __restrict__ y) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+  float mu = mean_a[(i / HW) % IC];
+  y[i] = from_f<TY>(((to_f(x[i]) - mu) * range) / range + mu);
+}
+
+int launch_affine_roundtrip(const void* x, int x_dt, int B, int IC, int HW, const float* mean, float range, void* y,
+                            int y_dt, cudaStream_t st) {
+  size_t total = (size_t)B * IC * HW;
+  float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  HB_DISPATCH_T(x_dt, T, {
+    HB_DISPATCH_T(y_dt, TY, {
+      affine_roundtrip_kernel<T, TY><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, IC, HW, total, m4,
+                                                                                    range, (TY*)y);
+    });
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Deterministic per-sample column sums (global average pools of ECA,
+// hat_arch.py:73, and of the ESC dynamic-kernel branch, esc_arch.py:96).
+// Stage 1: each block sums ROWS_PER_CHUNK consecutive tokens of one sample in a
+// fixed order; stage 2 (eca_finish / dyn_finish) adds the chunks in order.
+// ---------------------------------------------------------------------------
+constexpr int ROWS_PER_CHUNK = 128;
+int colsum_chunks(int HW) { return cdiv(HW, ROWS_PER_CHUNK); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ in, int pitch, int HW, int nc, int cpb,
+                                                     float* __restrict__ partial) {
+  __shared__ float red[256];
+  int chunk = blockIdx.x, b = blockIdx.y, nchunk = gridDim.x;
+  int groups = 256 / cpb;
+  int c = threadIdx.x % cpb, g = threadIdx.x / cpb;
+  int r0 = chunk * ROWS_PER_CHUNK;
+  int r1 = min(r0 + ROWS_PER_CHUNK, HW);
+  for (int cb = 0; cb < nc; cb += cpb) {
+    float s = 0.f;
+    if (g < groups && cb + c < nc)
+      for (int r = r0 + g; r < r1; r += groups) s += to_f(in[((size_t)b * HW + r) * pitch + cb + c]);
+    red[threadIdx.x] = s;
+    __syncthreads();
+    if (g == 0 && cb + c < nc) {
+      float t = 0.f;
+      for (int k = 0; k < groups; k++) t += red[k * cpb + c];
+      partial[((size_t)b * nchunk + chunk) * nc + cb + c] = t;
+    }
+    __syncthreads();
+  }
+}
+
+int launch_colsum(const void* in, int dt, int pitch, int B, int HW, int nc, float* partial, cudaStream_t st) {
+  int cpb = nc >= 256 ? 256 : (nc > 128 ? 256 : (nc > 64 ? 128 : (nc > 32 ? 64 : (nc > 16 ? 32 : 16))));
+  dim3 grid(colsum_chunks(HW), B);
+  HB_DISPATCH_T(dt, T, { colsum_kernel<T><<<grid, 256, 0, st>>>((const T*)in, pitch, HW, nc, cpb, partial); });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ECA gate: sigmoid(conv1d_k5(mean over HW)) across the channel axis, zero padded
+// ends, no bias (hat_arch.py:66-77).  One block per sample.
+__global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk, int C, float inv_hw,
+                                  const float* __restrict__ w5, float* __restrict__ scale) {
+  extern __shared__ float mean[];  // C
+  int b = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < nchunk; k++) s += partial[((size_t)b * nchunk + k) * C + c];
+    mean[c] = s * inv_hw;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+#pragma unroll
+    for (int j = 0; j < 5; j++) {
+      int cc = c + j - 2;
+      if (cc >= 0 && cc < C) a = fmaf(w5[j], mean[cc], a);
+    }
+    scale[(size_t)b * C + c] = sigmoid_f(a);
+  }
+}
+
+int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
+                      cudaStream_t st) {
+  eca_finish_kernel<<<B, 256, C * sizeof(float), st>>>(partial, nchunk, C, 1.0f / (float)HW, w5, scale);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ESC dynamic depthwise kernel per sample (esc_arch.py:95-100, :121):
+// dyn = W2 . gelu(W1 . GAP(x[:, :pdim]) + b1) + b2, reshaped (pdim, 3, 3).
+__global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,
+                                  const float* __restrict__ w1, const float* __restrict__ b1,
+                                  const float* __restrict__ w2, const float* __restrict__ b2,
+                                  float* __restrict__ dyn) {
+  __shared__ float mean[64];
+  __shared__ float hid[32];
+  int b = blockIdx.x, half = pdim / 2;
+  for (int c = threadIdx.x; c < pdim; c += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < nchunk; k++) s += partial[((size_t)b * nchunk + k) * pdim + c];
+    mean[c] = s * inv_hw;
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < half; o += blockDim.x) {
+    float a = b1[o];
+    for (int i = 0; i < pdim; i++) a = fmaf(w1[o * pdim + i], mean[i], a);
+    hid[o] = gelu_f(a);
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < pdim * 9; j += blockDim.x) {
+    float a = b2[j];
+    for (int i = 0; i < half; i++) a = fmaf(w2[j * half + i], hid[i], a);
+    dyn[(size_t)b * pdim * 9 + j] = a;
+  }
+}
+
+int launch_dyn_finish(const float* partial, int nchunk, int B, int pdim, int HW, const float* w1, const float* b1,
+                      const float* w2, const float* b2, float* dyn, cudaStream_t st) {
+  HB_REQUIRE(pdim <= 64 && pdim % 2 == 0, HATB200_EUNSUPPORTED, "esc pdim=%d unsupported", pdim);
+  dyn_finish_kernel<<<B, 160, 0, st>>>(partial, nchunk, pdim, 1.0f / (float)HW, w1, b1, w2, b2, dyn);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// GatedDconvFFN middle (hat_arch.py:112-116): depthwise 3x3 (+bias, zero pad) on
+// 2*hid channels, then out[j] = dw[j] * SiLU(dw[hid + j]).  HBM/L2-bound.
+// w: [9][2*hid] tap-major fp32.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) dwgate_kernel(const T* __restrict__ in, int in_pitch, int B, int H, int W,
+                                                     int hid, const float* __restrict__ w,
+                                                     const float* __restrict__ bias, T* __restrict__ out,
+                                                     int out_pitch, int zero_to) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int cols = max(hid, zero_to);
+  size_t total = (size_t)B * H * W * cols;
+  if (idx >= total) return;
+  int j = (int)(idx % cols);
+  size_t m = idx / cols;
+  if (j >= hid) { out[m * out_pitch + j] = from_f<T>(0.f); return; }
+  int px = (int)(m % W);
+  int py = (int)((m / W) % H);
+  float p = bias[j], g = bias[hid + j];
+#pragma unroll
+  for (int ky = 0; ky < 3; ky++) {
+    int yy = py + ky - 1;
+    if (yy < 0 || yy >= H) continue;
+#pragma unroll
+    for (int kx = 0; kx < 3; kx++) {
+      int xx = px + kx - 1;
+      if (xx < 0 || xx >= W) continue;
+      const T* src = in + (m + (size_t)((ky - 1) * W + (kx - 1))) * in_pitch;
+      const float* wt = w + (ky * 3 + kx) * 2 * hid;
+      p = fmaf(to_f(src[j]), wt[j], p);
+      g = fmaf(to_f(src[hid + j]), wt[hid + j], g);
+    }
+  }
+  out[m * out_pitch + j] = from_f<T>(p * silu_f(g));
+}
+
+int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
+                  void* out, int out_pitch, int zero_to, cudaStream_t st) {
+  size_t total = (size_t)B * H * W * (hid > zero_to ? hid : zero_to);
+  HB_DISPATCH_T(dt, T, {
+    dwgate_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)in, in_pitch, B, H, W, hid, w, b,
+                                                                     (T*)out, out_pitch, zero_to);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Tile-mode helpers (hat_model.py:16-26, :106-108)
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void crop_place_kernel(const T* __restrict__ src, int sh, int sw, int cy, int cx, T* __restrict__ dst,
+                                  int dh, int dw, int oy, int ox, int rh, int rw, size_t total) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int x = (int)(i % rw);
+  int y = (int)((i / rw) % rh);
+  size_t bc = i / ((size_t)rw * rh);
+  dst[(bc * dh + oy + y) * dw + ox + x] = src[(bc * sh + cy + y) * sw + cx + x];
+}
+
+int launch_crop_place(const void* src, int dt, int B, int C, int sh, int sw, int cy, int cx, void* dst, int dh, int dw,
+                      int oy, int ox, int rh, int rw, cudaStream_t st) {
+  HB_REQUIRE(cy >= 0 && cx >= 0 && cy + rh <= sh && cx + rw <= sw && oy >= 0 && ox >= 0 && oy + rh <= dh &&
+                 ox + rw <= dw, HATB200_EINVAL, "crop_place: rectangle out of range");
+  size_t total = (size_t)B * C * rh * rw;
+  if (total == 0) return 0;
+  HB_DISPATCH_T(dt, T, {
+    crop_place_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)src, sh, sw, cy, cx, (T*)dst, dh,
+                                                                         dw, oy, ox, rh, rw, total);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+template <typename T>
+__global__ void reflect_pad_kernel(const T* __restrict__ src, int h, int w, T* __restrict__ dst, int H2, int W2,
+                                   size_t total) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int x = (int)(i % W2);
+  int y = (int)((i / W2) % H2);
+  size_t bc = i / ((size_t)W2 * H2);
+  int sx = x < w ? x : 2 * (w - 1) - x;   // 'reflect' (edge not repeated), pad on the right/bottom only
+  int sy = y < h ? y : 2 * (h - 1) - y;
+  dst[i] = src[(bc * h + sy) * w + sx];
+}
+
+int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void* dst, int ph, int pw,
+                       cudaStream_t st) {
+  HB_REQUIRE(ph >= 0 && pw >= 0 && ph < h && pw < w, HATB200_EINVAL,
+             "reflect_pad: pad (%d,%d) must be smaller than the image (%d,%d)", ph, pw, h, w);
+  size_t total = (size_t)B * C * (h + ph) * (w + pw);
+  HB_DISPATCH_T(dt, T, {
+    reflect_pad_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)src, h, w, (T*)dst, h + ph,
+                                                                          w + pw, total);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace hb
+
+namespace hb {
+template <typename T>
+__global__ void add_convert_kernel(const float* __restrict__ a, const float* __restrict__ b, int C, int cols,
+                                   size_t total, float* out_f32, T* __restrict__ out_t, int out_pitch) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  int c = (int)(idx % cols);
+  size_t m = idx / cols;
+  if (c >= C) { if (out_t) out_t[m * out_pitch + c] = from_f<T>(0.f); return; }
+  float v = a[m * C + c] + (b ? b[m * C + c] : 0.f);
+  if (out_f32) out_f32[m * C + c] = v;
+  if (out_t) out_t[m * out_pitch + c] = from_f<T>(v);
+}
+
+int launch_add_convert(const float* a, const float* b, int M, int C, float* out_f32, void* out_t, int dt, int out_pitch,
+                       int zero_to, cudaStream_t st) {
+  int cols = (out_t && zero_to > C) ? zero_to : C;
+  size_t total = (size_t)M * cols;
+  HB_DISPATCH_T(dt, T, {
+    add_convert_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a, b, C, cols, total, out_f32, (T*)out_t,
+                                                                          out_pitch);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+}  // namespace hb

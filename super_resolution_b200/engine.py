@@ -1,0 +1,198 @@
+"""Host-side driver of one libhatb200 handle: binds a module's state_dict to the C ABI,
+owns the scratch workspace (torch caching allocator) and optional CUDA graphs.
+
+PyTorch is plumbing here (device memory, streams); all arithmetic happens in the
+hand-written CUDA library.  Nothing in this file computes on tensors.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import _lib
+
+
+def _config_from_module(m) -> _lib.Config:
+    c = _lib.Config()
+    c.struct_size = C.sizeof(_lib.Config)
+    c.in_chans = m.in_chans
+    c.embed_dim = m.embed_dim
+    c.num_layers = m.num_layers
+    if m.num_layers > _lib.MAX_LAYERS:
+        raise ValueError(f"at most {_lib.MAX_LAYERS} residual groups are supported")
+    for i in range(m.num_layers):
+        c.depths[i] = m.depths[i]
+        c.num_heads[i] = m.heads[i]
+    c.window_size = m.window_size
+    c.overlap_win_size = int(m.window_size * m.overlap_ratio) + m.window_size     # hat_arch.py:289
+    c.cab_mid = m.embed_dim // m.compress_ratio                                   # hat_arch.py:84
+    c.ffn_hidden = int(m.embed_dim * m.mlp_ratio)                                 # hat_arch.py:98
+    c.esc_pdim, c.esc_kernel = m.esc_pdim, m.esc_kernel
+    c.ocab_esc_enable = int(m.ocab_esc_enable)
+    c.ocab_esc_pdim, c.ocab_esc_kernel = m.ocab_esc_pdim, m.ocab_esc_kernel
+    c.upscale = m.upscale
+    c.upsampler = 1 if m.upsampler == 'pixelshuffle' else 0
+    c.resi_conv = 1 if m.resi_connection == '1conv' else 0
+    c.patch_norm = int(bool(m.patch_norm))
+    c.qkv_bias = int(bool(m.qkv_bias))
+    c.conv_scale = float(m.conv_scale)
+    c.img_range = float(m.img_range)
+    c.qk_scale = float(m.qk_scale) if m.qk_scale else 0.0
+    mean = [float(v) for v in m.mean.flatten().tolist()]
+    for i in range(4):
+        c.mean[i] = mean[i] if i < len(mean) else (mean[0] if len(mean) == 1 else 0.0)
+    return c
+
+
+class Engine:
+    def __init__(self, module):
+        self.module = module
+        self.lib = _lib.lib()          # raises if the CUDA library was not built: no fallback
+        self.handle = None
+        self.device = None
+        self._bound = None             # tensors borrowed by the handle (kept alive)
+        self._sample = None            # cheap staleness probe
+        self._probe_tensors = []
+        self._ws = None
+        self._graphs = {}
+        self.use_cuda_graph = os.environ.get("HATB200_CUDA_GRAPH", "1") != "0"
+        self.options = {}
+        self.last_launch_count = 0
+
+    # -- lifetime ---------------------------------------------------------------
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __deepcopy__(self, memo):
+        return None                    # a copied module builds its own engine lazily
+
+    def close(self):
+        self._graphs = {}
+        if self.handle is not None:
+            self.lib.hatb200_destroy(self.handle)
+            self.handle = None
+
+    def invalidate(self):
+        """Parameters changed (load_state_dict / .to()): re-bind and re-pack at the next forward."""
+        self._bound = None
+        self._graphs = {}
+
+    def set_option(self, name, value):
+        self.options[name] = int(value)
+        self._graphs = {}
+        if self.handle is not None:
+            _lib.check(self.lib.hatb200_set_option(self.handle, name.encode(), int(value)))
+
+    # -- binding ----------------------------------------------------------------
+    def _probe(self):
+        # cheap staleness check on a few parameters (in-place updates bump _version, .to() moves data_ptr);
+        # load_state_dict / _apply also call invalidate() explicitly
+        return tuple((t.data_ptr(), t._version, t.dtype) for t in self._probe_tensors)
+
+    def _ensure_bound(self, device):
+        m = self.module
+        if self.handle is not None and self.device != device:
+            self.close()
+            self._bound = None
+        if self.handle is None:
+            with torch.cuda.device(device):
+                h = C.c_void_p()
+                cfg = _config_from_module(m)
+                _lib.check(self.lib.hatb200_create(C.byref(cfg), C.byref(h)))
+                self.handle = h
+                self.device = device
+                for k, v in self.options.items():
+                    _lib.check(self.lib.hatb200_set_option(self.handle, k.encode(), v))
+        if self._bound is not None and self._probe() == self._sample:
+            return
+        sd = m.state_dict(keep_vars=True)
+        bound = {}
+        for k, v in sd.items():
+            t = v.detach()
+            if t.device != device:
+                raise RuntimeError(f"parameter '{k}' is on {t.device} but the input is on {device}; "
+                                   "move the module with .to(device) first")
+            if not t.is_contiguous():
+                t = t.contiguous()
+            shape = (C.c_int64 * max(t.dim(), 1))(*t.shape)
+            _lib.check(self.lib.hatb200_set_param(self.handle, k.encode(), C.c_void_p(t.data_ptr()),
+                                                  _lib.dtype_code(t.dtype), shape, t.dim()))
+            bound[k] = t
+        stream = torch.cuda.current_stream(device)
+        _lib.check(self.lib.hatb200_pack(self.handle, C.c_void_p(stream.cuda_stream)))
+        self._bound = bound
+        keys = list(sd.keys())
+        self._probe_tensors = [sd[k] for k in (keys[0], keys[len(keys) // 3], keys[2 * len(keys) // 3], keys[-1])]
+        self._sample = self._probe()
+        self._graphs = {}
+
+    # -- forward ----------------------------------------------------------------
+    def _workspace(self, B, H, W, code, device):
+        need = C.c_size_t()
+        _lib.check(self.lib.hatb200_workspace_bytes(self.handle, B, H, W, code, C.byref(need)))
+        if self._ws is None or self._ws.numel() < need.value or self._ws.device != device:
+            self._ws = None
+            self._graphs = {}
+            self._ws = torch.empty(need.value, dtype=torch.uint8, device=device)
+        return self._ws
+
+    def _launch(self, x, y, ws):
+        B, _, H, W = x.shape
+        stream = torch.cuda.current_stream(x.device)
+        code = _lib.dtype_code(x.dtype)
+        _lib.check(self.lib.hatb200_forward(self.handle, C.c_void_p(x.data_ptr()), code, B, H, W,
+                                            C.c_void_p(y.data_ptr()), _lib.dtype_code(y.dtype),
+                                            C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(stream.cuda_stream)))
+        self.last_launch_count = self.lib.hatb200_last_launch_count(self.handle)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        m = self.module
+        if not isinstance(x, torch.Tensor) or x.dim() != 4:
+            raise RuntimeError("HAT.forward expects a (B, C, H, W) tensor")
+        if not x.is_cuda:
+            raise RuntimeError("super_resolution_b200.HAT has no CPU path: the input must be a CUDA tensor "
+                               "(the forward runs in libhatb200 on sm_100a)")
+        if x.shape[1] != m.in_chans:
+            raise RuntimeError(f"expected {m.in_chans} input channels, got {x.shape[1]}")
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            raise NotImplementedError(f"input dtype {x.dtype}: float32 (parity path) and bfloat16 "
+                                      "(tensor-core path) are implemented")
+        B, _, H, W = x.shape
+        ws_ = m.window_size
+        if H % ws_ or W % ws_ or H < ws_ or W < ws_:     # reference: RuntimeError from window_partition's .view
+            raise RuntimeError(f"shape '[{H}, {W}]' is invalid: height and width must be multiples of "
+                               f"window_size {ws_}")
+        x = x.contiguous()
+        with torch.cuda.device(x.device):
+            self._ensure_bound(x.device)
+            s = m.upscale if m.upsampler == 'pixelshuffle' else 1
+            ws = self._workspace(B, H, W, _lib.dtype_code(x.dtype), x.device)
+            if not self.use_cuda_graph or torch.cuda.is_current_stream_capturing():
+                y = torch.empty((B, m.in_chans, H * s, W * s), dtype=x.dtype, device=x.device)
+                self._launch(x, y, ws)
+                return y
+            return self._forward_graphed(x, ws, s)
+
+    def _forward_graphed(self, x, ws, s):
+        key = (tuple(x.shape), x.dtype)
+        entry = self._graphs.get(key)
+        if entry is None:
+            B, _, H, W = x.shape
+            xs = torch.empty_like(x)
+            ys = torch.empty((B, self.module.in_chans, H * s, W * s), dtype=x.dtype, device=x.device)
+            xs.copy_(x)
+            self._launch(xs, ys, ws)             # eager warm-up (also surfaces errors outside capture)
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch(xs, ys, ws)
+            if len(self._graphs) >= 8:
+                self._graphs.pop(next(iter(self._graphs)))
+            entry = self._graphs[key] = (g, xs, ys, ws)
+        g, xs, ys, _ = entry
+        xs.copy_(x)
+        g.replay()
+        return ys.clone()

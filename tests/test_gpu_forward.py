@@ -1,0 +1,118 @@
+"""GPU: whole-forward parity of libhatb200 (through the drop-in HAT module and the C ABI) against the
+committed reference goldens and the CPU oracle."""
+import math
+
+import pytest
+import torch
+
+from oracle import hat_oracle as O
+from super_resolution_b200 import HAT
+from tests.helpers import FORWARD_CASES, load_case, psnr
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+FP32_TOL = 1e-4      # north_star: max-abs <= 1e-4 in fp32 (relative to max(1, |y|max) for the randomised weights)
+BF16_PSNR = 50.0     # north_star: PSNR >= 50 dB vs the fp32 reference in bf16
+
+
+def _net(cfg, sd):
+    net = HAT(**cfg).eval()
+    net.load_state_dict(sd, strict=True)
+    return net.to(DEV)
+
+
+@pytest.mark.parametrize("name", FORWARD_CASES)
+def test_fp32_forward_matches_reference_golden(name):
+    cfg, sd, x, y_ref = load_case(name)
+    net = _net(cfg, sd)
+    y = net(x.to(DEV))
+    assert y.dtype == torch.float32 and tuple(y.shape) == tuple(y_ref.shape)
+    err = (y.cpu() - y_ref).abs().max().item()
+    assert err <= FP32_TOL * max(1.0, y_ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("name", FORWARD_CASES)
+def test_bf16_forward_psnr_vs_fp32_reference(name):
+    cfg, sd, x, y_ref = load_case(name)
+    net = _net(cfg, sd)
+    y = net(x.to(DEV).bfloat16())
+    assert y.dtype == torch.bfloat16
+    peak = max(1.0, y_ref.abs().max().item())
+    assert psnr(y.float().cpu(), y_ref, peak) >= BF16_PSNR
+
+
+@pytest.mark.parametrize("tc", [0, 1])
+def test_fresh_init_image_range(tc):
+    """Reference-style initialisation (outputs are image-like, peak 1.0): the bf16 bar as stated."""
+    cfg = dict(upscale=4, window_size=16, embed_dim=180, depths=[2, 2], num_heads=[6, 6], compress_ratio=3,
+               mlp_ratio=2, upsampler='pixelshuffle', img_range=1.)
+    torch.manual_seed(0)
+    net = HAT(**cfg).eval()
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    x = torch.rand(1, 3, 32, 48, generator=torch.Generator().manual_seed(5))
+    y_ref = O.hat_forward(x, sd, cfg)
+    net = net.to(DEV)
+    net.engine().set_option("tensor_cores", tc)
+    assert (net(x.to(DEV)).cpu() - y_ref).abs().max().item() <= FP32_TOL
+    assert psnr(net(x.to(DEV).bfloat16()).float().cpu(), y_ref, 1.0) >= BF16_PSNR
+
+
+def test_batch_is_per_sample_and_input_untouched():
+    cfg, sd, x, y_ref = load_case("mini_x4_b3_32x32")
+    net = _net(cfg, sd)
+    xd = x.to(DEV)
+    keep = xd.clone()
+    y = net(xd)
+    assert torch.equal(xd, keep)
+    for i in range(x.shape[0]):
+        yi = net(xd[i:i + 1])
+        assert (yi - y[i:i + 1]).abs().max().item() <= 1e-5 * max(1.0, y_ref.abs().max().item())
+    # deterministic run to run
+    assert torch.equal(net(xd), y)
+
+
+def test_graph_and_eager_agree_and_shapes_vary():
+    cfg, sd, x, y_ref = load_case("mini_x2_32x48")
+    net = _net(cfg, sd)
+    eng = net.engine()
+    eng.use_cuda_graph = False
+    y0 = net(x.to(DEV))
+    eng.use_cuda_graph = True
+    y1 = net(x.to(DEV))
+    y2 = net(x.to(DEV))
+    assert torch.equal(y0, y1) and torch.equal(y1, y2)
+    other = torch.rand(2, 3, 16, 32, device=DEV)
+    ref = O.hat_forward(other.cpu(), sd, cfg)
+    assert (net(other).cpu() - ref).abs().max().item() <= FP32_TOL * max(1.0, ref.abs().max().item())
+    assert torch.equal(net(x.to(DEV)), y0)
+
+
+def test_errors_follow_reference():
+    cfg, sd, x, _ = load_case("mini_x4_32x32")
+    net = _net(cfg, sd)
+    with pytest.raises(RuntimeError):
+        net(torch.rand(1, 3, 24, 32, device=DEV))        # 72x72-style failure of the reference (.view)
+    with pytest.raises(RuntimeError):
+        net(torch.rand(1, 3, 8, 8, device=DEV))
+    with pytest.raises(RuntimeError):
+        net(torch.rand(1, 4, 32, 32, device=DEV))
+    with pytest.raises(NotImplementedError):
+        net(torch.rand(1, 3, 32, 32, device=DEV).half())
+
+
+def test_reload_state_dict_repacks():
+    cfg, sd, x, y_ref = load_case("mini_x4_32x32")
+    net = _net(cfg, sd)
+    y = net(x.to(DEV))
+    sd2 = O.randomized_state_dict(net.state_dict(), 77)
+    net.load_state_dict({k: v.to(DEV) for k, v in sd2.items()}, strict=True)
+    y2 = net(x.to(DEV))
+    ref2 = O.hat_forward(x, {k: v.cpu() for k, v in sd2.items()}, cfg)
+    assert (y2.cpu() - ref2).abs().max().item() <= FP32_TOL * max(1.0, ref2.abs().max().item())
+    assert not torch.equal(y, y2)
+
+
+def test_no_upsampler_path():
+    net = HAT(window_size=16, embed_dim=48, depths=[1], num_heads=[6], upsampler='').eval().to(DEV)
+    x = torch.rand(1, 3, 16, 16, device=DEV)
+    assert (net(x) - x).abs().max().item() <= 1e-6
