@@ -84,7 +84,7 @@ const char* hatb200_param_key(hatb200_handle* h, int i);
 /* Build the packed device copies (allocates; call outside stream capture). */
 int hatb200_pack(hatb200_handle* h, void* stream);
 
-/* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1). */
+/* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1), "op_timing" (0/1). */
 int hatb200_set_option(hatb200_handle* h, const char* name, int value);
 
 /* Bytes of scratch needed by hatb200_forward for (B,H,W) in the given compute
@@ -100,6 +100,10 @@ int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H,
                     void* y, int y_dtype, void* workspace, size_t ws_bytes, void* stream);
 /* Number of kernels launched by the last hatb200_forward on this handle. */
 int hatb200_last_launch_count(hatb200_handle* h);
+
+/* Per-op device times (CUDA events) of the last forward run with option "op_timing"=1, as a JSON
+ * object {"tag": {"launches","ms","flops","bytes"}} with ALGORITHMIC flops/bytes per tag. */
+int hatb200_op_profile(hatb200_handle* h, char* json, size_t cap);
 
 /* HATModel.tile_process geometry (hat_model.py:52-108).  Fills up to `cap`
  * rectangles of 12 ints each {in_x0,in_x1,in_y0,in_y1,out_x0,out_x1,out_y0,out_y1,

@@ -151,6 +151,7 @@ static void free_packed(hatb200_handle* h) {
 void hatb200_destroy(hatb200_handle* h) {
   if (!h) return;
   free_packed(h);
+  for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   delete h;
 }
 
@@ -191,10 +192,41 @@ int hatb200_set_option(hatb200_handle* h, const char* name, int value) {
   HB_REQUIRE(h && name, HATB200_EINVAL, "set_option: null argument");
   if (!strcmp(name, "tensor_cores")) h->use_tc = value != 0;
   else if (!strcmp(name, "sync_debug")) h->sync_debug = value != 0;
+  else if (!strcmp(name, "op_timing")) h->op_timing = value != 0;
   else { set_error("set_option: unknown option '%s'", name); return HATB200_EINVAL; }
   return 0;
 }
 
 int hatb200_last_launch_count(hatb200_handle* h) { return h ? h->last_launches : 0; }
+
+// Per-op device times of the last forward run with option "op_timing" = 1, as JSON:
+// {"tag": {"launches": n, "ms": t, "flops": f, "bytes": b}, ...}.  Synchronises.
+int hatb200_op_profile(hatb200_handle* h, char* json, size_t cap) {
+  HB_REQUIRE(h && json && cap > 2, HATB200_EINVAL, "op_profile: bad arguments");
+  struct Agg { int n = 0; double ms = 0, flops = 0, bytes = 0; };
+  std::map<std::string, Agg> agg;
+  std::vector<std::string> order;
+  for (const OpRec& r : h->recs) {
+    HB_CHECK_CUDA(cudaEventSynchronize(r.e1));
+    float ms = 0.f;
+    HB_CHECK_CUDA(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    if (!agg.count(r.tag)) order.push_back(r.tag);
+    Agg& a = agg[r.tag];
+    a.n++; a.ms += ms; a.flops += r.flops; a.bytes += r.bytes;
+  }
+  std::string out = "{";
+  for (size_t i = 0; i < order.size(); i++) {
+    const Agg& a = agg[order[i]];
+    char line[256];
+    snprintf(line, sizeof(line), "%s\"%s\": {\"launches\": %d, \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
+             i ? ", " : "", order[i].c_str(), a.n, a.ms, a.flops, a.bytes);
+    out += line;
+  }
+  out += "}";
+  HB_REQUIRE(out.size() + 1 <= cap, HATB200_ENOMEM, "op_profile: buffer of %zu bytes too small (%zu needed)", cap,
+             out.size() + 1);
+  memcpy(json, out.c_str(), out.size() + 1);
+  return 0;
+}
 
 }  // extern "C"

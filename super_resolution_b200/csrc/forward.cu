@@ -73,6 +73,22 @@ struct Fwd {
 
   bool tc() const { return h->use_tc && d.dt == HATB200_BF16; }
 
+  // op timing (bench roofline breakdown): CUDA events around each op on the launching stream
+  int t_begin(const char* tag, double flops, double bytes) {
+    if (!h->op_timing) return -1;
+    while (h->ev_pool.size() < h->ev_used + 2) {
+      cudaEvent_t e;
+      if (cudaEventCreate(&e) != cudaSuccess) return -1;
+      h->ev_pool.push_back(e);
+    }
+    OpRec r{tag, h->ev_pool[h->ev_used], h->ev_pool[h->ev_used + 1], flops, bytes};
+    h->ev_used += 2;
+    cudaEventRecord(r.e0, st);
+    h->recs.push_back(r);
+    return (int)h->recs.size() - 1;
+  }
+  void t_end(int id) { if (id >= 0) cudaEventRecord(h->recs[id].e1, st); }
+
   int dbg(const char* what) {
     if (!h->sync_debug) return 0;
     cudaError_t e = cudaStreamSynchronize(st);
@@ -85,7 +101,15 @@ struct Fwd {
   }
 
   // dense conv / linear over tokens; tensor cores when available for this shape
-  int conv(const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
+  int conv(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
+    double Mt = (double)d.B * H * W;
+    int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), Mt * (cw.I + cw.O) * d.es);
+    int r = conv_impl(cw, A, a_pitch, a_coff, H, W, ep);
+    t_end(tid);
+    return r;
+  }
+
+  int conv_impl(const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
     if (!ep.bias) ep.bias = cw.bias;
     if (tc() && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
@@ -112,6 +136,12 @@ struct Fwd {
 
   // standalone LayerNorm of the fp32 stream (+ compact head and its column sums)
   int ln(const float* x, const LNW& n, void* out, int head_c) {
+    int tid = t_begin("layernorm", 8.0 * d.M * d.C, (double)d.M * d.C * (4 + d.es));
+    int r = ln_impl(x, n, out, head_c);
+    t_end(tid);
+    return r;
+  }
+  int ln_impl(const float* x, const LNW& n, void* out, int head_c) {
     HB_TRY(launch_layernorm(x, d.M, d.C, n.g, n.b, out, d.dt, d.Cp, d.Cp, head_c ? w.X16 : nullptr, head_c, st));
     if (head_c) HB_TRY(launch_colsum(w.X16, d.dt, head_c, d.B, d.H * d.W, head_c, w.part16, st));
     return dbg("layernorm");
@@ -131,7 +161,7 @@ struct Fwd {
     Epilogue ep;
     ep.dyn_x = w.X16; ep.dyn_pitch = e.pdim; ep.dyn_k = w.dyn;
     ep.out_t = dst; ep.out_t_pitch = d.Cp; ep.out_t_coff = 0;
-    return conv(e.plk, w.X16, e.pdim, 0, d.H, d.W, ep);
+    return conv("esc_plk13", e.plk, w.X16, e.pdim, 0, d.H, d.W, ep);
   }
 
   // HAB.forward (hat_arch.py:217-238).  Entry: XN = norm1(src) (+X16, part16).  Exit: dst = block output
@@ -141,11 +171,11 @@ struct Fwd {
     int nchunk = colsum_chunks(d.H * d.W);
     {  // CAB conv1 + GELU
       Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.T1; ep.out_t_pitch = d.midp; ep.out_t_zero_to = d.midp;
-      HB_TRY(conv(b.cab0, w.XN, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("cab_conv1", b.cab0, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
     {  // CAB conv2 -> U, with GAP partials for ECA
       Epilogue ep; ep.out_t = w.U; ep.out_t_pitch = d.Cp; ep.colsum = w.part;
-      HB_TRY(conv(b.cab2, w.T1, d.midp, 0, d.H, d.W, ep));
+      HB_TRY(conv("cab_conv2", b.cab2, w.T1, d.midp, 0, d.H, d.W, ep));
       HB_TRY(launch_eca_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, st));
     }
     HB_TRY(esc_mix(b.esc, w.XN));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
@@ -154,16 +184,18 @@ struct Fwd {
       ep.eca_u = w.U; ep.eca_pitch = d.Cp; ep.eca_scale = w.eca_s; ep.eca_coef = c.conv_scale;
       ep.resid = src; ep.resid_pitch = d.C; ep.out_f32 = dst; ep.out_f32_pitch = d.C;
       set_ln(ep, &b.n2, w.XN2, 0);
-      HB_TRY(conv(b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("esc_aggr", b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
     {  // GatedDconvFFN (hat_arch.py:107-119)
       Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.hp4;
-      HB_TRY(conv(b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      int tid = t_begin("ffn_dwconv_gate", 2.0 * d.M * 2 * d.hid * 9, (double)d.M * 3 * d.hid * d.es);
       HB_TRY(launch_dwgate(w.H1, d.dt, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, w.G, d.hp2, d.hp2, st));
+      t_end(tid);
       HB_TRY(dbg("dwgate"));
       Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
       set_ln(e2, next_ln, w.XN, next_head);
-      HB_TRY(conv(b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
+      HB_TRY(conv("ffn_fc2", b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
     }
     return 0;
   }
@@ -178,31 +210,36 @@ struct Fwd {
       HB_CHECK_CUDA(cudaMemcpyAsync(w.XN2, w.XN, (size_t)d.M * d.Cp * d.es, cudaMemcpyDeviceToDevice, st));
       HB_TRY(esc_mix(o.esc, w.XN2));
       Epilogue ey; ey.out_t = w.U; ey.out_t_pitch = d.Cp; ey.out_t_zero_to = d.Cp;
-      HB_TRY(conv(o.esc.aggr, w.XN2, d.Cp, 0, d.H, d.W, ey));
+      HB_TRY(conv("esc_aggr", o.esc.aggr, w.XN2, d.Cp, 0, d.H, d.W, ey));
       Epilogue eq; eq.out_scale = scale; eq.scale_ncols = d.C; eq.out_t = w.H1; eq.out_t_pitch = d.qkvp;
-      HB_TRY(conv(o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
+      HB_TRY(conv("ocab_qkv", o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
       Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = d.qkvp; ek.out_t_coff = d.C;
-      HB_TRY(conv(o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
+      HB_TRY(conv("ocab_qkv", o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
     } else {
       Epilogue ep; ep.out_scale = scale; ep.scale_ncols = d.C; ep.out_t = w.H1; ep.out_t_pitch = d.qkvp;
-      HB_TRY(conv(o.qkv, w.XN, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("ocab_qkv", o.qkv, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
     AttnArgs a{w.H1, d.qkvp, d.B, d.H, d.W, d.C, o.heads, c.window_size, c.overlap_win_size, o.bias_compact,
                w.G, d.Cp, d.Cp};
-    if (tc() && attn_tc_supported(a)) HB_TRY(launch_attn_tc(a, st));
-    else HB_TRY(launch_attn_simt(d.dt, a, st));
+    {
+      double nk = (double)c.overlap_win_size * c.overlap_win_size;
+      int tid = t_begin("ocab_attention", 4.0 * d.M * nk * d.C, (double)d.M * 4 * d.C * d.es);
+      if (tc() && attn_tc_supported(a)) HB_TRY(launch_attn_tc(a, st));
+      else HB_TRY(launch_attn_simt(d.dt, a, st));
+      t_end(tid);
+    }
     HB_TRY(dbg("attention"));
     {  // proj + shortcut, norm2
       Epilogue ep; ep.resid = x; ep.resid_pitch = d.C; ep.out_f32 = x; ep.out_f32_pitch = d.C;
       set_ln(ep, &o.n2, w.XN2, 0);
-      HB_TRY(conv(o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("ocab_proj", o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
     }
     {  // MLP (hat_arch.py:309-313)
       Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.H1; ep.out_t_pitch = d.hp2; ep.out_t_zero_to = d.hp2;
-      HB_TRY(conv(o.mlp0, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("ocab_mlp0", o.mlp0, w.XN2, d.Cp, 0, d.H, d.W, ep));
       Epilogue e2; e2.resid = x; e2.resid_pitch = d.C; e2.out_f32 = x; e2.out_f32_pitch = d.C;
       if (want_copy) { e2.out_t = w.XN2; e2.out_t_pitch = d.Cp; e2.out_t_zero_to = d.Cp; }
-      HB_TRY(conv(o.mlp2, w.H1, d.hp2, 0, d.H, d.W, e2));
+      HB_TRY(conv("ocab_mlp2", o.mlp2, w.H1, d.hp2, 0, d.H, d.W, e2));
     }
     return 0;
   }
@@ -249,7 +286,7 @@ struct Fwd {
       if (c.resi_conv) {
         Epilogue ep; ep.resid = w.XA; ep.resid_pitch = d.C; ep.out_f32 = w.XA; ep.out_f32_pitch = d.C;
         set_ln(ep, nl, w.XN, nh);
-        HB_TRY(conv(lw.conv, w.XN2, d.Cp, 0, d.H, d.W, ep));
+        HB_TRY(conv("rhag_conv", lw.conv, w.XN2, d.Cp, 0, d.H, d.W, ep));
       } else {
         HB_TRY(launch_add_convert(w.XA, w.XB, d.M, d.C, w.XA, nullptr, d.dt, 0, 0, st));
         HB_TRY(ln(w.XA, *nl, w.XN, nh));
@@ -258,7 +295,7 @@ struct Fwd {
     // XN = norm(x) (hat_arch.py:844); conv_after_body + long skip (hat_arch.py:854) -> XN2 (T)
     if (c.resi_conv) {
       Epilogue ep; ep.resid = w.S; ep.resid_pitch = d.C; ep.out_t = w.XN2; ep.out_t_pitch = d.Cp; ep.out_t_zero_to = d.Cp;
-      HB_TRY(conv(h->conv_after_body, w.XN, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("conv_after_body", h->conv_after_body, w.XN, d.Cp, 0, d.H, d.W, ep));
     } else {
       HB_TRY(launch_layernorm(w.XA, d.M, d.C, h->final_norm.g, h->final_norm.b, w.XB, HATB200_F32, d.C, d.C, nullptr,
                               0, st));
@@ -266,29 +303,32 @@ struct Fwd {
     }
     {  // conv_before_upsample + LeakyReLU (hat_arch.py:855)
       Epilogue ep; ep.act = ACT_LRELU; ep.out_t = w.F64; ep.out_t_pitch = 64;
-      HB_TRY(conv(h->conv_before_up, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      HB_TRY(conv("conv_before_upsample", h->conv_before_up, w.XN2, d.Cp, 0, d.H, d.W, ep));
     }
     // Upsample: conv + PixelShuffle folded into the store (hat_arch.py:593-605)
     const void* hr = w.F64;
     int hh = d.H, hw = d.W;
     if (c.upscale == 3) {
       Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 3;
-      HB_TRY(conv(h->up0, w.F64, 64, 0, hh, hw, ep));
+      HB_TRY(conv("upsample_conv", h->up0, w.F64, 64, 0, hh, hw, ep));
       hr = w.UP1; hh *= 3; hw *= 3;
     } else {
       if (c.upscale >= 2) {
         Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 2;
-        HB_TRY(conv(h->up0, w.F64, 64, 0, hh, hw, ep));
+        HB_TRY(conv("upsample_conv", h->up0, w.F64, 64, 0, hh, hw, ep));
         hr = w.UP1; hh *= 2; hw *= 2;
       }
       if (c.upscale >= 4) {
         Epilogue ep; ep.out_t = w.UP2; ep.out_t_pitch = 64; ep.shuffle_r = 2;
-        HB_TRY(conv(h->up1, w.UP1, 64, 0, hh, hw, ep));
+        HB_TRY(conv("upsample_conv", h->up1, w.UP1, 64, 0, hh, hw, ep));
         hr = w.UP2; hh *= 2; hw *= 2;
       }
     }
+    int tid = t_begin("conv_last", 2.0 * d.B * hh * hw * 64 * 9 * c.in_chans,
+                      (double)d.B * hh * hw * (64 * d.es + c.in_chans * (y_dt == HATB200_F32 ? 4 : 2)));
     HB_TRY(launch_conv_last(hr, d.dt, 64, 64, d.B, hh, hw, h->conv_last_w, h->conv_last_b, c.in_chans, c.mean,
                             c.img_range, y, y_dt, st));
+    t_end(tid);
     return dbg("conv_last");
   }
 };
@@ -338,6 +378,8 @@ extern "C" int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, in
   char* base = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   plan(h->cfg, f.d, base, f.w);
   g_launches = 0;
+  h->recs.clear();
+  h->ev_used = 0;
   int r = f.run(x, x_dtype, y, y_dtype);
   h->last_launches = g_launches;
   return r;

@@ -73,8 +73,16 @@ struct Workspace {           // carved from the caller's scratch buffer
 
 }  // namespace hb
 
+namespace hb {
+struct OpRec { const char* tag; cudaEvent_t e0, e1; double flops, bytes; };
+}
+
 struct hatb200_handle {
   hatb200_config cfg;
+  bool op_timing = false;            // record CUDA events around every op (bench roofline breakdown)
+  std::vector<hb::OpRec> recs;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
   int device = 0;
   std::vector<hb::ParamRef> params;
   std::map<std::string, int> index;

@@ -196,3 +196,19 @@ class Engine:
         xs.copy_(x)
         g.replay()
         return ys.clone()
+
+    # -- per-op profile (bench roofline breakdown) ----------------------------------
+    def op_profile(self, x: torch.Tensor) -> dict:
+        """Run one eager forward with CUDA events around every op and return
+        {tag: {launches, ms, flops, bytes}} (algorithmic flops / bytes per tag)."""
+        import json
+        graph, self.use_cuda_graph = self.use_cuda_graph, False
+        try:
+            self.set_option("op_timing", 1)
+            self.forward(x)
+            buf = C.create_string_buffer(1 << 16)
+            _lib.check(self.lib.hatb200_op_profile(self.handle, buf, len(buf)))
+            return json.loads(buf.value.decode())
+        finally:
+            self.set_option("op_timing", 0)
+            self.use_cuda_graph = graph
