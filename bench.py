@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""bench.py -- HAT-SRx4 output megapixels/s on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): HAT SRx4 (embed_dim 180, 6x6 RHAG) bf16 forward, batch 16 of
+64x64 synthetic LR patches per GPU, random-init weights (seed 0), uniform[0,1) input (seed 0).
+A step = one forward over one batch.  Weak scaling: every rank runs its own batch (image-batch
+sharding), no collective on the data path; value = all ranks' output pixels / max-over-
+ranks device time.  One JSON line on rank 0.
+
+--impl reference: the reference's CPU forward (the oracle port -- the Python reference itself cannot
+travel to the GPU box) on the host cores, each step a bounded sample of the same workload.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+HAT_X4 = dict(upscale=4, in_chans=3, img_size=64, window_size=16, compress_ratio=3, squeeze_factor=30,
+              conv_scale=0.01, overlap_ratio=0.5, img_range=1., depths=[6] * 6, embed_dim=180,
+              num_heads=[6] * 6, mlp_ratio=2, upsampler='pixelshuffle', resi_connection='1conv')
+BATCH, LR = 16, 64
+MFLOP_PER_LR_PX = 45.3464          # SURVEY.md 8d / BASELINE.md 2 (algorithmic, no padding)
+METRIC = "HAT-SRx4 output megapixels/s (bf16 forward, batch 16 of 64x64 LR per GPU)"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf=d["bf16_tflops_sustained"], tf_burst=d["bf16_tflops"], src="measured")
+    return dict(hbm=6650.0, tf=1400.0, tf_burst=1590.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [v.strip() for v in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def cpu_forward_sample(n_samples, threads):
+    """Oracle port of the reference forward on the host cores: seconds for n_samples 64x64 patches."""
+    from oracle import hat_oracle as O
+    from super_resolution_b200 import HAT
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    net = HAT(**HAT_X4)
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    x = torch.rand(n_samples, 3, LR, LR, generator=torch.Generator().manual_seed(0))
+    O.hat_forward(x[:1], sd, HAT_X4)            # warm-up
+    t0 = time.perf_counter()
+    O.hat_forward(x, sd, HAT_X4)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n = 2                                     # LR patches per step (bounded sample of the batch of 16)
+    from oracle import hat_oracle as O
+    from super_resolution_b200 import HAT
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    net = HAT(**HAT_X4)
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    x = torch.rand(n, 3, LR, LR, generator=torch.Generator().manual_seed(0))
+    for _ in range(max(1, min(args.warmup, 2))):
+        O.hat_forward(x[:1], sd, HAT_X4)
+    times = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        O.hat_forward(x, sd, HAT_X4)
+        times.append(time.perf_counter() - t0)
+    t = sum(times) / len(times)
+    out_mp = n * (LR * 4) ** 2 / 1e6
+    val = out_mp / t
+    sample = (f"{n} of the {BATCH} 64x64 LR patches per step, fp32, oracle port of the reference forward "
+              f"(torch-CPU ops, {threads} threads); scaled figures assume linear cost in patches")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "MP/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "HAT SRx4 (embed_dim=180, 6x6 RHAG) forward, 64x64 LR patches, CPU sample",
+                   "patches_per_step": n, "full_batch": BATCH, "ms_per_full_batch_scaled": t * 1e3 * BATCH / n},
+        "cpu_baseline": {"value": val, "unit": "MP/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+KERNEL_OF_TAG = {"ocab_attention": "ocab_attention", "ffn_dwconv_gate": "dwconv_gate", "layernorm": "layernorm",
+                 "conv_last": "conv_last"}
+
+
+def summarize_profile(prof, peaks, tc_on):
+    groups = {}
+    for tag, r in prof.items():
+        k = KERNEL_OF_TAG.get(tag, "tapconv")
+        g = groups.setdefault(k, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
+        for f in ("launches", "ms", "flops", "bytes"):
+            g[f] += r[f]
+    total_ms = sum(g["ms"] for g in groups.values())
+    dom = max(groups, key=lambda k: groups[k]["ms"])
+    g = groups[dom]
+    if dom in ("tapconv", "ocab_attention"):
+        achieved = g["flops"] / (g["ms"] * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf"], "unit": "TFLOP/s",
+                "frac": achieved / peaks["tf"], "traffic": None}
+    else:
+        achieved = g["bytes"] / (g["ms"] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm"], "traffic": None}
+    roof.update({"kernel": dom + ("_tcgen05" if tc_on and dom in ("tapconv", "ocab_attention") else ""),
+                 "launches": g["launches"], "avg_launch_us": g["ms"] * 1e3 / max(1, g["launches"]),
+                 "share_of_step": g["ms"] / total_ms if total_ms else None,
+                 "peak_source": f"{peaks['src']} (sustained bf16 / copy bandwidth, MEASURED_PEAKS.json)"})
+    per_op = {t: {"launches": r["launches"], "ms": round(r["ms"], 4),
+                  "tflops": round(r["flops"] / (r["ms"] * 1e-3) / 1e12, 2) if r["ms"] > 0 else None,
+                  "gbs": round(r["bytes"] / (r["ms"] * 1e-3) / 1e9, 1) if r["ms"] > 0 else None}
+              for t, r in prof.items()}
+    return roof, per_op, total_ms
+
+
+def run_ours(args):
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        sys.exit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from super_resolution_b200 import HAT
+    peaks = load_peaks()
+    torch.manual_seed(0)
+    net = HAT(**HAT_X4).eval().to(dev)
+    eng = net.engine()
+    tc_on = os.environ.get("HATB200_TENSOR_CORES", "1") != "0"
+    eng.set_option("tensor_cores", int(tc_on))
+    g = torch.Generator().manual_seed(rank)
+    x_host = torch.rand(BATCH, 3, LR, LR, generator=g).bfloat16().pin_memory()
+    x = x_host.to(dev)
+    out_px = BATCH * (LR * 4) ** 2                           # delivered HR pixels per rank per step
+    W, K = max(3, args.warmup), args.steps
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    for _ in range(W):
+        y = net(x)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput: K steps, CUDA events per step, L2 flushed between steps ----
+    clocks = ClockSampler(local)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    clocks.start()
+    for e0, e1 in ev:
+        flush.zero_()
+        e0.record()
+        y = net(x)
+        e1.record()
+    barrier()
+    clk = clocks.stop()
+    total_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / K
+    value = world * out_px / 1e6 / (ms_step * 1e-3)
+
+    # ---- end to end through the public API: pinned host input -> H2D -> net(x) -> D2H of the HR batch ----
+    y_host = torch.empty((BATCH, 3, LR * 4, LR * 4), dtype=torch.bfloat16).pin_memory()
+    xd = torch.empty_like(x)
+    for _ in range(2):
+        xd.copy_(x_host, non_blocking=True)
+        y_host.copy_(net(xd), non_blocking=True)
+    barrier()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(K):
+        xd.copy_(x_host, non_blocking=True)
+        y_host.copy_(net(xd), non_blocking=True)
+    s1.record()
+    barrier()
+    t2 = torch.tensor([s0.elapsed_time(s1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_val = world * out_px / 1e6 / (t2.item() / K * 1e-3)
+
+    launches = eng.last_launch_count
+    if rank == 0:
+        prof = eng.op_profile(x)
+        torch.cuda.synchronize()
+        roof, per_op, prof_ms = summarize_profile(prof, peaks, tc_on)
+        lr_px = BATCH * LR * LR
+        whole = MFLOP_PER_LR_PX * 1e6 * lr_px / (ms_step * 1e-3) / 1e12
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            t1 = cpu_forward_sample(1, threads)
+            n = int(min(BATCH, max(2, 12.0 / max(t1, 1e-3))))
+            tn = cpu_forward_sample(n, threads)
+            cpu = {"value": n * (LR * 4) ** 2 / 1e6 / tn, "unit": "MP/s", "cores": threads, "kind": "port",
+                   "sample": f"{n} of the {BATCH} 64x64 LR patches, fp32, oracle port of the reference forward on "
+                             f"{threads} host threads ({tn:.2f} s)"}
+        line = {
+            "metric": METRIC, "value": value, "unit": "MP/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "HAT SRx4 (embed_dim=180, depths 6x6, heads 6, window 16) bf16 forward, "
+                                   "batch 16 of 64x64 LR patches per GPU (BASELINE configs[1])",
+                       "global_batch": BATCH * world, "lr_size": LR, "parallelism": f"image-batch shard x{world}",
+                       "l2": "256 MiB buffer written between timed steps (L2 flush)",
+                       "cuda_graph": bool(eng.use_cuda_graph), "tensor_cores": tc_on,
+                       "weights": "random init, seed 0"},
+            "clocks": clk,
+            "e2e": {"value": e2e_val, "unit": "MP/s", "h2d_bytes_per_step": x_host.numel() * 2,
+                    "d2h_bytes_per_step": y_host.numel() * 2},
+            "gpu_launches": launches * K,
+            "roofline": roof,
+            "whole_forward_tflops": whole, "whole_forward_frac_of_peak": whole / peaks["tf"],
+            "per_op": per_op, "profiled_eager_step_ms": prof_ms,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
