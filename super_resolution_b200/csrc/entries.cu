@@ -77,7 +77,7 @@ int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, in
   int taps = KH * KW, r;
   if (use_tc) {
     HB_REQUIRE(dtype == HATB200_BF16, HATB200_EINVAL, "conv_tokens: the tcgen05 kernel needs bf16 activations");
-    int Npad = round_up(N, 16), Kpad = Cin <= 16 ? 16 : (Cin <= 32 ? 32 : round_up(Cin, 64));
+    int Npad = tc_npad(N), Kpad = Cin <= 16 ? 16 : (Cin <= 32 ? 32 : round_up(Cin, 64));
     bf16* w16;
     HB_TRY(pool.alloc((void**)&w16, (size_t)taps * Npad * Kpad * sizeof(bf16), st));
     HB_TRY(launch_pack_w_bf16(w, HATB200_F32, N, Cin, taps, w16, Npad, Kpad, 0, Cin, st));

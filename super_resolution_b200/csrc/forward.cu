@@ -7,6 +7,8 @@
 //   residual stream  fp32 (M, C)      -- S (conv_first out, long skip), XA (group input), XB (running)
 //   activations      T    (M, pitch)  -- T = bf16 (tensor-core path) or fp32 (parity path); pitch = C rounded
 //                                        up to 64, pad columns are written as zero (K padding of the consumer)
+#include <stdlib.h>
+
 #include "model.cuh"
 
 namespace hb {
@@ -104,15 +106,23 @@ struct Fwd {
   int conv(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     double Mt = (double)d.B * H * W;
     int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), Mt * (cw.I + cw.O) * d.es);
-    int r = conv_impl(cw, A, a_pitch, a_coff, H, W, ep);
+    int r = conv_impl(tag, cw, A, a_pitch, a_coff, H, W, ep);
     t_end(tid);
     return r;
   }
 
-  int conv_impl(const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
+  // engineering switch: HATB200_TC_DISABLE=tag1,tag2 keeps the named ops on the CUDA-core kernel (bisecting)
+  static bool tc_disabled(const char* tag) {
+    const char* v = getenv("HATB200_TC_DISABLE");
+    if (!v || !*v) return false;
+    std::string list = std::string(",") + v + ",";
+    return list.find(std::string(",") + tag + ",") != std::string::npos;
+  }
+
+  int conv_impl(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
     if (!ep.bias) ep.bias = cw.bias;
-    if (tc() && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
+    if (tc() && !tc_disabled(tag) && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
       HB_TRY(launch_tapconv_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
       return dbg("tapconv_tc");
     }

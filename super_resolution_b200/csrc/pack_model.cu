@@ -48,7 +48,7 @@ struct Packer {
     w.Np = round_up(O, 64);
     HB_TRY(alloc((void**)&w.w32, (size_t)taps * I * w.Np * sizeof(float)));
     HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, O, I, taps, w.w32, w.Np, w.Np, st));
-    w.Npad = round_up(O, 16);
+    w.Npad = tc_npad(O);
     w.Kpad = kpad_of(I);
     HB_TRY(alloc((void**)&w.w16, (size_t)taps * w.Npad * w.Kpad * sizeof(bf16)));
     HB_TRY(launch_pack_w_bf16(p->ptr, p->dtype, O, I, taps, w.w16, w.Npad, w.Kpad, 0, I, st));
@@ -84,7 +84,7 @@ struct Packer {
     HB_TRY(alloc((void**)&w.w32, (size_t)C * w.Np * sizeof(float)));
     HB_TRY(launch_pack_w_f32(q->ptr, q->dtype, C, C, 1, w.w32, w.Np, C, st));
     HB_TRY(launch_pack_w_f32(kv->ptr, kv->dtype, 2 * C, C, 1, w.w32 + C, w.Np, w.Np - C, st));
-    w.Npad = round_up(3 * C, 16);
+    w.Npad = tc_npad(3 * C);
     w.Kpad = kpad_of(C);
     HB_TRY(alloc((void**)&w.w16, (size_t)w.Npad * w.Kpad * sizeof(bf16)));
     HB_TRY(launch_pack_w_bf16(q->ptr, q->dtype, C, C, 1, w.w16, C, w.Kpad, 0, C, st));

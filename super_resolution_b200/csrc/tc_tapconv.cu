@@ -1,0 +1,497 @@
+// tc_tapconv.cu -- dense conv / Linear over channels-last tokens on the 5th-gen tensor cores.
+//
+//   out[m, n] = sum_tap sum_k A[pix(m) + tap, k] * W[tap][n][k]        (bf16 x bf16 -> fp32 in TMEM)
+//
+// A conv KHxKW is KH*KW shifted GEMMs: one CTA owns a 16x8-pixel tile (128 rows = UMMA M) and a
+// BN-wide slice of output channels.  For every (tap, 64-channel block) the producer warp issues ONE
+// 4-D TMA box {64 ch, 16 x, 8 y, 1 b} at the shifted pixel coordinates -- TMA's out-of-bounds
+// zero fill IS the conv's zero padding, and the box lands in shared memory already in the
+// canonical K-major SWIZZLE_128B operand layout -- plus a 2-D box of the packed weights.  One thread
+// issues tcgen05.mma; completion is tracked with tcgen05.commit -> mbarrier.  Four epilogue warps
+// read the accumulator with tcgen05.ld (one token row per thread) and apply the fused epilogue:
+// bias, dynamic depthwise term, q-scale, GELU/LeakyReLU, ECA-rescaled CAB branch, fp32 residual,
+// fp32 stream store, bf16 store (optionally pixel-shuffled), per-tile column sums (global average
+// pool partials) and a full LayerNorm of the row (the row lives in ONE thread: no reduction).
+// Replaces F.conv2d / F.linear at hat_arch.py:84-86,:111,:117,:347-351,:391-392,:544,:854-856 and
+// esc_arch.py:122-123,:144.
+#include <stdlib.h>
+
+#include "kernels.cuh"
+#include "tc_common.cuh"
+
+namespace hb {
+
+using namespace tc;
+
+constexpr int TC_THREADS = 192;     // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue
+constexpr int TC_MAX_STAGES = 8;
+constexpr int TILE_W = 16, TILE_H = 8, TILE_M = 128;
+
+struct TcParams {
+  int B, H, W, KH, KW;
+  int a_coff, kblocks, BK;
+  int N, BN, Npad;
+  int tiles_x, tiles_y;
+  int stages, stage_bytes, a_bytes;
+  uint32_t tmem_cols;
+};
+
+// ---- epilogue helpers ------------------------------------------------------------------------------
+__device__ __forceinline__ void load16_f32(const float* p, int valid, float (&o)[16]) {
+  if (valid >= 16) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float4 t = q[i];
+      o[4 * i] = t.x; o[4 * i + 1] = t.y; o[4 * i + 2] = t.z; o[4 * i + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; i++) o[i] = i < valid ? p[i] : 0.f;
+  }
+}
+
+__device__ __forceinline__ void load16_bf16(const bf16* p, int valid, float (&o)[16]) {
+  if (valid >= 16) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      uint4 t = q[i];
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float2 f = __bfloat1622float2(h[j]);
+        o[8 * i + 2 * j] = f.x; o[8 * i + 2 * j + 1] = f.y;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; i++) o[i] = i < valid ? __bfloat162float(p[i]) : 0.f;
+  }
+}
+
+// store 16 values as bf16; `valid` of them are real, columns [valid, zero_valid) are written as zero
+__device__ __forceinline__ void store16_bf16(bf16* p, const float (&v)[16], int valid, int zero_valid, bool aligned) {
+  if (valid >= 16 && aligned) {
+    uint4 t[2];
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(t);
+#pragma unroll
+    for (int i = 0; i < 8; i++) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = t[0];
+    q[1] = t[1];
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+      if (i < valid) p[i] = __float2bfloat16_rn(v[i]);
+      else if (i < zero_valid) p[i] = __float2bfloat16_rn(0.f);
+    }
+  }
+}
+
+__device__ __forceinline__ void store16_f32(float* p, const float (&v)[16], int valid) {
+  if (valid >= 16) {
+    float4* q = reinterpret_cast<float4*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; i++) q[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+      if (i < valid) p[i] = v[i];
+  }
+}
+
+// ---- the kernel --------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TC_THREADS)
+tapconv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p,
+                  const Epilogue ep) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[TC_MAX_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[TC_MAX_STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ float sred[4][256];
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // tile coordinates: 16 x 8 pixels of one sample
+  const int tile = blockIdx.x;
+  const int tx = tile % p.tiles_x;
+  const int ty = (tile / p.tiles_x) % p.tiles_y;
+  const int b = tile / (p.tiles_x * p.tiles_y);
+  const int x0 = tx * TILE_W, y0 = ty * TILE_H;
+  const int n0 = blockIdx.y * p.BN;
+  const int total_it = p.KH * p.KW * p.kblocks;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < p.stages; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      const int ph = p.KH / 2, pw = p.KW / 2;
+      const uint32_t tx_bytes = (uint32_t)(p.a_bytes + p.BN * p.BK * 2);
+      int it = 0;
+      for (int tap = 0; tap < p.KH * p.KW; tap++) {
+        const int dy = tap / p.KW - ph, dx = tap % p.KW - pw;
+        for (int kb = 0; kb < p.kblocks; kb++, it++) {
+          const int s = it % p.stages;
+          const uint32_t par = (uint32_t)(it / p.stages) & 1u;
+          mbar_wait(&empty_bar[s], par ^ 1u);
+          uint8_t* sa = smem + (size_t)s * p.stage_bytes;
+          mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
+          tma_load_4d(sa, &tmA, &full_bar[s], p.a_coff + kb * p.BK, x0 + dx, y0 + dy, b);
+          tma_load_2d(sa + p.a_bytes, &tmB, &full_bar[s], kb * p.BK, tap * p.Npad + n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(TILE_M, p.BN);
+      const uint32_t row_bytes = (uint32_t)p.BK * 2;
+      for (int it = 0; it < total_it; it++) {
+        const int s = it % p.stages;
+        const uint32_t par = (uint32_t)(it / p.stages) & 1u;
+        mbar_wait(&full_bar[s], par);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + (size_t)s * p.stage_bytes);
+        const uint32_t sb = sa + (uint32_t)p.a_bytes;
+        for (int k = 0; k < p.BK / 16; k++) {
+          const uint64_t ad = make_smem_desc(sa + k * 32, row_bytes);
+          const uint64_t bd = make_smem_desc(sb + k * 32, row_bytes);
+          umma_bf16(tmem_base, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);     // frees the smem slot once these MMAs have read it
+      }
+      umma_commit(&tmem_full_bar);      // accumulator complete
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4, one token row per thread =====
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int py = y0 + row / TILE_W, px = x0 + row % TILE_W;
+    const int m = (b * p.H + py) * p.W + px;
+    const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const int N = p.N;
+    const int chunk_tile = ty * p.tiles_x + tx;                 // tile index inside the sample
+    const int nchunk = p.tiles_x * p.tiles_y;
+    const bool do_ln = ep.ln_out != nullptr;
+    const bool aligned_t = ((ep.out_t_coff & 7) == 0);
+
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+
+    float ln_k = 0.f, ln_s1 = 0.f, ln_s2 = 0.f;
+    for (int c = 0; c < p.BN / 16; c++) {
+      const int nb = n0 + c * 16;
+      const int valid = N - nb;                                   // real columns in this chunk (may be <= 0)
+      uint32_t r[16];
+      tmem_ld16(trow + (uint32_t)(c * 16), r);
+      tmem_ld_wait();
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; j++) v[j] = __uint_as_float(r[j]);
+      if (valid > 0) {
+        if (ep.bias) {
+#pragma unroll
+          for (int j = 0; j < 16; j++) if (j < valid) v[j] += __ldg(ep.bias + nb + j);
+        }
+        if (ep.dyn_k) {       // per-sample dynamic depthwise 3x3 on the compact channels (esc_arch.py:123)
+          const bf16* xs = (const bf16*)ep.dyn_x;
+          for (int ky = 0; ky < 3; ky++) {
+            const int yy = py + ky - 1;
+            if (yy < 0 || yy >= p.H) continue;
+            for (int kx = 0; kx < 3; kx++) {
+              const int xx = px + kx - 1;
+              if (xx < 0 || xx >= p.W) continue;
+              float xv[16];
+              load16_bf16(xs + (size_t)(m + (ky - 1) * p.W + (kx - 1)) * ep.dyn_pitch + nb, valid, xv);
+#pragma unroll
+              for (int j = 0; j < 16; j++)
+                if (j < valid) v[j] = fmaf(xv[j], __ldg(ep.dyn_k + ((size_t)b * N + nb + j) * 9 + ky * 3 + kx), v[j]);
+            }
+          }
+        }
+        if (ep.scale_ncols > 0) {
+#pragma unroll
+          for (int j = 0; j < 16; j++) if (nb + j < ep.scale_ncols) v[j] *= ep.out_scale;
+        }
+        if (ep.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < 16; j++) v[j] = gelu_f(v[j]);
+        } else if (ep.act == ACT_LRELU) {
+#pragma unroll
+          for (int j = 0; j < 16; j++) v[j] = lrelu_f(v[j]);
+        }
+        if (ep.eca_u) {
+          float u[16];
+          load16_bf16((const bf16*)ep.eca_u + (size_t)m * ep.eca_pitch + nb, valid, u);
+#pragma unroll
+          for (int j = 0; j < 16; j++)
+            if (j < valid) v[j] = fmaf(ep.eca_coef * __ldg(ep.eca_scale + (size_t)b * N + nb + j), u[j], v[j]);
+        }
+        if (ep.resid) {
+          float rs[16];
+          load16_f32(ep.resid + (size_t)m * ep.resid_pitch + nb, valid, rs);
+#pragma unroll
+          for (int j = 0; j < 16; j++) v[j] += rs[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j++) if (j >= valid) v[j] = 0.f;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; j++) v[j] = 0.f;
+      }
+      // ---- outputs ----
+      if (ep.out_f32 && valid > 0) store16_f32(ep.out_f32 + (size_t)m * ep.out_f32_pitch + nb, v, valid);
+      if (ep.out_t) {
+        bf16* ot = (bf16*)ep.out_t;
+        if (ep.shuffle_r == 1) {
+          const int zv = ep.out_t_zero_to - nb;
+          if (valid > 0 || zv > 0)
+            store16_bf16(ot + (size_t)m * ep.out_t_pitch + ep.out_t_coff + nb, v, valid, zv, aligned_t);
+        } else if (valid > 0) {
+          // PixelShuffle(r) folded into the store: out[b, c, y*r+i, x*r+j] = in[b, c*r*r + i*r + j, y, x]
+          const int r_ = ep.shuffle_r, rr = r_ * r_;
+          const size_t orow_w = (size_t)p.W * r_;
+          if (r_ == 2 && valid >= 16) {
+            const int c0 = nb >> 2;   // 4 channels, 4 sub-pixels
+#pragma unroll
+            for (int ij = 0; ij < 4; ij++) {
+              const size_t otk = ((size_t)b * p.H * 2 + (size_t)py * 2 + (ij >> 1)) * orow_w + (size_t)px * 2 + (ij & 1);
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[ij], v[4 + ij]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 + ij], v[12 + ij]);
+              uint2 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&h0);
+              pk.y = *reinterpret_cast<uint32_t*>(&h1);
+              *reinterpret_cast<uint2*>(ot + otk * ep.out_t_pitch + ep.out_t_coff + c0) = pk;
+            }
+          } else {
+            for (int j = 0; j < 16; j++) {
+              if (j >= valid) break;
+              const int n = nb + j;
+              const int cc = n / rr, ij = n - cc * rr, i = ij / r_, jj = ij - i * r_;
+              const size_t otk = ((size_t)b * p.H * r_ + (size_t)py * r_ + i) * orow_w + (size_t)px * r_ + jj;
+              ot[otk * ep.out_t_pitch + ep.out_t_coff + cc] = __float2bfloat16_rn(v[j]);
+            }
+          }
+        }
+      }
+      if (ep.colsum) {          // per-tile column sums of v (global-average-pool partials, fixed order)
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          float s = warp_sum(v[j]);
+          if (lane == 0) sred[quarter][c * 16 + j] = s;
+        }
+      }
+      if (do_ln) {
+        if (c == 0) ln_k = v[0];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          if (j < valid) {
+            const float dlt = v[j] - ln_k;
+            ln_s1 += dlt;
+            ln_s2 = fmaf(dlt, dlt, ln_s2);
+          }
+        }
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) w[j] = __float_as_uint(v[j]);
+        tmem_st16(trow + (uint32_t)(c * 16), w);     // keep the fp32 row in TMEM for the normalise pass
+      }
+    }
+    // trailing K-padding columns of the consumer that no n-tile covers
+    if (ep.out_t && ep.shuffle_r == 1 && blockIdx.y == gridDim.y - 1) {
+      bf16* ot = (bf16*)ep.out_t + (size_t)m * ep.out_t_pitch + ep.out_t_coff;
+      for (int n = n0 + p.BN; n < ep.out_t_zero_to; n++) ot[n] = __float2bfloat16_rn(0.f);
+    }
+    if (ep.colsum) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const int t = threadIdx.x - 64;
+      for (int n = t; n < p.BN; n += 128)
+        if (n0 + n < N)
+          ep.colsum[((size_t)b * nchunk + chunk_tile) * N + n0 + n] = sred[0][n] + sred[1][n] + sred[2][n] + sred[3][n];
+    }
+    if (do_ln) {
+      // fused LayerNorm of the row (eps 1e-5), shifted single-pass statistics in fp32
+      tmem_st_wait();
+      const float inv_n = 1.f / (float)N;
+      const float mean_d = ln_s1 * inv_n;
+      const float var = fmaxf(ln_s2 * inv_n - mean_d * mean_d, 0.f);
+      const float rstd = rsqrtf(var + 1e-5f);
+      const float mean = ln_k + mean_d;
+      bf16* lo = (bf16*)ep.ln_out + (size_t)m * ep.ln_pitch;
+      if (ep.ln_head_colsum) asm volatile("bar.sync 1, 128;" ::: "memory");   // sred reuse after colsum readers
+      for (int c = 0; c < p.BN / 16; c++) {
+        const int nb = n0 + c * 16;
+        const int valid = N - nb;
+        uint32_t r[16];
+        tmem_ld16(trow + (uint32_t)(c * 16), r);
+        tmem_ld_wait();
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          const float xv = __uint_as_float(r[j]);
+          v[j] = j < valid ? (xv - mean) * rstd * __ldg(ep.ln_gamma + nb + j) + __ldg(ep.ln_beta + nb + j) : 0.f;
+        }
+        store16_bf16(lo + nb, v, valid, ep.ln_pitch - nb, true);
+        if (c == 0 && ep.ln_head) {
+          bf16* hd = (bf16*)ep.ln_head + (size_t)m * ep.ln_head_c;
+          if (ep.ln_head_c == 16) {
+            store16_bf16(hd, v, 16, 16, true);
+          } else {
+            for (int j = 0; j < 16 && j < ep.ln_head_c; j++) hd[j] = __float2bfloat16_rn(v[j]);
+          }
+          if (ep.ln_head_colsum) {
+            // sums of the bf16-rounded head values (what the separate colsum kernel would read)
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              float s = warp_sum(__bfloat162float(__float2bfloat16_rn(v[j])));
+              if (lane == 0) sred[quarter][j] = s;
+            }
+          }
+        }
+      }
+      for (int n = n0 + p.BN; n < ep.ln_pitch; n++) lo[n] = __float2bfloat16_rn(0.f);
+      if (ep.ln_head_colsum) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int t = threadIdx.x - 64;
+        if (t < ep.ln_head_c && t < 16)
+          ep.ln_head_colsum[((size_t)b * nchunk + chunk_tile) * ep.ln_head_c + t] =
+              sred[0][t] + sred[1][t] + sred[2][t] + sred[3][t];
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// ---- host ------------------------------------------------------------------------------------------
+namespace tc {
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box, int inner_bytes) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  HB_REQUIRE(fn != nullptr, HATB200_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; i++) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; i++) gstr[i] = strides_bytes[i];
+  CUtensorMapSwizzle sw = inner_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                        : inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HB_REQUIRE(r == CUDA_SUCCESS, HATB200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d)", (int)r, rank);
+  return 0;
+}
+
+}  // namespace tc
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+static bool tc_geometry(const ConvArgs& a, int Npad, int Kpad, TcParams& p) {
+  if (a.W % TILE_W || a.H % TILE_H) return false;
+  if (!(a.KH & 1) || !(a.KW & 1)) return false;
+  p.BK = Kpad == 16 ? 16 : (Kpad == 32 ? 32 : 64);
+  if (Kpad % p.BK || Kpad < a.Cin) return false;
+  if ((a.a_pitch * 2) % 16 || (a.a_coff * 2) % 16) return false;
+  p.BN = tc_bn(a.N);
+  if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
+  p.B = a.B; p.H = a.H; p.W = a.W; p.KH = a.KH; p.KW = a.KW;
+  p.a_coff = a.a_coff; p.kblocks = Kpad / p.BK; p.N = a.N; p.Npad = Npad;
+  p.tiles_x = a.W / TILE_W; p.tiles_y = a.H / TILE_H;
+  p.a_bytes = TILE_M * p.BK * 2;
+  p.stage_bytes = round_up(p.a_bytes + p.BN * p.BK * 2, 1024);
+  uint32_t cols = 32;
+  while ((int)cols < p.BN) cols <<= 1;
+  p.tmem_cols = cols;
+  // pipeline depth: long main loops (3x3 convs) take the whole SM's shared memory; short ones (1x1) leave room
+  // for a second resident CTA whose epilogue overlaps this one's main loop
+  int iters = a.KH * a.KW * p.kblocks;
+  int budget = iters >= 12 ? 200 * 1024 : 100 * 1024;
+  int st = budget / p.stage_bytes;
+  st = st > 6 ? 6 : st;
+  st = st > iters ? iters : st;
+  st = st < 2 ? (iters < 2 ? 1 : 2) : st;
+  int forced = env_int("HATB200_TC_STAGES", 0);
+  if (forced > 0) st = forced > TC_MAX_STAGES ? TC_MAX_STAGES : forced;
+  p.stages = st;
+  return true;
+}
+
+bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
+  TcParams p;
+  if (!tc_geometry(a, Npad, Kpad, p)) return false;
+  if (ep.ln_out && (Npad != p.BN || ep.ln_pitch > 512)) return false;     // LN needs the whole row in one CTA
+  if (ep.ln_head && ep.ln_head_c > 16) return false;
+  if (ep.dyn_k && a.N > 16) return false;
+  if (tc::encode_tiled_fn() == nullptr) return false;
+  return true;
+}
+
+int launch_tapconv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
+  TcParams p;
+  HB_REQUIRE(tc_geometry(a, Npad, Kpad, p), HATB200_EUNSUPPORTED, "tapconv_tc: unsupported shape");
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)a.a_pitch, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
+    uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.W * a.a_pitch * 2, (uint64_t)a.H * a.W * a.a_pitch * 2};
+    uint32_t box[4] = {(uint32_t)p.BK, TILE_W, TILE_H, 1};
+    HB_TRY(tc::make_tmap_bf16(&tmA, a.A, 4, dims, str, box, p.BK * 2));
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)Kpad, (uint64_t)a.KH * a.KW * Npad};
+    uint64_t str[1] = {(uint64_t)Kpad * 2};
+    uint32_t box[2] = {(uint32_t)p.BK, (uint32_t)p.BN};
+    HB_TRY(tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, p.BK * 2));
+  }
+  size_t smem = (size_t)p.stages * p.stage_bytes + 1024;
+  static size_t smem_attr = 0;
+  if (smem > smem_attr) {
+    HB_CHECK_CUDA(cudaFuncSetAttribute(tapconv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 6144));
+    smem_attr = 227 * 1024;
+  }
+  dim3 grid(a.B * p.tiles_x * p.tiles_y, Npad / p.BN);
+  tapconv_tc_kernel<<<grid, TC_THREADS, smem, st>>>(tmA, tmB, p, ep);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace hb

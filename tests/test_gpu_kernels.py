@@ -1,0 +1,195 @@
+"""GPU: single-kernel parity through the C ABI entry points (include/hatb200.h) against torch-CPU fp32
+restatements of the same op (the oracle's building blocks)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import hat_oracle as O
+from super_resolution_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _tokens(x_bchw, pitch, dtype):
+    """(B,C,H,W) cpu fp32 -> channels-last tokens (B*H*W, pitch) on device, zero padded."""
+    b, c, h, w = x_bchw.shape
+    t = torch.zeros(b * h * w, pitch, dtype=dtype, device=DEV)
+    t[:, :c] = x_bchw.permute(0, 2, 3, 1).reshape(-1, c).to(DEV).to(dtype)
+    return t
+
+
+def _conv_case(B, H, W, Cin, N, k, dtype, use_tc, act=0, coff=0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, Cin + coff, H, W, generator=g)
+    w = torch.randn(N, Cin, k, k, generator=g) * (1.0 / (Cin * k * k) ** 0.5)
+    bias = torch.randn(N, generator=g) * 0.1
+    pitch = Cin + coff if Cin + coff == 16 else ((Cin + coff + 63) // 64) * 64
+    opitch = ((N + 63) // 64) * 64
+    xin = x.bfloat16().float() if dtype == torch.bfloat16 else x
+    win = w.bfloat16().float() if (dtype == torch.bfloat16 and use_tc) else w
+    ref = F.conv2d(xin[:, coff:], win, bias, padding=k // 2)
+    if act == 1:
+        ref = F.gelu(ref)
+    elif act == 2:
+        ref = F.leaky_relu(ref, 0.01)
+    xt = _tokens(x, pitch, dtype)
+    out = torch.full((B * H * W, opitch), 7.0, dtype=dtype, device=DEV)
+    wd, bd = w.to(DEV), bias.to(DEV)
+    rc = _lib.lib().hatb200_conv_tokens(_p(xt), _lib.dtype_code(dtype), pitch, coff, Cin, B, H, W, _p(wd), _p(bd), N,
+                                        k, k, act, _p(out), opitch, use_tc, _stream())
+    _lib.check(rc)
+    torch.cuda.synchronize()
+    got = out[:, :N].float().cpu().view(B, H, W, N).permute(0, 3, 1, 2)
+    return got, ref
+
+
+CONV_SHAPES = [
+    # B, H, W, Cin, N, k   (the shapes of HAT's layers)
+    (1, 16, 16, 180, 180, 1),     # esc aggr / proj / q_proj
+    (2, 16, 32, 180, 720, 1),     # ffn fc1 (3 n-tiles of 240)
+    (1, 16, 16, 360, 180, 1),     # ffn fc2
+    (1, 32, 16, 180, 540, 1),     # fused q/kv projection (3 n-tiles of 192)
+    (1, 16, 32, 180, 60, 3),      # CAB conv1
+    (2, 16, 16, 60, 180, 3),      # CAB conv2
+    (1, 32, 32, 180, 180, 3),     # RHAG conv / conv_after_body
+    (1, 16, 16, 64, 256, 3),      # upsample conv
+    (1, 16, 16, 180, 64, 3),      # conv_before_upsample
+    (2, 32, 16, 16, 16, 13),      # ESC large-kernel conv on the 16-channel slice
+    (1, 16, 16, 144, 6, 3),       # HAT-S CAB conv1 (mid = 6)
+    (1, 16, 16, 6, 144, 3),       # HAT-S CAB conv2
+    (1, 16, 16, 48, 96, 1),       # small dims
+]
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_conv_tokens_fp32_cuda_core(shape):
+    got, ref = _conv_case(*shape, torch.float32, 0, act=1)
+    assert (got - ref).abs().max().item() <= 2e-5 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+@pytest.mark.parametrize("use_tc", [0, 1])
+def test_conv_tokens_bf16(shape, use_tc):
+    got, ref = _conv_case(*shape, torch.bfloat16, use_tc, act=2)
+    # inputs are bf16-exact in the reference; the only error is fp32 accumulation order + bf16 output rounding
+    tol = 2.0 ** -8 * max(1.0, ref.abs().max().item())
+    assert (got - ref).abs().max().item() <= tol
+
+
+def test_conv_tokens_channel_offset_tc():
+    got, ref = _conv_case(1, 16, 16, 64, 64, 3, torch.bfloat16, 1, coff=64)
+    assert (got - ref).abs().max().item() <= 2.0 ** -8 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_layernorm(dtype):
+    M, Cn = 512, 180
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(M, Cn, generator=g) * 3 + 1.5
+    gamma, beta = torch.randn(Cn, generator=g), torch.randn(Cn, generator=g)
+    ref = F.layer_norm(x, (Cn,), gamma, beta, 1e-5)
+    out = torch.full((M, 192), 7.0, dtype=dtype, device=DEV)
+    head = torch.zeros(M, 16, dtype=dtype, device=DEV)
+    xd, gd, bd = x.to(DEV), gamma.to(DEV), beta.to(DEV)
+    _lib.check(_lib.lib().hatb200_layernorm(_p(xd), M, Cn, _p(gd), _p(bd), _p(out), _lib.dtype_code(dtype), 192,
+                                            _p(head), 16, _stream()))
+    torch.cuda.synchronize()
+    tol = 1e-5 if dtype == torch.float32 else 2.0 ** -7
+    assert (out[:, :Cn].float().cpu() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    assert out[:, Cn:].abs().max().item() == 0              # K padding of the consumer is zero
+    assert torch.equal(head.cpu(), out[:, :16].cpu())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dwconv_gate(dtype):
+    B, H, W, hid = 2, 16, 32, 360
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(B, 2 * hid, H, W, generator=g)
+    w = torch.randn(2 * hid, 1, 3, 3, generator=g) * 0.3
+    b = torch.randn(2 * hid, generator=g) * 0.1
+    xin = x.bfloat16().float() if dtype == torch.bfloat16 else x
+    t = F.conv2d(xin, w, b, padding=1, groups=2 * hid)
+    ref = t[:, :hid] * F.silu(t[:, hid:])
+    xt = _tokens(x, 768, dtype)
+    out = torch.zeros(B * H * W, 384, dtype=dtype, device=DEV)
+    wd, bd = w.to(DEV), b.to(DEV)
+    _lib.check(_lib.lib().hatb200_dwconv_gate(_p(xt), _lib.dtype_code(dtype), 768, B, H, W, hid, _p(wd), _p(bd),
+                                              _p(out), 384, _stream()))
+    torch.cuda.synchronize()
+    got = out[:, :hid].float().cpu().view(B, H, W, hid).permute(0, 3, 1, 2)
+    tol = 1e-5 if dtype == torch.float32 else 2.0 ** -7
+    assert (got - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+def _attention_reference(qkv, B, H, W, Cn, heads, ws, ows, table_compact):
+    """OCAB core (hat_arch.py:354-388) on (B,H,W,3C) with pre-scaled q, unfold zero padding, unmasked keys."""
+    d = Cn // heads
+    q, k, v = qkv[..., :Cn], qkv[..., Cn:2 * Cn], qkv[..., 2 * Cn:]
+    nwy, nwx = H // ws, W // ws
+    qw = q.view(B, nwy, ws, nwx, ws, Cn).permute(0, 1, 3, 2, 4, 5).reshape(-1, ws * ws, Cn)
+    kv = torch.cat([k, v], -1).permute(0, 3, 1, 2)
+    u = F.unfold(kv, kernel_size=ows, stride=ws, padding=(ows - ws) // 2)
+    u = u.view(B, 2, Cn, ows * ows, nwy * nwx).permute(1, 0, 4, 3, 2).reshape(2, -1, ows * ows, Cn)
+    nb = qw.shape[0]
+    qh = qw.view(nb, -1, heads, d).permute(0, 2, 1, 3)
+    kh = u[0].view(nb, -1, heads, d).permute(0, 2, 1, 3)
+    vh = u[1].view(nb, -1, heads, d).permute(0, 2, 1, 3)
+    T = ws + ows - 1
+    qi, ki = torch.arange(ws * ws), torch.arange(ows * ows)
+    slot = ((ki // ows)[None, :] - (qi // ws)[:, None] + ws - 1) * T + ((ki % ows)[None, :] - (qi % ws)[:, None] + ws - 1)
+    bias = table_compact[:, slot]                                    # (heads, nq, nk)
+    a = torch.softmax(qh @ kh.transpose(-2, -1) + bias[None], -1)
+    o = (a @ vh).transpose(1, 2).reshape(nb, ws * ws, Cn)
+    return o.view(B, nwy, nwx, ws, ws, Cn).permute(0, 1, 3, 2, 4, 5).reshape(B, H, W, Cn)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("geom", [(1, 16, 16, 180, 6), (2, 32, 48, 180, 6), (1, 32, 32, 144, 6), (1, 16, 32, 48, 6)])
+def test_ocab_attention_cuda_core(dtype, geom):
+    B, H, W, Cn, heads = geom
+    ws, ows = 16, 24
+    g = torch.Generator().manual_seed(3)
+    qkv = torch.randn(B, H, W, 3 * Cn, generator=g)
+    qkv[..., :Cn] *= (Cn // heads) ** -0.5
+    table = torch.randn(heads, 39 * 39, generator=g) * 0.5
+    src = qkv.bfloat16().float() if dtype == torch.bfloat16 else qkv
+    ref = _attention_reference(src, B, H, W, Cn, heads, ws, ows, table)
+    pitch = ((3 * Cn + 63) // 64) * 64
+    t = torch.zeros(B * H * W, pitch, dtype=dtype, device=DEV)
+    t[:, :3 * Cn] = qkv.view(-1, 3 * Cn).to(DEV).to(dtype)
+    opitch = ((Cn + 63) // 64) * 64
+    out = torch.zeros(B * H * W, opitch, dtype=dtype, device=DEV)
+    td = table.to(DEV)
+    _lib.check(_lib.lib().hatb200_ocab_attention(_p(t), _lib.dtype_code(dtype), pitch, B, H, W, Cn, heads, ws, ows,
+                                                 _p(td), _p(out), opitch, 0, _stream()))
+    torch.cuda.synchronize()
+    got = out[:, :Cn].float().cpu().view(B, H, W, Cn)
+    tol = 2e-5 if dtype == torch.float32 else 2.0 ** -7
+    assert (got - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+def test_tile_helpers_bit_exact():
+    B, Cn, h, w = 2, 3, 37, 45
+    x = torch.rand(B, Cn, h, w, device=DEV)
+    ph, pw = O.mod_pad(h, w, 16)
+    dst = torch.empty(B, Cn, h + ph, w + pw, device=DEV)
+    _lib.check(_lib.lib().hatb200_reflect_pad(_p(x), _lib.F32, B, Cn, h, w, _p(dst), ph, pw, _stream()))
+    assert torch.equal(dst, F.pad(x, (0, pw, 0, ph), "reflect"))
+    big = torch.zeros(B, Cn, 64, 80, device=DEV)
+    _lib.check(_lib.lib().hatb200_crop_place(_p(dst), _lib.F32, B, Cn, h + ph, w + pw, 5, 7, _p(big), 64, 80, 11, 13,
+                                             20, 30, _stream()))
+    want = torch.zeros_like(big)
+    want[:, :, 11:31, 13:43] = dst[:, :, 5:25, 7:37]
+    assert torch.equal(big, want)
