@@ -43,6 +43,13 @@ int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int
 // out_t[m, c] = a[m, c] + b[m, c] (b optional), fp32 in (M, C); optional fp32 copy to out_f32 (may alias a)
 int launch_add_convert(const float* a, const float* b, int M, int C, float* out_f32, void* out_t, int dt, int out_pitch,
                        int zero_to, cudaStream_t st);
+// bf16 fast paths (hbm_kernels.cu)
+bool dwgate_bf16_ok(int in_pitch, int W, int hid, int out_pitch, int zero_to);
+int launch_dwgate_bf16(const bf16* in, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
+                       bf16* out, int out_pitch, cudaStream_t st);
+bool conv_last_bf16_ok(int dt, int pitch, int Cin, int OC);
+int launch_conv_last_bf16(const bf16* in, int B, int H, int W, const float* w, const float* bias, int OC,
+                          const float* mean, float range, void* y, int y_dt, cudaStream_t st);
 int launch_crop_place(const void* src, int dt, int B, int C, int sh, int sw, int cy, int cx, void* dst, int dh, int dw,
                       int oy, int ox, int rh, int rw, cudaStream_t st);
 int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void* dst, int ph, int pw, cudaStream_t st);

@@ -158,6 +158,8 @@ __global__ void __launch_bounds__(256) conv_last_kernel(const T* __restrict__ in
 int launch_conv_last(const void* in, int dt, int pitch, int Cin, int B, int H, int W, const float* w,
                      const float* bias, int OC, const float* mean, float range, void* y, int y_dt, cudaStream_t st) {
   HB_REQUIRE(OC >= 1 && OC <= 4, HATB200_EUNSUPPORTED, "conv_last: out channels=%d not in 1..4", OC);
+  if (conv_last_bf16_ok(dt, pitch, Cin, OC))
+    return launch_conv_last_bf16((const bf16*)in, B, H, W, w, bias, OC, mean, range, y, y_dt, st);
   size_t total = (size_t)B * H * W;
   float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
   size_t smem = (size_t)9 * Cin * OC * sizeof(float);
@@ -342,6 +344,8 @@ __global__ void __launch_bounds__(256) dwgate_kernel(const T* __restrict__ in, i
 
 int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
                   void* out, int out_pitch, int zero_to, cudaStream_t st) {
+  if (dt == HATB200_BF16 && dwgate_bf16_ok(in_pitch, W, hid, out_pitch, zero_to))
+    return launch_dwgate_bf16((const bf16*)in, in_pitch, B, H, W, hid, w, b, (bf16*)out, out_pitch, st);
   size_t total = (size_t)B * H * W * (hid > zero_to ? hid : zero_to);
   HB_DISPATCH_T(dt, T, {
     dwgate_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)in, in_pitch, B, H, W, hid, w, b,
