@@ -81,9 +81,9 @@ int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, in
     bf16* w16;
     HB_TRY(pool.alloc((void**)&w16, (size_t)taps * Npad * Kpad * sizeof(bf16), st));
     HB_TRY(launch_pack_w_bf16(w, HATB200_F32, N, Cin, taps, w16, Npad, Kpad, 0, Cin, st));
-    HB_REQUIRE(tapconv_tc_supported(a, Npad, Kpad, ep), HATB200_EUNSUPPORTED,
+    HB_REQUIRE(conv_tc_supported(a, Npad, Kpad, ep), HATB200_EUNSUPPORTED,
                "conv_tokens: shape not supported by the tcgen05 kernel");
-    r = launch_tapconv_tc(a, w16, Npad, Kpad, ep, st);
+    r = launch_conv_tc(a, w16, Npad, Kpad, ep, st);
   } else {
     int Np = round_up(N, 64);
     float* w32;

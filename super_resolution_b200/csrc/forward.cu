@@ -122,8 +122,8 @@ struct Fwd {
   int conv_impl(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
     if (!ep.bias) ep.bias = cw.bias;
-    if (tc() && !tc_disabled(tag) && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
-      HB_TRY(launch_tapconv_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
+    if (tc() && !tc_disabled(tag) && conv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
+      HB_TRY(launch_conv_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
       return dbg("tapconv_tc");
     }
     // CUDA-core path: LayerNorm / column sums are separate kernels

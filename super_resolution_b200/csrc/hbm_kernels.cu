@@ -23,10 +23,58 @@ __device__ __forceinline__ void unpack8(const uint4& t, float (&o)[8]) {
 // ---------------------------------------------------------------------------------------------------
 constexpr int DW_PX = 4;
 
-__global__ void __launch_bounds__(256) dwgate_bf16_kernel(const bf16* __restrict__ in, int in_pitch, int B, int H,
-                                                          int W, int hid, const float* __restrict__ w,
-                                                          const float* __restrict__ bias, bf16* __restrict__ out,
-                                                          int out_pitch) {
+// depthwise 3x3 of 8 consecutive channels starting at `ch` for DW_PX pixels of one row (sliding window)
+__device__ __forceinline__ void dw_pass(const bf16* __restrict__ in, int in_pitch, int b, int y, int x0, int H, int W,
+                                        int ch, int wpitch, const float* __restrict__ w,
+                                        const float* __restrict__ bias, float (&acc)[DW_PX][8]) {
+  {
+    const float4* b4 = reinterpret_cast<const float4*>(bias + ch);
+    const float4 t0 = __ldg(b4), t1 = __ldg(b4 + 1);
+#pragma unroll
+    for (int p = 0; p < DW_PX; p++) {
+      acc[p][0] = t0.x; acc[p][1] = t0.y; acc[p][2] = t0.z; acc[p][3] = t0.w;
+      acc[p][4] = t1.x; acc[p][5] = t1.y; acc[p][6] = t1.z; acc[p][7] = t1.w;
+    }
+  }
+#pragma unroll
+  for (int ky = 0; ky < 3; ky++) {
+    const int yy = y + ky - 1;
+    if (yy < 0 || yy >= H) continue;
+    float wk[3][8];
+#pragma unroll
+    for (int kx = 0; kx < 3; kx++) {
+      const float4* a4 = reinterpret_cast<const float4*>(w + (size_t)(ky * 3 + kx) * wpitch + ch);
+      const float4 t0 = __ldg(a4), t1 = __ldg(a4 + 1);
+      wk[kx][0] = t0.x; wk[kx][1] = t0.y; wk[kx][2] = t0.z; wk[kx][3] = t0.w;
+      wk[kx][4] = t1.x; wk[kx][5] = t1.y; wk[kx][6] = t1.z; wk[kx][7] = t1.w;
+    }
+    const bf16* rowp = in + (((size_t)b * H + yy) * W) * in_pitch + ch;
+    uint4 raw[DW_PX + 2];
+#pragma unroll
+    for (int cx = 0; cx < DW_PX + 2; cx++) {          // input columns x0-1 .. x0+DW_PX (all loads in flight together)
+      const int xx = x0 + cx - 1;
+      raw[cx] = (xx >= 0 && xx < W) ? *reinterpret_cast<const uint4*>(rowp + (size_t)xx * in_pitch)
+                                    : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int cx = 0; cx < DW_PX + 2; cx++) {
+      float v[8];
+      unpack8(raw[cx], v);
+#pragma unroll
+      for (int kx = 0; kx < 3; kx++) {
+        const int p = cx - kx;                         // output pixel that sees this column through tap kx
+        if (p < 0 || p >= DW_PX) continue;
+#pragma unroll
+        for (int c = 0; c < 8; c++) acc[p][c] = fmaf(v[c], wk[kx][c], acc[p][c]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128, 4) dwgate_bf16_kernel(const bf16* __restrict__ in, int in_pitch, int B, int H,
+                                                             int W, int hid, const float* __restrict__ w,
+                                                             const float* __restrict__ bias, bf16* __restrict__ out,
+                                                             int out_pitch) {
   const int vec_out = out_pitch / 8;                 // channel vectors per token in the output (incl. zero pad)
   const int wq = W / DW_PX;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -46,63 +94,22 @@ __global__ void __launch_bounds__(256) dwgate_bf16_kernel(const bf16* __restrict
     for (int p = 0; p < DW_PX; p++) *reinterpret_cast<uint4*>(out + (row_tok + x0 + p) * out_pitch + j0) = z;
     return;
   }
-  float accp[DW_PX][8], accg[DW_PX][8];
-  {
-    float bp[8], bg[8];
-    const float4* b4 = reinterpret_cast<const float4*>(bias + j0);
-    const float4* g4 = reinterpret_cast<const float4*>(bias + hid + j0);
-    float4 t0 = b4[0], t1 = b4[1], u0 = g4[0], u1 = g4[1];
-    bp[0] = t0.x; bp[1] = t0.y; bp[2] = t0.z; bp[3] = t0.w; bp[4] = t1.x; bp[5] = t1.y; bp[6] = t1.z; bp[7] = t1.w;
-    bg[0] = u0.x; bg[1] = u0.y; bg[2] = u0.z; bg[3] = u0.w; bg[4] = u1.x; bg[5] = u1.y; bg[6] = u1.z; bg[7] = u1.w;
+  // gate half first (hat_arch.py:115-116: x_proj * silu(x_gate)), folded to its SiLU, then the proj half
+  float s[DW_PX][8];
+  dw_pass(in, in_pitch, b, y, x0, H, W, hid + j0, 2 * hid, w, bias, s);
 #pragma unroll
-    for (int p = 0; p < DW_PX; p++)
+  for (int p = 0; p < DW_PX; p++)
 #pragma unroll
-      for (int c = 0; c < 8; c++) { accp[p][c] = bp[c]; accg[p][c] = bg[c]; }
-  }
-#pragma unroll
-  for (int ky = 0; ky < 3; ky++) {
-    const int yy = y + ky - 1;
-    if (yy < 0 || yy >= H) continue;
-    float wp[3][8], wg[3][8];
-#pragma unroll
-    for (int kx = 0; kx < 3; kx++) {
-      const float* wt = w + (size_t)(ky * 3 + kx) * 2 * hid;
-      const float4* a4 = reinterpret_cast<const float4*>(wt + j0);
-      const float4* c4 = reinterpret_cast<const float4*>(wt + hid + j0);
-      float4 t0 = a4[0], t1 = a4[1], u0 = c4[0], u1 = c4[1];
-      wp[kx][0] = t0.x; wp[kx][1] = t0.y; wp[kx][2] = t0.z; wp[kx][3] = t0.w;
-      wp[kx][4] = t1.x; wp[kx][5] = t1.y; wp[kx][6] = t1.z; wp[kx][7] = t1.w;
-      wg[kx][0] = u0.x; wg[kx][1] = u0.y; wg[kx][2] = u0.z; wg[kx][3] = u0.w;
-      wg[kx][4] = u1.x; wg[kx][5] = u1.y; wg[kx][6] = u1.z; wg[kx][7] = u1.w;
-    }
-    const bf16* rowp = in + (((size_t)b * H + yy) * W) * in_pitch;
-#pragma unroll
-    for (int cx = 0; cx < DW_PX + 2; cx++) {          // input columns x0-1 .. x0+4
-      const int xx = x0 + cx - 1;
-      if (xx < 0 || xx >= W) continue;
-      const bf16* src = rowp + (size_t)xx * in_pitch;
-      float vp[8], vg[8];
-      unpack8(*reinterpret_cast<const uint4*>(src + j0), vp);
-      unpack8(*reinterpret_cast<const uint4*>(src + hid + j0), vg);
-#pragma unroll
-      for (int kx = 0; kx < 3; kx++) {
-        const int p = cx - kx;                         // output pixel that sees this column through tap kx
-        if (p < 0 || p >= DW_PX) continue;
-#pragma unroll
-        for (int c = 0; c < 8; c++) {
-          accp[p][c] = fmaf(vp[c], wp[kx][c], accp[p][c]);
-          accg[p][c] = fmaf(vg[c], wg[kx][c], accg[p][c]);
-        }
-      }
-    }
-  }
+    for (int c = 0; c < 8; c++) s[p][c] = silu_f(s[p][c]);
+  float a[DW_PX][8];
+  dw_pass(in, in_pitch, b, y, x0, H, W, j0, 2 * hid, w, bias, a);
 #pragma unroll
   for (int p = 0; p < DW_PX; p++) {
     uint4 o;
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
     for (int c = 0; c < 4; c++)
-      h[c] = __floats2bfloat162_rn(accp[p][2 * c] * silu_f(accg[p][2 * c]), accp[p][2 * c + 1] * silu_f(accg[p][2 * c + 1]));
+      h[c] = __floats2bfloat162_rn(a[p][2 * c] * s[p][2 * c], a[p][2 * c + 1] * s[p][2 * c + 1]);
     *reinterpret_cast<uint4*>(out + (row_tok + x0 + p) * out_pitch + j0) = o;
   }
 }
@@ -114,7 +121,7 @@ bool dwgate_bf16_ok(int in_pitch, int W, int hid, int out_pitch, int zero_to) {
 int launch_dwgate_bf16(const bf16* in, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
                        bf16* out, int out_pitch, cudaStream_t st) {
   size_t total = (size_t)B * H * (W / DW_PX) * (out_pitch / 8);
-  dwgate_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, in_pitch, B, H, W, hid, w, b, out, out_pitch);
+  dwgate_bf16_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(in, in_pitch, B, H, W, hid, w, b, out, out_pitch);
   HB_CHECK_LAUNCH();
   return 0;
 }

@@ -68,6 +68,17 @@ inline int tc_bn(int O) { int n16 = round_up(O, 16); int nt = cdiv(n16, 256); re
 inline int tc_npad(int O) { int n16 = round_up(O, 16); return cdiv(n16, 256) * tc_bn(O); }
 int launch_tapconv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
 bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
+// persistent weight-stationary tcgen05 GEMM for 1x1 layers (tc_gemm.cu); same packed weights and epilogue
+int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
+bool gemm_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
+// picks the tcgen05 kernel for the shape (1x1 -> tc_gemm, else tc_tapconv)
+inline bool conv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
+  return gemm_tc_supported(a, Npad, Kpad, ep) || tapconv_tc_supported(a, Npad, Kpad, ep);
+}
+inline int launch_conv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
+  if (gemm_tc_supported(a, Npad, Kpad, ep)) return launch_gemm_tc(a, w, Npad, Kpad, ep, st);
+  return launch_tapconv_tc(a, w, Npad, Kpad, ep, st);
+}
 
 // ---- OCAB attention core (hat_arch.py:354-388) ----
 struct AttnArgs {

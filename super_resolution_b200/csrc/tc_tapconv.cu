@@ -17,7 +17,7 @@
 #include <stdlib.h>
 
 #include "kernels.cuh"
-#include "tc_common.cuh"
+#include "tc_epilogue.cuh"
 
 namespace hb {
 
@@ -35,71 +35,6 @@ struct TcParams {
   int stages, stage_bytes, a_bytes;
   uint32_t tmem_cols;
 };
-
-// ---- epilogue helpers ------------------------------------------------------------------------------
-__device__ __forceinline__ void load16_f32(const float* p, int valid, float (&o)[16]) {
-  if (valid >= 16) {
-    const float4* q = reinterpret_cast<const float4*>(p);
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      float4 t = q[i];
-      o[4 * i] = t.x; o[4 * i + 1] = t.y; o[4 * i + 2] = t.z; o[4 * i + 3] = t.w;
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 16; i++) o[i] = i < valid ? p[i] : 0.f;
-  }
-}
-
-__device__ __forceinline__ void load16_bf16(const bf16* p, int valid, float (&o)[16]) {
-  if (valid >= 16) {
-    const uint4* q = reinterpret_cast<const uint4*>(p);
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-      uint4 t = q[i];
-      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        float2 f = __bfloat1622float2(h[j]);
-        o[8 * i + 2 * j] = f.x; o[8 * i + 2 * j + 1] = f.y;
-      }
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 16; i++) o[i] = i < valid ? __bfloat162float(p[i]) : 0.f;
-  }
-}
-
-// store 16 values as bf16; `valid` of them are real, columns [valid, zero_valid) are written as zero
-__device__ __forceinline__ void store16_bf16(bf16* p, const float (&v)[16], int valid, int zero_valid, bool aligned) {
-  if (valid >= 16 && aligned) {
-    uint4 t[2];
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(t);
-#pragma unroll
-    for (int i = 0; i < 8; i++) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-    uint4* q = reinterpret_cast<uint4*>(p);
-    q[0] = t[0];
-    q[1] = t[1];
-  } else {
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-      if (i < valid) p[i] = __float2bfloat16_rn(v[i]);
-      else if (i < zero_valid) p[i] = __float2bfloat16_rn(0.f);
-    }
-  }
-}
-
-__device__ __forceinline__ void store16_f32(float* p, const float (&v)[16], int valid) {
-  if (valid >= 16) {
-    float4* q = reinterpret_cast<float4*>(p);
-#pragma unroll
-    for (int i = 0; i < 4; i++) q[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-  } else {
-#pragma unroll
-    for (int i = 0; i < 16; i++)
-      if (i < valid) p[i] = v[i];
-  }
-}
 
 // ---- the kernel --------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TC_THREADS)
@@ -184,198 +119,20 @@ tapconv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4, one token row per thread =====
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    const int py = y0 + row / TILE_W, px = x0 + row % TILE_W;
-    const int m = (b * p.H + py) * p.W + px;
-    const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const int N = p.N;
-    const int chunk_tile = ty * p.tiles_x + tx;                 // tile index inside the sample
-    const int nchunk = p.tiles_x * p.tiles_y;
-    const bool do_ln = ep.ln_out != nullptr;
-    const bool aligned_t = ((ep.out_t_coff & 7) == 0);
-
+    EpiCtx c;
+    c.py = y0 + row / TILE_W; c.px = x0 + row % TILE_W;
+    c.b = b; c.H = p.H; c.W = p.W;
+    c.m = (b * p.H + c.py) * p.W + c.px;
+    c.trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    c.N = p.N; c.n0 = n0; c.BN = p.BN;
+    c.last_ntile = blockIdx.y == gridDim.y - 1;
+    c.chunk = ty * p.tiles_x + tx;                 // tile index inside the sample
+    c.nchunk = p.tiles_x * p.tiles_y;
+    c.quarter = quarter; c.lane = lane; c.gtid = threadIdx.x - 64; c.bar_id = 1;
+    c.sred = sred;
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
-
-    float ln_k = 0.f, ln_s1 = 0.f, ln_s2 = 0.f;
-    for (int c = 0; c < p.BN / 16; c++) {
-      const int nb = n0 + c * 16;
-      const int valid = N - nb;                                   // real columns in this chunk (may be <= 0)
-      uint32_t r[16];
-      tmem_ld16(trow + (uint32_t)(c * 16), r);
-      tmem_ld_wait();
-      float v[16];
-#pragma unroll
-      for (int j = 0; j < 16; j++) v[j] = __uint_as_float(r[j]);
-      if (valid > 0) {
-        if (ep.bias) {
-#pragma unroll
-          for (int j = 0; j < 16; j++) if (j < valid) v[j] += __ldg(ep.bias + nb + j);
-        }
-        if (ep.dyn_k) {       // per-sample dynamic depthwise 3x3 on the compact channels (esc_arch.py:123)
-          const bf16* xs = (const bf16*)ep.dyn_x;
-          for (int ky = 0; ky < 3; ky++) {
-            const int yy = py + ky - 1;
-            if (yy < 0 || yy >= p.H) continue;
-            for (int kx = 0; kx < 3; kx++) {
-              const int xx = px + kx - 1;
-              if (xx < 0 || xx >= p.W) continue;
-              float xv[16];
-              load16_bf16(xs + (size_t)(m + (ky - 1) * p.W + (kx - 1)) * ep.dyn_pitch + nb, valid, xv);
-#pragma unroll
-              for (int j = 0; j < 16; j++)
-                if (j < valid) v[j] = fmaf(xv[j], __ldg(ep.dyn_k + ((size_t)b * N + nb + j) * 9 + ky * 3 + kx), v[j]);
-            }
-          }
-        }
-        if (ep.scale_ncols > 0) {
-#pragma unroll
-          for (int j = 0; j < 16; j++) if (nb + j < ep.scale_ncols) v[j] *= ep.out_scale;
-        }
-        if (ep.act == ACT_GELU) {
-#pragma unroll
-          for (int j = 0; j < 16; j++) v[j] = gelu_f(v[j]);
-        } else if (ep.act == ACT_LRELU) {
-#pragma unroll
-          for (int j = 0; j < 16; j++) v[j] = lrelu_f(v[j]);
-        }
-        if (ep.eca_u) {
-          float u[16];
-          load16_bf16((const bf16*)ep.eca_u + (size_t)m * ep.eca_pitch + nb, valid, u);
-#pragma unroll
-          for (int j = 0; j < 16; j++)
-            if (j < valid) v[j] = fmaf(ep.eca_coef * __ldg(ep.eca_scale + (size_t)b * N + nb + j), u[j], v[j]);
-        }
-        if (ep.resid) {
-          float rs[16];
-          load16_f32(ep.resid + (size_t)m * ep.resid_pitch + nb, valid, rs);
-#pragma unroll
-          for (int j = 0; j < 16; j++) v[j] += rs[j];
-        }
-#pragma unroll
-        for (int j = 0; j < 16; j++) if (j >= valid) v[j] = 0.f;
-      } else {
-#pragma unroll
-        for (int j = 0; j < 16; j++) v[j] = 0.f;
-      }
-      // ---- outputs ----
-      if (ep.out_f32 && valid > 0) store16_f32(ep.out_f32 + (size_t)m * ep.out_f32_pitch + nb, v, valid);
-      if (ep.out_t) {
-        bf16* ot = (bf16*)ep.out_t;
-        if (ep.shuffle_r == 1) {
-          const int zv = ep.out_t_zero_to - nb;
-          if (valid > 0 || zv > 0)
-            store16_bf16(ot + (size_t)m * ep.out_t_pitch + ep.out_t_coff + nb, v, valid, zv, aligned_t);
-        } else if (valid > 0) {
-          // PixelShuffle(r) folded into the store: out[b, c, y*r+i, x*r+j] = in[b, c*r*r + i*r + j, y, x]
-          const int r_ = ep.shuffle_r, rr = r_ * r_;
-          const size_t orow_w = (size_t)p.W * r_;
-          if (r_ == 2 && valid >= 16) {
-            const int c0 = nb >> 2;   // 4 channels, 4 sub-pixels
-#pragma unroll
-            for (int ij = 0; ij < 4; ij++) {
-              const size_t otk = ((size_t)b * p.H * 2 + (size_t)py * 2 + (ij >> 1)) * orow_w + (size_t)px * 2 + (ij & 1);
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[ij], v[4 + ij]);
-              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 + ij], v[12 + ij]);
-              uint2 pk;
-              pk.x = *reinterpret_cast<uint32_t*>(&h0);
-              pk.y = *reinterpret_cast<uint32_t*>(&h1);
-              *reinterpret_cast<uint2*>(ot + otk * ep.out_t_pitch + ep.out_t_coff + c0) = pk;
-            }
-          } else {
-            for (int j = 0; j < 16; j++) {
-              if (j >= valid) break;
-              const int n = nb + j;
-              const int cc = n / rr, ij = n - cc * rr, i = ij / r_, jj = ij - i * r_;
-              const size_t otk = ((size_t)b * p.H * r_ + (size_t)py * r_ + i) * orow_w + (size_t)px * r_ + jj;
-              ot[otk * ep.out_t_pitch + ep.out_t_coff + cc] = __float2bfloat16_rn(v[j]);
-            }
-          }
-        }
-      }
-      if (ep.colsum) {          // per-tile column sums of v (global-average-pool partials, fixed order)
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          float s = warp_sum(v[j]);
-          if (lane == 0) sred[quarter][c * 16 + j] = s;
-        }
-      }
-      if (do_ln) {
-        if (c == 0) ln_k = v[0];
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          if (j < valid) {
-            const float dlt = v[j] - ln_k;
-            ln_s1 += dlt;
-            ln_s2 = fmaf(dlt, dlt, ln_s2);
-          }
-        }
-        uint32_t w[16];
-#pragma unroll
-        for (int j = 0; j < 16; j++) w[j] = __float_as_uint(v[j]);
-        tmem_st16(trow + (uint32_t)(c * 16), w);     // keep the fp32 row in TMEM for the normalise pass
-      }
-    }
-    // trailing K-padding columns of the consumer that no n-tile covers
-    if (ep.out_t && ep.shuffle_r == 1 && blockIdx.y == gridDim.y - 1) {
-      bf16* ot = (bf16*)ep.out_t + (size_t)m * ep.out_t_pitch + ep.out_t_coff;
-      for (int n = n0 + p.BN; n < ep.out_t_zero_to; n++) ot[n] = __float2bfloat16_rn(0.f);
-    }
-    if (ep.colsum) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      const int t = threadIdx.x - 64;
-      for (int n = t; n < p.BN; n += 128)
-        if (n0 + n < N)
-          ep.colsum[((size_t)b * nchunk + chunk_tile) * N + n0 + n] = sred[0][n] + sred[1][n] + sred[2][n] + sred[3][n];
-    }
-    if (do_ln) {
-      // fused LayerNorm of the row (eps 1e-5), shifted single-pass statistics in fp32
-      tmem_st_wait();
-      const float inv_n = 1.f / (float)N;
-      const float mean_d = ln_s1 * inv_n;
-      const float var = fmaxf(ln_s2 * inv_n - mean_d * mean_d, 0.f);
-      const float rstd = rsqrtf(var + 1e-5f);
-      const float mean = ln_k + mean_d;
-      bf16* lo = (bf16*)ep.ln_out + (size_t)m * ep.ln_pitch;
-      if (ep.ln_head_colsum) asm volatile("bar.sync 1, 128;" ::: "memory");   // sred reuse after colsum readers
-      for (int c = 0; c < p.BN / 16; c++) {
-        const int nb = n0 + c * 16;
-        const int valid = N - nb;
-        uint32_t r[16];
-        tmem_ld16(trow + (uint32_t)(c * 16), r);
-        tmem_ld_wait();
-        float v[16];
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-          const float xv = __uint_as_float(r[j]);
-          v[j] = j < valid ? (xv - mean) * rstd * __ldg(ep.ln_gamma + nb + j) + __ldg(ep.ln_beta + nb + j) : 0.f;
-        }
-        store16_bf16(lo + nb, v, valid, ep.ln_pitch - nb, true);
-        if (c == 0 && ep.ln_head) {
-          bf16* hd = (bf16*)ep.ln_head + (size_t)m * ep.ln_head_c;
-          if (ep.ln_head_c == 16) {
-            store16_bf16(hd, v, 16, 16, true);
-          } else {
-            for (int j = 0; j < 16 && j < ep.ln_head_c; j++) hd[j] = __float2bfloat16_rn(v[j]);
-          }
-          if (ep.ln_head_colsum) {
-            // sums of the bf16-rounded head values (what the separate colsum kernel would read)
-#pragma unroll
-            for (int j = 0; j < 16; j++) {
-              float s = warp_sum(__bfloat162float(__float2bfloat16_rn(v[j])));
-              if (lane == 0) sred[quarter][j] = s;
-            }
-          }
-        }
-      }
-      for (int n = n0 + p.BN; n < ep.ln_pitch; n++) lo[n] = __float2bfloat16_rn(0.f);
-      if (ep.ln_head_colsum) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int t = threadIdx.x - 64;
-        if (t < ep.ln_head_c && t < 16)
-          ep.ln_head_colsum[((size_t)b * nchunk + chunk_tile) * ep.ln_head_c + t] =
-              sred[0][t] + sred[1][t] + sred[2][t] + sred[3][t];
-      }
-    }
+    run_epilogue(ep, c);
   }
   tc_fence_before();
   __syncthreads();
