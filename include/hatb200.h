@@ -142,7 +142,9 @@ int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, in
 /* OCAB attention core (hat_arch.py:354-388): qkv (M, pitch) holding q (already
  * scaled) at channel 0, k at C, v at 2C; bias_table (heads, (ws+ows-1)^2)
  * compact relative-position table indexed by (ky-qy+ws-1, kx-qx+ws-1);
- * out (M,out_pitch).  Keys outside the image are zero vectors, not masked. */
+ * out (M,out_pitch).  Keys outside the image are zero vectors, not masked.
+ * use_tc=1 (BF16, ws 16, ows 24, head_dim <= 32) runs the tcgen05 flash-style kernel;
+ * this test entry converts to and from the head-padded layout the forward uses. */
 int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, int W, int C,
                            int heads, int ws, int ows, const float* bias_table,
                            void* out, int out_pitch, int use_tc, void* stream);

@@ -101,9 +101,27 @@ int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, 
   HB_REQUIRE(qkv && bias_table && out, HATB200_EINVAL, "ocab_attention: null tensor");
   AttnArgs a{qkv, pitch, B, H, W, C, heads, ws, ows, bias_table, out, out_pitch, 0};
   if (use_tc) {
-    HB_REQUIRE(dtype == HATB200_BF16 && attn_tc_supported(a), HATB200_EUNSUPPORTED,
-               "ocab_attention: shape/dtype not supported by the tcgen05 kernel");
-    return launch_attn_tc(a, (cudaStream_t)stream);
+    // the tcgen05 kernel works on the head-padded layout the forward's qkv GEMM produces: convert around the call
+    cudaStream_t st = (cudaStream_t)stream;
+    HB_REQUIRE(dtype == HATB200_BF16 && heads >= 1 && C % heads == 0, HATB200_EUNSUPPORTED,
+               "ocab_attention: the tcgen05 kernel needs bf16 and C divisible by heads");
+    const int hp = heads * ATTN_TC_DP;
+    const size_t M = (size_t)B * H * W;
+    TmpPool pool;
+    bf16 *qkv_p, *out_p;
+    float* bias_l2;
+    HB_TRY(pool.alloc((void**)&qkv_p, M * 3 * hp * sizeof(bf16), st));
+    HB_TRY(pool.alloc((void**)&out_p, M * hp * sizeof(bf16), st));
+    HB_TRY(pool.alloc((void**)&bias_l2, (size_t)heads * ATTN_TC_BIAS_FLOATS * sizeof(float), st));
+    AttnTcArgs ta{qkv_p, 3 * hp, B, H, W, heads, C / heads, ws, ows, bias_l2, out_p, hp};
+    HB_REQUIRE(attn_tc_supported(ta), HATB200_EUNSUPPORTED, "ocab_attention: shape not supported by the tcgen05 kernel");
+    HB_TRY(launch_headpad_qkv((const bf16*)qkv, pitch, C, heads, M, qkv_p, 3 * hp, st));
+    HB_TRY(launch_bias_l2(bias_table, heads, ws, ows, bias_l2, st));
+    int r = launch_attn_tc(ta, st);
+    if (r == 0) r = launch_headunpad_out(out_p, hp, C, heads, M, (bf16*)out, out_pitch, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (r == 0 && e != cudaSuccess) { set_error("ocab_attention: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
+    return r;
   }
   return launch_attn_simt(dtype, a, (cudaStream_t)stream);
 }

@@ -14,7 +14,7 @@
 namespace hb {
 
 struct Dims {
-  int B, H, W, M, C, Cp, mid, midp, hid, hp2, hp4, qkvp, h1p, pdim, opdim;
+  int B, H, W, M, C, Cp, mid, midp, hid, hp2, hp4, qkvp, h1p, pdim, opdim, hpad;
   int dt;      // storage dtype of activations
   size_t es;   // element size of T
 };
@@ -26,6 +26,10 @@ static Dims make_dims(const hatb200_config& c, int B, int H, int W, int dt) {
   d.mid = c.cab_mid; d.midp = round_up(d.mid, 64);
   d.hid = c.ffn_hidden; d.hp2 = round_up(d.hid, 64); d.hp4 = round_up(2 * d.hid, 64);
   d.qkvp = round_up(3 * d.C, 64);
+  d.hpad = 0;                                   // tcgen05 attention: heads * 32 channels per q / k / v
+  for (int L = 0; L < c.num_layers; L++)
+    if (c.num_heads[L] * ATTN_TC_DP > d.hpad) d.hpad = c.num_heads[L] * ATTN_TC_DP;
+  if (3 * d.hpad > d.qkvp) d.qkvp = round_up(3 * d.hpad, 64);
   d.h1p = d.hp4 > d.qkvp ? d.hp4 : d.qkvp;
   d.pdim = c.esc_pdim; d.opdim = c.ocab_esc_enable ? c.ocab_esc_pdim : 0;
   d.dt = dt; d.es = dt == HATB200_F32 ? 4 : 2;
@@ -51,6 +55,7 @@ static void plan(const hatb200_config& c, const Dims& d, char* base, Workspace& 
   w.T1 = take(M * d.midp * d.es);
   w.H1 = take(M * d.h1p * d.es);
   size_t gp = d.hp2 > d.Cp ? d.hp2 : d.Cp;
+  if ((size_t)round_up(d.hpad, 64) > gp) gp = round_up(d.hpad, 64);
   w.G = take(M * gp * d.es);
   if (c.upsampler == 1) {
     int s = c.upscale;
@@ -105,7 +110,8 @@ struct Fwd {
   // dense conv / linear over tokens; tensor cores when available for this shape
   int conv(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     double Mt = (double)d.B * H * W;
-    int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), Mt * (cw.I + cw.O) * d.es);
+    const double fo = cw.algoO ? cw.algoO : cw.O, fi = cw.algoI ? cw.algoI : cw.I;
+    int tid = t_begin(tag, 2.0 * Mt * fo * fi * cw.taps(), Mt * (fi + fo) * d.es);
     int r = conv_impl(tag, cw, A, a_pitch, a_coff, H, W, ep);
     t_end(tid);
     return r;
@@ -216,6 +222,11 @@ struct Fwd {
     const hatb200_config& c = h->cfg;
     int dh = d.C / o.heads;
     float scale = c.qk_scale > 0.f ? c.qk_scale : 1.0f / sqrtf((float)dh);
+    // tcgen05 attention (bf16 path, default geometry): head-padded qkv / proj weights
+    const int hp = o.heads * ATTN_TC_DP;
+    AttnTcArgs ta{w.H1, 3 * hp, d.B, d.H, d.W, o.heads, dh, c.window_size, c.overlap_win_size, o.bias_l2, w.G, hp};
+    const bool use_attn_tc = tc() && !c.ocab_esc_enable && o.bias_l2 != nullptr && !tc_disabled("ocab_attention") &&
+                             attn_tc_supported(ta);
     if (c.ocab_esc_enable) {   // K/V from y = ConvAttnWrapper(xn) (hat_arch.py:336-344)
       HB_CHECK_CUDA(cudaMemcpyAsync(w.XN2, w.XN, (size_t)d.M * d.Cp * d.es, cudaMemcpyDeviceToDevice, st));
       HB_TRY(esc_mix(o.esc, w.XN2));
@@ -225,24 +236,31 @@ struct Fwd {
       HB_TRY(conv("ocab_qkv", o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
       Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = d.qkvp; ek.out_t_coff = d.C;
       HB_TRY(conv("ocab_qkv", o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
+    } else if (use_attn_tc) {
+      Epilogue ep; ep.out_scale = scale; ep.scale_ncols = hp; ep.out_t = w.H1; ep.out_t_pitch = 3 * hp;
+      HB_TRY(conv("ocab_qkv", o.qkv_tc, w.XN, d.Cp, 0, d.H, d.W, ep));
     } else {
       Epilogue ep; ep.out_scale = scale; ep.scale_ncols = d.C; ep.out_t = w.H1; ep.out_t_pitch = d.qkvp;
       HB_TRY(conv("ocab_qkv", o.qkv, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
-    AttnArgs a{w.H1, d.qkvp, d.B, d.H, d.W, d.C, o.heads, c.window_size, c.overlap_win_size, o.bias_compact,
-               w.G, d.Cp, d.Cp};
     {
       double nk = (double)c.overlap_win_size * c.overlap_win_size;
       int tid = t_begin("ocab_attention", 4.0 * d.M * nk * d.C, (double)d.M * 4 * d.C * d.es);
-      if (tc() && attn_tc_supported(a)) HB_TRY(launch_attn_tc(a, st));
-      else HB_TRY(launch_attn_simt(d.dt, a, st));
+      if (use_attn_tc) {
+        HB_TRY(launch_attn_tc(ta, st));
+      } else {
+        AttnArgs a{w.H1, d.qkvp, d.B, d.H, d.W, d.C, o.heads, c.window_size, c.overlap_win_size, o.bias_compact,
+                   w.G, d.Cp, d.Cp};
+        HB_TRY(launch_attn_simt(d.dt, a, st));
+      }
       t_end(tid);
     }
     HB_TRY(dbg("attention"));
     {  // proj + shortcut, norm2
       Epilogue ep; ep.resid = x; ep.resid_pitch = d.C; ep.out_f32 = x; ep.out_f32_pitch = d.C;
       set_ln(ep, &o.n2, w.XN2, 0);
-      HB_TRY(conv("ocab_proj", o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
+      if (use_attn_tc) HB_TRY(conv("ocab_proj", o.proj_tc, w.G, hp, 0, d.H, d.W, ep));
+      else HB_TRY(conv("ocab_proj", o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
     }
     {  // MLP (hat_arch.py:309-313)
       Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.H1; ep.out_t_pitch = d.hp2; ep.out_t_zero_to = d.hp2;

@@ -88,8 +88,29 @@ struct AttnArgs {
   void* out; int out_pitch; int out_zero_to;
 };
 int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st);
-int launch_attn_tc(const AttnArgs& a, cudaStream_t st);
-bool attn_tc_supported(const AttnArgs& a);
+// tcgen05 kernel (tc_attn.cu): head-padded bf16 layout, head_dim padded to 32 channels (pad channels zero):
+// q at [0, heads*32) (pre-scaled), k at [heads*32, 2*heads*32), v at [2*heads*32, 3*heads*32); out (M, out_pitch)
+// holds heads*32 channels.
+struct AttnTcArgs {
+  const void* qkv; int pitch;
+  int B, H, W, heads, head_dim, ws, ows;
+  const float* bias_l2;              // (heads, 1536): compact table * log2(e), zero padded (launch_bias_l2)
+  void* out; int out_pitch;
+};
+int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st);
+bool attn_tc_supported(const AttnTcArgs& a);
+constexpr int ATTN_TC_DP = 32, ATTN_TC_BIAS_FLOATS = 1536;
+// pack-time helpers for the head-padded layout (tc_attn.cu)
+int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
+                             cudaStream_t st);
+int launch_pack_vec_headpad(const void* src, int dt, int C, int heads, int nblk, float* dst, int dst0, cudaStream_t st);
+int launch_pack_cols_headpad(const void* src, int dt, int O, int C, int heads, bf16* dst, int Npad, int Kpad,
+                             cudaStream_t st);
+int launch_bias_l2(const float* compact, int heads, int ws, int ows, float* dst, cudaStream_t st);
+int launch_headpad_qkv(const bf16* src, int src_pitch, int C, int heads, size_t M, bf16* dst, int dst_pitch,
+                       cudaStream_t st);
+int launch_headunpad_out(const bf16* src, int src_pitch, int C, int heads, size_t M, bf16* dst, int dst_pitch,
+                         cudaStream_t st);
 // compact[h][(dy+ws-1)*(ws+ows-1) + dx+ws-1] = table[wrap(rpi[q][k])][h]; also verifies on device that
 // the index buffer is translation invariant (err_flag != 0 otherwise).
 int launch_pack_ocab_bias(const void* table, int table_dt, const int64_t* rpi, int heads, int ws, int ows,

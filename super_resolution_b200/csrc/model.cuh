@@ -22,6 +22,7 @@ struct ConvW {               // dense conv / Linear weight in both kernel layout
   float* w32 = nullptr; int Np = 0;            // fp32 [taps][I][Np]        (CUDA-core kernels)
   bf16* w16 = nullptr; int Npad = 0, Kpad = 0;  // bf16 [taps][Npad][Kpad]   (tcgen05 kernels)
   float* bias = nullptr;                        // fp32 [O] (zeros when the layer has no bias)
+  int algoO = 0, algoI = 0;                     // un-padded sizes for FLOP accounting when O / I include layout padding
   int taps() const { return KH * KW; }
 };
 
@@ -48,6 +49,9 @@ struct OcabW {
   ConvW qkv;                 // q_proj rows [0,C) then kv_proj rows [C,3C)
   ConvW q, kv;               // separate copies (ocab_esc_enable: K/V come from another input)
   float* bias_compact = nullptr;   // (heads, (ws+ows-1)^2)
+  // tcgen05 attention path: head-padded (head_dim -> 32) qkv / proj weights and the log2e-scaled bias table
+  ConvW qkv_tc, proj_tc;
+  float* bias_l2 = nullptr;        // (heads, 1536)
   ConvW proj, mlp0, mlp2;
   EscW esc;
   int heads = 0;

@@ -100,6 +100,38 @@ struct Packer {
     return 0;
   }
 
+  // tcgen05 attention path: qkv / proj weights in the head-padded layout (head_dim -> 32), bias table * log2(e)
+  int ocab_tc(const std::string& op, OcabW& o, int C, int ws, int ows) {
+    const int heads = o.heads, HP = heads * ATTN_TC_DP;
+    if (C % heads || C / heads > ATTN_TC_DP) return 0;           // unsupported head size: CUDA-core attention only
+    const ParamRef *q, *kv, *pr;
+    HB_TRY(get(op + ".q_proj.weight", &q));
+    HB_TRY(get(op + ".kv_proj.weight", &kv));
+    HB_TRY(get(op + ".proj.weight", &pr));
+    ConvW& w = o.qkv_tc;
+    w.O = 3 * HP; w.I = C; w.KH = w.KW = 1; w.algoO = 3 * C; w.algoI = C;
+    w.Npad = tc_npad(w.O); w.Kpad = kpad_of(C);
+    HB_TRY(alloc((void**)&w.w16, (size_t)w.Npad * w.Kpad * sizeof(bf16)));
+    HB_TRY(launch_pack_rows_headpad(q->ptr, q->dtype, C, heads, 1, w.w16, w.Kpad, 0, st));
+    HB_TRY(launch_pack_rows_headpad(kv->ptr, kv->dtype, C, heads, 2, w.w16, w.Kpad, HP, st));
+    HB_TRY(alloc((void**)&w.bias, (size_t)w.O * sizeof(float)));
+    if (has(op + ".q_proj.bias")) {
+      const ParamRef *qb, *kvb;
+      HB_TRY(get(op + ".q_proj.bias", &qb));
+      HB_TRY(get(op + ".kv_proj.bias", &kvb));
+      HB_TRY(launch_pack_vec_headpad(qb->ptr, qb->dtype, C, heads, 1, w.bias, 0, st));
+      HB_TRY(launch_pack_vec_headpad(kvb->ptr, kvb->dtype, C, heads, 2, w.bias, HP, st));
+    }
+    ConvW& pj = o.proj_tc;
+    pj.O = C; pj.I = HP; pj.KH = pj.KW = 1; pj.algoO = C; pj.algoI = C;
+    pj.Npad = tc_npad(C); pj.Kpad = kpad_of(HP);
+    HB_TRY(alloc((void**)&pj.w16, (size_t)pj.Npad * pj.Kpad * sizeof(bf16)));
+    HB_TRY(launch_pack_cols_headpad(pr->ptr, pr->dtype, C, C, heads, pj.w16, pj.Npad, pj.Kpad, st));
+    pj.bias = o.proj.bias;
+    HB_TRY(alloc((void**)&o.bias_l2, (size_t)heads * ATTN_TC_BIAS_FLOATS * sizeof(float)));
+    return launch_bias_l2(o.bias_compact, heads, ws, ows, o.bias_l2, st);
+  }
+
   int run() {
     const hatb200_config& c = h->cfg;
     const int C = c.embed_dim, hid = c.ffn_hidden, ws = c.window_size, ows = c.overlap_win_size;
@@ -156,6 +188,7 @@ struct Packer {
       HB_TRY(alloc((void**)&o.bias_compact, (size_t)o.heads * T * T * sizeof(float)));
       HB_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
                                    h->err_flag, st));
+      if (ws == 16 && ows == 24 && !c.ocab_esc_enable) HB_TRY(ocab_tc(op, o, C, ws, ows));
       if (c.resi_conv) HB_TRY(conv(lp + ".conv", lw.conv, C, C, 3, 3));
     }
     HB_TRY(ln("norm", h->final_norm));

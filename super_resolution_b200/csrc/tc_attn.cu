@@ -1,0 +1,451 @@
+// tc_attn.cu -- OCAB overlapping-window attention core on the 5th-gen tensor cores (flash style).
+//
+// Reference: OCAB.forward, hat_arch.py:354-388 (window_size 16, overlap window 24, 6 heads):
+//   per (window, head):  S = (q*scale) k^T + rel-pos-bias   (256 x 576),  softmax over the 576 keys,  O = P v
+// Keys/values of a window are the 24x24 pixels around it; positions outside the image are ZERO vectors
+// that still take softmax mass (nn.Unfold pads after the projection, hat_arch.py:296-297,:359-360).
+//
+// B200 mapping.  The qkv GEMM writes a head-padded layout (head_dim 30 -> 32: q | k | v, each heads x 32
+// channels, pad channels exactly zero), so every operand tile is a TMA box of the token tensor:
+//   Q   {32 ch, 16 x, 16 y}              -> 256 rows x 64 B  (K-major A operand, SWIZZLE_64B)
+//   K,V {32 ch, 24 x, 4 y} per key chunk ->  96 rows x 64 B  (K: K-major B operand; V: MN-major B operand)
+// with TMA out-of-bounds zero fill standing in for the unfold padding -- no unfold tensor, no S matrix in HBM
+// (reference: 906 MB of fp32 logits at the bench config).
+// A persistent CTA walks (window, head) units.  Warp roles (320 threads):
+//   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (8-stage ring, prefetches across units)
+//   warp 1   MMA issuer:   S[g] = Q[g] K_c^T  (M128 N96 K32)  and  O[g] = P[g] V_c  (M128 N32 K96)
+//   warps 2-5 / 6-9  softmax warpgroups g = 0/1, one query row per thread (rows 0-127 / 128-255):
+//            pass 1: S*log2e + bias -> running max (row parked back in TMEM); pass 2: exp2, row sum, P as bf16
+//            into shared memory in the UMMA K-major layout; the per-chunk O (fp32, TMEM) is folded into
+//            registers with the usual online-softmax rescale, so nothing is ever renormalised in TMEM.
+// TMEM: S double-buffered per warpgroup (4 x 96 columns) + O double-buffered per warpgroup (4 x 32) = 512.
+#include "kernels.cuh"
+#include "tc_common.cuh"
+
+namespace hb {
+
+using namespace tc;
+
+namespace {
+constexpr int AT_THREADS = 320;
+constexpr int WS = 16, OWS = 24, PADW = 4, DP = 32, TN = 39;     // window, overlap window, ring, padded head dim, 16+24-1
+constexpr int KC = 96, NCH = 6, KROWS = 4;                       // keys per chunk (4 key rows), chunks per unit
+constexpr int KV_STAGES = 8;
+constexpr int Q_BYTES = 256 * 64, BIAS_FLOATS = 1536, BIAS_BYTES = BIAS_FLOATS * 4;
+constexpr int QST_BYTES = Q_BYTES + BIAS_BYTES;                  // 22528
+constexpr int K_BYTES = KC * 64, KVST_BYTES = 2 * K_BYTES;       // 6144, 12288
+constexpr int P_BYTES = 3 * 128 * 64;                            // 24576 per warpgroup
+constexpr int SMEM_BYTES = 2 * QST_BYTES + KV_STAGES * KVST_BYTES + 2 * P_BYTES + 1024;
+constexpr uint32_t S_COLS = 96, O_COL0 = 384;
+constexpr float LOG2E = 1.4426950408889634f;
+
+struct AttnParams {
+  int B, H, W, heads, nwx, nwy, units;
+  int k_off, v_off;          // first k / v channel
+  const float* bias_l2;      // (heads, 1536): compact rel-pos bias * log2(e)
+  bf16* out;
+  int out_pitch;
+};
+
+// MN-major (B = V[key][d]) shared-memory descriptor: 64-byte rows, SWIZZLE_64B, 8-key groups 512 B apart
+__device__ __forceinline__ uint64_t make_desc_mn64(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(512 >> 4) << 16;      // LBO (next 32-wide MN atom; unused for N = 32)
+  d |= (uint64_t)(512 >> 4) << 32;      // SBO: next group of 8 K rows
+  d |= 1ull << 46;
+  d |= 4ull << 61;                      // SWIZZLE_64B
+  return d;
+}
+}  // namespace
+
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t q_full[2], q_empty[2];
+  __shared__ __align__(8) uint64_t kv_full[KV_STAGES], kv_empty[KV_STAGES];
+  __shared__ __align__(8) uint64_t s_full[2][2], s_empty[2][2];
+  __shared__ __align__(8) uint64_t p_full[2], o_full[2][2];
+  __shared__ uint32_t tmem_slot;
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sm_q = smem;                                  // [2][Q 16 KB | bias 6 KB]
+  uint8_t* sm_kv = sm_q + 2 * QST_BYTES;                 // [KV_STAGES][K 6 KB | V 6 KB]
+  uint8_t* sm_p = sm_kv + KV_STAGES * KVST_BYTES;        // [2][3 blocks of 128 rows x 64 B]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmKV);
+    for (int i = 0; i < 2; i++) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1 + 256);
+      mbar_init(&p_full[i], 128);
+      for (int j = 0; j < 2; j++) {
+        mbar_init(&s_full[i][j], 1);
+        mbar_init(&s_empty[i][j], 128);
+        mbar_init(&o_full[i][j], 1);
+      }
+    }
+    for (int i = 0; i < KV_STAGES; i++) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int wins = p.nwx * p.nwy;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int ui = 0, kvit = 0;
+      for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
+        const int head = u % p.heads, win = u / p.heads;
+        const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
+        const int qb = ui & 1;
+        mbar_wait(&q_empty[qb], (((uint32_t)ui >> 1) & 1u) ^ 1u);
+        uint8_t* qs = sm_q + qb * QST_BYTES;
+        mbar_arrive_expect_tx(&q_full[qb], QST_BYTES);
+        tma_load_4d(qs, &tmQ, &q_full[qb], head * DP, wx * WS, wy * WS, b);
+        bulk_load_1d(qs + Q_BYTES, p.bias_l2 + (size_t)head * BIAS_FLOATS, BIAS_BYTES, &q_full[qb]);
+        for (int kc = 0; kc < NCH; kc++, kvit++) {
+          const int st = kvit % KV_STAGES;
+          mbar_wait(&kv_empty[st], (((uint32_t)(kvit / KV_STAGES)) & 1u) ^ 1u);
+          uint8_t* ks = sm_kv + st * KVST_BYTES;
+          mbar_arrive_expect_tx(&kv_full[st], KVST_BYTES);
+          const int x0 = wx * WS - PADW, y0 = wy * WS - PADW + kc * KROWS;
+          tma_load_4d(ks, &tmKV, &kv_full[st], p.k_off + head * DP, x0, y0, b);
+          tma_load_4d(ks + K_BYTES, &tmKV, &kv_full[st], p.v_off + head * DP, x0, y0, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc_bf16(128, KC);
+      const uint32_t idesc_o = make_idesc_bf16(128, DP) | (1u << 16);     // B operand MN-major
+      int ui = 0, kvit = 0;
+      for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
+        const int qb = ui & 1;
+        const uint32_t q_addr = smem_u32(sm_q + qb * QST_BYTES);
+        mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
+        tc_fence_after();
+        auto issue_pv = [&](int kc, int kvslot) {
+          const uint32_t v_addr = smem_u32(sm_kv + kvslot * KVST_BYTES + K_BYTES);
+          for (int g = 0; g < 2; g++) {
+            mbar_wait(&p_full[g], (uint32_t)(ui * NCH + kc) & 1u);
+            tc_fence_after();
+            const uint32_t p_addr = smem_u32(sm_p + g * P_BYTES);
+            const uint32_t d_o = tmem_base + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP;
+#pragma unroll
+            for (int j = 0; j < KC / 16; j++) {
+              const uint64_t ad = make_smem_desc(p_addr + (j >> 1) * 8192 + (j & 1) * 32, 64);
+              const uint64_t bd = make_desc_mn64(v_addr + j * 1024);
+              umma_bf16(d_o, ad, bd, idesc_o, j != 0 ? 1u : 0u);
+            }
+            umma_commit(&o_full[g][kc & 1]);
+          }
+          umma_commit(&kv_empty[kvslot]);
+        };
+        int prev_slot = 0;
+        for (int kc = 0; kc < NCH; kc++, kvit++) {
+          const int st = kvit % KV_STAGES;
+          mbar_wait(&kv_full[st], ((uint32_t)(kvit / KV_STAGES)) & 1u);
+          tc_fence_after();
+          const uint32_t k_addr = smem_u32(sm_kv + st * KVST_BYTES);
+          const int sb = kc & 1;
+          for (int g = 0; g < 2; g++) {
+            mbar_wait(&s_empty[g][sb], ((uint32_t)(ui * 3 + (kc >> 1)) & 1u) ^ 1u);
+            tc_fence_after();
+            const uint32_t d_s = tmem_base + (uint32_t)(g * 2 + sb) * S_COLS;
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+              const uint64_t ad = make_smem_desc(q_addr + g * 8192 + k * 32, 64);
+              const uint64_t bd = make_smem_desc(k_addr + k * 32, 64);
+              umma_bf16(d_s, ad, bd, idesc_s, k);
+            }
+            umma_commit(&s_full[g][sb]);
+          }
+          if (kc == NCH - 1) umma_commit(&q_empty[qb]);      // Q tile consumed once these MMAs complete
+          if (kc >= 1) issue_pv(kc - 1, prev_slot);
+          prev_slot = st;
+        }
+        issue_pv(NCH - 1, prev_slot);
+      }
+    }
+  } else {
+    // ===== softmax warpgroups =====
+    const int g = (warp - 2) >> 2;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;            // query row inside this warpgroup's half
+    const int qi = g * 128 + row;
+    const int qy = qi / WS, qx = qi % WS;
+    const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+    uint8_t* prow = sm_p + g * P_BYTES + row * 64;
+    const int psw = (row >> 1) & 3;                 // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
+    int ui = 0;
+    for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
+      const int head = u % p.heads, win = u / p.heads;
+      const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
+      const int qb = ui & 1;
+      mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
+      const float* bias_s = reinterpret_cast<const float*>(sm_q + qb * QST_BYTES + Q_BYTES) + (WS - 1 - qy) * TN +
+                            (WS - 1 - qx);
+      float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+      float o_reg[DP];
+#pragma unroll
+      for (int i = 0; i < DP; i++) o_reg[i] = 0.f;
+
+      auto fold_o = [&](int kc) {      // o_reg = o_reg * alpha(kc) + O(kc)
+        mbar_wait(&o_full[g][kc & 1], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
+        tc_fence_after();
+        uint32_t r[32];
+        tmem_ld32(tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < DP; i++) o_reg[i] = fmaf(o_reg[i], alpha_prev, __uint_as_float(r[i]));
+      };
+
+      for (int kc = 0; kc < NCH; kc++) {
+        const int sb = kc & 1;
+        const uint32_t s_addr = tmem_base + lane_sel + (uint32_t)(g * 2 + sb) * S_COLS;
+        mbar_wait(&s_full[g][sb], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
+        tc_fence_after();
+        const float* bchunk = bias_s + kc * KROWS * TN;
+        // ---- pass 1: logits in the log2 domain, running max; the row is parked back in TMEM ----
+        float cmax = -INFINITY;
+#pragma unroll
+        for (int sub = 0; sub < 3; sub++) {
+          uint32_t r[32];
+          tmem_ld32(s_addr + sub * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            const int local = sub * 32 + j;                     // key inside the chunk: 4 rows of 24
+            const float v = fmaf(__uint_as_float(r[j]), LOG2E, bchunk[(local / OWS) * TN + (local % OWS)]);
+            cmax = fmaxf(cmax, v);
+            r[j] = __float_as_uint(v);
+          }
+          tmem_st32(s_addr + sub * 32, r);
+        }
+        tmem_st_wait();
+        const float m_new = fmaxf(m_run, cmax);
+        const float alpha = ex2_approx(m_run - m_new);          // 0 for the first chunk (m_run = -inf)
+        // PV of the previous chunk must have finished reading P before it is overwritten; fold its O
+        if (kc > 0) fold_o(kc - 1);
+        // ---- pass 2: p = 2^(s - m), row sum, P (bf16) into the K-major SWIZZLE_64B operand layout ----
+        float csum = 0.f;
+#pragma unroll
+        for (int sub = 0; sub < 3; sub++) {
+          uint32_t r[32];
+          tmem_ld32(s_addr + sub * 32, r);
+          tmem_ld_wait();
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; j++) {
+            const float p0 = ex2_approx(__uint_as_float(r[2 * j]) - m_new);
+            const float p1 = ex2_approx(__uint_as_float(r[2 * j + 1]) - m_new);
+            csum += p0 + p1;
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+            pk[j] = *reinterpret_cast<uint32_t*>(&h2);
+          }
+          uint8_t* blk = prow + sub * 8192;
+#pragma unroll
+          for (int c = 0; c < 4; c++)
+            *reinterpret_cast<uint4*>(blk + ((c ^ psw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+        }
+        l_run = fmaf(l_run, alpha, csum);
+        m_run = m_new;
+        alpha_prev = alpha;
+        fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
+        tc_fence_before();
+        mbar_arrive(&p_full[g]);
+        mbar_arrive(&s_empty[g][sb]);
+      }
+      fold_o(NCH - 1);
+      // ---- normalise and store: 32 (padded) head channels of one token ----
+      const float inv = 1.f / l_run;
+      const size_t tok = ((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx;
+      bf16* orow = p.out + tok * p.out_pitch + head * DP;
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        uint4 t;
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+        for (int j = 0; j < 4; j++) h2[j] = __floats2bfloat162_rn(o_reg[8 * c + 2 * j] * inv, o_reg[8 * c + 2 * j + 1] * inv);
+        reinterpret_cast<uint4*>(orow)[c] = t;
+      }
+      mbar_arrive(&q_empty[qb]);        // bias table of this stage consumed
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ---- host ------------------------------------------------------------------------------------------
+bool attn_tc_supported(const AttnTcArgs& a) {
+  if (a.ws != WS || a.ows != OWS || a.head_dim > DP || a.head_dim < 1) return false;
+  if (a.H % WS || a.W % WS) return false;
+  if ((a.pitch * 2) % 16 || (a.out_pitch * 2) % 16) return false;
+  if (a.pitch < 3 * a.heads * DP || a.out_pitch < a.heads * DP) return false;
+  if (tc::encode_tiled_fn() == nullptr) return false;
+  return true;
+}
+
+int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st) {
+  HB_REQUIRE(attn_tc_supported(a), HATB200_EUNSUPPORTED, "attn_tc: unsupported shape");
+  CUtensorMap tmQ, tmKV;
+  uint64_t dims[4] = {(uint64_t)a.pitch, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
+  uint64_t str[3] = {(uint64_t)a.pitch * 2, (uint64_t)a.W * a.pitch * 2, (uint64_t)a.H * a.W * a.pitch * 2};
+  {
+    uint32_t box[4] = {DP, WS, WS, 1};
+    HB_TRY(tc::make_tmap_bf16(&tmQ, a.qkv, 4, dims, str, box, DP * 2));
+  }
+  {
+    uint32_t box[4] = {DP, OWS, KROWS, 1};
+    HB_TRY(tc::make_tmap_bf16(&tmKV, a.qkv, 4, dims, str, box, DP * 2));
+  }
+  AttnParams p;
+  p.B = a.B; p.H = a.H; p.W = a.W; p.heads = a.heads;
+  p.nwx = a.W / WS; p.nwy = a.H / WS;
+  p.units = a.B * p.nwx * p.nwy * a.heads;
+  p.k_off = a.heads * DP; p.v_off = 2 * a.heads * DP;
+  p.bias_l2 = a.bias_l2;
+  p.out = (bf16*)a.out; p.out_pitch = a.out_pitch;
+  static bool attr_set = false;
+  if (!attr_set) {
+    HB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int grid = p.units < sms ? p.units : sms;
+  attn_tc_kernel<<<grid, AT_THREADS, SMEM_BYTES, st>>>(tmQ, tmKV, p);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- head-padded packing helpers (pack time / test entry) ---------------------------------------------
+// dst[(blk*heads + h)*32 + i][k] = src[blk*C + h*d + i][k] (i < d, k < C), zero elsewhere; dst is (nblk*heads*32, Kpad)
+__global__ void pack_rows_headpad_kernel(const void* __restrict__ src, int dt, int C, int heads, int d, int nblk,
+                                         bf16* __restrict__ dst, int Kpad, int dst_row0) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)nblk * heads * DP * Kpad;
+  if (idx >= total) return;
+  int k = (int)(idx % Kpad);
+  int r = (int)(idx / Kpad);
+  int i = r % DP, h = (r / DP) % heads, blk = r / (DP * heads);
+  float v = 0.f;
+  if (i < d && k < C) {
+    size_t s = ((size_t)blk * C + h * d + i) * C + k;
+    v = dt == HATB200_F32 ? ((const float*)src)[s] : (dt == HATB200_BF16 ? to_f(((const bf16*)src)[s]) : to_f(((const __half*)src)[s]));
+  }
+  dst[((size_t)dst_row0 + r) * Kpad + k] = __float2bfloat16_rn(v);
+}
+__global__ void pack_vec_headpad_kernel(const void* __restrict__ src, int dt, int C, int heads, int d, int nblk,
+                                        float* __restrict__ dst, int dst0) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nblk * heads * DP) return;
+  int i = idx % DP, h = (idx / DP) % heads, blk = idx / (DP * heads);
+  float v = 0.f;
+  if (i < d) {
+    size_t s = (size_t)blk * C + h * d + i;
+    v = dt == HATB200_F32 ? ((const float*)src)[s] : (dt == HATB200_BF16 ? to_f(((const bf16*)src)[s]) : to_f(((const __half*)src)[s]));
+  }
+  dst[dst0 + idx] = v;
+}
+// dst[n][h*32 + i] = src[n][h*d + i] (n < O), zero elsewhere; dst is (Npad, Kpad)
+__global__ void pack_cols_headpad_kernel(const void* __restrict__ src, int dt, int O, int C, int heads, int d,
+                                         bf16* __restrict__ dst, int Npad, int Kpad) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)Npad * Kpad;
+  if (idx >= total) return;
+  int k = (int)(idx % Kpad), n = (int)(idx / Kpad);
+  int h = k / DP, i = k % DP;
+  float v = 0.f;
+  if (n < O && h < heads && i < d) {
+    size_t s = (size_t)n * C + h * d + i;
+    v = dt == HATB200_F32 ? ((const float*)src)[s] : (dt == HATB200_BF16 ? to_f(((const bf16*)src)[s]) : to_f(((const __half*)src)[s]));
+  }
+  dst[idx] = __float2bfloat16_rn(v);
+}
+__global__ void bias_l2_kernel(const float* __restrict__ compact, int heads, int rows, float* __restrict__ dst) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= heads * BIAS_FLOATS) return;
+  int h = idx / BIAS_FLOATS, i = idx % BIAS_FLOATS;
+  dst[idx] = i < rows ? compact[(size_t)h * rows + i] * LOG2E : 0.f;
+}
+
+int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
+                             cudaStream_t st) {
+  size_t total = (size_t)nblk * heads * DP * Kpad;
+  pack_rows_headpad_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(src, dt, C, heads, C / heads, nblk, dst, Kpad,
+                                                                           dst_row0);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+int launch_pack_vec_headpad(const void* src, int dt, int C, int heads, int nblk, float* dst, int dst0, cudaStream_t st) {
+  int total = nblk * heads * DP;
+  pack_vec_headpad_kernel<<<(total + 255) / 256, 256, 0, st>>>(src, dt, C, heads, C / heads, nblk, dst, dst0);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+int launch_pack_cols_headpad(const void* src, int dt, int O, int C, int heads, bf16* dst, int Npad, int Kpad,
+                             cudaStream_t st) {
+  size_t total = (size_t)Npad * Kpad;
+  pack_cols_headpad_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(src, dt, O, C, heads, C / heads, dst, Npad, Kpad);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+int launch_bias_l2(const float* compact, int heads, int ws, int ows, float* dst, cudaStream_t st) {
+  int rows = (ws + ows - 1) * (ws + ows - 1);
+  HB_REQUIRE(rows <= BIAS_FLOATS, HATB200_EUNSUPPORTED, "bias_l2: table too large");
+  bias_l2_kernel<<<(heads * BIAS_FLOATS + 255) / 256, 256, 0, st>>>(compact, heads, rows, dst);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- layout converters for the single-kernel test entry (compact <-> head-padded) ----
+__global__ void headpad_qkv_kernel(const bf16* __restrict__ src, int src_pitch, int C, int heads, int d, size_t M,
+                                   bf16* __restrict__ dst, int dst_pitch) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t per = (size_t)3 * heads * DP;
+  if (idx >= M * per) return;
+  size_t m = idx / per;
+  int c = (int)(idx % per);
+  int i = c % DP, h = (c / DP) % heads, blk = c / (DP * heads);
+  dst[m * dst_pitch + c] = i < d ? src[m * src_pitch + blk * C + h * d + i] : __float2bfloat16_rn(0.f);
+}
+__global__ void headunpad_out_kernel(const bf16* __restrict__ src, int src_pitch, int C, int heads, int d, size_t M,
+                                     bf16* __restrict__ dst, int dst_pitch) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * C) return;
+  size_t m = idx / C;
+  int c = (int)(idx % C);
+  dst[m * dst_pitch + c] = src[m * src_pitch + (c / d) * DP + c % d];
+}
+int launch_headpad_qkv(const bf16* src, int src_pitch, int C, int heads, size_t M, bf16* dst, int dst_pitch,
+                       cudaStream_t st) {
+  size_t total = M * 3 * heads * DP;
+  headpad_qkv_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(src, src_pitch, C, heads, C / heads, M, dst, dst_pitch);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+int launch_headunpad_out(const bf16* src, int src_pitch, int C, int heads, size_t M, bf16* dst, int dst_pitch,
+                         cudaStream_t st) {
+  size_t total = M * C;
+  headunpad_out_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(src, src_pitch, C, heads, C / heads, M, dst, dst_pitch);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace hb

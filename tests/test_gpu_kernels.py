@@ -158,6 +158,17 @@ def _attention_reference(qkv, B, H, W, Cn, heads, ws, ows, table_compact):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("geom", [(1, 16, 16, 180, 6), (2, 32, 48, 180, 6), (1, 32, 32, 144, 6), (1, 16, 32, 48, 6)])
 def test_ocab_attention_cuda_core(dtype, geom):
+    _attention_case(dtype, geom, 0)
+
+
+@pytest.mark.parametrize("geom", [(1, 16, 16, 180, 6), (2, 32, 48, 180, 6), (1, 32, 32, 144, 6), (1, 16, 32, 48, 6),
+                                  (3, 64, 64, 180, 6)])
+def test_ocab_attention_tcgen05(geom):
+    """tcgen05 flash-style kernel (tc_attn.cu): bf16 operands, fp32 softmax; P is rounded to bf16 for the PV MMA."""
+    _attention_case(torch.bfloat16, geom, 1)
+
+
+def _attention_case(dtype, geom, use_tc):
     B, H, W, Cn, heads = geom
     ws, ows = 16, 24
     g = torch.Generator().manual_seed(3)
@@ -173,7 +184,7 @@ def test_ocab_attention_cuda_core(dtype, geom):
     out = torch.zeros(B * H * W, opitch, dtype=dtype, device=DEV)
     td = table.to(DEV)
     _lib.check(_lib.lib().hatb200_ocab_attention(_p(t), _lib.dtype_code(dtype), pitch, B, H, W, Cn, heads, ws, ows,
-                                                 _p(td), _p(out), opitch, 0, _stream()))
+                                                 _p(td), _p(out), opitch, use_tc, _stream()))
     torch.cuda.synchronize()
     got = out[:, :Cn].float().cpu().view(B, H, W, Cn)
     tol = 2e-5 if dtype == torch.float32 else 2.0 ** -7
