@@ -106,6 +106,7 @@ struct Epilogue {
   int ln_pitch = 0;
   void* ln_head = nullptr;           // T (M, ln_head_c) compact copy of the first channels
   int ln_head_c = 0;
+  void* ln_head_pad = nullptr;       // optional second copy of the head, x-padded (B, H, W+12, ln_head_c) for tc_plk.cu
   float* ln_head_colsum = nullptr;   // fp32 (num_m_tiles, ln_head_c) per-tile column sums of the LN head
   float* colsum = nullptr;           // fp32 (num_m_tiles, N) per-tile column sums of v (GAP partials)
 };

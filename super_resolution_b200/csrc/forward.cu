@@ -52,6 +52,7 @@ static void plan(const hatb200_config& c, const Dims& d, char* base, Workspace& 
   w.U = take(M * d.Cp * d.es);
   int pd = d.pdim > d.opdim ? d.pdim : d.opdim;
   w.X16 = take(M * pd * d.es);
+  w.X16P = take((size_t)d.B * d.H * (d.W + 12) * 16 * 2);
   w.T1 = take(M * d.midp * d.es);
   w.H1 = take(M * d.h1p * d.es);
   size_t gp = d.hp2 > d.Cp ? d.hp2 : d.Cp;
@@ -98,6 +99,8 @@ struct Fwd {
 
   int dbg(const char* what) {
     if (!h->sync_debug) return 0;
+    static const bool trace = getenv("HATB200_TRACE") != nullptr;
+    if (trace) fprintf(stderr, "[hatb200] sync after %s\n", what);
     cudaError_t e = cudaStreamSynchronize(st);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -157,16 +160,23 @@ struct Fwd {
     t_end(tid);
     return r;
   }
+  bool plk_tc(int pdim) const {
+    return tc() && !tc_disabled("esc_plk13") && plk_tc_supported(pdim, h->cfg.esc_kernel, d.H, d.W, d.Cp);
+  }
   int ln_impl(const float* x, const LNW& n, void* out, int head_c) {
     HB_TRY(launch_layernorm(x, d.M, d.C, n.g, n.b, out, d.dt, d.Cp, d.Cp, head_c ? w.X16 : nullptr, head_c, st));
     if (head_c) HB_TRY(launch_colsum(w.X16, d.dt, head_c, d.B, d.H * d.W, head_c, w.part16, st));
+    if (head_c && plk_tc(head_c)) HB_TRY(launch_plk_pad_copy((const bf16*)w.X16, d.B, d.H, d.W, (bf16*)w.X16P, st));
     return dbg("layernorm");
   }
 
   void set_ln(Epilogue& ep, const LNW* n, void* out, int head_c) {
     if (!n) return;
     ep.ln_gamma = n->g; ep.ln_beta = n->b; ep.ln_out = out; ep.ln_pitch = d.Cp;
-    if (head_c) { ep.ln_head = w.X16; ep.ln_head_c = head_c; ep.ln_head_colsum = w.part16; }
+    if (head_c) {
+      ep.ln_head = w.X16; ep.ln_head_c = head_c; ep.ln_head_colsum = w.part16;
+      if (plk_tc(head_c)) ep.ln_head_pad = w.X16P;
+    }
   }
 
   // ESC ConvAttn core on xn (esc_arch.py:119-123): writes the mixed first-pdim channels into
@@ -174,6 +184,14 @@ struct Fwd {
   int esc_mix(const EscW& e, void* dst) {
     int nchunk = colsum_chunks(d.H * d.W);
     HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
+    if (e.plk_wt && plk_tc(e.pdim)) {
+      double Mt = (double)d.M;
+      int tid = t_begin("esc_plk13", 2.0 * Mt * e.pdim * e.pdim * (e.plk.taps() + 9.0 / e.pdim), Mt * 2 * e.pdim * d.es);
+      int r = launch_plk_tc((const bf16*)w.X16P, d.B, d.H, d.W, e.plk_wt, w.dyn, (bf16*)dst, d.Cp, st);
+      t_end(tid);
+      HB_TRY(r);
+      return dbg("plk_tc");
+    }
     Epilogue ep;
     ep.dyn_x = w.X16; ep.dyn_pitch = e.pdim; ep.dyn_k = w.dyn;
     ep.out_t = dst; ep.out_t_pitch = d.Cp; ep.out_t_coff = 0;
@@ -276,6 +294,7 @@ struct Fwd {
     const hatb200_config& c = h->cfg;
     if (c.upsampler != 1)   // hat_arch.py:852: no tail -> only the (de)normalisation remains
       return launch_affine_roundtrip(x, x_dt, d.B, c.in_chans, d.H * d.W, c.mean, c.img_range, y, y_dt, st);
+    if (tc()) HB_CHECK_CUDA(cudaMemsetAsync(w.X16P, 0, (size_t)d.B * d.H * (d.W + 12) * 16 * 2, st));   // x pads stay zero
     HB_TRY(launch_conv_first(x, x_dt, d.B, c.in_chans, d.H, d.W, h->conv_first_w, h->conv_first_b, d.C, c.mean,
                              c.img_range, w.S, st));
     HB_TRY(dbg("conv_first"));

@@ -80,6 +80,14 @@ inline int launch_conv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, 
   return launch_tapconv_tc(a, w, Npad, Kpad, ep, st);
 }
 
+// ---- ESC 13x13 conv + dynamic depthwise on tensor cores (tc_plk.cu) ----
+bool plk_tc_supported(int pdim, int ksize, int H, int W, int out_pitch);
+size_t plk_toeplitz_elems();
+int launch_pack_plk_toeplitz(const void* src, int dt, bf16* dst, cudaStream_t st);
+int launch_plk_pad_copy(const bf16* src, int B, int H, int W, bf16* dst, cudaStream_t st);
+int launch_plk_tc(const bf16* xpad, int B, int H, int W, const bf16* wt, const float* dyn, bf16* out, int out_pitch,
+                  cudaStream_t st);
+
 // ---- OCAB attention core (hat_arch.py:354-388) ----
 struct AttnArgs {
   const void* qkv; int pitch;        // (M, pitch): q at 0 (pre-scaled), k at C, v at 2C

@@ -31,6 +31,7 @@ struct LNW { float* g = nullptr; float* b = nullptr; };
 struct EscW {                // ESC ConvAttn (esc_arch.py:89-145): plk_filter, dwc_proj, aggr
   int pdim = 0;
   ConvW plk;                 // (pdim, pdim, k, k), no bias
+  bf16* plk_wt = nullptr;    // banded Toeplitz form [k][4*pdim][16*pdim] for tc_plk.cu (pdim 16, k 13 only)
   float *w1 = nullptr, *b1 = nullptr, *w2 = nullptr, *b2 = nullptr;   // dwc_proj.1 / dwc_proj.3
   ConvW aggr;                // 1x1 C->C
 };
@@ -67,6 +68,7 @@ struct Workspace {           // carved from the caller's scratch buffer
   float *S = nullptr, *XA = nullptr, *XB = nullptr;      // fp32 (M, C): shallow, group input, running stream
   void *XN = nullptr, *XN2 = nullptr, *U = nullptr;      // T (M, Cp)
   void *X16 = nullptr;                                   // T (M, pdim)
+  void *X16P = nullptr;                                  // bf16 (B, H, W+12, 16): x-padded copy for tc_plk.cu
   void *T1 = nullptr;                                    // T (M, midp)
   void *H1 = nullptr;                                    // T (M, max(hp4, qkvp))
   void *G = nullptr;                                     // T (M, hp2)

@@ -67,6 +67,12 @@ struct Packer {
   int esc(const std::string& core, const std::string& plk_key, EscW& e, int C, int pdim, int k) {
     e.pdim = pdim;
     HB_TRY(conv(plk_key, "", e.plk, pdim, pdim, k, k));
+    if (pdim == 16 && k == 13) {
+      const ParamRef* pw;
+      HB_TRY(get(plk_key, &pw));
+      HB_TRY(alloc((void**)&e.plk_wt, plk_toeplitz_elems() * sizeof(bf16)));
+      HB_TRY(launch_pack_plk_toeplitz(pw->ptr, pw->dtype, e.plk_wt, st));
+    }
     HB_TRY(vec(core + ".plk.dwc_proj.1.weight", &e.w1));
     HB_TRY(vec(core + ".plk.dwc_proj.1.bias", &e.b1));
     HB_TRY(vec(core + ".plk.dwc_proj.3.weight", &e.w2));

@@ -303,6 +303,10 @@ __device__ __forceinline__ void run_epilogue(const Epilogue& ep, const EpiCtx& c
           for (int j = 0; j < 16; j++)
             if (j < ep.ln_head_c) hd[j] = __float2bfloat16_rn(v[j]);
         }
+        if (ep.ln_head_pad && ep.ln_head_c == 16) {
+          bf16* hp = (bf16*)ep.ln_head_pad + (((size_t)b * c.H + c.py) * (c.W + 12) + c.px + 6) * 16;
+          st16_bf16(hp, v, 16, 16);
+        }
         if (ep.ln_head_colsum) {
           // sums of the bf16-rounded head values (what the separate colsum kernel would read)
 #pragma unroll
