@@ -191,6 +191,8 @@ EncodeTiledFn encode_tiled_fn();
 // bf16 tensor, `rank` dims (innermost first), byte strides for dims 1..rank-1, box per dim; swizzle by inner box bytes
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, int inner_bytes);
+int make_tmap_f32(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                  const uint32_t* box, int inner_bytes);
 
 }  // namespace tc
 }  // namespace hb

@@ -29,6 +29,8 @@ struct EpiCtx {
   int gtid;           // 0..127 inside the epilogue warpgroup
   int bar_id;         // named barrier of this epilogue warpgroup (128 threads)
   float (*sred)[256]; // [4][256] shared scratch of this warpgroup
+  uint8_t* wstage = nullptr;      // tc_epilogue2: 2 KB store-staging scratch of this WARP
+  float (*hsum)[16] = nullptr;    // tc_epilogue2: [4][16] per-warp column sums of the LN head
 };
 
 __device__ __forceinline__ void epi_bar(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }

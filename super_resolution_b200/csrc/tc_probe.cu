@@ -90,3 +90,13 @@ extern "C" int hatb200_probe_umma(const void* a, int R, const void* b, int r0, i
   HB_CHECK_LAUNCH();
   return 0;
 }
+
+// engineering: copy the last traced GEMM launch's per-CTA event timestamps (ns) to the host: (1024, 64) uint64
+namespace hb { unsigned long long* gemm_trace_buffer(); }
+extern "C" int hatb200_debug_gemm_trace(unsigned long long* host, void* stream) {
+  unsigned long long* d = hb::gemm_trace_buffer();
+  HB_REQUIRE(d && host, HATB200_EINVAL, "gemm trace not enabled (HATB200_GEMM_TRACE=1)");
+  HB_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  HB_CHECK_CUDA(cudaMemcpy(host, d, 1024 * 64 * 8, cudaMemcpyDeviceToHost));
+  return 0;
+}
