@@ -2,11 +2,12 @@
 
 Public surface (mirrors the reference's own for this path):
   * `HAT`            -- drop-in for `hat.archs.hat_arch.HAT` (same ctor, same state_dict)
-  * `tile_process`   -- HATModel.pre_process/tile_process/post_process on device, optionally
+  * `HATModel`       -- HATModel.pre_process/process/tile_process/post_process on device, tiles optionally
                         sharded over ranks (reference: HAT/hat/models/hat_model.py:16-112)
 The arithmetic lives in `libhatb200.so` (csrc/, include/hatb200.h).
 """
 from .hat_arch import HAT  # noqa: F401
+from .hat_model import HATModel  # noqa: F401
 
-__all__ = ["HAT"]
+__all__ = ["HAT", "HATModel"]
 __version__ = "0.1.0"
