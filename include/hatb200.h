@@ -139,6 +139,19 @@ int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, in
                         int KH, int KW, int act, void* out, int out_pitch, int use_tc,
                         void* stream);
 
+/* Linear (1x1 conv) with the fused epilogue of the persistent tcgen05 GEMM (bf16 only; csrc/tc_gemm.cu):
+ *   v = act(a . w^T + bias) + eca_coef * eca_scale[b,n] * u[m,n] + resid[m,n]
+ * (hat_arch.py:117,:236-237,:391-392; esc_arch.py:144).  a: bf16 (M, a_pitch), w: fp32 (N, Cin), resid / out_f32:
+ * fp32 (M, N), u: bf16 (M, u_pitch), eca_scale: fp32 (B, N).  Optional outputs: out_f32, out_t bf16 (M,
+ * out_t_pitch; columns [N, out_t_zero_to) written as zero), ln_out = LayerNorm(v; gamma, beta, eps 1e-5) bf16 (M,
+ * ln_pitch; pad columns zero), ln_head bf16 (M, 16) = first 16 channels of ln_out, head_colsum fp32
+ * (M / 128, 16) per-128-token column sums of ln_head.  Any optional pointer may be NULL. */
+int hatb200_linear_fused(const void* a, int a_pitch, int Cin, int B, int H, int W, const float* w,
+                         const float* bias, int N, int act, const float* resid, const void* u, int u_pitch,
+                         const float* eca_scale, float eca_coef, float* out_f32, void* out_t, int out_t_pitch,
+                         int out_t_zero_to, const float* gamma, const float* beta, void* ln_out, int ln_pitch,
+                         void* ln_head, float* head_colsum, void* stream);
+
 /* OCAB attention core (hat_arch.py:354-388): qkv (M, pitch) holding q (already
  * scaled) at channel 0, k at C, v at 2C; bias_table (heads, (ws+ows-1)^2)
  * compact relative-position table indexed by (ky-qy+ws-1, kx-qx+ws-1);

@@ -96,6 +96,37 @@ int hatb200_conv_tokens(const void* in, int dtype, int in_pitch, int in_coff, in
   return r;
 }
 
+int hatb200_linear_fused(const void* a, int a_pitch, int Cin, int B, int H, int W, const float* w, const float* bias,
+                         int N, int act, const float* resid, const void* u, int u_pitch, const float* eca_scale,
+                         float eca_coef, float* out_f32, void* out_t, int out_t_pitch, int out_t_zero_to,
+                         const float* gamma, const float* beta, void* ln_out, int ln_pitch, void* ln_head,
+                         float* head_colsum, void* stream) {
+  HB_REQUIRE(a && w && N >= 1 && Cin >= 1, HATB200_EINVAL, "linear_fused: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  TmpPool pool;
+  ConvArgs ca{a, a_pitch, 0, Cin, B, H, W, 1, 1, N};
+  Epilogue ep;
+  ep.bias = bias; ep.act = act;
+  ep.resid = resid; ep.resid_pitch = N;
+  ep.eca_u = u; ep.eca_pitch = u_pitch; ep.eca_scale = eca_scale; ep.eca_coef = eca_coef;
+  ep.out_f32 = out_f32; ep.out_f32_pitch = N;
+  ep.out_t = out_t; ep.out_t_pitch = out_t_pitch; ep.out_t_zero_to = out_t_zero_to;
+  if (ln_out) {
+    ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = ln_out; ep.ln_pitch = ln_pitch;
+    if (ln_head) { ep.ln_head = ln_head; ep.ln_head_c = 16; ep.ln_head_colsum = head_colsum; }
+  }
+  const int Npad = tc_npad(N), Kpad = round_up(Cin, 64);
+  bf16* w16;
+  HB_TRY(pool.alloc((void**)&w16, (size_t)Npad * Kpad * sizeof(bf16), st));
+  HB_TRY(launch_pack_w_bf16(w, HATB200_F32, N, Cin, 1, w16, Npad, Kpad, 0, Cin, st));
+  HB_REQUIRE(gemm_tc_supported(ca, Npad, Kpad, ep), HATB200_EUNSUPPORTED,
+             "linear_fused: shape / epilogue not supported by the persistent tcgen05 GEMM");
+  int r = launch_gemm_tc(ca, w16, Npad, Kpad, ep, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (r == 0 && e != cudaSuccess) { set_error("linear_fused: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
+  return r;
+}
+
 int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, int W, int C, int heads, int ws,
                            int ows, const float* bias_table, void* out, int out_pitch, int use_tc, void* stream) {
   HB_REQUIRE(qkv && bias_table && out, HATB200_EINVAL, "ocab_attention: null tensor");
@@ -134,7 +165,7 @@ int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, i
   float* wt;
   HB_TRY(pool.alloc((void**)&wt, (size_t)9 * 2 * hid * sizeof(float), st));
   HB_TRY(launch_pack_w_f32(dw_w, HATB200_F32, 2 * hid, 1, 9, wt, 2 * hid, 2 * hid, st));
-  int r = launch_dwgate(in, dtype, in_pitch, B, H, W, hid, wt, dw_b, out, out_pitch, hid, st);
+  int r = launch_dwgate(in, dtype, in_pitch, B, H, W, hid, wt, dw_b, out, out_pitch, out_pitch, st);   // pad columns zeroed, as in the forward
   cudaError_t e = cudaStreamSynchronize(st);
   if (r == 0 && e != cudaSuccess) { set_error("dwconv_gate: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
   return r;

@@ -131,6 +131,11 @@ struct Fwd {
   int conv_impl(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
     if (!ep.bias) ep.bias = cw.bias;
+    static const bool trace = getenv("HATB200_TRACE") != nullptr;
+    if (trace)
+      fprintf(stderr, "[hatb200] %s: N=%d Cin=%d k=%d Npad=%d Kpad=%d gemm=%d tap=%d\n", tag, cw.O, cw.I, cw.KH, cw.Npad,
+              cw.Kpad, (int)(tc() && gemm_tc_supported(a, cw.Npad, cw.Kpad, ep)),
+              (int)(tc() && tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)));
     if (tc() && !tc_disabled(tag) && conv_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
       HB_TRY(launch_conv_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
       return dbg("tapconv_tc");

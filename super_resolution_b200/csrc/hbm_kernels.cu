@@ -1,6 +1,7 @@
 // hbm_kernels.cu -- bf16 fast paths of the bandwidth-bound ops (16-byte vector access, register / shared
 // memory reuse of the 3x3 halo).  The generic (any dtype, any size) versions live in simt_kernels.cu.
 #include "kernels.cuh"
+#include "tc_common.cuh"
 
 namespace hb {
 
@@ -15,113 +16,169 @@ __device__ __forceinline__ void unpack8(const uint4& t, float (&o)[8]) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// GatedDconvFFN middle (hat_arch.py:112-116), bf16: each thread owns 4 consecutive pixels of one row
-// and 8 channel pairs (proj j..j+7, gate hid+j..hid+j+7).  Per kernel row it loads the 6 input columns
-// once (sliding-window reuse across the 4 pixels) -> 9 + 9 vector loads per pixel instead of 18 + 36.
-// in (M, in_pitch) -> out (M, out_pitch); columns [hid, out_pitch) are written as zero.
-// Algorithmic bytes: (2*hid + hid) * 2 B per token.
+// GatedDconvFFN middle (hat_arch.py:112-116), bf16: depthwise 3x3 (+bias, zero pad) on 2*hid channels, then
+// out[j] = dw[j] * SiLU(dw[hid + j]).  in (M, in_pitch) -> out (M, out_pitch); columns [hid, out_pitch) are
+// written as zero (K padding of fc2).  Algorithmic bytes: (2*hid + hid) * 2 B per token.
+//
+// History (ncu, B200): v1 (thread = 8 channels x 4 px of one row, 16-byte loads) issued 89 instructions per output
+// value at 1.4 TB/s; v2 (thread = channel pair x 4 px x 8-row strip, every input row loaded once) was latency
+// bound at 1.7 TB/s: 12 dependent global loads per row and 18 warps per SM.  v3 below:
+//   * a CTA owns a 16 x 8 pixel tile and 64 proj + 64 gate channels; ONE thread issues two 4-D TMA boxes
+//     {64 ch, 18 x, 10 y} (halo included; TMA's out-of-bounds zero fill IS the conv padding) into shared memory,
+//     four CTAs per SM keep ~180 KB of loads in flight with no registers or address arithmetic spent on them;
+//   * a thread owns one channel pair (36 weights in registers), 4 pixels and the 8-row strip: each halo row is
+//     read once from shared memory (conflict-free 4-byte reads) and scattered into three rolling accumulator
+//     rows with packed FFMA2 (both channels of the pair per instruction);
+//   * SiLU through tanh.approx: x * sigmoid(x) = h + h * tanh(h), h = x / 2  (one MUFU instead of EX2 + RCP).
 // ---------------------------------------------------------------------------------------------------
-constexpr int DW_PX = 4;
+constexpr int DW_TW = 16, DW_TH = 8, DW_PX = 4, DW_CC = 64;        // tile, pixels per thread, channels per CTA
+constexpr int DW_HW = DW_TW + 2, DW_HH = DW_TH + 2;               // halo
+constexpr int DW_HALF_BYTES = DW_HH * DW_HW * DW_CC * 2;          // 23040
+constexpr int DW_THREADS = (DW_CC / 2) * (DW_TW / DW_PX);         // 128
+constexpr int DW_SMEM = 2 * DW_HALF_BYTES + 128;
 
-// depthwise 3x3 of 8 consecutive channels starting at `ch` for DW_PX pixels of one row (sliding window)
-__device__ __forceinline__ void dw_pass(const bf16* __restrict__ in, int in_pitch, int b, int y, int x0, int H, int W,
-                                        int ch, int wpitch, const float* __restrict__ w,
-                                        const float* __restrict__ bias, float (&acc)[DW_PX][8]) {
-  {
-    const float4* b4 = reinterpret_cast<const float4*>(bias + ch);
-    const float4 t0 = __ldg(b4), t1 = __ldg(b4 + 1);
-#pragma unroll
-    for (int p = 0; p < DW_PX; p++) {
-      acc[p][0] = t0.x; acc[p][1] = t0.y; acc[p][2] = t0.z; acc[p][3] = t0.w;
-      acc[p][4] = t1.x; acc[p][5] = t1.y; acc[p][6] = t1.z; acc[p][7] = t1.w;
-    }
+__device__ __forceinline__ unsigned long long dw_pk(float a, float b) {
+  return (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
+}
+// bf16 pair -> packed f32x2 (low half first)
+__device__ __forceinline__ unsigned long long dw_unpack(uint32_t v) {
+  return (unsigned long long)(v << 16) | ((unsigned long long)(v & 0xffff0000u) << 32);
+}
+__device__ __forceinline__ unsigned long long dw_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t dw_lds(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float dw_silu(float x) {
+  const float h = 0.5f * x;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  return fmaf(h, t, h);
+}
+
+__global__ void __launch_bounds__(DW_THREADS, 4)
+dwgate_bf16_kernel(const __grid_constant__ CUtensorMap tmIn, int H, int W, int hid, const float* __restrict__ w,
+                   const float* __restrict__ bias, bf16* __restrict__ out, int out_pitch) {
+  extern __shared__ __align__(128) uint8_t dw_smem[];          // TMA destination (no swizzle): 128-byte aligned
+  uint8_t* sp = dw_smem;
+  uint8_t* sg = sp + DW_HALF_BYTES;
+  __shared__ __align__(8) uint64_t bar;
+  const int tiles_x = W / DW_TW;
+  const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+  const int x0 = tx * DW_TW, y0 = ty * DW_TH;
+  const int c0 = blockIdx.y * DW_CC;
+  const int b = blockIdx.z;
+  if (threadIdx.x == 0) {
+    tc::mbar_init(&bar, 1);
+    tc::fence_barrier_init();
+    tc::mbar_arrive_expect_tx(&bar, 2 * DW_HALF_BYTES);
+    tc::tma_load_4d(sp, &tmIn, &bar, c0, x0 - 1, y0 - 1, b);
+    tc::tma_load_4d(sg, &tmIn, &bar, hid + c0, x0 - 1, y0 - 1, b);
   }
+  const int pair = threadIdx.x & 31, xq = threadIdx.x >> 5;
+  const int c = c0 + 2 * pair;                                    // first channel of this thread's pair
+  const int xs = xq * DW_PX;                                      // first pixel column inside the tile
+  const size_t img = (size_t)b * H * W;
+  bf16* orow = out + (img + (size_t)y0 * W + x0 + xs) * out_pitch + c;
+  const bool active = c < hid;            // lanes past hid only write the K padding of fc2's A operand
+  const int cl = active ? c : 0;          // keep the (unused) loads of inactive lanes in bounds
+  unsigned long long wp[9], wg[9];
 #pragma unroll
-  for (int ky = 0; ky < 3; ky++) {
-    const int yy = y + ky - 1;
-    if (yy < 0 || yy >= H) continue;
-    float wk[3][8];
+  for (int t = 0; t < 9; t++) {
+    const float2 a = __ldg(reinterpret_cast<const float2*>(w + (size_t)t * 2 * hid + cl));
+    const float2 g = __ldg(reinterpret_cast<const float2*>(w + (size_t)t * 2 * hid + hid + cl));
+    wp[t] = dw_pk(a.x, a.y);
+    wg[t] = dw_pk(g.x, g.y);
+  }
+  const float2 bpf = __ldg(reinterpret_cast<const float2*>(bias + cl));
+  const float2 bgf = __ldg(reinterpret_cast<const float2*>(bias + hid + cl));
+  const unsigned long long bp = dw_pk(bpf.x, bpf.y), bg = dw_pk(bgf.x, bgf.y);
+  // rolling accumulators: slot 0 = output row r-1, 1 = row r, 2 = row r+1 (r = current halo row)
+  unsigned long long ap[3][DW_PX], ag[3][DW_PX];
 #pragma unroll
-    for (int kx = 0; kx < 3; kx++) {
-      const float4* a4 = reinterpret_cast<const float4*>(w + (size_t)(ky * 3 + kx) * wpitch + ch);
-      const float4 t0 = __ldg(a4), t1 = __ldg(a4 + 1);
-      wk[kx][0] = t0.x; wk[kx][1] = t0.y; wk[kx][2] = t0.z; wk[kx][3] = t0.w;
-      wk[kx][4] = t1.x; wk[kx][5] = t1.y; wk[kx][6] = t1.z; wk[kx][7] = t1.w;
-    }
-    const bf16* rowp = in + (((size_t)b * H + yy) * W) * in_pitch + ch;
-    uint4 raw[DW_PX + 2];
+  for (int s = 0; s < 3; s++)
 #pragma unroll
-    for (int cx = 0; cx < DW_PX + 2; cx++) {          // input columns x0-1 .. x0+DW_PX (all loads in flight together)
-      const int xx = x0 + cx - 1;
-      raw[cx] = (xx >= 0 && xx < W) ? *reinterpret_cast<const uint4*>(rowp + (size_t)xx * in_pitch)
-                                    : make_uint4(0, 0, 0, 0);
+    for (int p = 0; p < DW_PX; p++) { ap[s][p] = bp; ag[s][p] = bg; }
+  __syncthreads();                                                // barrier initialised and armed (block-uniform point)
+  tc::mbar_wait(&bar, 0);
+  if (!active) {
+    if (c < out_pitch)
+      for (int y = 0; y < DW_TH; y++)
+#pragma unroll
+        for (int p = 0; p < DW_PX; p++)
+          *reinterpret_cast<uint32_t*>(orow + ((size_t)y * W + p) * out_pitch) = 0u;
+    return;
+  }
+  const uint32_t tp = tc::smem_u32(sp) + (xs * DW_CC + 2 * pair) * 2;   // halo column xs of row 0, this pair
+  const uint32_t tg = tp + DW_HALF_BYTES;
+#pragma unroll
+  for (int i = 0; i < DW_HH; i++) {                               // halo row i = image row y0 - 1 + i
+    uint32_t rp[DW_PX + 2], rg[DW_PX + 2];
+#pragma unroll
+    for (int cx = 0; cx < DW_PX + 2; cx++) {
+      rp[cx] = dw_lds(tp + (i * DW_HW + cx) * (DW_CC * 2));
+      rg[cx] = dw_lds(tg + (i * DW_HW + cx) * (DW_CC * 2));
     }
 #pragma unroll
     for (int cx = 0; cx < DW_PX + 2; cx++) {
-      float v[8];
-      unpack8(raw[cx], v);
+      const unsigned long long vp = dw_unpack(rp[cx]), vg = dw_unpack(rg[cx]);
 #pragma unroll
       for (int kx = 0; kx < 3; kx++) {
-        const int p = cx - kx;                         // output pixel that sees this column through tap kx
+        const int p = cx - kx;                                    // output pixel that sees this column through tap kx
         if (p < 0 || p >= DW_PX) continue;
 #pragma unroll
-        for (int c = 0; c < 8; c++) acc[p][c] = fmaf(v[c], wk[kx][c], acc[p][c]);
+        for (int ky = 0; ky < 3; ky++) {                          // output row (i - 1) + 1 - ky lives in slot 2 - ky
+          const int s = 2 - ky, t = ky * 3 + kx;
+          if (i - ky < 0 || i - ky >= DW_TH) continue;            // that output row is outside the strip
+          ap[s][p] = dw_fma2(vp, wp[t], ap[s][p]);
+          ag[s][p] = dw_fma2(vg, wg[t], ag[s][p]);
+        }
       }
     }
-  }
-}
-
-__global__ void __launch_bounds__(128, 4) dwgate_bf16_kernel(const bf16* __restrict__ in, int in_pitch, int B, int H,
-                                                             int W, int hid, const float* __restrict__ w,
-                                                             const float* __restrict__ bias, bf16* __restrict__ out,
-                                                             int out_pitch) {
-  const int vec_out = out_pitch / 8;                 // channel vectors per token in the output (incl. zero pad)
-  const int wq = W / DW_PX;
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t total = (size_t)B * H * wq * vec_out;
-  if (idx >= total) return;
-  const int cv = (int)(idx % vec_out);
-  size_t g = idx / vec_out;
-  const int xq = (int)(g % wq);
-  const int y = (int)((g / wq) % H);
-  const int b = (int)(g / ((size_t)wq * H));
-  const int x0 = xq * DW_PX;
-  const int j0 = cv * 8;
-  const size_t row_tok = ((size_t)b * H + y) * W;
-  if (j0 >= hid) {                                    // K padding of fc2's A operand
-    const uint4 z = make_uint4(0, 0, 0, 0);
+    if (i >= 2) {                                                 // output row i - 2 of the strip is complete
 #pragma unroll
-    for (int p = 0; p < DW_PX; p++) *reinterpret_cast<uint4*>(out + (row_tok + x0 + p) * out_pitch + j0) = z;
-    return;
-  }
-  // gate half first (hat_arch.py:115-116: x_proj * silu(x_gate)), folded to its SiLU, then the proj half
-  float s[DW_PX][8];
-  dw_pass(in, in_pitch, b, y, x0, H, W, hid + j0, 2 * hid, w, bias, s);
+      for (int p = 0; p < DW_PX; p++) {
+        const float px_ = __uint_as_float((uint32_t)ap[0][p]), py_ = __uint_as_float((uint32_t)(ap[0][p] >> 32));
+        const float gx_ = __uint_as_float((uint32_t)ag[0][p]), gy_ = __uint_as_float((uint32_t)(ag[0][p] >> 32));
+        const __nv_bfloat162 h = __floats2bfloat162_rn(px_ * dw_silu(gx_), py_ * dw_silu(gy_));
+        *reinterpret_cast<__nv_bfloat162*>(orow + ((size_t)(i - 2) * W + p) * out_pitch) = h;
+      }
+    }
 #pragma unroll
-  for (int p = 0; p < DW_PX; p++)
-#pragma unroll
-    for (int c = 0; c < 8; c++) s[p][c] = silu_f(s[p][c]);
-  float a[DW_PX][8];
-  dw_pass(in, in_pitch, b, y, x0, H, W, j0, 2 * hid, w, bias, a);
-#pragma unroll
-  for (int p = 0; p < DW_PX; p++) {
-    uint4 o;
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-    for (int c = 0; c < 4; c++)
-      h[c] = __floats2bfloat162_rn(a[p][2 * c] * s[p][2 * c], a[p][2 * c + 1] * s[p][2 * c + 1]);
-    *reinterpret_cast<uint4*>(out + (row_tok + x0 + p) * out_pitch + j0) = o;
+    for (int p = 0; p < DW_PX; p++) {                             // roll (register renaming after full unroll)
+      ap[0][p] = ap[1][p]; ap[1][p] = ap[2][p]; ap[2][p] = bp;
+      ag[0][p] = ag[1][p]; ag[1][p] = ag[2][p]; ag[2][p] = bg;
+    }
   }
 }
 
 bool dwgate_bf16_ok(int in_pitch, int W, int hid, int out_pitch, int zero_to) {
-  return hid % 8 == 0 && in_pitch % 8 == 0 && out_pitch % 8 == 0 && W % DW_PX == 0 && zero_to == out_pitch;
+  return hid % 8 == 0 && in_pitch % 8 == 0 && out_pitch % 2 == 0 && W % DW_TW == 0 && zero_to == out_pitch &&
+         in_pitch >= 2 * hid && tc::encode_tiled_fn() != nullptr;
 }
 
 int launch_dwgate_bf16(const bf16* in, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
                        bf16* out, int out_pitch, cudaStream_t st) {
-  size_t total = (size_t)B * H * (W / DW_PX) * (out_pitch / 8);
-  dwgate_bf16_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(in, in_pitch, B, H, W, hid, w, b, out, out_pitch);
+  HB_REQUIRE(H % DW_TH == 0 && W % DW_TW == 0, HATB200_EUNSUPPORTED, "dwgate: %dx%d is not a multiple of the 16x8 tile", W, H);
+  CUtensorMap tm;
+  {
+    uint64_t dims[4] = {(uint64_t)in_pitch, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+    uint64_t str[3] = {(uint64_t)in_pitch * 2, (uint64_t)W * in_pitch * 2, (uint64_t)H * W * in_pitch * 2};
+    uint32_t box[4] = {DW_CC, DW_HW, DW_HH, 1};
+    HB_TRY(tc::make_tmap_bf16(&tm, in, 4, dims, str, box, 0));     // inner_bytes 0: no swizzle
+  }
+  static bool attr = false;
+  if (!attr) {
+    HB_CHECK_CUDA(cudaFuncSetAttribute(dwgate_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM));
+    attr = true;
+  }
+  dim3 grid((W / DW_TW) * (H / DW_TH), cdiv(out_pitch, DW_CC), B);
+  dwgate_bf16_kernel<<<grid, DW_THREADS, DW_SMEM, st>>>(tm, H, W, hid, w, b, out, out_pitch);
   HB_CHECK_LAUNCH();
   return 0;
 }

@@ -64,7 +64,8 @@ struct ConvArgs {
 int launch_tapconv_simt(int dt, const ConvArgs& a, const float* w, int Np, const Epilogue& ep, cudaStream_t st);
 // tcgen05 path (bf16 storage, fp32 accumulate in TMEM); w: bf16 [taps][Npad][Kpad].
 // Output channels are split into n-tiles of tc_bn(O) <= 256 columns; Npad = tc_npad(O) = n_tiles * tc_bn(O).
-inline int tc_bn(int O) { int n16 = round_up(O, 16); int nt = cdiv(n16, 256); return round_up(cdiv(n16, nt), 16); }
+// n-tiles wider than 32 columns are multiples of 64 so that epilogue stores leave as whole 128-byte rows
+inline int tc_bn(int O) { int n16 = round_up(O, 16); int nt = cdiv(n16, 256); return round_up(cdiv(n16, nt), n16 > 32 ? 64 : 16); }
 inline int tc_npad(int O) { int n16 = round_up(O, 16); return cdiv(n16, 256) * tc_bn(O); }
 int launch_tapconv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
 bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);

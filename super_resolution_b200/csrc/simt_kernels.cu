@@ -74,10 +74,48 @@ int launch_layernorm(const float* x, int M, int C, const float* gamma, const flo
 // conv_first with the input normalisation folded in (hat_arch.py:849-853).
 // One thread per (token, channel); the 9*IC inputs are warp-broadcast loads.
 // ---------------------------------------------------------------------------
+// One thread per (token, 4 consecutive channels): the 9*IC normalised inputs are loaded once per thread
+// (warp-broadcast when the lanes share a token) and the weights as float4.
 template <typename T>
 __global__ void __launch_bounds__(256) conv_first_kernel(const T* __restrict__ x, int B, int IC, int H, int W,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          int C, float4 mean, float range, float* __restrict__ out) {
+  const int C4 = C >> 2;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)B * H * W * C4;
+  if (idx >= total) return;
+  const int c = (int)(idx % C4) * 4;
+  const size_t m = idx / C4;
+  const int px = (int)(m % W);
+  const int py = (int)((m / W) % H);
+  const int b = (int)(m / ((size_t)W * H));
+  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+  float4 acc = bias ? __ldg(reinterpret_cast<const float4*>(bias + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const T* xb = x + (size_t)b * IC * H * W;
+#pragma unroll
+  for (int ky = 0; ky < 3; ky++) {
+    const int yy = py + ky - 1;
+    if (yy < 0 || yy >= H) continue;
+#pragma unroll
+    for (int kx = 0; kx < 3; kx++) {
+      const int xx = px + kx - 1;
+      if (xx < 0 || xx >= W) continue;
+      for (int i = 0; i < IC; i++) {
+        const float v = (to_f(xb[((size_t)i * H + yy) * W + xx]) - mean_a[i]) * range;
+        const float4 wv = __ldg(reinterpret_cast<const float4*>(w + ((ky * 3 + kx) * IC + i) * C + c));
+        acc.x = fmaf(v, wv.x, acc.x); acc.y = fmaf(v, wv.y, acc.y);
+        acc.z = fmaf(v, wv.z, acc.z); acc.w = fmaf(v, wv.w, acc.w);
+      }
+    }
+  }
+  *reinterpret_cast<float4*>(out + m * C + c) = acc;
+}
+
+// generic channel count (C % 4 != 0): one thread per (token, channel)
+template <typename T>
+__global__ void __launch_bounds__(256) conv_first_kernel1(const T* __restrict__ x, int B, int IC, int H, int W,
+                                                          const float* __restrict__ w, const float* __restrict__ bias,
+                                                          int C, float4 mean, float range, float* __restrict__ out) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   size_t total = (size_t)B * H * W * C;
   if (idx >= total) return;
@@ -106,11 +144,16 @@ __global__ void __launch_bounds__(256) conv_first_kernel(const T* __restrict__ x
 int launch_conv_first(const void* x, int x_dt, int B, int IC, int H, int W, const float* w, const float* bias, int C,
                       const float* mean, float range, float* out, cudaStream_t st) {
   HB_REQUIRE(IC >= 1 && IC <= 4, HATB200_EUNSUPPORTED, "conv_first: in_chans=%d not in 1..4", IC);
-  size_t total = (size_t)B * H * W * C;
   float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  const bool v4 = C % 4 == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)out & 15) == 0 && (!bias || ((uintptr_t)bias & 15) == 0);
+  size_t total = (size_t)B * H * W * (v4 ? C / 4 : C);
   HB_DISPATCH_T(x_dt, T, {
-    conv_first_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
-                                                                         range, out);
+    if (v4)
+      conv_first_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
+                                                                           range, out);
+    else
+      conv_first_kernel1<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
+                                                                            range, out);
   });
   HB_CHECK_LAUNCH();
   return 0;
@@ -344,7 +387,7 @@ __global__ void __launch_bounds__(256) dwgate_kernel(const T* __restrict__ in, i
 
 int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w, const float* b,
                   void* out, int out_pitch, int zero_to, cudaStream_t st) {
-  if (dt == HATB200_BF16 && dwgate_bf16_ok(in_pitch, W, hid, out_pitch, zero_to))
+  if (dt == HATB200_BF16 && H % 8 == 0 && W % 16 == 0 && dwgate_bf16_ok(in_pitch, W, hid, out_pitch, zero_to))
     return launch_dwgate_bf16((const bf16*)in, in_pitch, B, H, W, hid, w, b, (bf16*)out, out_pitch, st);
   size_t total = (size_t)B * H * W * (hid > zero_to ? hid : zero_to);
   HB_DISPATCH_T(dt, T, {

@@ -1,82 +1,240 @@
-// tc_gemm.cu -- Linear / 1x1 conv over channels-last tokens as a PERSISTENT, weight-stationary tcgen05 GEMM.
+// tc_gemm.cu -- Linear / 1x1 conv over channels-last tokens as a PERSISTENT tcgen05 GEMM with a warp-independent,
+// TMA-fed and TMA-drained fused epilogue (third generation).
 //
-//   out[m, n] = sum_k A[m, k] * W[n, k]          (bf16 x bf16 -> fp32 in TMEM), fused epilogue (tc_epilogue.cuh)
+//   out[m, n] = sum_k A[m, k] * W[n, k]          (bf16 x bf16 -> fp32 in TMEM)
+//   v = acc + bias; v *= q-scale; v = act(v); v += conv_scale * eca_scale[b,n] * U[m,n]; v += resid[m,n]
+//   outputs: fp32 residual stream, bf16 activation, LayerNorm(v) in bf16 (+ compact 16-channel head, its x-padded
+//   copy and its per-tile column sums)                                   (value order of common.cuh, struct Epilogue)
 //
-// Why a second kernel next to tc_tapconv.cu: a 1x1 layer has K <= 384, so a 128-row tile does only 3-6
-// k-blocks of MMA work while the one-tile-per-CTA kernel re-streams the whole weight panel (up to
-// 147 KB) from L2 for every tile and pays TMEM allocation + barrier setup + an un-overlapped epilogue
-// per tile -- measured 35-110 TFLOP/s, L2->SM bandwidth bound.  Here:
-//   * one CTA per SM (grid <= #SMs), each CTA owns one n-tile (<= 256 output channels) and walks the
-//     128-token tiles m = blockIdx.x, blockIdx.x + gridDim.x, ...;
-//   * the weight panel (BN x Kpad bf16) is loaded ONCE per CTA by TMA and stays in shared memory;
-//   * only the activation tile (128 x 64 bf16 per k-block, SWIZZLE_128B) streams through a TMA ring;
-//   * two TMEM accumulator stages: while epilogue warpgroup g drains tile i, the MMA warp already
-//     accumulates tile i+1 into the other stage (warpgroup 0 takes even tiles, warpgroup 1 odd tiles,
-//     so a token row still lives in ONE thread and the fused LayerNorm needs no cross-thread reduce).
-// Warp roles (320 threads): warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2-5 / 6-9 the
-// two epilogue warpgroups (TMEM lane quarter = warp % 4).
+// Why a third generation (B200 measurements of the second one, profiles/r01_ncu_full_gemm_v2_summary.csv and the
+// globaltimer trace tools/trace_gemm.py): a 128 x 240 tile took ~9 us to drain even for a bias-only epilogue, the
+// tensor pipe was 1-3 % busy, 38 thread-instructions per output element, stalls = long scoreboard (per-thread
+// global operands), the warpgroup barrier that guarded the 2-stage operand ring, and instruction fetch (117 KB of
+// SASS).  Here:
+//   * one CTA per SM walks 128-token tiles; the weight panel stays resident in shared memory when it fits
+//     (else it streams with the activations); two TMEM accumulator stages, the two epilogue warpgroups take
+//     alternate tiles so a token row lives in ONE thread (row-local LayerNorm, fp32 row parked in TMEM);
+//   * every epilogue WARP is independent: no warpgroup barrier inside a tile.  The global operands (fp32 residual,
+//     bf16 CAB branch) are TMA-loaded by a dedicated producer warp per warpgroup into a ring of 128-row x CW-column
+//     chunks, released as soon as the four warps have pulled their rows into registers;
+//   * every output leaves through TMA: a warp parks its 32 rows x CW columns in a private double-buffered staging
+//     tile (swizzled, conflict-free) and one lane issues cp.async.bulk.tensor stores.  The tensor maps clip the
+//     ragged edge (N = 180 of 192), TMA loads zero-fill it, weights / bias / gamma / beta are zero padded: the
+//     epilogue has no per-column predicates at all;
+//   * bias, gamma, beta and the per-sample ECA coefficients live in shared-memory tables; fp32 pair math uses
+//     the packed FFMA2 / FADD2 / FMUL2 forms.
+// Warp roles (384 threads): 0 TMA producer (A, W), 1 MMA issuer + TMEM owner, 2-5 / 6-9 epilogue warpgroups
+// (TMEM lane quarter = warp % 4), 10 / 11 operand-ring producers of warpgroup 0 / 1.
 // Replaces F.linear / 1x1 F.conv2d at hat_arch.py:111,:117,:347-351,:391-392 and esc_arch.py:144.
 #include <stdlib.h>
 
 #include "kernels.cuh"
-#include "tc_epilogue2.cuh"
+#include "tc_common.cuh"
 
 namespace hb {
 
 using namespace tc;
+
+namespace {
 
 __device__ __forceinline__ unsigned long long gtime_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-#define GM_TRACE(slot) do { if (p.trace) p.trace[((size_t)(blockIdx.y * gridDim.x + blockIdx.x)) * 64 + (slot)] = gtime_ns(); } while (0)
+#define G3_TRACE(slot) do { if (p.trace) p.trace[((size_t)(blockIdx.y * gridDim.x + blockIdx.x)) * 64 + (slot)] = gtime_ns(); } while (0)
 
-constexpr int GM_THREADS = 320;
-constexpr int GM_MAX_STAGES = 8;
-constexpr int GM_TILE_M = 128;
-constexpr int GM_BK = 64;
-constexpr int GM_DYN_SMEM = 227 * 1024 - 18 * 1024;   // static: 16 KB store staging + barriers   // static shared memory (barriers, 8 KB reduction scratch) stays below 10 KB
+constexpr int G3_THREADS = 384;
+constexpr int G3_MAX_STAGES = 8;       // activation ring
+constexpr int G3_MAX_OPS = 4;          // operand ring stages per warpgroup
+constexpr int G3_TILE_M = 128;
+constexpr int G3_BK = 64;
+constexpr int CW = 16;                 // epilogue column chunk (one tcgen05.ld 32x32b.x16 per thread)
+constexpr int G3_SMEM_LIMIT = 227 * 1024 - 2048;   // static shared memory (barriers) stays below 2 KB
 
-struct GemmParams {
-  int M, H, W;              // tokens; image size (pixel coordinates / per-sample chunks for the epilogue)
-  int a_coff, kblocks;      // first input channel, Kpad / 64
+struct G3Params {
+  int M, H, W, hw;
+  int a_coff, kblocks;
   int N, BN, Npad;
-  int m_tiles;              // M / 128
-  int stages;               // activation ring depth
-  int b_bytes;              // BN * Kpad * 2: resident weight panel
-  uint32_t acc_stride;      // TMEM columns between the two accumulator stages
-  uint32_t tmem_cols;       // allocation (power of two)
-  int op_resid, op_u;       // epilogue operands fed by TMA (fp32 residual stream, bf16 CAB branch)
-  int op_stage_bytes;       // bytes of one operand-ring stage (resid chunk + U chunk), 1024-aligned
-  int op_u_off;
-  int dbg;                     // engineering bit mask (HATB200_GEMM_DBG): 1 = no out_t store, 2 = no bias
-  unsigned long long* trace;   // engineering: per-CTA event timestamps (HATB200_GEMM_TRACE=1), else null
+  int m_tiles;
+  int b_resident;           // weight panel resident in shared memory (else streamed per k-block with A)
+  int stages, stage_bytes;  // activation ring (stage = A tile [+ W k-block])
+  int ops, op_stage_bytes, op_u_off;   // operand ring per warpgroup
+  int has_resid, has_u;
+  uint32_t acc_stride, tmem_cols;
+  // shared memory offsets (bytes from the 1024-aligned base)
+  int off_b, off_a, off_op, off_stg32, off_stg16, off_tab, smem_bytes;
+  int stg_bufs;             // staging buffers per warp and element type (2, or 1 when both types stage in pass 1)
+  int share_stg;            // fp32 and bf16 staging alias (pass 1 writes only fp32, pass 2 only bf16)
+  unsigned long long* trace;
 };
 
-template <int CW>
-__global__ void __launch_bounds__(GM_THREADS, 1)
+// ---- small PTX helpers -------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long pk(float a, float b) {
+  return (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
+}
+__device__ __forceinline__ void upk(unsigned long long v, float& a, float& b) {
+  a = __uint_as_float((uint32_t)v); b = __uint_as_float((uint32_t)(v >> 32));
+}
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)), "l"(pk(c0, c1)));
+  upk(r, d0, d1);
+}
+__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)));
+  upk(r, d0, d1);
+}
+__device__ __forceinline__ void mul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)));
+  upk(r, d0, d1);
+}
+
+
+// swizzle of 16-byte granule index for a tile whose rows are RB bytes wide (TMA SWIZZLE_{32,64,128}B, tile base
+// aligned to the swizzle period)
+template <int RB>
+__device__ __forceinline__ int sw_gran(int row) {
+  return RB == 128 ? (row & 7) : (RB == 64 ? ((row >> 1) & 3) : ((row >> 2) & 1));
+}
+// this thread's row (CW fp32) of a swizzled tile
+__device__ __forceinline__ void row_read_f32(const uint8_t* tile, int row, float (&o)[CW]) {
+  constexpr int RB = CW * 4;
+  const int sw = sw_gran<RB>(row);
+  const uint32_t base = smem_u32(tile) + row * RB;
+#pragma unroll
+  for (int c = 0; c < RB / 16; c++) {
+    const uint4 t = lds128(base + ((c ^ sw) << 4));
+    o[4 * c] = __uint_as_float(t.x); o[4 * c + 1] = __uint_as_float(t.y);
+    o[4 * c + 2] = __uint_as_float(t.z); o[4 * c + 3] = __uint_as_float(t.w);
+  }
+}
+__device__ __forceinline__ void row_read_bf16(const uint8_t* tile, int row, float (&o)[CW]) {
+  constexpr int RB = CW * 2;
+  const int sw = sw_gran<RB>(row);
+  const uint32_t base = smem_u32(tile) + row * RB;
+#pragma unroll
+  for (int c = 0; c < RB / 16; c++) {
+    const uint4 t = lds128(base + ((c ^ sw) << 4));
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      o[8 * c + 2 * j] = __uint_as_float(w[j] << 16);
+      o[8 * c + 2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+    }
+  }
+}
+// CW consecutive floats of a shared-memory table (same address for the whole warp: broadcast)
+__device__ __forceinline__ void tab_read(const float* tab, float (&o)[CW]) {
+#pragma unroll
+  for (int c = 0; c < CW / 4; c++) {
+    const uint4 t = lds128(smem_u32(tab) + 16 * c);
+    o[4 * c] = __uint_as_float(t.x); o[4 * c + 1] = __uint_as_float(t.y);
+    o[4 * c + 2] = __uint_as_float(t.z); o[4 * c + 3] = __uint_as_float(t.w);
+  }
+}
+
+// Per-warp output staging.  GW consecutive chunks (CW columns each, EB bytes per element) of the warp's 32 rows are
+// collected in one swizzled tile whose rows are RB = CW * EB * GW bytes (128 B when grouped) and leave with ONE TMA
+// store; two buffers alternate so that the store of group q overlaps the arithmetic of group q + 1.
+template <int EB, int GW>
+struct Stager {
+  static constexpr int RB = CW * EB * GW;
+  static constexpr int BUF = 32 * RB;
+  uint8_t* base;
+  uint32_t n = 0;                    // stores issued by this warp
+  int nbuf = 2;                      // 2: double buffered; 1: single buffer (shared memory is short)
+  __device__ __forceinline__ uint8_t* buf() const { return base + (nbuf == 2 ? (n & 1) : 0) * BUF; }
+  // before the first write of a group: the store that last read this buffer must be done reading it
+  __device__ __forceinline__ void begin(int lane) const {
+    if (lane == 0) { if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>(); }
+    __syncwarp();
+  }
+  __device__ __forceinline__ void put_f32(int lane, int slot, const float (&v)[CW]) const {
+    const uint32_t row = smem_u32(buf()) + lane * RB;
+    const int sw = sw_gran<RB>(lane);
+#pragma unroll
+    for (int c = 0; c < 4; c++)
+      sts128(row + (((slot * 4 + c) ^ sw) << 4), __float_as_uint(v[4 * c]), __float_as_uint(v[4 * c + 1]),
+             __float_as_uint(v[4 * c + 2]), __float_as_uint(v[4 * c + 3]));
+  }
+  __device__ __forceinline__ void put_bf16(int lane, int slot, const float (&v)[CW]) const {
+    const uint32_t row = smem_u32(buf()) + lane * RB;
+    const int sw = sw_gran<RB>(lane);
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      uint4 t;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+      for (int j = 0; j < 4; j++) h[j] = __floats2bfloat162_rn(v[8 * c + 2 * j], v[8 * c + 2 * j + 1]);
+      sts128(row + (((slot * 2 + c) ^ sw) << 4), t.x, t.y, t.z, t.w);
+    }
+  }
+  __device__ __forceinline__ void put_zero(int lane) const {
+    const uint32_t row = smem_u32(buf()) + lane * RB;
+#pragma unroll
+    for (int c = 0; c < RB / 16; c++) sts128(row + 16 * c, 0u, 0u, 0u, 0u);
+  }
+  // after the last write of a group: hand the tile to the async proxy; columns past the map's width are clipped
+  __device__ __forceinline__ void flush(const CUtensorMap* tm, int lane, int c0, int r0) {
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(tm, buf(), c0, r0);
+      bulk_commit();
+    }
+    n++;
+  }
+};
+
+}  // namespace
+
+// ---- the kernel ----------------------------------------------------------------------------------------
+template <bool RING, bool GROUPED>
+__global__ void __launch_bounds__(G3_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU, const GemmParams p,
-               const Epilogue ep) {
+               const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU,
+               const __grid_constant__ CUtensorMap tmOF, const __grid_constant__ CUtensorMap tmOT,
+               const __grid_constant__ CUtensorMap tmLN, const G3Params p, const Epilogue ep) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[GM_MAX_STAGES];
-  __shared__ __align__(8) uint64_t empty_bar[GM_MAX_STAGES];
+  __shared__ __align__(8) uint64_t full_bar[G3_MAX_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[G3_MAX_STAGES];
   __shared__ __align__(8) uint64_t b_bar;
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
-  __shared__ __align__(8) uint64_t op_full[2][2];
+  __shared__ __align__(8) uint64_t op_full[2][G3_MAX_OPS];
+  __shared__ __align__(8) uint64_t op_empty[2][G3_MAX_OPS];
   __shared__ uint32_t tmem_slot;
-  __shared__ __align__(16) uint8_t wstage[8][2048];   // per epilogue warp: store staging (32 rows x 64 B)
-  __shared__ float hsum[2][4][16];                    // per warpgroup: column sums of the LN head
+  __shared__ float hsum[8][16];                       // per epilogue warp: column sums of the LN head
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* smem_b = smem;                                   // [kblocks][BN rows x 128 B], SWIZZLE_128B
-  uint8_t* smem_a = smem + ((p.b_bytes + 1023) & ~1023);    // [stages][128 rows x 128 B]
-  constexpr int A_BYTES = GM_TILE_M * GM_BK * 2;
-  uint8_t* smem_op = smem_a + (size_t)p.stages * A_BYTES;   // [2 warpgroups][2 stages][op_stage_bytes]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.y * p.BN;
+  constexpr int A_BYTES = G3_TILE_M * G3_BK * 2;
+  float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);   // [BN]
+  float* tab_gamma = tab_bias + p.BN;                             // [BN]
+  float* tab_beta = tab_gamma + p.BN;                             // [BN]
+  float* tab_coef = tab_beta + p.BN;                              // [2][BN]: per-warpgroup ECA coefficients of its tile
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -89,12 +247,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int g = 0; g < 2; g++) {
       mbar_init(&tmem_full_bar[g], 1);
       mbar_init(&tmem_empty_bar[g], 128);
-      mbar_init(&op_full[g][0], 1);
-      mbar_init(&op_full[g][1], 1);
+      for (int s = 0; s < G3_MAX_OPS; s++) {
+        mbar_init(&op_full[g][s], 1);
+        mbar_init(&op_empty[g][s], 4);
+      }
     }
-    if (p.op_resid) prefetch_tmap(&tmR);
-    if (p.op_u) prefetch_tmap(&tmU);
     fence_barrier_init();
+  }
+  // tables: zero padded beyond N, so pad columns come out as exact zeros with no predicate
+  for (int i = threadIdx.x; i < p.BN; i += G3_THREADS) {
+    const int n = n0 + i;
+    const bool ok = n < p.N;
+    tab_bias[i] = (ok && ep.bias) ? __ldg(ep.bias + n) : 0.f;
+    tab_gamma[i] = (ok && ep.ln_gamma) ? __ldg(ep.ln_gamma + n) : 0.f;
+    tab_beta[i] = (ok && ep.ln_beta) ? __ldg(ep.ln_beta + n) : 0.f;
   }
   if (warp == 1) tmem_alloc(&tmem_slot, p.tmem_cols);
   tc_fence_before();
@@ -103,114 +269,296 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer: weights once (resident) or per k-block (streamed), activations through the ring =====
     if (lane == 0) {
-      mbar_arrive_expect_tx(&b_bar, (uint32_t)p.b_bytes);
-      for (int kb = 0; kb < p.kblocks; kb++)
-        tma_load_2d(smem_b + (size_t)kb * p.BN * 128, &tmB, &b_bar, kb * GM_BK, n0);
+      if (p.b_resident) {
+        mbar_arrive_expect_tx(&b_bar, (uint32_t)(p.kblocks * p.BN * 128));
+        for (int kb = 0; kb < p.kblocks; kb++)
+          tma_load_2d(smem + p.off_b + (size_t)kb * p.BN * 128, &tmB, &b_bar, kb * G3_BK, n0);
+      }
+      const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
       int it = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
         for (int kb = 0; kb < p.kblocks; kb++, it++) {
           const int s = it % p.stages;
           const uint32_t par = (uint32_t)(it / p.stages) & 1u;
           mbar_wait(&empty_bar[s], par ^ 1u);
-          mbar_arrive_expect_tx(&full_bar[s], A_BYTES);
-          tma_load_2d(smem_a + (size_t)s * A_BYTES, &tmA, &full_bar[s], p.a_coff + kb * GM_BK, t * GM_TILE_M);
+          uint8_t* sa = smem + p.off_a + (size_t)s * p.stage_bytes;
+          mbar_arrive_expect_tx(&full_bar[s], tx);
+          tma_load_2d(sa, &tmA, &full_bar[s], p.a_coff + kb * G3_BK, t * G3_TILE_M);
+          if (!p.b_resident) tma_load_2d(sa + A_BYTES, &tmB, &full_bar[s], kb * G3_BK, n0);
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(GM_TILE_M, p.BN);
-      GM_TRACE(0);
-      mbar_wait(&b_bar, 0);
-      GM_TRACE(1);
+      const uint32_t idesc = make_idesc_bf16(G3_TILE_M, p.BN);
+      G3_TRACE(0);
+      if (p.b_resident) mbar_wait(&b_bar, 0);
+      G3_TRACE(1);
       int it = 0, i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         const int g = i & 1;
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
         tc_fence_after();
-        if (i < 6) GM_TRACE(8 + 2 * i);
+        if (i < 6) G3_TRACE(8 + 2 * i);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
         for (int kb = 0; kb < p.kblocks; kb++, it++) {
           const int s = it % p.stages;
           const uint32_t par = (uint32_t)(it / p.stages) & 1u;
           mbar_wait(&full_bar[s], par);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem_a + (size_t)s * A_BYTES);
-          const uint32_t sb = smem_u32(smem_b + (size_t)kb * p.BN * 128);
+          const uint32_t sa = smem_u32(smem + p.off_a + (size_t)s * p.stage_bytes);
+          const uint32_t sb = p.b_resident ? smem_u32(smem + p.off_b + (size_t)kb * p.BN * 128) : sa + A_BYTES;
 #pragma unroll
-          for (int k = 0; k < GM_BK / 16; k++) {
+          for (int k = 0; k < G3_BK / 16; k++) {
             const uint64_t ad = make_smem_desc(sa + k * 32, 128);
             const uint64_t bd = make_smem_desc(sb + k * 32, 128);
             umma_bf16(acc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty_bar[s]);       // frees the activation slot once these MMAs have read it
+          umma_commit(&empty_bar[s]);       // frees the ring slot once these MMAs have read it
         }
         umma_commit(&tmem_full_bar[g]);     // accumulator of tile i complete
-        if (i < 6) GM_TRACE(9 + 2 * i);
+        if (i < 6) G3_TRACE(9 + 2 * i);
+      }
+    }
+  } else if (warp >= 10) {
+    // ===== operand-ring producer of warpgroup g: residual / CAB-branch chunks, as far ahead as the ring allows =====
+    const int g = warp - 10;
+    if (RING && lane == 0) {
+      if (p.has_resid) prefetch_tmap(&tmR);
+      if (p.has_u) prefetch_tmap(&tmU);
+      const int nch = p.BN / CW;
+      const uint32_t bytes = (uint32_t)((p.has_resid ? G3_TILE_M * CW * 4 : 0) + (p.has_u ? G3_TILE_M * CW * 2 : 0));
+      uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
+      uint32_t k = 0;
+      int i = 0;
+      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
+        if ((i & 1) != g) continue;
+        for (int ci = 0; ci < nch; ci++, k++) {
+          const int s = k % p.ops;
+          const uint32_t par = (k / p.ops) & 1u;
+          mbar_wait(&op_empty[g][s], par ^ 1u);
+          uint8_t* st = ring + (size_t)s * p.op_stage_bytes;
+          mbar_arrive_expect_tx(&op_full[g][s], bytes);
+          if (p.has_resid) tma_load_2d(st, &tmR, &op_full[g][s], n0 + ci * CW, t * G3_TILE_M);
+          if (p.has_u) tma_load_2d(st + p.op_u_off, &tmU, &op_full[g][s], n0 + ci * CW, t * G3_TILE_M);
+        }
       }
     }
   } else {
-    // ===== epilogue warpgroups: warps 2-5 take even local tiles, warps 6-9 odd ones =====
+    // ===== epilogue warps: warpgroup g = (warp - 2) / 4 takes local tiles i with (i & 1) == g =====
     const int g = (warp - 2) >> 2;
-    const int quarter = warp & 3;
-    const int row = quarter * 32 + lane;
-    const int hw = p.H * p.W;
-    EpiCtx c;
-    c.H = p.H; c.W = p.W; c.N = p.N; c.n0 = n0; c.BN = p.BN;
-    c.last_ntile = blockIdx.y == gridDim.y - 1;
-    c.nchunk = hw / GM_TILE_M;
-    c.quarter = quarter; c.lane = lane; c.gtid = (threadIdx.x - 64) & 127; c.bar_id = 1 + g;
-    c.sred = nullptr;
-    c.wstage = wstage[warp - 2];
-    c.hsum = hsum[g];
-    c.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(quarter * 32) << 16);
-    // operand ring of this warpgroup: residual / CAB-branch chunks arrive by TMA two chunks ahead
-    OpRing ring;
-    OpRing* rg = nullptr;
-    if (p.op_resid || p.op_u) {
-      rg = &ring;
-      ring.stage[0] = smem_op + (size_t)(g * 2) * p.op_stage_bytes;
-      ring.stage[1] = ring.stage[0] + p.op_stage_bytes;
-      ring.full[0] = &op_full[g][0];
-      ring.full[1] = &op_full[g][1];
-      ring.tm_resid = &tmR; ring.tm_u = &tmU;
-      ring.has_resid = p.op_resid != 0; ring.has_u = p.op_u != 0;
-      ring.bytes = (uint32_t)((p.op_resid ? GM_TILE_M * CW * 4 : 0) + (p.op_u ? GM_TILE_M * CW * 2 : 0));
-      ring.u_off = p.op_u_off;
-      ring.nch = p.BN / CW;
-      ring.tile_stride = 2 * gridDim.x;
-      ring.m_tiles = p.m_tiles;
-      ring.k = 0;
-      if (c.gtid == 0) {                 // prologue: the first two chunks of this warpgroup's first tile(s)
-        int tn = blockIdx.x + g * gridDim.x, cn = 0;
-        for (uint32_t kk = 0; kk < 2; kk++) {
-          if (tn < p.m_tiles) ring_issue<CW>(ring, kk, tn, cn, n0);
-          if (++cn >= ring.nch) { cn = 0; tn += ring.tile_stride; }
-        }
-      }
+    const int ew = warp - 2;                          // 0..7
+    const int quarter = warp & 3;                     // TMEM lane quarter this warp may access
+    const int row = quarter * 32 + lane;              // row of the tile owned by this thread
+    const int wg_tid = ((warp - 2) & 3) * 32 + lane;  // 0..127 inside the warpgroup
+    const int nch = p.BN / CW;
+    const bool do_ln = ep.ln_out != nullptr;
+    const uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
+    constexpr int GW32 = GROUPED ? 2 : 1, GW16 = GROUPED ? 4 : 1;      // chunks per store: 128-byte rows when grouped
+    Stager<4, GW32> st32;
+    Stager<2, GW16> st16;
+    st32.nbuf = st16.nbuf = p.stg_bufs;
+    st32.base = smem + p.off_stg32 + (size_t)ew * (p.stg_bufs * Stager<4, GW32>::BUF);
+    st16.base = smem + p.off_stg16 + (size_t)ew * (p.stg_bufs * Stager<2, GW16>::BUF);
+    float* coef = tab_coef + g * p.BN;
+    uint32_t k = 0;          // operand chunks consumed by this warpgroup
+    if (lane == 0) {
+      if (ep.out_f32) prefetch_tmap(&tmOF);
+      if (ep.out_t) prefetch_tmap(&tmOT);
+      if (do_ln) prefetch_tmap(&tmLN);
     }
     int i = 0;
     for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
       if ((i & 1) != g) continue;
-      const int m = t * GM_TILE_M + row;
-      c.m = m;
-      c.b = m / hw;
-      const int rem = m - c.b * hw;
-      c.py = rem / p.W; c.px = rem - c.py * p.W;
-      c.chunk = (t * GM_TILE_M - c.b * hw) / GM_TILE_M;
-      const bool tr = c.gtid == 0 && (i >> 1) < 4;
-      if (tr) GM_TRACE(24 + g * 16 + 4 * (i >> 1));
+      const int m0 = t * G3_TILE_M;
+      const int m = m0 + row;
+      const int r0 = m0 + quarter * 32;               // first token row of this warp
+      const int b = m0 / p.hw;                        // a tile never straddles two samples (hw % 128 == 0)
+      const uint32_t trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(quarter * 32) << 16);
+      const bool tr = wg_tid == 0 && (i >> 1) < 4;
+      if (RING && ep.eca_u) {
+        // per-sample ECA coefficients of this tile (hat_arch.py:236: conv_scale * sigmoid gate), zero beyond N
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");          // previous tile's readers are done
+        for (int j = wg_tid; j < p.BN; j += 128) {
+          const int n = n0 + j;
+          coef[j] = n < p.N ? ep.eca_coef * ep.eca_scale[(size_t)b * p.N + n] : 0.f;
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+      }
+      if (tr) G3_TRACE(24 + g * 16 + 4 * (i >> 1));
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
-      if (tr) GM_TRACE(25 + g * 16 + 4 * (i >> 1));
-      run_epilogue2<CW>(ep, c, rg, row, t);
+      if (tr) G3_TRACE(25 + g * 16 + 4 * (i >> 1));
+
+      float ln_k = 0.f, s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
+      if (p.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }     // previous tile's bf16 stores have left it
+      // ---------------- pass 1: value, fp32 / bf16 outputs, LayerNorm statistics ----------------
+      uint32_t r[CW];
+      tmem_ld16(trow, r);                             // software pipeline: chunk ci + 1 loads while chunk ci is processed
+      for (int ci = 0; ci < nch; ci++) {
+        const int nb = ci * CW;                       // column inside the n-tile
+        float v[CW], tb[CW], acc[CW];
+        tab_read(tab_bias + nb, tb);
+        float u[CW], rs[CW], cf[CW];
+        if constexpr (RING) {
+          const int s = k % p.ops;
+          mbar_wait(&op_full[g][s], (k / p.ops) & 1u);
+          const uint8_t* st = ring + (size_t)s * p.op_stage_bytes;
+          if (p.has_u) { row_read_bf16(st + p.op_u_off, row, u); tab_read(coef + nb, cf); }
+          if (p.has_resid) row_read_f32(st, row, rs);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&op_empty[g][s]);      // this warp's rows are in registers
+          k++;
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
+        if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
+#pragma unroll
+        for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], acc[j], acc[j + 1], tb[j], tb[j + 1]);
+        if (n0 + nb < ep.scale_ncols) {               // q pre-scaling (hat_arch.py:375); scale_ncols % CW == 0
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) mul2(v[j], v[j + 1], v[j], v[j + 1], ep.out_scale, ep.out_scale);
+        }
+        if (ep.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < CW; j++) v[j] = gelu_f(v[j]);
+        } else if (ep.act == ACT_LRELU) {
+#pragma unroll
+          for (int j = 0; j < CW; j++) v[j] = lrelu_f(v[j]);
+        }
+        if (RING && p.has_u) {
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) fma2(v[j], v[j + 1], cf[j], cf[j + 1], u[j], u[j + 1], v[j], v[j + 1]);
+        }
+        if (RING && p.has_resid) {
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], v[j], v[j + 1], rs[j], rs[j + 1]);
+        }
+        if (do_ln) {
+          if (ci == 0) ln_k = v[0];
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) {
+            float d0, d1;
+            add2(d0, d1, v[j], v[j + 1], -ln_k, -ln_k);
+            add2(s1a, s1b, s1a, s1b, d0, d1);
+            fma2(s2a, s2b, d0, d1, d0, d1, s2a, s2b);
+          }
+          uint32_t w[CW];
+#pragma unroll
+          for (int j = 0; j < CW; j++) w[j] = __float_as_uint(v[j]);
+          tmem_st16(trow + (uint32_t)nb, w);          // fp32 row parked in TMEM for the normalise pass
+        }
+        if (ep.out_f32) {
+          const int slot = ci % GW32;
+          if (slot == 0) st32.begin(lane);
+          st32.put_f32(lane, slot, v);
+          if (slot == GW32 - 1 || ci == nch - 1) st32.flush(&tmOF, lane, n0 + (ci - slot) * CW, r0);
+        }
+        if (ep.out_t) {
+          const int slot = ci % GW16;
+          if (slot == 0) st16.begin(lane);
+          st16.put_bf16(lane, slot, v);
+          if (slot == GW16 - 1 || ci == nch - 1) st16.flush(&tmOT, lane, n0 + (ci - slot) * CW, r0);
+        }
+      }
+      if (tr) G3_TRACE(27 + g * 16 + 4 * (i >> 1));                  // end of pass 1
+      // K-padding columns of the consumer that no n-tile covers: [Npad, out_t_zero_to), written by the last n-tile
+      if (ep.out_t && blockIdx.y == gridDim.y - 1) {
+        for (int nb = p.BN; n0 + nb < ep.out_t_zero_to; nb += CW * GW16) {
+          st16.begin(lane);
+          st16.put_zero(lane);
+          st16.flush(&tmOT, lane, n0 + nb, r0);
+        }
+      }
+      // ---------------- pass 2: LayerNorm of the row (eps 1e-5), bf16 output, 16-channel head ----------------
+      if (do_ln) {
+        if (p.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
+        tmem_st_wait();
+        // pad columns hold exact zeros: remove their contribution to the shifted sums
+        const float npad = (float)(p.BN - p.N);
+        const float s1 = s1a + s1b + npad * ln_k;
+        const float s2 = s2a + s2b - npad * ln_k * ln_k;
+        const float inv_n = 1.f / (float)p.N;
+        const float mean_d = s1 * inv_n;
+        const float var = fmaxf(s2 * inv_n - mean_d * mean_d, 0.f);
+        const float rstd = rsqrtf(var + 1e-5f);
+        const float nmr = -(ln_k + mean_d) * rstd;    // (x - mean) * rstd = x * rstd + nmr
+        tmem_ld16(trow, r);
+        for (int ci = 0; ci < nch; ci++) {
+          const int nb = ci * CW;
+          float ga[CW], be[CW], v[CW], acc[CW];
+          tab_read(tab_gamma + nb, ga);
+          tab_read(tab_beta + nb, be);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
+          if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) {
+            float t0, t1;
+            fma2(t0, t1, acc[j], acc[j + 1], rstd, rstd, nmr, nmr);
+            fma2(v[j], v[j + 1], t0, t1, ga[j], ga[j + 1], be[j], be[j + 1]);
+          }
+          const int slot = ci % GW16;
+          if (slot == 0) st16.begin(lane);
+          st16.put_bf16(lane, slot, v);
+          if (slot == GW16 - 1 || ci == nch - 1) st16.flush(&tmLN, lane, (ci - slot) * CW, r0);
+          if (ci == 0 && ep.ln_head) {    // compact / x-padded copies of the first channels + their column sums
+            const int rem = m - b * p.hw;
+            const int py = rem / p.W, px = rem - py * p.W;
+            uint4 q[2];
+            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(q);
+#pragma unroll
+            for (int j = 0; j < 8; j++) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            bf16* hd = (bf16*)ep.ln_head + (size_t)m * ep.ln_head_c;
+            if (ep.ln_head_c == 16) {
+              reinterpret_cast<uint4*>(hd)[0] = q[0];
+              reinterpret_cast<uint4*>(hd)[1] = q[1];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; j++)
+                if (j < ep.ln_head_c) hd[j] = __float2bfloat16_rn(v[j]);
+            }
+            if (ep.ln_head_pad && ep.ln_head_c == 16) {
+              bf16* hp = (bf16*)ep.ln_head_pad + (((size_t)b * p.H + py) * (p.W + 12) + px + 6) * 16;
+              reinterpret_cast<uint4*>(hp)[0] = q[0];
+              reinterpret_cast<uint4*>(hp)[1] = q[1];
+            }
+            if (ep.ln_head_colsum) {      // sums of the bf16-rounded head values, fixed order
+#pragma unroll
+              for (int j = 0; j < 16; j++) {
+                const float sj = warp_sum(__bfloat162float(__float2bfloat16_rn(v[j])));
+                if (lane == 0) hsum[ew][j] = sj;
+              }
+            }
+          }
+        }
+        for (int nb = p.BN; nb < ep.ln_pitch; nb += CW * GW16) {   // pad columns beyond the (single) n-tile
+          st16.begin(lane);
+          st16.put_zero(lane);
+          st16.flush(&tmLN, lane, nb, r0);
+        }
+        if (ep.ln_head_colsum) {
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+          if (wg_tid < ep.ln_head_c && wg_tid < 16) {
+            // warps of this warpgroup in row order: quarter q is warp ((q + 2) & 3) of the group
+            const int e0 = g * 4;
+            const int chunk = (m0 - b * p.hw) / G3_TILE_M, nchunk = p.hw / G3_TILE_M;
+            ep.ln_head_colsum[((size_t)b * nchunk + chunk) * ep.ln_head_c + wg_tid] =
+                hsum[e0 + 2][wg_tid] + hsum[e0 + 3][wg_tid] + hsum[e0 + 0][wg_tid] + hsum[e0 + 1][wg_tid];
+          }
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");       // hsum is reused by the next tile
+        }
+      }
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
-      if (tr) GM_TRACE(26 + g * 16 + 4 * (i >> 1));
+      if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
     }
+    if (lane == 0) bulk_wait_all();       // staging buffers must outlive the last stores
   }
   tc_fence_before();
   __syncthreads();
@@ -235,105 +583,158 @@ static int sm_count() {
   return n;
 }
 
-static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep, GemmParams& p, int& cw) {
+static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep, G3Params& p, bool& grouped) {
   if (a.KH != 1 || a.KW != 1) return false;
   const long long M = (long long)a.B * a.H * a.W;
-  if (M % GM_TILE_M || (a.H * a.W) % GM_TILE_M) return false;
-  if (Kpad % GM_BK || Kpad < a.Cin) return false;
+  if (M % G3_TILE_M || (a.H * a.W) % G3_TILE_M) return false;
+  if (Kpad % G3_BK || Kpad < a.Cin) return false;
   if ((a.a_pitch * 2) % 16 || (a.a_coff * 2) % 16) return false;
   p.BN = tc_bn(a.N);
   if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
-  // epilogue features / alignment the second-generation epilogue relies on (else: tc_tapconv.cu handles the layer)
+  // features this kernel does not implement (tc_tapconv.cu handles those layers)
   if (ep.colsum || ep.dyn_k || ep.shuffle_r != 1) return false;
-  if (a.N % 4) return false;
-  if (ep.out_f32 && (ep.out_f32_pitch % 4 || ((uintptr_t)ep.out_f32 & 15))) return false;
-  if (ep.out_t && (ep.out_t_pitch % 8 || ep.out_t_coff % 8 || ((uintptr_t)ep.out_t & 15))) return false;
-  if (ep.out_t && (ep.out_t_zero_to % 8 || (a.N % 8 && ep.out_t_zero_to < round_up(a.N, 8)))) return false;   // 16-byte store granules
-  if (ep.ln_out && ep.ln_pitch < round_up(a.N, 8)) return false;
-  if (ep.ln_out && (ep.ln_pitch % 8 || ((uintptr_t)ep.ln_out & 15))) return false;
-  if (ep.resid && (ep.resid_pitch % 4 || ((uintptr_t)ep.resid & 15))) return false;
-  if (ep.eca_u && (ep.eca_pitch % 8 || ((uintptr_t)ep.eca_u & 15) || ep.eca_pitch < round_up(a.N, 32))) return false;
-  p.M = (int)M; p.H = a.H; p.W = a.W;
-  p.a_coff = a.a_coff; p.kblocks = Kpad / GM_BK;
+  if (ep.scale_ncols % CW) return false;
+  // TMA alignment: 16-byte row pitches and bases
+  if (ep.out_f32 && ((ep.out_f32_pitch * 4) % 16 || ((uintptr_t)ep.out_f32 & 15))) return false;
+  if (ep.out_t && ((ep.out_t_pitch * 2) % 16 || (ep.out_t_coff * 2) % 16 || ((uintptr_t)ep.out_t & 15))) return false;
+  if (ep.out_t && ep.out_t_pitch - ep.out_t_coff < (ep.out_t_zero_to > a.N ? ep.out_t_zero_to : a.N)) return false;
+  if (ep.ln_out && ((ep.ln_pitch * 2) % 16 || ((uintptr_t)ep.ln_out & 15) || ep.ln_pitch < a.N)) return false;
+  if (ep.resid && ((ep.resid_pitch * 4) % 16 || ((uintptr_t)ep.resid & 15))) return false;
+  if (ep.eca_u && ((ep.eca_pitch * 2) % 16 || ((uintptr_t)ep.eca_u & 15) || ep.eca_pitch < a.N)) return false;
+  if (ep.ln_out && Npad != p.BN) return false;                    // LayerNorm needs the whole row in one CTA
+  if (ep.ln_head && (ep.ln_head_c > 16 || !ep.ln_out)) return false;
+  p.M = (int)M; p.H = a.H; p.W = a.W; p.hw = a.H * a.W;
+  p.a_coff = a.a_coff; p.kblocks = Kpad / G3_BK;
   p.N = a.N; p.Npad = Npad;
-  p.m_tiles = (int)(M / GM_TILE_M);
-  p.b_bytes = p.BN * Kpad * 2;
+  p.m_tiles = (int)(M / G3_TILE_M);
   p.acc_stride = (uint32_t)round_up(p.BN, 32);
   uint32_t cols = 32;
   while (cols < 2 * p.acc_stride) cols <<= 1;
+  if (cols > 512) return false;
   p.tmem_cols = cols;
-  p.op_resid = ep.resid != nullptr; p.op_u = ep.eca_u != nullptr;
-  const int budget = GM_DYN_SMEM - 1024 - round_up(p.b_bytes, 1024);
-  for (cw = (p.BN % 32 == 0) ? 32 : 16; cw >= 16; cw -= 16) {
-    const int rb = p.op_resid ? GM_TILE_M * cw * 4 : 0, ub = p.op_u ? GM_TILE_M * cw * 2 : 0;
-    p.op_u_off = rb;
-    p.op_stage_bytes = round_up(rb + ub, 1024);
-    int st = (budget - 4 * p.op_stage_bytes) / (GM_TILE_M * GM_BK * 2);
-    if (st >= 2) {
-      p.stages = st > GM_MAX_STAGES ? GM_MAX_STAGES : st;
-      return true;
+  p.has_resid = ep.resid != nullptr; p.has_u = ep.eca_u != nullptr;
+  const bool ring = p.has_resid || p.has_u;
+  grouped = p.BN % 64 == 0;                 // stores leave as 128-byte rows (2 fp32 / 4 bf16 chunks per TMA store)
+  const bool f32o = ep.out_f32 != nullptr, bf16o = ep.out_t != nullptr || ep.ln_out != nullptr;
+  // fp32 staging is idle during the LayerNorm pass and vice versa: share it unless pass 1 also writes bf16
+  p.share_stg = f32o && bf16o && ep.out_t == nullptr;
+  const int b_bytes = p.BN * Kpad * 2;
+  const int tab = round_up(5 * p.BN * 4, 1024);
+  p.stg_bufs = (f32o && ep.out_t != nullptr) ? 1 : 2;
+  const int stg32 = f32o ? 8 * p.stg_bufs * 32 * (grouped ? 128 : 64) : 0;
+  const int stg16 = bf16o && !p.share_stg ? 8 * p.stg_bufs * 32 * (grouped ? 128 : 32) : 0;
+  const int rb = p.has_resid ? G3_TILE_M * CW * 4 : 0, ub = p.has_u ? G3_TILE_M * CW * 2 : 0;
+  p.op_u_off = rb;
+  p.op_stage_bytes = round_up(rb + ub, 1024);
+  // weights resident when the pipeline still gets >= 3 activation stages (>= 2 for short K), else streamed
+  for (int pass = 0; pass < 4; pass++) {
+    const int resident = pass < 2 ? 1 : 0;
+    const int want = (pass & 1) ? 2 : 3;
+    const int stage = G3_TILE_M * G3_BK * 2 + (resident ? 0 : p.BN * 128);
+    const int fixed = tab + stg32 + stg16 + (resident ? round_up(b_bytes, 1024) : 0);
+    int best_ops = -1, best_st = 0;
+    for (int ops = ring ? 3 : 0; ops >= (ring ? 2 : 0); ops--) {
+      const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes;
+      const int st = avail > 0 ? avail / stage : 0;
+      if (st >= want) { best_ops = ops; best_st = st; break; }
     }
+    if (best_ops < 0) continue;
+    if (resident && want == 2 && p.kblocks >= 4) continue;     // long K with a starved ring: stream the weights instead
+    p.b_resident = resident;
+    p.stage_bytes = stage;
+    p.stages = best_st > G3_MAX_STAGES ? G3_MAX_STAGES : best_st;
+    p.ops = best_ops;
+    if (ring) {                                                 // spend what is left on a deeper operand ring
+      int left = G3_SMEM_LIMIT - fixed - 2 * p.ops * p.op_stage_bytes - p.stages * stage;
+      while (p.ops < G3_MAX_OPS && left >= 2 * p.op_stage_bytes) { p.ops++; left -= 2 * p.op_stage_bytes; }
+    }
+    int off = 0;
+    p.off_b = off; off += resident ? round_up(b_bytes, 1024) : 0;
+    p.off_a = off; off += p.stages * stage;
+    p.off_op = off; off += 2 * p.ops * p.op_stage_bytes;
+    p.off_stg32 = off; off += stg32;
+    p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += stg16;
+    p.off_tab = off; off += tab;
+    p.smem_bytes = off;
+    return off <= G3_SMEM_LIMIT;
   }
   return false;
 }
 
 bool gemm_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
-  GemmParams p;
-  int cw;
-  if (!gemm_geometry(a, Npad, Kpad, ep, p, cw)) return false;
-  if (ep.ln_out && (Npad != p.BN || ep.ln_pitch > 512)) return false;     // LN needs the whole row in one CTA
-  if (ep.ln_head && ep.ln_head_c > 16) return false;
+  G3Params p;
+  bool grouped;
+  if (!gemm_geometry(a, Npad, Kpad, ep, p, grouped)) return false;
   if (tc::encode_tiled_fn() == nullptr) return false;
-  const char* v = getenv("HATB200_GEMM_V2");
+  const char* v = getenv("HATB200_GEMM_V3");
   if (v && *v == '0') return false;
   return true;
 }
 
 int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
-  GemmParams p;
-  int cw;
-  HB_REQUIRE(gemm_geometry(a, Npad, Kpad, ep, p, cw), HATB200_EUNSUPPORTED, "gemm_tc: unsupported shape");
-  CUtensorMap tmA, tmB, tmR, tmU;
+  G3Params p;
+  bool grouped;
+  HB_REQUIRE(gemm_geometry(a, Npad, Kpad, ep, p, grouped), HATB200_EUNSUPPORTED, "gemm_tc: unsupported shape");
+  CUtensorMap tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN;
   {
     uint64_t dims[2] = {(uint64_t)a.a_pitch, (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)a.a_pitch * 2};
-    uint32_t box[2] = {GM_BK, GM_TILE_M};
-    HB_TRY(tc::make_tmap_bf16(&tmA, a.A, 2, dims, str, box, GM_BK * 2));
+    uint32_t box[2] = {G3_BK, G3_TILE_M};
+    HB_TRY(tc::make_tmap_bf16(&tmA, a.A, 2, dims, str, box, G3_BK * 2));
   }
   {
     uint64_t dims[2] = {(uint64_t)Kpad, (uint64_t)Npad};
     uint64_t str[1] = {(uint64_t)Kpad * 2};
-    uint32_t box[2] = {GM_BK, (uint32_t)p.BN};
-    HB_TRY(tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, GM_BK * 2));
+    uint32_t box[2] = {G3_BK, (uint32_t)p.BN};
+    HB_TRY(tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, G3_BK * 2));
   }
-  tmR = tmA; tmU = tmA;     // placeholders when the operand is absent (never dereferenced)
-  if (p.op_resid) {
-    uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};            // columns >= N read as zero
+  tmR = tmA; tmU = tmA; tmOF = tmA; tmOT = tmA; tmLN = tmA;     // placeholders for absent operands (never dereferenced)
+  const uint32_t w32 = grouped ? 32 : 16, w16 = grouped ? 64 : 16;   // store box widths (columns)
+  if (p.has_resid) {     // columns >= N read as zero
+    uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)ep.resid_pitch * 4};
-    uint32_t box[2] = {(uint32_t)cw, GM_TILE_M};
-    HB_TRY(tc::make_tmap_f32(&tmR, ep.resid, 2, dims, str, box, cw * 4));
+    uint32_t box[2] = {(uint32_t)CW, G3_TILE_M};
+    HB_TRY(tc::make_tmap_f32(&tmR, ep.resid, 2, dims, str, box, CW * 4));
   }
-  if (p.op_u) {
-    uint64_t dims[2] = {(uint64_t)ep.eca_pitch, (uint64_t)p.M};
+  if (p.has_u) {         // columns >= N read as zero (U's own pad columns are never touched)
+    uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)ep.eca_pitch * 2};
-    uint32_t box[2] = {(uint32_t)cw, GM_TILE_M};
-    HB_TRY(tc::make_tmap_bf16(&tmU, ep.eca_u, 2, dims, str, box, cw * 2));
+    uint32_t box[2] = {(uint32_t)CW, G3_TILE_M};
+    HB_TRY(tc::make_tmap_bf16(&tmU, ep.eca_u, 2, dims, str, box, CW * 2));
+  }
+  if (ep.out_f32) {      // stores clip at N
+    uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)ep.out_f32_pitch * 4};
+    uint32_t box[2] = {w32, 32};
+    HB_TRY(tc::make_tmap_f32(&tmOF, ep.out_f32, 2, dims, str, box, w32 * 4));
+  }
+  if (ep.out_t) {        // stores clip at max(N, zero_to): the pad columns in between receive computed zeros
+    const int width = ep.out_t_zero_to > p.N ? ep.out_t_zero_to : p.N;
+    uint64_t dims[2] = {(uint64_t)width, (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)ep.out_t_pitch * 2};
+    uint32_t box[2] = {w16, 32};
+    HB_TRY(tc::make_tmap_bf16(&tmOT, (const bf16*)ep.out_t + ep.out_t_coff, 2, dims, str, box, w16 * 2));
+  }
+  if (ep.ln_out) {       // LayerNorm output: pad columns up to ln_pitch are written as zero
+    uint64_t dims[2] = {(uint64_t)ep.ln_pitch, (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)ep.ln_pitch * 2};
+    uint32_t box[2] = {w16, 32};
+    HB_TRY(tc::make_tmap_bf16(&tmLN, ep.ln_out, 2, dims, str, box, w16 * 2));
   }
   p.trace = nullptr;
-  { const char* d = getenv("HATB200_GEMM_DBG"); p.dbg = d ? atoi(d) : 0; }
   if (getenv("HATB200_GEMM_TRACE")) {
-    if (!g_gemm_trace) {
-      HB_CHECK_CUDA(cudaMalloc(&g_gemm_trace, 1024 * 64 * 8));
-    }
+    if (!g_gemm_trace) HB_CHECK_CUDA(cudaMalloc(&g_gemm_trace, 1024 * 64 * 8));
     HB_CHECK_CUDA(cudaMemsetAsync(g_gemm_trace, 0, 1024 * 64 * 8, st));
     p.trace = g_gemm_trace;
   }
-  const size_t smem = (size_t)round_up(p.b_bytes, 1024) + (size_t)p.stages * GM_TILE_M * GM_BK * 2 +
-                      4 * (size_t)p.op_stage_bytes + 1024;
+  const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_DYN_SMEM));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_DYN_SMEM));
+    const int lim = G3_SMEM_LIMIT + 1024;
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
@@ -341,8 +742,11 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   if (per_n < 1) per_n = 1;
   if (per_n > p.m_tiles) per_n = p.m_tiles;
   dim3 grid(per_n, n_tiles);
-  if (cw == 32) gemm_tc_kernel<32><<<grid, GM_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, p, ep);
-  else gemm_tc_kernel<16><<<grid, GM_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, p, ep);
+  const bool ring = p.has_resid || p.has_u;
+#define G3_LAUNCH(R_, G_) gemm_tc_kernel<R_, G_><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep)
+  if (ring) { if (grouped) G3_LAUNCH(true, true); else G3_LAUNCH(true, false); }
+  else { if (grouped) G3_LAUNCH(false, true); else G3_LAUNCH(false, false); }
+#undef G3_LAUNCH
   HB_CHECK_LAUNCH();
   return 0;
 }

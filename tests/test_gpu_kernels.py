@@ -204,3 +204,79 @@ def test_tile_helpers_bit_exact():
     want = torch.zeros_like(big)
     want[:, :, 11:31, 13:43] = dst[:, :, 5:25, 7:37]
     assert torch.equal(big, want)
+
+
+# ---- persistent tcgen05 GEMM with the fused epilogue (csrc/tc_gemm.cu) ------------------------------------
+def _linear_fused_case(B, H, W, Cin, N, resid, eca, ln, head, out_t, act=0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    M = B * H * W
+    pitch = -(-Cin // 64) * 64
+    a = torch.zeros(M, pitch, dtype=torch.bfloat16)
+    a[:, :Cin] = torch.randn(M, Cin, generator=g).bfloat16()
+    w = (torch.randn(N, Cin, generator=g) * 0.08)
+    bias = torch.randn(N, generator=g) * 0.3
+    npitch = -(-N // 64) * 64
+    r = torch.randn(M, N, generator=g) if resid else None
+    u = torch.full((M, npitch), float("nan"), dtype=torch.bfloat16)       # pad columns must never be read as values
+    u[:, :N] = torch.randn(M, N, generator=g).bfloat16()
+    sc = torch.rand(B, N, generator=g)
+    gamma = 1.0 + 0.2 * torch.randn(N, generator=g)
+    beta = 0.1 * torch.randn(N, generator=g)
+    # reference (fp32 math on the bf16-rounded operands)
+    v = a[:, :Cin].float() @ w.bfloat16().float().t() + bias
+    if act == 1:
+        v = F.gelu(v)
+    if eca:
+        v = v + 0.01 * sc.repeat_interleave(H * W, 0) * u[:, :N].float()
+    if resid:
+        v = v + r
+    ln_ref = F.layer_norm(v, (N,), gamma, beta, 1e-5)
+    d = lambda t: None if t is None else t.to(DEV)
+    a_d, w_d, b_d, r_d, u_d, sc_d, g_d, be_d = map(d, (a, w, bias, r, u, sc, gamma, beta))
+    out_f32 = torch.full((M, N), float("nan"), device=DEV) if resid else None
+    ot = torch.full((M, npitch), float("nan"), dtype=torch.bfloat16, device=DEV) if out_t else None
+    lo = torch.full((M, npitch), float("nan"), dtype=torch.bfloat16, device=DEV) if ln else None
+    hd = torch.full((M, 16), float("nan"), dtype=torch.bfloat16, device=DEV) if head else None
+    cs = torch.full((M // 128, 16), float("nan"), device=DEV) if head else None
+    p = lambda t: None if t is None else _p(t)
+    n16 = -(-N // 16) * 16
+    nt = -(-n16 // 256)
+    npad = nt * (-(-(-(-n16 // nt)) // 16) * 16)                           # kernels.cuh tc_npad()
+    zero_to = npitch if (out_t and npitch <= npad) else 0
+    _lib.check(_lib.lib().hatb200_linear_fused(
+        p(a_d), pitch, Cin, B, H, W, p(w_d), p(b_d), N, act, p(r_d), p(u_d) if eca else None, npitch,
+        p(sc_d) if eca else None, 0.01, p(out_f32), p(ot), npitch, zero_to, p(g_d), p(be_d), p(lo), npitch,
+        p(hd), p(cs), _stream()))
+    torch.cuda.synchronize()
+    scale = max(1.0, v.abs().max().item())
+    if out_f32 is not None:
+        assert (out_f32.cpu() - v).abs().max().item() <= 2e-4 * scale
+    if ot is not None:
+        got = ot.float().cpu()
+        assert (got[:, :N] - v).abs().max().item() <= 2.0 ** -7 * scale
+        if zero_to:
+            assert torch.equal(got[:, N:zero_to], torch.zeros(M, zero_to - N))   # K padding of the consumer
+    if lo is not None:
+        got = lo.float().cpu()
+        assert (got[:, :N] - ln_ref).abs().max().item() <= 2.0 ** -6 * max(1.0, ln_ref.abs().max().item())
+        assert torch.equal(got[:, N:], torch.zeros(M, npitch - N))
+        if hd is not None:
+            assert torch.equal(hd.cpu(), lo[:, :16].cpu())
+            want = lo[:, :16].float().view(M // 128, 128, 16).sum(1).cpu()
+            assert (cs.cpu() - want).abs().max().item() <= 1e-3 * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [
+    # B, H, W, Cin, N, resid, eca, ln, head, out_t, act
+    (2, 16, 16, 180, 720, False, False, False, False, True, 0),     # ffn fc1: 3 n-tiles of 240, output only
+    (2, 16, 16, 192, 576, False, False, False, False, True, 0),     # head-padded qkv: 32-column chunks
+    (2, 32, 16, 180, 360, False, False, False, False, True, 1),     # OCAB mlp.0 + GELU, zero-padded to 384
+    (3, 16, 16, 180, 180, True, True, True, False, False, 0),       # ESC aggr + HAB combine + norm2
+    (2, 16, 32, 360, 180, True, False, True, True, False, 0),       # ffn fc2 + residual + next norm1 + head
+    (1, 16, 16, 360, 180, True, False, False, False, True, 0),      # OCAB mlp.2 + residual + bf16 copy
+    (2, 16, 16, 48, 48, True, True, True, True, False, 0),          # mini model width
+    (5, 32, 32, 144, 144, True, False, True, True, False, 0),       # HAT-S width, many tiles per CTA
+])
+def test_linear_fused_tcgen05(shape):
+    _linear_fused_case(*shape)

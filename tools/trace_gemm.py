@@ -1,22 +1,44 @@
-"""Per-CTA timeline of one persistent GEMM launch (engineering aid, HATB200_GEMM_TRACE=1)."""
+"""Per-CTA timeline of one persistent GEMM launch (engineering aid, HATB200_GEMM_TRACE=1).
+    python tools/trace_gemm.py Cin N [plain|resid|aggr]
+Slots (us since the first event): 0/1 MMA warp start / weights resident; 8+2i / 9+2i MMA of local tile i issued /
+committed; 24+16g+4k+{0,1,3,2}: epilogue warpgroup g, its k-th tile: waiting, accumulator ready, pass 1 done, tile done.
+"""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["HATB200_GEMM_TRACE"] = "1"
 import numpy as np, torch
 from super_resolution_b200 import _lib
-from tests.test_gpu_kernels import _p, _stream  # noqa
 lib = C.CDLL(_lib.LIB_PATH)
 L = _lib.lib()
-M_B, H, W = 16, 64, 64
+p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+B, H, W = 16, 64, 64
 Cin, N = int(sys.argv[1]) if len(sys.argv) > 1 else 180, int(sys.argv[2]) if len(sys.argv) > 2 else 720
+mode = sys.argv[3] if len(sys.argv) > 3 else "plain"
+M = B * H * W
 pitch = ((Cin + 63) // 64) * 64
-x = torch.zeros(M_B * H * W, pitch, dtype=torch.bfloat16, device="cuda"); x[:, :Cin] = torch.randn(M_B * H * W, Cin, device="cuda").bfloat16()
-w = torch.randn(N, Cin, 1, 1, device="cuda") * 0.05
+x = torch.zeros(M, pitch, dtype=torch.bfloat16, device="cuda"); x[:, :Cin] = torch.randn(M, Cin, device="cuda").bfloat16()
+w = torch.randn(N, Cin, device="cuda") * 0.05
 b = torch.randn(N, device="cuda")
 opitch = ((N + 63) // 64) * 64
-out = torch.zeros(M_B * H * W, opitch, dtype=torch.bfloat16, device="cuda")
+st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+if mode == "plain":
+    out = torch.zeros(M, opitch, dtype=torch.bfloat16, device="cuda")
+    run = lambda: _lib.check(L.hatb200_linear_fused(p(x), pitch, Cin, B, H, W, p(w), p(b), N, 0, None, None, 0, None, 0.0,
+                                                    None, p(out), opitch, 0, None, None, None, 0, None, None, st))
+else:
+    r = torch.randn(M, N, device="cuda"); o32 = torch.empty(M, N, device="cuda")
+    u = torch.randn(M, opitch, device="cuda").bfloat16(); sc = torch.rand(B, N, device="cuda")
+    g = torch.ones(N, device="cuda"); be = torch.zeros(N, device="cuda")
+    lo = torch.empty(M, opitch, dtype=torch.bfloat16, device="cuda")
+    hd = torch.empty(M, 16, dtype=torch.bfloat16, device="cuda"); cs = torch.empty(M // 128, 16, device="cuda")
+    eca = mode == "aggr"
+    run = lambda: _lib.check(L.hatb200_linear_fused(p(x), pitch, Cin, B, H, W, p(w), p(b), N, 0, p(r), p(u) if eca else None,
+                                                    opitch, p(sc) if eca else None, 0.01, p(o32), None, 0, 0, p(g), p(be),
+                                                    p(lo), opitch, p(hd), p(cs), st))
 for _ in range(3):
-    _lib.check(L.hatb200_conv_tokens(_p(x), _lib.BF16, pitch, 0, Cin, M_B, H, W, _p(w), _p(b), N, 1, 1, 0, _p(out), opitch, 1, _stream()))
+    flush.zero_()
+    run()
 torch.cuda.synchronize()
 buf = np.zeros((1024, 64), dtype=np.uint64)
 lib.hatb200_debug_gemm_trace.argtypes = [C.c_void_p, C.c_void_p]
@@ -24,8 +46,8 @@ rc = lib.hatb200_debug_gemm_trace(buf.ctypes.data, None)
 t = buf.astype(np.int64)
 live = t[:, 0] > 0
 t0 = t[live, 0].min()
-print("ctas", live.sum())
+print(mode, Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
-    r = t[cta]
-    ev = {k: int(r[k] - t0) for k in range(64) if r[k] > 0}
+    r_ = t[cta]
+    ev = {k: int(r_[k] - t0) for k in range(64) if r_[k] > 0}
     print("cta", cta, {k: round(v / 1000, 2) for k, v in sorted(ev.items())})
