@@ -152,6 +152,16 @@ int hatb200_linear_fused(const void* a, int a_pitch, int Cin, int B, int H, int 
                          int out_t_zero_to, const float* gamma, const float* beta, void* ln_out, int ln_pitch,
                          void* ln_head, float* head_colsum, void* stream);
 
+/* Dense conv (ksize 1 or 3, zero pad) with the fused epilogue of the persistent tcgen05 kernels (bf16 only;
+ * csrc/tc_gemm.cu, csrc/tc_conv3.cu):  v = act(conv(a, w) + bias) + resid  (hat_arch.py:84-86,:544,:556,:854).
+ * w: fp32 (N, Cin, ksize, ksize).  Optional outputs as in hatb200_linear_fused, plus colsum fp32
+ * (B * H * W / 128, N): column sums of v over each 128-pixel tile (global-average-pool partials, hat_arch.py:73;
+ * tiles are 8 x 16 pixels, numbered row-major inside a sample). */
+int hatb200_conv_fused(const void* a, int a_pitch, int Cin, int B, int H, int W, const float* w,
+                       const float* bias, int N, int ksize, int act, const float* resid, float* out_f32,
+                       void* out_t, int out_t_pitch, int out_t_zero_to, const float* gamma, const float* beta,
+                       void* ln_out, int ln_pitch, void* ln_head, float* head_colsum, float* colsum, void* stream);
+
 /* OCAB attention core (hat_arch.py:354-388): qkv (M, pitch) holding q (already
  * scaled) at channel 0, k at C, v at 2C; bias_table (heads, (ws+ows-1)^2)
  * compact relative-position table indexed by (ky-qy+ws-1, kx-qx+ws-1);

@@ -127,6 +127,36 @@ int hatb200_linear_fused(const void* a, int a_pitch, int Cin, int B, int H, int 
   return r;
 }
 
+int hatb200_conv_fused(const void* a, int a_pitch, int Cin, int B, int H, int W, const float* w, const float* bias, int N,
+                       int ksize, int act, const float* resid, float* out_f32, void* out_t, int out_t_pitch,
+                       int out_t_zero_to, const float* gamma, const float* beta, void* ln_out, int ln_pitch,
+                       void* ln_head, float* head_colsum, float* colsum, void* stream) {
+  HB_REQUIRE(a && w && N >= 1 && Cin >= 1 && (ksize == 1 || ksize == 3), HATB200_EINVAL, "conv_fused: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  TmpPool pool;
+  ConvArgs ca{a, a_pitch, 0, Cin, B, H, W, ksize, ksize, N};
+  Epilogue ep;
+  ep.bias = bias; ep.act = act;
+  ep.resid = resid; ep.resid_pitch = N;
+  ep.out_f32 = out_f32; ep.out_f32_pitch = N;
+  ep.out_t = out_t; ep.out_t_pitch = out_t_pitch; ep.out_t_zero_to = out_t_zero_to;
+  ep.colsum = colsum;
+  if (ln_out) {
+    ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = ln_out; ep.ln_pitch = ln_pitch;
+    if (ln_head) { ep.ln_head = ln_head; ep.ln_head_c = 16; ep.ln_head_colsum = head_colsum; }
+  }
+  const int taps = ksize * ksize, Npad = tc_npad(N), Kpad = round_up(Cin, 64);
+  bf16* w16;
+  HB_TRY(pool.alloc((void**)&w16, (size_t)taps * Npad * Kpad * sizeof(bf16), st));
+  HB_TRY(launch_pack_w_bf16(w, HATB200_F32, N, Cin, taps, w16, Npad, Kpad, 0, Cin, st));
+  const bool ok = ksize == 1 ? gemm_tc_supported(ca, Npad, Kpad, ep) : conv3_tc_supported(ca, Npad, Kpad, ep);
+  HB_REQUIRE(ok, HATB200_EUNSUPPORTED, "conv_fused: shape / epilogue not supported by the persistent tcgen05 kernels");
+  int r = ksize == 1 ? launch_gemm_tc(ca, w16, Npad, Kpad, ep, st) : launch_conv3_tc(ca, w16, Npad, Kpad, ep, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (r == 0 && e != cudaSuccess) { set_error("conv_fused: %s", cudaGetErrorString(e)); return HATB200_ECUDA; }
+  return r;
+}
+
 int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, int W, int C, int heads, int ws,
                            int ows, const float* bias_table, void* out, int out_pitch, int use_tc, void* stream) {
   HB_REQUIRE(qkv && bias_table && out, HATB200_EINVAL, "ocab_attention: null tensor");

@@ -72,12 +72,17 @@ bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
 // persistent weight-stationary tcgen05 GEMM for 1x1 layers (tc_gemm.cu); same packed weights and epilogue
 int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
 bool gemm_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
-// picks the tcgen05 kernel for the shape (1x1 -> tc_gemm, else tc_tapconv)
+// persistent halo-resident tcgen05 3x3 conv (tc_conv3.cu); same packed weights and epilogue semantics
+int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
+bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
+// picks the tcgen05 kernel for the shape (1x1 -> tc_gemm, 3x3 -> tc_conv3, else / fallback tc_tapconv)
 inline bool conv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
-  return gemm_tc_supported(a, Npad, Kpad, ep) || tapconv_tc_supported(a, Npad, Kpad, ep);
+  return gemm_tc_supported(a, Npad, Kpad, ep) || conv3_tc_supported(a, Npad, Kpad, ep) ||
+         tapconv_tc_supported(a, Npad, Kpad, ep);
 }
 inline int launch_conv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
   if (gemm_tc_supported(a, Npad, Kpad, ep)) return launch_gemm_tc(a, w, Npad, Kpad, ep, st);
+  if (conv3_tc_supported(a, Npad, Kpad, ep)) return launch_conv3_tc(a, w, Npad, Kpad, ep, st);
   return launch_tapconv_tc(a, w, Npad, Kpad, ep, st);
 }
 

@@ -1,0 +1,386 @@
+// tc_conv3.cu -- dense 3x3 conv (stride 1, zero pad 1) over channels-last tokens as a PERSISTENT, halo-resident
+// tcgen05 implicit GEMM with the warp-independent TMA epilogue of tc_epilogue3.cuh.
+//
+//   out[pix, n] = sum_{ky,kx} sum_k A[pix + (ky-1, kx-1), k] * W[ky*3+kx][n][k]      (bf16 x bf16 -> fp32 in TMEM)
+//
+// Why (B200 measurements of the one-tile-per-CTA kernel tc_tapconv.cu, profiles/r01_*): CAB conv1 / conv2 ran at
+// 91 / 60 us per launch with the tensor pipe 2-3 % busy.  Every (tap, 64-channel block) re-fetched its 16 KB
+// activation box from L2 (9x the tile), a CTA lived for ONE tile (barrier / TMEM set-up and an un-overlapped
+// epilogue per tile, 1-2 CTAs per SM), and the epilogue stored one 16-byte granule per thread and line.  Here:
+//   * one CTA per SM walks 8 (x) x 16 (y) pixel tiles.  The (8+2) x (16+2) halo of a tile is TMA-loaded ONCE per
+//     64-channel block ({64 ch, 10 x, 18 y} box, out-of-bounds zero fill = the conv padding) and all nine taps
+//     address it IN PLACE: the A descriptor of tap (ky, kx) starts at halo row ky*10 + kx and its 8-row groups
+//     (8 consecutive x of one image row) are one halo row (1280 B) apart -- tcgen05 swizzles on absolute address
+//     bits, so the unaligned start is legal (measured with tc_probe.cu, used by tc_plk.cu);
+//   * only the weight slices (BN x 64 per tap and block) stream through a TMA ring; halos are double buffered when
+//     shared memory allows, so the next tile's halo lands while this tile's 9 x kblocks x 4 MMAs run;
+//   * two TMEM accumulator stages; the two epilogue warpgroups take alternate tiles and run the shared epilogue
+//     (bias, GELU / LeakyReLU, fp32 residual through a TMA ring, fp32 / bf16 TMA stores as 4-D boxes
+//     {cols, 8 x, 4 y}, pool partials, row-local LayerNorm + 16-channel head).
+// Warp roles (384 threads): 0 TMA producer (halos, weights), 1 MMA issuer + TMEM owner, 2-5 / 6-9 epilogue
+// warpgroups, 10 / 11 operand-ring producers.
+// Replaces F.conv2d at hat_arch.py:84-86 (CAB), :544 (RHAG conv), :854 (conv_after_body), :855 (conv_before_upsample).
+#include <stdlib.h>
+
+#include "tc_epilogue3.cuh"
+
+namespace hb {
+
+using namespace tc;
+using namespace epi3;
+
+namespace {
+
+constexpr int C3_THREADS = 384;
+constexpr int C3_TW = 8, C3_TH = 16;                   // tile: 128 pixels = UMMA M
+constexpr int C3_HW = C3_TW + 2, C3_HH = C3_TH + 2;    // halo
+constexpr int C3_HROW = C3_HW * 128;                   // bytes between two halo image rows of one 64-channel block
+constexpr int C3_HALO_KB = ((C3_HH * C3_HW * 128 + 1023) / 1024) * 1024;   // 23552: one 64-channel block of a halo
+constexpr int C3_MAX_HST = 2, C3_MAX_WST = 8;
+constexpr int C3_SMEM_LIMIT = 227 * 1024 - 2048;
+
+struct C3Params {
+  int B, H, W, hw, tiles_x, tiles_y, tiles;
+  int a_coff, kblocks;
+  int N, BN, Npad;
+  int hst, halo_stage_bytes;     // halo stages, kblocks * C3_HALO_KB
+  int wst, w_stage_bytes;        // weight ring, BN * 128
+  int ops, op_stage_bytes, op_u_off, has_resid, has_u;
+  uint32_t acc_stride, tmem_cols;
+  int off_halo, off_w, off_op, off_stg32, off_stg16, off_tab, off_sred, smem_bytes;
+  int stg_bufs, share_stg;
+};
+
+__device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
+  const int tx = t % p.tiles_x, ty = (t / p.tiles_x) % p.tiles_y;
+  b = t / (p.tiles_x * p.tiles_y);
+  x0 = tx * C3_TW; y0 = ty * C3_TH;
+}
+
+}  // namespace
+
+template <bool RING, bool GROUPED>
+__global__ void __launch_bounds__(C3_THREADS, 1)
+conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmOF,
+                const __grid_constant__ CUtensorMap tmOT, const __grid_constant__ CUtensorMap tmLN, const C3Params p,
+                const Epilogue ep) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t halo_full[C3_MAX_HST];
+  __shared__ __align__(8) uint64_t halo_empty[C3_MAX_HST];
+  __shared__ __align__(8) uint64_t w_full[C3_MAX_WST];
+  __shared__ __align__(8) uint64_t w_empty[C3_MAX_WST];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ __align__(8) uint64_t op_full[2][MAX_OPS];
+  __shared__ __align__(8) uint64_t op_empty[2][MAX_OPS];
+  __shared__ uint32_t tmem_slot;
+  __shared__ float hsum[8][16];
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.y * p.BN;
+  float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);
+  float* tab_gamma = tab_bias + p.BN;
+  float* tab_beta = tab_gamma + p.BN;
+  float* tab_coef = tab_beta + p.BN;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < p.hst; s++) { mbar_init(&halo_full[s], 1); mbar_init(&halo_empty[s], 1); }
+    for (int s = 0; s < p.wst; s++) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+    for (int g = 0; g < 2; g++) {
+      mbar_init(&tmem_full_bar[g], 1);
+      mbar_init(&tmem_empty_bar[g], 128);
+      for (int s = 0; s < MAX_OPS; s++) { mbar_init(&op_full[g][s], 1); mbar_init(&op_empty[g][s], 4); }
+    }
+    fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < p.BN; i += C3_THREADS) {
+    const int n = n0 + i;
+    const bool ok = n < p.N;
+    tab_bias[i] = (ok && ep.bias) ? __ldg(ep.bias + n) : 0.f;
+    tab_gamma[i] = (ok && ep.ln_gamma) ? __ldg(ep.ln_gamma + n) : 0.f;
+    tab_beta[i] = (ok && ep.ln_beta) ? __ldg(ep.ln_beta + n) : 0.f;
+  }
+  if (warp == 1) tmem_alloc(&tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: one halo per tile (kblocks boxes), 9 * kblocks weight slices per tile =====
+    if (lane == 0) {
+      int i = 0, wit = 0;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+        int x0, y0, b;
+        tile_coords(p, t, x0, y0, b);
+        const int hs = i % p.hst;
+        mbar_wait(&halo_empty[hs], (((uint32_t)(i / p.hst)) & 1u) ^ 1u);
+        uint8_t* hb_ = smem + p.off_halo + (size_t)hs * p.halo_stage_bytes;
+        mbar_arrive_expect_tx(&halo_full[hs], (uint32_t)(p.kblocks * C3_HH * C3_HW * 128));
+        for (int kb = 0; kb < p.kblocks; kb++)
+          tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
+        for (int tap = 0; tap < 9; tap++) {
+          for (int kb = 0; kb < p.kblocks; kb++, wit++) {
+            const int s = wit % p.wst;
+            mbar_wait(&w_empty[s], (((uint32_t)(wit / p.wst)) & 1u) ^ 1u);
+            mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+            tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.BN);
+      int i = 0, wit = 0;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+        const int g = i & 1;
+        mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
+        const int hs = i % p.hst;
+        mbar_wait(&halo_full[hs], ((uint32_t)(i / p.hst)) & 1u);
+        tc_fence_after();
+        const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
+        const uint32_t h_addr = smem_u32(smem + p.off_halo + (size_t)hs * p.halo_stage_bytes);
+        int it = 0;
+        for (int tap = 0; tap < 9; tap++) {
+          const int ky = tap / 3, kx = tap - ky * 3;
+          for (int kb = 0; kb < p.kblocks; kb++, wit++, it++) {
+            const int s = wit % p.wst;
+            mbar_wait(&w_full[s], ((uint32_t)(wit / p.wst)) & 1u);
+            tc_fence_after();
+            const uint32_t sa = h_addr + (uint32_t)(kb * C3_HALO_KB + (ky * C3_HW + kx) * 128);
+            const uint32_t sb = smem_u32(smem + p.off_w + (size_t)s * p.w_stage_bytes);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              // A: accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx; 8-row groups are one halo image row apart
+              uint64_t ad = make_smem_desc(sa + k * 32, 128);
+              ad &= ~(0x3FFFull << 32);
+              ad |= (uint64_t)(C3_HROW >> 4) << 32;
+              const uint64_t bd = make_smem_desc(sb + k * 32, 128);
+              umma_bf16(acc, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(&w_empty[s]);         // frees the weight slot once these MMAs have read it
+          }
+        }
+        umma_commit(&halo_empty[hs]);         // halo may be overwritten
+        umma_commit(&tmem_full_bar[g]);       // accumulator of tile i complete
+      }
+    }
+  } else if (warp >= 10) {
+    // ===== operand-ring producer of warpgroup g (fp32 residual chunks) =====
+    const int g = warp - 10;
+    if (RING && lane == 0) {
+      prefetch_tmap(&tmR);
+      uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
+      uint32_t k = 0;
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+        if ((i & 1) != g) continue;
+        Tile4D ts;
+        tile_coords(p, t, ts.x0, ts.y0, ts.b);
+        produce_tile(ts, &tmR, &tmR, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid, 0,
+                     n0, p.BN / CW, k);
+      }
+    }
+  } else {
+    // ===== epilogue warps =====
+    const int g = (warp - 2) >> 2;
+    WarpState<GROUPED> ws;
+    ws.g = g; ws.ew = warp - 2; ws.quarter = warp & 3; ws.lane = lane;
+    ws.row = ws.quarter * 32 + lane;
+    ws.wg_tid = ((warp - 2) & 3) * 32 + lane;
+    ws.BN = p.BN; ws.N = p.N; ws.n0 = n0; ws.nch = p.BN / CW; ws.H = p.H; ws.W = p.W; ws.hw = p.hw;
+    ws.last_ntile = blockIdx.y == gridDim.y - 1;
+    ws.tab_bias = tab_bias; ws.tab_gamma = tab_gamma; ws.tab_beta = tab_beta; ws.coef = tab_coef + g * p.BN;
+    ws.ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
+    ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
+    ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
+    ws.has_resid = p.has_resid; ws.has_u = 0; ws.share_stg = p.share_stg;
+    ws.hsum = hsum;
+    ws.sred = reinterpret_cast<float (*)[256]>(smem + p.off_sred + (size_t)g * 4096);
+    ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
+    ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
+    ws.st16.base = smem + p.off_stg16 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st16)::BUF);
+    if (lane == 0) {
+      if (ep.out_f32) prefetch_tmap(&tmOF);
+      if (ep.out_t) prefetch_tmap(&tmOT);
+      if (ep.ln_out) prefetch_tmap(&tmLN);
+    }
+    int i = 0;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+      if ((i & 1) != g) continue;
+      Tile4D ts;
+      tile_coords(p, t, ts.x0, ts.y0, ts.b);
+      RowInfo ri;
+      ri.b = ts.b;
+      ri.py = ts.y0 + ws.row / C3_TW; ri.px = ts.x0 + ws.row % C3_TW;
+      ri.m = (ts.b * p.H + ri.py) * p.W + ri.px;
+      ri.nchunk = p.tiles_x * p.tiles_y;
+      ri.chunk = t - ts.b * ri.nchunk;
+      ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
+      mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
+      tc_fence_after();
+      run_tile<RING, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[g]);
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// ---- host ------------------------------------------------------------------------------------------
+static int c3_sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep, C3Params& p, bool& grouped) {
+  if (a.KH != 3 || a.KW != 3) return false;
+  if (a.W % C3_TW || a.H % C3_TH) return false;
+  if (Kpad % 64 || Kpad < a.Cin) return false;
+  if ((a.a_pitch * 2) % 16 || (a.a_coff * 2) % 16) return false;
+  p.BN = tc_bn(a.N);
+  if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
+  if (ep.dyn_k || ep.shuffle_r != 1 || ep.eca_u || ep.scale_ncols) return false;      // tc_tapconv.cu keeps those layers
+  if (ep.out_f32 && ((ep.out_f32_pitch * 4) % 16 || ((uintptr_t)ep.out_f32 & 15))) return false;
+  if (ep.out_t && ((ep.out_t_pitch * 2) % 16 || (ep.out_t_coff * 2) % 16 || ((uintptr_t)ep.out_t & 15))) return false;
+  if (ep.out_t && ep.out_t_pitch - ep.out_t_coff < (ep.out_t_zero_to > a.N ? ep.out_t_zero_to : a.N)) return false;
+  if (ep.ln_out && ((ep.ln_pitch * 2) % 16 || ((uintptr_t)ep.ln_out & 15) || ep.ln_pitch < a.N)) return false;
+  if (ep.resid && ((ep.resid_pitch * 4) % 16 || ((uintptr_t)ep.resid & 15))) return false;
+  if (ep.ln_out && Npad != p.BN) return false;
+  if (ep.ln_head && (ep.ln_head_c > 16 || !ep.ln_out)) return false;
+  if (ep.colsum && p.BN > 256) return false;
+  p.B = a.B; p.H = a.H; p.W = a.W; p.hw = a.H * a.W;
+  p.tiles_x = a.W / C3_TW; p.tiles_y = a.H / C3_TH; p.tiles = a.B * p.tiles_x * p.tiles_y;
+  p.a_coff = a.a_coff; p.kblocks = Kpad / 64;
+  p.N = a.N; p.Npad = Npad;
+  p.acc_stride = (uint32_t)round_up(p.BN, 32);
+  uint32_t cols = 32;
+  while (cols < 2 * p.acc_stride) cols <<= 1;
+  if (cols > 512) return false;
+  p.tmem_cols = cols;
+  p.has_resid = ep.resid != nullptr; p.has_u = 0;
+  const bool ring = p.has_resid;
+  grouped = p.BN % 64 == 0;
+  const bool f32o = ep.out_f32 != nullptr, bf16o = ep.out_t != nullptr || ep.ln_out != nullptr;
+  p.share_stg = f32o && bf16o && ep.out_t == nullptr;
+  const int tab = round_up(5 * p.BN * 4, 1024);
+  const int sred = ep.colsum ? 2 * 4096 : 0;
+  p.op_u_off = 128 * CW * 4;
+  p.op_stage_bytes = ring ? 128 * CW * 4 : 0;
+  p.halo_stage_bytes = p.kblocks * C3_HALO_KB;
+  p.w_stage_bytes = p.BN * 128;
+  p.ops = ring ? 2 : 0;
+  // prefer double-buffered halos and double-buffered staging; give what is left to the weight ring (>= 3 slices)
+  for (int pass = 0; pass < 8; pass++) {
+    const int hst = (pass & 2) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2, want = pass < 4 ? 3 : 2;
+    const int stg32 = f32o ? 8 * bufs * 32 * (grouped ? 128 : 64) : 0;
+    const int stg16 = bf16o && !p.share_stg ? 8 * bufs * 32 * (grouped ? 128 : 32) : 0;
+    const int fixed = tab + sred + stg32 + stg16 + 2 * p.ops * p.op_stage_bytes + hst * p.halo_stage_bytes;
+    const int avail = C3_SMEM_LIMIT - fixed;
+    const int wst = avail > 0 ? avail / p.w_stage_bytes : 0;
+    if (wst < want) continue;
+    p.hst = hst; p.stg_bufs = bufs;
+    p.wst = wst > C3_MAX_WST ? C3_MAX_WST : wst;
+    if (ring) {                      // spend what is left on a deeper operand ring
+      int left = avail - p.wst * p.w_stage_bytes;
+      while (p.ops < MAX_OPS && left >= 2 * p.op_stage_bytes) { p.ops++; left -= 2 * p.op_stage_bytes; }
+    }
+    int off = 0;
+    p.off_halo = off; off += hst * p.halo_stage_bytes;
+    p.off_w = off; off += p.wst * p.w_stage_bytes;
+    p.off_op = off; off += 2 * p.ops * p.op_stage_bytes;
+    p.off_stg32 = off; off += stg32;
+    p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += stg16;
+    p.off_tab = off; off += tab;
+    p.off_sred = off; off += sred;
+    p.smem_bytes = off;
+    return off <= C3_SMEM_LIMIT;
+  }
+  return false;
+}
+
+bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
+  C3Params p;
+  bool grouped;
+  if (!conv3_geometry(a, Npad, Kpad, ep, p, grouped)) return false;
+  if (tc::encode_tiled_fn() == nullptr) return false;
+  const char* v = getenv("HATB200_CONV3");
+  if (v && *v == '0') return false;
+  return true;
+}
+
+int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
+  C3Params p;
+  bool grouped;
+  HB_REQUIRE(conv3_geometry(a, Npad, Kpad, ep, p, grouped), HATB200_EUNSUPPORTED, "conv3_tc: unsupported shape");
+  CUtensorMap tmA, tmB, tmR, tmOF, tmOT, tmLN;
+  {
+    uint64_t dims[4] = {(uint64_t)a.a_pitch, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
+    uint64_t str[3] = {(uint64_t)a.a_pitch * 2, (uint64_t)a.W * a.a_pitch * 2, (uint64_t)a.H * a.W * a.a_pitch * 2};
+    uint32_t box[4] = {64, C3_HW, C3_HH, 1};
+    HB_TRY(tc::make_tmap_bf16(&tmA, a.A, 4, dims, str, box, 128));
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)Kpad, (uint64_t)9 * Npad};
+    uint64_t str[1] = {(uint64_t)Kpad * 2};
+    uint32_t box[2] = {64, (uint32_t)p.BN};
+    HB_TRY(tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, 128));
+  }
+  tmR = tmA; tmOF = tmA; tmOT = tmA; tmLN = tmA;      // placeholders for absent operands (never dereferenced)
+  const uint32_t w32 = grouped ? 32 : 16, w16 = grouped ? 64 : 16;
+  auto map4 = [&](CUtensorMap* tm, bool f32, const void* base, int width, int pitch, uint32_t bw, uint32_t bx, uint32_t by) -> int {
+    const int es = f32 ? 4 : 2;
+    uint64_t dims[4] = {(uint64_t)width, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
+    uint64_t str[3] = {(uint64_t)pitch * es, (uint64_t)a.W * pitch * es, (uint64_t)a.H * a.W * pitch * es};
+    uint32_t box[4] = {bw, bx, by, 1};
+    return f32 ? tc::make_tmap_f32(tm, base, 4, dims, str, box, (int)bw * es) : tc::make_tmap_bf16(tm, base, 4, dims, str, box, (int)bw * es);
+  };
+  if (p.has_resid) HB_TRY(map4(&tmR, true, ep.resid, p.N, ep.resid_pitch, CW, C3_TW, C3_TH));
+  if (ep.out_f32) HB_TRY(map4(&tmOF, true, ep.out_f32, p.N, ep.out_f32_pitch, w32, C3_TW, 4));
+  if (ep.out_t) {
+    const int width = ep.out_t_zero_to > p.N ? ep.out_t_zero_to : p.N;
+    HB_TRY(map4(&tmOT, false, (const bf16*)ep.out_t + ep.out_t_coff, width, ep.out_t_pitch, w16, C3_TW, 4));
+  }
+  if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
+  const size_t smem = (size_t)p.smem_bytes + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    const int lim = C3_SMEM_LIMIT + 1024;
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+    attr_set = true;
+  }
+  const int n_tiles = Npad / p.BN;
+  int per_n = c3_sm_count() / n_tiles;
+  if (per_n < 1) per_n = 1;
+  if (per_n > p.tiles) per_n = p.tiles;
+  dim3 grid(per_n, n_tiles);
+#define C3_LAUNCH(R_, G_) conv3_tc_kernel<R_, G_><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep)
+  if (p.has_resid) { if (grouped) C3_LAUNCH(true, true); else C3_LAUNCH(true, false); }
+  else { if (grouped) C3_LAUNCH(false, true); else C3_LAUNCH(false, false); }
+#undef C3_LAUNCH
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace hb

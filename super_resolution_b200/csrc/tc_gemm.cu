@@ -28,12 +28,12 @@
 // Replaces F.linear / 1x1 F.conv2d at hat_arch.py:111,:117,:347-351,:391-392 and esc_arch.py:144.
 #include <stdlib.h>
 
-#include "kernels.cuh"
-#include "tc_common.cuh"
+#include "tc_epilogue3.cuh"
 
 namespace hb {
 
 using namespace tc;
+using namespace epi3;
 
 namespace {
 
@@ -46,10 +46,9 @@ __device__ __forceinline__ unsigned long long gtime_ns() {
 
 constexpr int G3_THREADS = 384;
 constexpr int G3_MAX_STAGES = 8;       // activation ring
-constexpr int G3_MAX_OPS = 4;          // operand ring stages per warpgroup
+constexpr int G3_MAX_OPS = MAX_OPS;    // operand ring stages per warpgroup
 constexpr int G3_TILE_M = 128;
 constexpr int G3_BK = 64;
-constexpr int CW = 16;                 // epilogue column chunk (one tcgen05.ld 32x32b.x16 per thread)
 constexpr int G3_SMEM_LIMIT = 227 * 1024 - 2048;   // static shared memory (barriers) stays below 2 KB
 
 struct G3Params {
@@ -67,144 +66,6 @@ struct G3Params {
   int stg_bufs;             // staging buffers per warp and element type (2, or 1 when both types stage in pass 1)
   int share_stg;            // fp32 and bf16 staging alias (pass 1 writes only fp32, pass 2 only bf16)
   unsigned long long* trace;
-};
-
-// ---- small PTX helpers -------------------------------------------------------------------------------
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m),
-               "r"(smem_u32(src)), "r"(c0), "r"(c1)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint4 lds128(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long pk(float a, float b) {
-  return (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
-}
-__device__ __forceinline__ void upk(unsigned long long v, float& a, float& b) {
-  a = __uint_as_float((uint32_t)v); b = __uint_as_float((uint32_t)(v >> 32));
-}
-__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0, float c1) {
-  unsigned long long r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)), "l"(pk(c0, c1)));
-  upk(r, d0, d1);
-}
-__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
-  unsigned long long r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)));
-  upk(r, d0, d1);
-}
-__device__ __forceinline__ void mul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
-  unsigned long long r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a0, a1)), "l"(pk(b0, b1)));
-  upk(r, d0, d1);
-}
-
-
-// swizzle of 16-byte granule index for a tile whose rows are RB bytes wide (TMA SWIZZLE_{32,64,128}B, tile base
-// aligned to the swizzle period)
-template <int RB>
-__device__ __forceinline__ int sw_gran(int row) {
-  return RB == 128 ? (row & 7) : (RB == 64 ? ((row >> 1) & 3) : ((row >> 2) & 1));
-}
-// this thread's row (CW fp32) of a swizzled tile
-__device__ __forceinline__ void row_read_f32(const uint8_t* tile, int row, float (&o)[CW]) {
-  constexpr int RB = CW * 4;
-  const int sw = sw_gran<RB>(row);
-  const uint32_t base = smem_u32(tile) + row * RB;
-#pragma unroll
-  for (int c = 0; c < RB / 16; c++) {
-    const uint4 t = lds128(base + ((c ^ sw) << 4));
-    o[4 * c] = __uint_as_float(t.x); o[4 * c + 1] = __uint_as_float(t.y);
-    o[4 * c + 2] = __uint_as_float(t.z); o[4 * c + 3] = __uint_as_float(t.w);
-  }
-}
-__device__ __forceinline__ void row_read_bf16(const uint8_t* tile, int row, float (&o)[CW]) {
-  constexpr int RB = CW * 2;
-  const int sw = sw_gran<RB>(row);
-  const uint32_t base = smem_u32(tile) + row * RB;
-#pragma unroll
-  for (int c = 0; c < RB / 16; c++) {
-    const uint4 t = lds128(base + ((c ^ sw) << 4));
-    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      o[8 * c + 2 * j] = __uint_as_float(w[j] << 16);
-      o[8 * c + 2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
-    }
-  }
-}
-// CW consecutive floats of a shared-memory table (same address for the whole warp: broadcast)
-__device__ __forceinline__ void tab_read(const float* tab, float (&o)[CW]) {
-#pragma unroll
-  for (int c = 0; c < CW / 4; c++) {
-    const uint4 t = lds128(smem_u32(tab) + 16 * c);
-    o[4 * c] = __uint_as_float(t.x); o[4 * c + 1] = __uint_as_float(t.y);
-    o[4 * c + 2] = __uint_as_float(t.z); o[4 * c + 3] = __uint_as_float(t.w);
-  }
-}
-
-// Per-warp output staging.  GW consecutive chunks (CW columns each, EB bytes per element) of the warp's 32 rows are
-// collected in one swizzled tile whose rows are RB = CW * EB * GW bytes (128 B when grouped) and leave with ONE TMA
-// store; two buffers alternate so that the store of group q overlaps the arithmetic of group q + 1.
-template <int EB, int GW>
-struct Stager {
-  static constexpr int RB = CW * EB * GW;
-  static constexpr int BUF = 32 * RB;
-  uint8_t* base;
-  uint32_t n = 0;                    // stores issued by this warp
-  int nbuf = 2;                      // 2: double buffered; 1: single buffer (shared memory is short)
-  __device__ __forceinline__ uint8_t* buf() const { return base + (nbuf == 2 ? (n & 1) : 0) * BUF; }
-  // before the first write of a group: the store that last read this buffer must be done reading it
-  __device__ __forceinline__ void begin(int lane) const {
-    if (lane == 0) { if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>(); }
-    __syncwarp();
-  }
-  __device__ __forceinline__ void put_f32(int lane, int slot, const float (&v)[CW]) const {
-    const uint32_t row = smem_u32(buf()) + lane * RB;
-    const int sw = sw_gran<RB>(lane);
-#pragma unroll
-    for (int c = 0; c < 4; c++)
-      sts128(row + (((slot * 4 + c) ^ sw) << 4), __float_as_uint(v[4 * c]), __float_as_uint(v[4 * c + 1]),
-             __float_as_uint(v[4 * c + 2]), __float_as_uint(v[4 * c + 3]));
-  }
-  __device__ __forceinline__ void put_bf16(int lane, int slot, const float (&v)[CW]) const {
-    const uint32_t row = smem_u32(buf()) + lane * RB;
-    const int sw = sw_gran<RB>(lane);
-#pragma unroll
-    for (int c = 0; c < 2; c++) {
-      uint4 t;
-      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
-#pragma unroll
-      for (int j = 0; j < 4; j++) h[j] = __floats2bfloat162_rn(v[8 * c + 2 * j], v[8 * c + 2 * j + 1]);
-      sts128(row + (((slot * 2 + c) ^ sw) << 4), t.x, t.y, t.z, t.w);
-    }
-  }
-  __device__ __forceinline__ void put_zero(int lane) const {
-    const uint32_t row = smem_u32(buf()) + lane * RB;
-#pragma unroll
-    for (int c = 0; c < RB / 16; c++) sts128(row + 16 * c, 0u, 0u, 0u, 0u);
-  }
-  // after the last write of a group: hand the tile to the async proxy; columns past the map's width are clipped
-  __device__ __forceinline__ void flush(const CUtensorMap* tm, int lane, int c0, int r0) {
-    fence_proxy_async();
-    __syncwarp();
-    if (lane == 0) {
-      tma_store_2d(tm, buf(), c0, r0);
-      bulk_commit();
-    }
-    n++;
-  }
 };
 
 }  // namespace
@@ -329,231 +190,57 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (RING && lane == 0) {
       if (p.has_resid) prefetch_tmap(&tmR);
       if (p.has_u) prefetch_tmap(&tmU);
-      const int nch = p.BN / CW;
-      const uint32_t bytes = (uint32_t)((p.has_resid ? G3_TILE_M * CW * 4 : 0) + (p.has_u ? G3_TILE_M * CW * 2 : 0));
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       uint32_t k = 0;
       int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
-        for (int ci = 0; ci < nch; ci++, k++) {
-          const int s = k % p.ops;
-          const uint32_t par = (k / p.ops) & 1u;
-          mbar_wait(&op_empty[g][s], par ^ 1u);
-          uint8_t* st = ring + (size_t)s * p.op_stage_bytes;
-          mbar_arrive_expect_tx(&op_full[g][s], bytes);
-          if (p.has_resid) tma_load_2d(st, &tmR, &op_full[g][s], n0 + ci * CW, t * G3_TILE_M);
-          if (p.has_u) tma_load_2d(st + p.op_u_off, &tmU, &op_full[g][s], n0 + ci * CW, t * G3_TILE_M);
-        }
+        const Tile2D ts{t * G3_TILE_M};
+        produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
+                     p.has_u, n0, p.BN / CW, k);
       }
     }
   } else {
     // ===== epilogue warps: warpgroup g = (warp - 2) / 4 takes local tiles i with (i & 1) == g =====
     const int g = (warp - 2) >> 2;
-    const int ew = warp - 2;                          // 0..7
-    const int quarter = warp & 3;                     // TMEM lane quarter this warp may access
-    const int row = quarter * 32 + lane;              // row of the tile owned by this thread
-    const int wg_tid = ((warp - 2) & 3) * 32 + lane;  // 0..127 inside the warpgroup
-    const int nch = p.BN / CW;
-    const bool do_ln = ep.ln_out != nullptr;
-    const uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
-    constexpr int GW32 = GROUPED ? 2 : 1, GW16 = GROUPED ? 4 : 1;      // chunks per store: 128-byte rows when grouped
-    Stager<4, GW32> st32;
-    Stager<2, GW16> st16;
-    st32.nbuf = st16.nbuf = p.stg_bufs;
-    st32.base = smem + p.off_stg32 + (size_t)ew * (p.stg_bufs * Stager<4, GW32>::BUF);
-    st16.base = smem + p.off_stg16 + (size_t)ew * (p.stg_bufs * Stager<2, GW16>::BUF);
-    float* coef = tab_coef + g * p.BN;
-    uint32_t k = 0;          // operand chunks consumed by this warpgroup
+    WarpState<GROUPED> ws;
+    ws.g = g; ws.ew = warp - 2; ws.quarter = warp & 3; ws.lane = lane;
+    ws.row = ws.quarter * 32 + lane;                     // row of the tile owned by this thread (TMEM lane)
+    ws.wg_tid = ((warp - 2) & 3) * 32 + lane;            // 0..127 inside the warpgroup
+    ws.BN = p.BN; ws.N = p.N; ws.n0 = n0; ws.nch = p.BN / CW; ws.H = p.H; ws.W = p.W; ws.hw = p.hw;
+    ws.last_ntile = blockIdx.y == gridDim.y - 1;
+    ws.tab_bias = tab_bias; ws.tab_gamma = tab_gamma; ws.tab_beta = tab_beta; ws.coef = tab_coef + g * p.BN;
+    ws.ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
+    ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
+    ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
+    ws.has_resid = p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
+    ws.hsum = hsum; ws.sred = nullptr;                   // no tile column sums in the 1x1 layers
+    ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
+    ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
+    ws.st16.base = smem + p.off_stg16 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st16)::BUF);
     if (lane == 0) {
       if (ep.out_f32) prefetch_tmap(&tmOF);
       if (ep.out_t) prefetch_tmap(&tmOT);
-      if (do_ln) prefetch_tmap(&tmLN);
+      if (ep.ln_out) prefetch_tmap(&tmLN);
     }
     int i = 0;
     for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
       if ((i & 1) != g) continue;
       const int m0 = t * G3_TILE_M;
-      const int m = m0 + row;
-      const int r0 = m0 + quarter * 32;               // first token row of this warp
-      const int b = m0 / p.hw;                        // a tile never straddles two samples (hw % 128 == 0)
-      const uint32_t trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(quarter * 32) << 16);
-      const bool tr = wg_tid == 0 && (i >> 1) < 4;
-      if (RING && ep.eca_u) {
-        // per-sample ECA coefficients of this tile (hat_arch.py:236: conv_scale * sigmoid gate), zero beyond N
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");          // previous tile's readers are done
-        for (int j = wg_tid; j < p.BN; j += 128) {
-          const int n = n0 + j;
-          coef[j] = n < p.N ? ep.eca_coef * ep.eca_scale[(size_t)b * p.N + n] : 0.f;
-        }
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
-      }
+      RowInfo ri;
+      ri.m = m0 + ws.row;
+      ri.b = m0 / p.hw;                                  // a tile never straddles two samples (hw % 128 == 0)
+      const int rem = ri.m - ri.b * p.hw;
+      ri.py = rem / p.W; ri.px = rem - ri.py * p.W;
+      ri.chunk = (m0 - ri.b * p.hw) / G3_TILE_M; ri.nchunk = p.hw / G3_TILE_M;
+      ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
+      const bool tr = ws.wg_tid == 0 && (i >> 1) < 4;
       if (tr) G3_TRACE(24 + g * 16 + 4 * (i >> 1));
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
       if (tr) G3_TRACE(25 + g * 16 + 4 * (i >> 1));
-
-      float ln_k = 0.f, s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
-      if (p.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }     // previous tile's bf16 stores have left it
-      // ---------------- pass 1: value, fp32 / bf16 outputs, LayerNorm statistics ----------------
-      uint32_t r[CW];
-      tmem_ld16(trow, r);                             // software pipeline: chunk ci + 1 loads while chunk ci is processed
-      for (int ci = 0; ci < nch; ci++) {
-        const int nb = ci * CW;                       // column inside the n-tile
-        float v[CW], tb[CW], acc[CW];
-        tab_read(tab_bias + nb, tb);
-        float u[CW], rs[CW], cf[CW];
-        if constexpr (RING) {
-          const int s = k % p.ops;
-          mbar_wait(&op_full[g][s], (k / p.ops) & 1u);
-          const uint8_t* st = ring + (size_t)s * p.op_stage_bytes;
-          if (p.has_u) { row_read_bf16(st + p.op_u_off, row, u); tab_read(coef + nb, cf); }
-          if (p.has_resid) row_read_f32(st, row, rs);
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&op_empty[g][s]);      // this warp's rows are in registers
-          k++;
-        }
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
-        if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
-#pragma unroll
-        for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], acc[j], acc[j + 1], tb[j], tb[j + 1]);
-        if (n0 + nb < ep.scale_ncols) {               // q pre-scaling (hat_arch.py:375); scale_ncols % CW == 0
-#pragma unroll
-          for (int j = 0; j < CW; j += 2) mul2(v[j], v[j + 1], v[j], v[j + 1], ep.out_scale, ep.out_scale);
-        }
-        if (ep.act == ACT_GELU) {
-#pragma unroll
-          for (int j = 0; j < CW; j++) v[j] = gelu_f(v[j]);
-        } else if (ep.act == ACT_LRELU) {
-#pragma unroll
-          for (int j = 0; j < CW; j++) v[j] = lrelu_f(v[j]);
-        }
-        if (RING && p.has_u) {
-#pragma unroll
-          for (int j = 0; j < CW; j += 2) fma2(v[j], v[j + 1], cf[j], cf[j + 1], u[j], u[j + 1], v[j], v[j + 1]);
-        }
-        if (RING && p.has_resid) {
-#pragma unroll
-          for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], v[j], v[j + 1], rs[j], rs[j + 1]);
-        }
-        if (do_ln) {
-          if (ci == 0) ln_k = v[0];
-#pragma unroll
-          for (int j = 0; j < CW; j += 2) {
-            float d0, d1;
-            add2(d0, d1, v[j], v[j + 1], -ln_k, -ln_k);
-            add2(s1a, s1b, s1a, s1b, d0, d1);
-            fma2(s2a, s2b, d0, d1, d0, d1, s2a, s2b);
-          }
-          uint32_t w[CW];
-#pragma unroll
-          for (int j = 0; j < CW; j++) w[j] = __float_as_uint(v[j]);
-          tmem_st16(trow + (uint32_t)nb, w);          // fp32 row parked in TMEM for the normalise pass
-        }
-        if (ep.out_f32) {
-          const int slot = ci % GW32;
-          if (slot == 0) st32.begin(lane);
-          st32.put_f32(lane, slot, v);
-          if (slot == GW32 - 1 || ci == nch - 1) st32.flush(&tmOF, lane, n0 + (ci - slot) * CW, r0);
-        }
-        if (ep.out_t) {
-          const int slot = ci % GW16;
-          if (slot == 0) st16.begin(lane);
-          st16.put_bf16(lane, slot, v);
-          if (slot == GW16 - 1 || ci == nch - 1) st16.flush(&tmOT, lane, n0 + (ci - slot) * CW, r0);
-        }
-      }
-      if (tr) G3_TRACE(27 + g * 16 + 4 * (i >> 1));                  // end of pass 1
-      // K-padding columns of the consumer that no n-tile covers: [Npad, out_t_zero_to), written by the last n-tile
-      if (ep.out_t && blockIdx.y == gridDim.y - 1) {
-        for (int nb = p.BN; n0 + nb < ep.out_t_zero_to; nb += CW * GW16) {
-          st16.begin(lane);
-          st16.put_zero(lane);
-          st16.flush(&tmOT, lane, n0 + nb, r0);
-        }
-      }
-      // ---------------- pass 2: LayerNorm of the row (eps 1e-5), bf16 output, 16-channel head ----------------
-      if (do_ln) {
-        if (p.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
-        tmem_st_wait();
-        // pad columns hold exact zeros: remove their contribution to the shifted sums
-        const float npad = (float)(p.BN - p.N);
-        const float s1 = s1a + s1b + npad * ln_k;
-        const float s2 = s2a + s2b - npad * ln_k * ln_k;
-        const float inv_n = 1.f / (float)p.N;
-        const float mean_d = s1 * inv_n;
-        const float var = fmaxf(s2 * inv_n - mean_d * mean_d, 0.f);
-        const float rstd = rsqrtf(var + 1e-5f);
-        const float nmr = -(ln_k + mean_d) * rstd;    // (x - mean) * rstd = x * rstd + nmr
-        tmem_ld16(trow, r);
-        for (int ci = 0; ci < nch; ci++) {
-          const int nb = ci * CW;
-          float ga[CW], be[CW], v[CW], acc[CW];
-          tab_read(tab_gamma + nb, ga);
-          tab_read(tab_beta + nb, be);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
-          if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
-#pragma unroll
-          for (int j = 0; j < CW; j += 2) {
-            float t0, t1;
-            fma2(t0, t1, acc[j], acc[j + 1], rstd, rstd, nmr, nmr);
-            fma2(v[j], v[j + 1], t0, t1, ga[j], ga[j + 1], be[j], be[j + 1]);
-          }
-          const int slot = ci % GW16;
-          if (slot == 0) st16.begin(lane);
-          st16.put_bf16(lane, slot, v);
-          if (slot == GW16 - 1 || ci == nch - 1) st16.flush(&tmLN, lane, (ci - slot) * CW, r0);
-          if (ci == 0 && ep.ln_head) {    // compact / x-padded copies of the first channels + their column sums
-            const int rem = m - b * p.hw;
-            const int py = rem / p.W, px = rem - py * p.W;
-            uint4 q[2];
-            __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(q);
-#pragma unroll
-            for (int j = 0; j < 8; j++) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-            bf16* hd = (bf16*)ep.ln_head + (size_t)m * ep.ln_head_c;
-            if (ep.ln_head_c == 16) {
-              reinterpret_cast<uint4*>(hd)[0] = q[0];
-              reinterpret_cast<uint4*>(hd)[1] = q[1];
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; j++)
-                if (j < ep.ln_head_c) hd[j] = __float2bfloat16_rn(v[j]);
-            }
-            if (ep.ln_head_pad && ep.ln_head_c == 16) {
-              bf16* hp = (bf16*)ep.ln_head_pad + (((size_t)b * p.H + py) * (p.W + 12) + px + 6) * 16;
-              reinterpret_cast<uint4*>(hp)[0] = q[0];
-              reinterpret_cast<uint4*>(hp)[1] = q[1];
-            }
-            if (ep.ln_head_colsum) {      // sums of the bf16-rounded head values, fixed order
-#pragma unroll
-              for (int j = 0; j < 16; j++) {
-                const float sj = warp_sum(__bfloat162float(__float2bfloat16_rn(v[j])));
-                if (lane == 0) hsum[ew][j] = sj;
-              }
-            }
-          }
-        }
-        for (int nb = p.BN; nb < ep.ln_pitch; nb += CW * GW16) {   // pad columns beyond the (single) n-tile
-          st16.begin(lane);
-          st16.put_zero(lane);
-          st16.flush(&tmLN, lane, nb, r0);
-        }
-        if (ep.ln_head_colsum) {
-          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
-          if (wg_tid < ep.ln_head_c && wg_tid < 16) {
-            // warps of this warpgroup in row order: quarter q is warp ((q + 2) & 3) of the group
-            const int e0 = g * 4;
-            const int chunk = (m0 - b * p.hw) / G3_TILE_M, nchunk = p.hw / G3_TILE_M;
-            ep.ln_head_colsum[((size_t)b * nchunk + chunk) * ep.ln_head_c + wg_tid] =
-                hsum[e0 + 2][wg_tid] + hsum[e0 + 3][wg_tid] + hsum[e0 + 0][wg_tid] + hsum[e0 + 1][wg_tid];
-          }
-          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");       // hsum is reused by the next tile
-        }
-      }
+      const Tile2D ts{m0};
+      run_tile<RING, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));

@@ -280,3 +280,82 @@ def _linear_fused_case(B, H, W, Cin, N, resid, eca, ln, head, out_t, act=0, seed
 ])
 def test_linear_fused_tcgen05(shape):
     _linear_fused_case(*shape)
+
+
+# ---- persistent halo-resident tcgen05 3x3 conv with the fused epilogue (csrc/tc_conv3.cu) ---------------------
+def _conv3_fused_case(B, H, W, Cin, N, resid, ln, head, out_t, colsum, act=0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    M = B * H * W
+    pitch = -(-Cin // 64) * 64
+    x = torch.randn(B, Cin, H, W, generator=g)
+    a = torch.full((M, pitch), float("nan"), dtype=torch.bfloat16)
+    a[:, Cin:] = 0                                       # K padding of the producer; real channels below
+    a[:, :Cin] = x.permute(0, 2, 3, 1).reshape(M, Cin).bfloat16()
+    w = torch.randn(N, Cin, 3, 3, generator=g) * 0.05
+    bias = torch.randn(N, generator=g) * 0.3
+    npitch = -(-N // 64) * 64
+    r = torch.randn(M, N, generator=g) if resid else None
+    gamma = 1.0 + 0.2 * torch.randn(N, generator=g)
+    beta = 0.1 * torch.randn(N, generator=g)
+    xin = a[:, :Cin].float().view(B, H, W, Cin).permute(0, 3, 1, 2)
+    v = F.conv2d(xin, w.bfloat16().float(), bias, padding=1).permute(0, 2, 3, 1).reshape(M, N)
+    if act == 1:
+        v = F.gelu(v)
+    elif act == 2:
+        v = F.leaky_relu(v, 0.01)
+    if resid:
+        v = v + r
+    ln_ref = F.layer_norm(v, (N,), gamma, beta, 1e-5)
+    d = lambda t: None if t is None else t.to(DEV)
+    a_d, w_d, b_d, r_d, g_d, be_d = map(d, (a, w, bias, r, gamma, beta))
+    out_f32 = torch.full((M, N), float("nan"), device=DEV) if resid else None
+    ot = torch.full((M, npitch), float("nan"), dtype=torch.bfloat16, device=DEV) if out_t else None
+    lo = torch.full((M, npitch), float("nan"), dtype=torch.bfloat16, device=DEV) if ln else None
+    hd = torch.full((M, 16), float("nan"), dtype=torch.bfloat16, device=DEV) if head else None
+    hcs = torch.full((M // 128, 16), float("nan"), device=DEV) if head else None
+    cs = torch.full((M // 128, N), float("nan"), device=DEV) if colsum else None
+    p = lambda t: None if t is None else _p(t)
+    n16 = -(-N // 16) * 16
+    nt = -(-n16 // 256)
+    per = -(-n16 // nt)
+    npad = nt * (-(-per // (64 if n16 > 32 else 16)) * (64 if n16 > 32 else 16))      # kernels.cuh tc_npad()
+    zero_to = npitch if (out_t and npitch <= npad) else 0
+    _lib.check(_lib.lib().hatb200_conv_fused(
+        p(a_d), pitch, Cin, B, H, W, p(w_d), p(b_d), N, 3, act, p(r_d), p(out_f32), p(ot), npitch, zero_to, p(g_d),
+        p(be_d), p(lo), npitch, p(hd), p(hcs), p(cs), _stream()))
+    torch.cuda.synchronize()
+    scale = max(1.0, v.abs().max().item())
+    if out_f32 is not None:
+        assert (out_f32.cpu() - v).abs().max().item() <= 3e-4 * scale
+    if ot is not None:
+        got = ot.float().cpu()
+        assert (got[:, :N] - v).abs().max().item() <= 2.0 ** -7 * scale
+        if zero_to:
+            assert torch.equal(got[:, N:zero_to], torch.zeros(M, zero_to - N))
+    if lo is not None:
+        got = lo.float().cpu()
+        assert (got[:, :N] - ln_ref).abs().max().item() <= 2.0 ** -6 * max(1.0, ln_ref.abs().max().item())
+        assert torch.equal(got[:, N:], torch.zeros(M, npitch - N))
+        if hd is not None:
+            # head rows are tokens; column sums are per 8 x 16 pixel tile, tiles numbered row-major inside a sample
+            assert torch.equal(hd.cpu(), lo[:, :16].cpu())
+            t = lo[:, :16].float().cpu().view(B, H // 16, 16, W // 8, 8, 16).sum((2, 4)).reshape(-1, 16)
+            assert (hcs.cpu() - t).abs().max().item() <= 1e-3 * max(1.0, t.abs().max().item())
+    if cs is not None:
+        t = v.view(B, H // 16, 16, W // 8, 8, N).sum((2, 4)).reshape(-1, N)
+        assert (cs.cpu() - t).abs().max().item() <= 1e-3 * max(1.0, t.abs().max().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [
+    # B, H, W, Cin, N, resid, ln, head, out_t, colsum, act
+    (2, 16, 32, 180, 60, False, False, False, True, False, 1),      # CAB conv1 + GELU
+    (2, 32, 16, 60, 180, False, False, False, True, True, 0),       # CAB conv2 + pool partials
+    (1, 32, 32, 180, 180, True, True, True, False, False, 0),       # RHAG conv + group residual + next norm1 + head
+    (3, 16, 16, 180, 180, True, False, False, True, False, 0),      # conv_after_body + long skip
+    (1, 16, 16, 180, 64, False, False, False, True, False, 2),      # conv_before_upsample + LeakyReLU
+    (5, 32, 32, 144, 144, True, True, True, False, False, 0),       # HAT-S width, several tiles per CTA
+    (1, 64, 64, 64, 256, False, False, False, True, False, 0),      # upsample-sized n-tile (256 columns)
+])
+def test_conv3_fused_tcgen05(shape):
+    _conv3_fused_case(*shape)
