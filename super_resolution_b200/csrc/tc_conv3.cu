@@ -29,14 +29,23 @@ namespace hb {
 using namespace tc;
 using namespace epi3;
 
+unsigned long long* gemm_trace_arm(cudaStream_t st);
+
 namespace {
+
+__device__ __forceinline__ unsigned long long c3_time() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define C3_TRACE(slot) do { if (p.trace) p.trace[(size_t)blockIdx.x * 64 + (slot)] = c3_time(); } while (0)
 
 constexpr int C3_THREADS = 384;
 constexpr int C3_TW = 8, C3_TH = 16;                   // tile: 128 pixels = UMMA M
 constexpr int C3_HW = C3_TW + 2, C3_HH = C3_TH + 2;    // halo
 constexpr int C3_HROW = C3_HW * 128;                   // bytes between two halo image rows of one 64-channel block
 constexpr int C3_HALO_KB = ((C3_HH * C3_HW * 128 + 1023) / 1024) * 1024;   // 23552: one 64-channel block of a halo
-constexpr int C3_MAX_HST = 2, C3_MAX_WST = 8;
+constexpr int C3_MAX_HST = 2, C3_MAX_WST = 16;
 constexpr int C3_SMEM_LIMIT = 227 * 1024 - 2048;
 
 struct C3Params {
@@ -49,6 +58,8 @@ struct C3Params {
   uint32_t acc_stride, tmem_cols;
   int off_halo, off_w, off_op, off_stg32, off_stg16, off_tab, off_sred, smem_bytes;
   int stg_bufs, share_stg;
+  unsigned long long* trace;     // engineering: per-CTA timestamps (HATB200_GEMM_TRACE)
+  int dbg_aligned;               // engineering: 1024-aligned A descriptors (wrong results; timing experiment)
 };
 
 __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
@@ -109,6 +120,12 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  // Every CTA streams the SAME 9 * kblocks weight slices for every tile.  Walking them in the same order on all
+  // 148 SMs makes each slice an L2 hot spot (measured: ~0.4 us per slice whatever its size, 100 ns per MMA); each
+  // CTA therefore starts at a different slice and wraps around -- the accumulation order differs per CTA, the
+  // sum does not.
+  const int nsl = 9 * p.kblocks;
+  const int rot = (int)((blockIdx.x * 7u) % (unsigned)nsl);
 
   if (warp == 0) {
     // ===== TMA producer: one halo per tile (kblocks boxes), 9 * kblocks weight slices per tile =====
@@ -123,13 +140,14 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_arrive_expect_tx(&halo_full[hs], (uint32_t)(p.kblocks * C3_HH * C3_HW * 128));
         for (int kb = 0; kb < p.kblocks; kb++)
           tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
-        for (int tap = 0; tap < 9; tap++) {
-          for (int kb = 0; kb < p.kblocks; kb++, wit++) {
-            const int s = wit % p.wst;
-            mbar_wait(&w_empty[s], (((uint32_t)(wit / p.wst)) & 1u) ^ 1u);
-            mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
-            tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
-          }
+        for (int j = 0; j < nsl; j++, wit++) {
+          int id = j + rot;                             // rotated slice order (see rot)
+          if (id >= nsl) id -= nsl;
+          const int tap = id / p.kblocks, kb = id - tap * p.kblocks;
+          const int s = wit % p.wst;
+          mbar_wait(&w_empty[s], (((uint32_t)(wit / p.wst)) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+          tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
         }
       }
     }
@@ -140,33 +158,40 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int i = 0, wit = 0;
       for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
         const int g = i & 1;
+        if (i < 4) C3_TRACE(4 * i);
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
         const int hs = i % p.hst;
+        if (i < 4) C3_TRACE(4 * i + 1);
         mbar_wait(&halo_full[hs], ((uint32_t)(i / p.hst)) & 1u);
         tc_fence_after();
+        if (i < 4) C3_TRACE(4 * i + 2);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
         const uint32_t h_addr = smem_u32(smem + p.off_halo + (size_t)hs * p.halo_stage_bytes);
-        int it = 0;
-        for (int tap = 0; tap < 9; tap++) {
-          const int ky = tap / 3, kx = tap - ky * 3;
-          for (int kb = 0; kb < p.kblocks; kb++, wit++, it++) {
+        for (int it = 0; it < nsl; it++, wit++) {
+          {
+            int id = it + rot;
+            if (id >= nsl) id -= nsl;
+            const int tap = id / p.kblocks, kb = id - tap * p.kblocks;
+            const int ky = tap / 3, kx = tap - ky * 3;
             const int s = wit % p.wst;
             mbar_wait(&w_full[s], ((uint32_t)(wit / p.wst)) & 1u);
             tc_fence_after();
-            const uint32_t sa = h_addr + (uint32_t)(kb * C3_HALO_KB + (ky * C3_HW + kx) * 128);
+            const uint32_t sa = p.dbg_aligned ? h_addr + (uint32_t)(kb * C3_HALO_KB + tap * 1024)
+                                              : h_addr + (uint32_t)(kb * C3_HALO_KB + (ky * C3_HW + kx) * 128);
             const uint32_t sb = smem_u32(smem + p.off_w + (size_t)s * p.w_stage_bytes);
 #pragma unroll
             for (int k = 0; k < 4; k++) {
               // A: accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx; 8-row groups are one halo image row apart
               uint64_t ad = make_smem_desc(sa + k * 32, 128);
               ad &= ~(0x3FFFull << 32);
-              ad |= (uint64_t)(C3_HROW >> 4) << 32;
+              ad |= (uint64_t)((p.dbg_aligned ? 1024 : C3_HROW) >> 4) << 32;
               const uint64_t bd = make_smem_desc(sb + k * 32, 128);
               umma_bf16(acc, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
             }
             umma_commit(&w_empty[s]);         // frees the weight slot once these MMAs have read it
           }
         }
+        if (i < 4) C3_TRACE(4 * i + 3);
         umma_commit(&halo_empty[hs]);         // halo may be overwritten
         umma_commit(&tmem_full_bar[g]);       // accumulator of tile i complete
       }
@@ -223,11 +248,15 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       ri.nchunk = p.tiles_x * p.tiles_y;
       ri.chunk = t - ts.b * ri.nchunk;
       ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
+      const bool tr = ws.wg_tid == 0 && i < 4;
+      if (tr) C3_TRACE(16 + 4 * i);
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
+      if (tr) C3_TRACE(17 + 4 * i);
       run_tile<RING, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
+      if (tr) C3_TRACE(18 + 4 * i);
     }
     if (lane == 0) bulk_wait_all();
   }
@@ -290,7 +319,12 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
   p.ops = ring ? 2 : 0;
   // prefer double-buffered halos and double-buffered staging; give what is left to the weight ring (>= 3 slices)
   for (int pass = 0; pass < 8; pass++) {
-    const int hst = (pass & 2) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2, want = pass < 4 ? 3 : 2;
+    static const int force_hst = getenv("HATB200_C3_HST") ? atoi(getenv("HATB200_C3_HST")) : 0;
+    static const int force_bufs = getenv("HATB200_C3_BUFS") ? atoi(getenv("HATB200_C3_BUFS")) : 0;
+    int hst = (pass & 2) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2;
+    const int want = pass < 4 ? 3 : 2;
+    if (force_hst) hst = force_hst;
+    if (force_bufs) bufs = force_bufs;
     const int stg32 = f32o ? 8 * bufs * 32 * (grouped ? 128 : 64) : 0;
     const int stg16 = bf16o && !p.share_stg ? 8 * bufs * 32 * (grouped ? 128 : 32) : 0;
     const int fixed = tab + sred + stg32 + stg16 + 2 * p.ops * p.op_stage_bytes + hst * p.halo_stage_bytes;
@@ -360,6 +394,8 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     HB_TRY(map4(&tmOT, false, (const bf16*)ep.out_t + ep.out_t_coff, width, ep.out_t_pitch, w16, C3_TW, 4));
   }
   if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
+  p.trace = gemm_trace_arm(st);
+  p.dbg_aligned = getenv("HATB200_C3_ALIGNED") ? atoi(getenv("HATB200_C3_ALIGNED")) : 0;
   const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {

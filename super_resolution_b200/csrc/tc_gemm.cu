@@ -128,6 +128,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  const int krot = p.b_resident ? 0 : (int)(blockIdx.x % (unsigned)p.kblocks);
 
   if (warp == 0) {
     // ===== TMA producer: weights once (resident) or per k-block (streamed), activations through the ring =====
@@ -140,7 +141,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
       int it = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
-        for (int kb = 0; kb < p.kblocks; kb++, it++) {
+        for (int j = 0; j < p.kblocks; j++, it++) {
+          int kb = j + krot;                 // rotated k-block order: streamed weight blocks are not an L2 hot spot
+          if (kb >= p.kblocks) kb -= p.kblocks;
           const int s = it % p.stages;
           const uint32_t par = (uint32_t)(it / p.stages) & 1u;
           mbar_wait(&empty_bar[s], par ^ 1u);
@@ -165,7 +168,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         if (i < 6) G3_TRACE(8 + 2 * i);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
-        for (int kb = 0; kb < p.kblocks; kb++, it++) {
+        for (int j = 0; j < p.kblocks; j++, it++) {
+          int kb = j + krot;
+          if (kb >= p.kblocks) kb -= p.kblocks;
           const int s = it % p.stages;
           const uint32_t par = (uint32_t)(it / p.stages) & 1u;
           mbar_wait(&full_bar[s], par);
@@ -176,7 +181,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int k = 0; k < G3_BK / 16; k++) {
             const uint64_t ad = make_smem_desc(sa + k * 32, 128);
             const uint64_t bd = make_smem_desc(sb + k * 32, 128);
-            umma_bf16(acc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16(acc, ad, bd, idesc, (j | k) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);       // frees the ring slot once these MMAs have read it
         }
@@ -258,6 +263,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // ---- host ------------------------------------------------------------------------------------------
 static unsigned long long* g_gemm_trace = nullptr;
 unsigned long long* gemm_trace_buffer() { return g_gemm_trace; }
+// engineering: (re)arm the per-CTA timestamp buffer when HATB200_GEMM_TRACE is set; null otherwise
+unsigned long long* gemm_trace_arm(cudaStream_t st) {
+  if (!getenv("HATB200_GEMM_TRACE")) return nullptr;
+  if (!g_gemm_trace && cudaMalloc(&g_gemm_trace, 1024 * 64 * 8) != cudaSuccess) return nullptr;
+  cudaMemsetAsync(g_gemm_trace, 0, 1024 * 64 * 8, st);
+  return g_gemm_trace;
+}
 
 static int sm_count() {
   static int n = 0;
