@@ -102,7 +102,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
+    if (elect_one()) {
       int ui = 0, kvit = 0;
       for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
         const int head = u % p.heads, win = u / p.heads;
@@ -126,7 +126,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc_s = make_idesc_bf16(128, KC);
       const uint32_t idesc_o = make_idesc_bf16(128, DP) | (1u << 16);     // B operand MN-major
       int ui = 0, kvit = 0;

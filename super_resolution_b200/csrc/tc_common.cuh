@@ -58,6 +58,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Ring cursor: slot index + phase bit, advanced without division.  The rings have run-time depths, and a
+// run-time `%` / `/` pair on the single issuing thread costs ~100-200 cycles -- more than the MMA it precedes
+// (tools/umma_probe.cu: the tensor pipe itself sustains one M=128,N=256,K=16 MMA per 128 cycles, commits free).
+struct RingPos {
+  int s = 0;
+  uint32_t ph = 0;
+  __device__ __forceinline__ void next(int depth) {
+    if (++s == depth) { s = 0; ph ^= 1u; }
+  }
+};
+
 // ---- TMA ------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");

@@ -120,74 +120,67 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
-  // Every CTA streams the SAME 9 * kblocks weight slices for every tile.  Walking them in the same order on all
-  // 148 SMs makes each slice an L2 hot spot (measured: ~0.4 us per slice whatever its size, 100 ns per MMA); each
-  // CTA therefore starts at a different slice and wraps around -- the accumulation order differs per CTA, the
-  // sum does not.
-  const int nsl = 9 * p.kblocks;
-  const int rot = (int)((blockIdx.x * 7u) % (unsigned)nsl);
-
   if (warp == 0) {
     // ===== TMA producer: one halo per tile (kblocks boxes), 9 * kblocks weight slices per tile =====
-    if (lane == 0) {
-      int i = 0, wit = 0;
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+    // (the single issuing thread is picked with elect.sync, not `lane == 0`: ptxas then knows the region is
+    //  one-thread and emits UTMALDG / UTCHMMA straight from uniform registers instead of a per-lane waterfall loop)
+    if (elect_one()) {
+      RingPos hp, wp;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, hp.next(p.hst)) {
         int x0, y0, b;
         tile_coords(p, t, x0, y0, b);
-        const int hs = i % p.hst;
-        mbar_wait(&halo_empty[hs], (((uint32_t)(i / p.hst)) & 1u) ^ 1u);
+        const int hs = hp.s;
+        mbar_wait(&halo_empty[hs], hp.ph ^ 1u);
         uint8_t* hb_ = smem + p.off_halo + (size_t)hs * p.halo_stage_bytes;
         mbar_arrive_expect_tx(&halo_full[hs], (uint32_t)(p.kblocks * C3_HH * C3_HW * 128));
         for (int kb = 0; kb < p.kblocks; kb++)
           tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
-        for (int j = 0; j < nsl; j++, wit++) {
-          int id = j + rot;                             // rotated slice order (see rot)
-          if (id >= nsl) id -= nsl;
-          const int tap = id / p.kblocks, kb = id - tap * p.kblocks;
-          const int s = wit % p.wst;
-          mbar_wait(&w_empty[s], (((uint32_t)(wit / p.wst)) & 1u) ^ 1u);
-          mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
-          tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
-        }
+        for (int tap = 0; tap < 9; tap++)
+          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst)) {
+            const int s = wp.s;
+            mbar_wait(&w_empty[s], wp.ph ^ 1u);
+            mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+            tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
+          }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one elected thread) =====
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, p.BN);
-      int i = 0, wit = 0;
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+      RingPos hp, wp;
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++, hp.next(p.hst)) {
         const int g = i & 1;
         if (i < 4) C3_TRACE(4 * i);
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
-        const int hs = i % p.hst;
+        const int hs = hp.s;
         if (i < 4) C3_TRACE(4 * i + 1);
-        mbar_wait(&halo_full[hs], ((uint32_t)(i / p.hst)) & 1u);
+        mbar_wait(&halo_full[hs], hp.ph);
         tc_fence_after();
         if (i < 4) C3_TRACE(4 * i + 2);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
         const uint32_t h_addr = smem_u32(smem + p.off_halo + (size_t)hs * p.halo_stage_bytes);
-        for (int it = 0; it < nsl; it++, wit++) {
-          {
-            int id = it + rot;
-            if (id >= nsl) id -= nsl;
-            const int tap = id / p.kblocks, kb = id - tap * p.kblocks;
-            const int ky = tap / 3, kx = tap - ky * 3;
-            const int s = wit % p.wst;
-            mbar_wait(&w_full[s], ((uint32_t)(wit / p.wst)) & 1u);
+        // A descriptor template: 128-byte swizzled rows, 8-row groups one halo image row (C3_HROW bytes) apart
+        const uint64_t a_tmpl = (make_smem_desc(0, 128) & ~(0x3FFFull << 32)) |
+                                ((uint64_t)((p.dbg_aligned ? 1024 : C3_HROW) >> 4) << 32);
+        const uint64_t b_tmpl = make_smem_desc(0, 128);
+        uint32_t first = 0;
+        for (int tap = 0; tap < 9; tap++) {
+          const int ky = tap / 3, kx = tap - ky * 3;
+          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst)) {
+            const int s = wp.s;
+            mbar_wait(&w_full[s], wp.ph);
             tc_fence_after();
+            // accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx
             const uint32_t sa = p.dbg_aligned ? h_addr + (uint32_t)(kb * C3_HALO_KB + tap * 1024)
                                               : h_addr + (uint32_t)(kb * C3_HALO_KB + (ky * C3_HW + kx) * 128);
             const uint32_t sb = smem_u32(smem + p.off_w + (size_t)s * p.w_stage_bytes);
+            const uint64_t ad = a_tmpl | (uint64_t)((sa & 0x3FFFF) >> 4);
+            const uint64_t bd = b_tmpl | (uint64_t)((sb & 0x3FFFF) >> 4);
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              // A: accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx; 8-row groups are one halo image row apart
-              uint64_t ad = make_smem_desc(sa + k * 32, 128);
-              ad &= ~(0x3FFFull << 32);
-              ad |= (uint64_t)((p.dbg_aligned ? 1024 : C3_HROW) >> 4) << 32;
-              const uint64_t bd = make_smem_desc(sb + k * 32, 128);
-              umma_bf16(acc, ad, bd, idesc, (it | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < 4; k++) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, first | (uint32_t)k);
+            first = 1;
             umma_commit(&w_empty[s]);         // frees the weight slot once these MMAs have read it
           }
         }
@@ -199,10 +192,10 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp >= 10) {
     // ===== operand-ring producer of warpgroup g (fp32 residual chunks) =====
     const int g = warp - 10;
-    if (RING && lane == 0) {
+    if (RING && elect_one()) {
       prefetch_tmap(&tmR);
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
-      uint32_t k = 0;
+      RingPos k;
       int i = 0;
       for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
@@ -258,7 +251,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) C3_TRACE(18 + 4 * i);
     }
-    if (lane == 0) bulk_wait_all();
+    if (elect_one()) bulk_wait_all();
   }
   tc_fence_before();
   __syncthreads();

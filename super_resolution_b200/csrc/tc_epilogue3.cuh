@@ -128,7 +128,7 @@ struct Stager {
   __device__ __forceinline__ uint8_t* buf() const { return base + (nbuf == 2 ? (n & 1) : 0) * BUF; }
   // before the first write of a group: the store that last read this buffer must be done reading it
   __device__ __forceinline__ void begin(int lane) const {
-    if (lane == 0) { if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>(); }
+    if (elect_one()) { if (nbuf == 2) bulk_wait_read<1>(); else bulk_wait_read<0>(); }
     __syncwarp();
   }
   __device__ __forceinline__ void put_f32(int lane, int slot, const float (&v)[CW]) const {
@@ -161,7 +161,7 @@ struct Stager {
   __device__ __forceinline__ void flush(const CUtensorMap* tm, int lane, int c0, const TS& ts, int quarter) {
     fence_proxy_async();
     __syncwarp();
-    if (lane == 0) {
+    if (elect_one()) {               // same leader every time (full mask): bulk groups are per-thread state
       ts.store(tm, buf(), c0, quarter);
       bulk_commit();
     }
@@ -240,7 +240,7 @@ struct WarpState {
   int ops, op_stage_bytes, op_u_off, has_resid, has_u, share_stg;
   float (*hsum)[16];                              // [8][16]: per epilogue warp column sums of the LN head
   float (*sred)[256];                             // [4][256]: this warpgroup's scratch for tile column sums
-  uint32_t k = 0;                                 // operand chunks consumed by this warpgroup
+  RingPos k;                                      // operand-ring cursor of this warpgroup (consumer side)
   int g, ew, quarter, lane, wg_tid, row;
   int BN, N, n0, nch, H, W, hw;
   bool last_ntile;
@@ -273,7 +273,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
   }
   float ln_k = 0.f, s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
-  if (ws.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }     // previous tile's bf16 stores have left it
+  if (ws.share_stg) { if (elect_one()) bulk_wait_read<0>(); __syncwarp(); }     // previous tile's bf16 stores have left it
   // ---------------- pass 1: value, fp32 / bf16 outputs, column sums, LayerNorm statistics ----------------
   uint32_t r[CW];
   tmem_ld16(trow, r);                             // software pipeline: chunk ci + 1 loads while chunk ci is processed
@@ -283,14 +283,14 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     tab_read(ws.tab_bias + nb, tb);
     float u[CW], rs[CW], cf[CW];
     if constexpr (RING) {
-      const int s = ws.k % ws.ops;
-      mbar_wait(&ws.op_full[s], (ws.k / ws.ops) & 1u);
+      const int s = ws.k.s;
+      mbar_wait(&ws.op_full[s], ws.k.ph);
       const uint8_t* st = ws.ring + (size_t)s * ws.op_stage_bytes;
       if (ws.has_u) { row_read_bf16(st + ws.op_u_off, row, u); tab_read(ws.coef + nb, cf); }
       if (ws.has_resid) row_read_f32(st, row, rs);
       __syncwarp();
       if (lane == 0) mbar_arrive(&ws.op_empty[s]);      // this warp's rows are in registers
-      ws.k++;
+      ws.k.next(ws.ops);
     }
     tmem_ld_wait();
 #pragma unroll
@@ -366,7 +366,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
   }
   // ---------------- pass 2: LayerNorm of the row (eps 1e-5), bf16 output, 16-channel head ----------------
   if (do_ln) {
-    if (ws.share_stg) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
+    if (ws.share_stg) { if (elect_one()) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
     tmem_st_wait();
     // pad columns hold exact zeros: remove their contribution to the shifted sums
     const float npad = (float)(ws.BN - ws.N);
@@ -447,11 +447,11 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
 template <class TS>
 __device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tmR, const CUtensorMap* tmU, uint8_t* ring,
                                              uint64_t* op_full, uint64_t* op_empty, int ops, int op_stage_bytes,
-                                             int op_u_off, int has_resid, int has_u, int n0, int nch, uint32_t& k) {
+                                             int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k) {
   const uint32_t bytes = (uint32_t)((has_resid ? 128 * CW * 4 : 0) + (has_u ? 128 * CW * 2 : 0));
-  for (int ci = 0; ci < nch; ci++, k++) {
-    const int s = k % ops;
-    mbar_wait(&op_empty[s], ((k / ops) & 1u) ^ 1u);
+  for (int ci = 0; ci < nch; ci++, k.next(ops)) {
+    const int s = k.s;
+    mbar_wait(&op_empty[s], k.ph ^ 1u);
     uint8_t* st = ring + (size_t)s * op_stage_bytes;
     mbar_arrive_expect_tx(&op_full[s], bytes);
     if (has_resid) ts.load(st, tmR, &op_full[s], n0 + ci * CW);

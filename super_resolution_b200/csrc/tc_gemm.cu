@@ -128,25 +128,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
-  const int krot = p.b_resident ? 0 : (int)(blockIdx.x % (unsigned)p.kblocks);
 
   if (warp == 0) {
     // ===== TMA producer: weights once (resident) or per k-block (streamed), activations through the ring =====
-    if (lane == 0) {
+    // (single issuing threads are picked with elect.sync, not `lane == 0`: ptxas then knows the region is
+    //  one-thread and emits UTMALDG / UTCHMMA from uniform registers without a per-lane waterfall loop)
+    if (elect_one()) {
       if (p.b_resident) {
         mbar_arrive_expect_tx(&b_bar, (uint32_t)(p.kblocks * p.BN * 128));
         for (int kb = 0; kb < p.kblocks; kb++)
           tma_load_2d(smem + p.off_b + (size_t)kb * p.BN * 128, &tmB, &b_bar, kb * G3_BK, n0);
       }
       const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
-      int it = 0;
+      RingPos rp;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
-        for (int j = 0; j < p.kblocks; j++, it++) {
-          int kb = j + krot;                 // rotated k-block order: streamed weight blocks are not an L2 hot spot
-          if (kb >= p.kblocks) kb -= p.kblocks;
-          const int s = it % p.stages;
-          const uint32_t par = (uint32_t)(it / p.stages) & 1u;
-          mbar_wait(&empty_bar[s], par ^ 1u);
+        for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
+          const int s = rp.s;
+          mbar_wait(&empty_bar[s], rp.ph ^ 1u);
           uint8_t* sa = smem + p.off_a + (size_t)s * p.stage_bytes;
           mbar_arrive_expect_tx(&full_bar[s], tx);
           tma_load_2d(sa, &tmA, &full_bar[s], p.a_coff + kb * G3_BK, t * G3_TILE_M);
@@ -155,34 +153,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one elected thread) =====
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(G3_TILE_M, p.BN);
       G3_TRACE(0);
       if (p.b_resident) mbar_wait(&b_bar, 0);
       G3_TRACE(1);
-      int it = 0, i = 0;
+      RingPos rp;
+      int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         const int g = i & 1;
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
         tc_fence_after();
         if (i < 6) G3_TRACE(8 + 2 * i);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
-        for (int j = 0; j < p.kblocks; j++, it++) {
-          int kb = j + krot;
-          if (kb >= p.kblocks) kb -= p.kblocks;
-          const int s = it % p.stages;
-          const uint32_t par = (uint32_t)(it / p.stages) & 1u;
-          mbar_wait(&full_bar[s], par);
+        for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
+          const int s = rp.s;
+          mbar_wait(&full_bar[s], rp.ph);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + p.off_a + (size_t)s * p.stage_bytes);
           const uint32_t sb = p.b_resident ? smem_u32(smem + p.off_b + (size_t)kb * p.BN * 128) : sa + A_BYTES;
+          const uint64_t ad = make_smem_desc(sa, 128), bd = make_smem_desc(sb, 128);
 #pragma unroll
-          for (int k = 0; k < G3_BK / 16; k++) {
-            const uint64_t ad = make_smem_desc(sa + k * 32, 128);
-            const uint64_t bd = make_smem_desc(sb + k * 32, 128);
-            umma_bf16(acc, ad, bd, idesc, (j | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 0; k < G3_BK / 16; k++) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)(kb | k));
           umma_commit(&empty_bar[s]);       // frees the ring slot once these MMAs have read it
         }
         umma_commit(&tmem_full_bar[g]);     // accumulator of tile i complete
@@ -192,11 +185,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 10) {
     // ===== operand-ring producer of warpgroup g: residual / CAB-branch chunks, as far ahead as the ring allows =====
     const int g = warp - 10;
-    if (RING && lane == 0) {
+    if (RING && elect_one()) {
       if (p.has_resid) prefetch_tmap(&tmR);
       if (p.has_u) prefetch_tmap(&tmU);
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
-      uint32_t k = 0;
+      RingPos k;
       int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
@@ -250,7 +243,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
     }
-    if (lane == 0) bulk_wait_all();       // staging buffers must outlive the last stores
+    if (elect_one()) bulk_wait_all();       // staging buffers must outlive the last stores
   }
   tc_fence_before();
   __syncthreads();

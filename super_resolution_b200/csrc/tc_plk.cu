@@ -72,7 +72,7 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(&halo_bar, HALO_BYTES);
       tma_load_4d(sm_h, &tmX, &halo_bar, 0, gx0, y0 - PH, b);
       for (int dy = 0; dy < PK; dy++) {
@@ -83,7 +83,7 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, 64);
       mbar_wait(&halo_bar, 0);
       tc_fence_after();

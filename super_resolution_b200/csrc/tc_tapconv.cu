@@ -77,16 +77,17 @@ tapconv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     // ===== TMA producer =====
-    if (lane == 0) {
+    if (elect_one()) {
       const int ph = p.KH / 2, pw = p.KW / 2;
       const uint32_t tx_bytes = (uint32_t)(p.a_bytes + p.BN * p.BK * 2);
-      int it = 0;
-      for (int tap = 0; tap < p.KH * p.KW; tap++) {
-        const int dy = tap / p.KW - ph, dx = tap % p.KW - pw;
-        for (int kb = 0; kb < p.kblocks; kb++, it++) {
-          const int s = it % p.stages;
-          const uint32_t par = (uint32_t)(it / p.stages) & 1u;
-          mbar_wait(&empty_bar[s], par ^ 1u);
+      RingPos rp;
+      int tap = 0;
+      for (int ky = 0; ky < p.KH; ky++)
+       for (int kx = 0; kx < p.KW; kx++, tap++) {
+        const int dy = ky - ph, dx = kx - pw;
+        for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
+          const int s = rp.s;
+          mbar_wait(&empty_bar[s], rp.ph ^ 1u);
           uint8_t* sa = smem + (size_t)s * p.stage_bytes;
           mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
           tma_load_4d(sa, &tmA, &full_bar[s], p.a_coff + kb * p.BK, x0 + dx, y0 + dy, b);
@@ -96,13 +97,13 @@ tapconv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(TILE_M, p.BN);
       const uint32_t row_bytes = (uint32_t)p.BK * 2;
-      for (int it = 0; it < total_it; it++) {
-        const int s = it % p.stages;
-        const uint32_t par = (uint32_t)(it / p.stages) & 1u;
-        mbar_wait(&full_bar[s], par);
+      RingPos rp;
+      for (int it = 0; it < total_it; it++, rp.next(p.stages)) {
+        const int s = rp.s;
+        mbar_wait(&full_bar[s], rp.ph);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + (size_t)s * p.stage_bytes);
         const uint32_t sb = sa + (uint32_t)p.a_bytes;
