@@ -70,7 +70,7 @@ __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, i
 
 }  // namespace
 
-template <bool RING, bool GROUPED>
+template <class F, bool GROUPED>
 __global__ void __launch_bounds__(C3_THREADS, 1)
 conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmOF,
@@ -192,16 +192,18 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp >= 10) {
     // ===== operand-ring producer of warpgroup g (fp32 residual chunks) =====
     const int g = warp - 10;
-    if (RING && elect_one()) {
+    if (feat_ring<F>() && p.has_resid && elect_one()) {
       prefetch_tmap(&tmR);
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       RingPos k;
       int i = 0;
       for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
-        Tile4D ts;
+        Tile4D ts, nx;
         tile_coords(p, t, ts.x0, ts.y0, ts.b);
-        produce_tile(ts, &tmR, &tmR, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid, 0,
+        const int tn = t + 2 * (int)gridDim.x;
+        tile_coords(p, tn < p.tiles ? tn : t, nx.x0, nx.y0, nx.b);
+        produce_tile(ts, nx, i < 2, tn < p.tiles, &tmR, &tmR, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid, 0,
                      n0, p.BN / CW, k);
       }
     }
@@ -246,7 +248,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
       if (tr) C3_TRACE(17 + 4 * i);
-      run_tile<RING, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+      run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) C3_TRACE(18 + 4 * i);
@@ -393,10 +395,11 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   static bool attr_set = false;
   if (!attr_set) {
     const int lim = C3_SMEM_LIMIT + 1024;
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+#define C3_ATTR(F_) \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim)); \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
+    C3_ATTR(FeatAll); C3_ATTR(FeatPlain); C3_ATTR(FeatColsum); C3_ATTR(FeatResLn);
+#undef C3_ATTR
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
@@ -404,9 +407,18 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles) per_n = p.tiles;
   dim3 grid(per_n, n_tiles);
-#define C3_LAUNCH(R_, G_) conv3_tc_kernel<R_, G_><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep)
-  if (p.has_resid) { if (grouped) C3_LAUNCH(true, true); else C3_LAUNCH(true, false); }
-  else { if (grouped) C3_LAUNCH(false, true); else C3_LAUNCH(false, false); }
+#define C3_LAUNCH(F_)                                                                                              \
+  do {                                                                                                             \
+    if (grouped) conv3_tc_kernel<F_, true><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
+    else conv3_tc_kernel<F_, false><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
+  } while (0)
+  static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;
+  switch (generic_only ? FEAT_ALL : feat_select(ep)) {
+    case FEAT_PLAIN: C3_LAUNCH(FeatPlain); break;
+    case FEAT_COLSUM: C3_LAUNCH(FeatColsum); break;
+    case FEAT_RESLN: C3_LAUNCH(FeatResLn); break;
+    default: C3_LAUNCH(FeatAll); break;
+  }
 #undef C3_LAUNCH
   HB_CHECK_LAUNCH();
   return 0;

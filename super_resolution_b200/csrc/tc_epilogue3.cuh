@@ -180,6 +180,7 @@ struct Tile2D {
   __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col) const {
     tma_load_2d(dst, tm, bar, col, m0);
   }
+  __device__ __forceinline__ void prefetch(const CUtensorMap* tm, int col) const { tma_prefetch_2d(tm, col, m0); }
 };
 // Tile4D: rows are the 8 (x) x 16 (y) pixels of one sample starting at (x0, y0), row r = (y0 + r / 8, x0 + r % 8);
 // maps are 4-D (col, x, y, b): store box {w, 8, 4, 1} (one warp = 4 image rows), load box {CW, 8, 16, 1}.
@@ -191,6 +192,7 @@ struct Tile4D {
   __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col) const {
     tma_load_4d(dst, tm, bar, col, x0, y0, b);
   }
+  __device__ __forceinline__ void prefetch(const CUtensorMap* tm, int col) const { tma_prefetch_4d(tm, col, x0, y0, b); }
 };
 
 // Column sums of a 32-row x 16-column register block: after five butterfly rounds lane l (l even) holds the sum
@@ -244,6 +246,8 @@ struct WarpState {
   int g, ew, quarter, lane, wg_tid, row;
   int BN, N, n0, nch, H, W, hw;
   bool last_ntile;
+  bool prof = false;                              // engineering: accumulate wait cycles (HATB200_GEMM_TRACE)
+  long long t_ring = 0, t_stg = 0, t_p1 = 0, t_p2 = 0;
 };
 
 // Per-tile facts of the calling thread's row.
@@ -255,15 +259,55 @@ struct RowInfo {
   int chunk, nchunk;   // index of this tile inside its sample / tiles per sample (partial-sum slots)
 };
 
-// The whole epilogue of one tile for the calling warp.  TS: Tile2D / Tile4D.
-template <bool RING, bool GROUPED, class TS>
+// Compile-time feature sets.  A kernel instantiated on F contains code only for the features F enables; with
+// EXACT the structural ones (U, RESID, OUT32, OUT16, LN, COLSUM) are known PRESENT as well, so the chunk loop has
+// no feature branches at all (the generic body costs 266 instructions per 16-column chunk, 40 of them arithmetic,
+// and the epilogue warps -- two per scheduler -- are issue/latency bound: profiles/r01_ncu_fc2_*).  ACT, SCALE and
+// HEAD stay run-time inside a set that enables them.  The host picks the first matching set (feat_match).
+struct FeatAll    { static constexpr bool EXACT = 0, ACT = 1, SCALE = 1, U = 1, RESID = 1, OUT32 = 1, OUT16 = 1, LN = 1, HEAD = 1, COLSUM = 1; };
+struct FeatPlain  { static constexpr bool EXACT = 1, ACT = 1, SCALE = 1, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 0; };
+struct FeatColsum { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 1; };
+struct FeatResLn  { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 1, COLSUM = 0; };
+struct FeatResULn { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 1, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 0, COLSUM = 0; };
+template <class F> constexpr bool feat_ring() { return F::U || F::RESID; }
+
+// does the feature set F cover this epilogue exactly (EXACT) / at least (generic)?
+template <class F>
+inline bool feat_match(const Epilogue& ep) {
+  const bool u = ep.eca_u != nullptr, r = ep.resid != nullptr, o32 = ep.out_f32 != nullptr, o16 = ep.out_t != nullptr;
+  const bool ln = ep.ln_out != nullptr, cs = ep.colsum != nullptr;
+  if (ep.act != ACT_NONE && !F::ACT) return false;
+  if (ep.scale_ncols > 0 && !F::SCALE) return false;
+  if (ep.ln_head && !F::HEAD) return false;
+  if (F::EXACT) return u == F::U && r == F::RESID && o32 == F::OUT32 && o16 == F::OUT16 && ln == F::LN && cs == F::COLSUM;
+  return (!u || F::U) && (!r || F::RESID) && (!o32 || F::OUT32) && (!o16 || F::OUT16) && (!ln || F::LN) && (!cs || F::COLSUM);
+}
+enum { FEAT_ALL = 0, FEAT_PLAIN, FEAT_COLSUM, FEAT_RESLN, FEAT_RESULN };
+inline int feat_select(const Epilogue& ep) {
+  if (feat_match<FeatPlain>(ep)) return FEAT_PLAIN;
+  if (feat_match<FeatColsum>(ep)) return FEAT_COLSUM;
+  if (feat_match<FeatResLn>(ep)) return FEAT_RESLN;
+  if (feat_match<FeatResULn>(ep)) return FEAT_RESULN;
+  return FEAT_ALL;
+}
+
+// The whole epilogue of one tile for the calling warp.  F: feature set; TS: Tile2D / Tile4D.
+template <class F, bool GROUPED, class TS>
 __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>& ws, const RowInfo& ri, const TS& ts,
                                          const CUtensorMap* tmOF, const CUtensorMap* tmOT, const CUtensorMap* tmLN) {
   constexpr int GW32 = WarpState<GROUPED>::GW32, GW16 = WarpState<GROUPED>::GW16;
+  constexpr bool RING = feat_ring<F>();
   const int lane = ws.lane, quarter = ws.quarter, row = ws.row, g = ws.g, n0 = ws.n0, nch = ws.nch;
-  const bool do_ln = ep.ln_out != nullptr;
+  // feature present?  compile-time for an EXACT set, a uniform run-time test otherwise
+  const bool has_u = F::U && (F::EXACT || ws.has_u), has_resid = F::RESID && (F::EXACT || ws.has_resid);
+  const bool do_ln = F::LN && (F::EXACT || ep.ln_out != nullptr);
+  const bool out32 = F::OUT32 && (F::EXACT || ep.out_f32 != nullptr), out16 = F::OUT16 && (F::EXACT || ep.out_t != nullptr);
+  const bool do_cs = F::COLSUM && (F::EXACT || ep.colsum != nullptr);
+  const int act = F::ACT ? ep.act : ACT_NONE;
+  const int scale_ncols = F::SCALE ? ep.scale_ncols : 0;
+  const float out_scale = ep.out_scale;
   const uint32_t trow = ri.trow;
-  if (RING && ep.eca_u) {
+  if (has_u) {
     // per-sample ECA coefficients of this tile (hat_arch.py:236: conv_scale * sigmoid gate), zero beyond N
     asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");          // previous tile's readers are done
     for (int j = ws.wg_tid; j < ws.BN; j += 128) {
@@ -274,46 +318,50 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
   }
   float ln_k = 0.f, s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
   if (ws.share_stg) { if (elect_one()) bulk_wait_read<0>(); __syncwarp(); }     // previous tile's bf16 stores have left it
+  long long tp = 0;
+  if (ws.prof) tp = clock64();
   // ---------------- pass 1: value, fp32 / bf16 outputs, column sums, LayerNorm statistics ----------------
-  uint32_t r[CW];
-  tmem_ld16(trow, r);                             // software pipeline: chunk ci + 1 loads while chunk ci is processed
-  for (int ci = 0; ci < nch; ci++) {
+  // Software pipeline over two register sets: while chunk ci is processed out of one, chunk ci + 1 loads into
+  // the other (no register copies between iterations).
+  auto pass1 = [&](const int ci, uint32_t (&rc)[CW], uint32_t (&rn)[CW]) __attribute__((always_inline)) {
     const int nb = ci * CW;                       // column inside the n-tile
-    float v[CW], tb[CW], acc[CW];
+    float v[CW], tb[CW];
     tab_read(ws.tab_bias + nb, tb);
     float u[CW], rs[CW], cf[CW];
-    if constexpr (RING) {
+    if (RING && (has_u || has_resid)) {
       const int s = ws.k.s;
+      long long tw = 0;
+      if (ws.prof) tw = clock64();
       mbar_wait(&ws.op_full[s], ws.k.ph);
+      if (ws.prof) ws.t_ring += clock64() - tw;
       const uint8_t* st = ws.ring + (size_t)s * ws.op_stage_bytes;
-      if (ws.has_u) { row_read_bf16(st + ws.op_u_off, row, u); tab_read(ws.coef + nb, cf); }
-      if (ws.has_resid) row_read_f32(st, row, rs);
+      if (has_u) { row_read_bf16(st + ws.op_u_off, row, u); tab_read(ws.coef + nb, cf); }
+      if (has_resid) row_read_f32(st, row, rs);
       __syncwarp();
       if (lane == 0) mbar_arrive(&ws.op_empty[s]);      // this warp's rows are in registers
       ws.k.next(ws.ops);
     }
     tmem_ld_wait();
+    if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), rn);
 #pragma unroll
-    for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
-    if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
+    for (int j = 0; j < CW; j += 2)
+      add2(v[j], v[j + 1], __uint_as_float(rc[j]), __uint_as_float(rc[j + 1]), tb[j], tb[j + 1]);
+    if (F::SCALE && n0 + nb < scale_ncols) {      // q pre-scaling (hat_arch.py:375); scale_ncols % CW == 0
 #pragma unroll
-    for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], acc[j], acc[j + 1], tb[j], tb[j + 1]);
-    if (n0 + nb < ep.scale_ncols) {               // q pre-scaling (hat_arch.py:375); scale_ncols % CW == 0
-#pragma unroll
-      for (int j = 0; j < CW; j += 2) mul2(v[j], v[j + 1], v[j], v[j + 1], ep.out_scale, ep.out_scale);
+      for (int j = 0; j < CW; j += 2) mul2(v[j], v[j + 1], v[j], v[j + 1], out_scale, out_scale);
     }
-    if (ep.act == ACT_GELU) {
+    if (F::ACT && act == ACT_GELU) {
 #pragma unroll
       for (int j = 0; j < CW; j++) v[j] = gelu_f(v[j]);
-    } else if (ep.act == ACT_LRELU) {
+    } else if (F::ACT && act == ACT_LRELU) {
 #pragma unroll
       for (int j = 0; j < CW; j++) v[j] = lrelu_f(v[j]);
     }
-    if (RING && ws.has_u) {
+    if (has_u) {
 #pragma unroll
       for (int j = 0; j < CW; j += 2) fma2(v[j], v[j + 1], cf[j], cf[j + 1], u[j], u[j + 1], v[j], v[j + 1]);
     }
-    if (RING && ws.has_resid) {
+    if (has_resid) {
 #pragma unroll
       for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], v[j], v[j + 1], rs[j], rs[j + 1]);
     }
@@ -331,32 +379,41 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
       for (int j = 0; j < CW; j++) w[j] = __float_as_uint(v[j]);
       tmem_st16(trow + (uint32_t)nb, w);          // fp32 row parked in TMEM for the normalise pass
     }
-    if (ep.colsum) {                              // per-tile column sums of v (global-average-pool partials)
+    if (do_cs) {                                  // per-tile column sums of v (global-average-pool partials)
       const float cs = colsum16(v, lane);
       if ((lane & 1) == 0) ws.sred[quarter][nb + colsum16_col(lane)] = cs;
     }
-    if (ep.out_f32) {
+    if (out32) {
       const int slot = ci % GW32;
+      long long tw = 0;
+      if (ws.prof) tw = clock64();
       if (slot == 0) ws.st32.begin(lane);
+      if (ws.prof) ws.t_stg += clock64() - tw;
       ws.st32.put_f32(lane, slot, v);
       if (slot == GW32 - 1 || ci == nch - 1) ws.st32.flush(tmOF, lane, n0 + (ci - slot) * CW, ts, quarter);
     }
-    if (ep.out_t) {
+    if (out16) {
       const int slot = ci % GW16;
       if (slot == 0) ws.st16.begin(lane);
       ws.st16.put_bf16(lane, slot, v);
       if (slot == GW16 - 1 || ci == nch - 1) ws.st16.flush(tmOT, lane, n0 + (ci - slot) * CW, ts, quarter);
     }
+  };
+  uint32_t ra[CW], rb[CW];
+  tmem_ld16(trow, ra);
+  for (int ci = 0; ci < nch; ci += 2) {
+    pass1(ci, ra, rb);
+    if (ci + 1 < nch) pass1(ci + 1, rb, ra);
   }
   // K-padding columns of the consumer that no n-tile covers: [Npad, out_t_zero_to), written by the last n-tile
-  if (ep.out_t && ws.last_ntile) {
+  if (out16 && ws.last_ntile) {
     for (int nb = ws.BN; n0 + nb < ep.out_t_zero_to; nb += CW * GW16) {
       ws.st16.begin(lane);
       ws.st16.put_zero(lane);
       ws.st16.flush(tmOT, lane, n0 + nb, ts, quarter);
     }
   }
-  if (ep.colsum) {
+  if (do_cs) {
     asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
     for (int n = ws.wg_tid; n < ws.BN; n += 128)
       if (n0 + n < ws.N)
@@ -364,6 +421,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
             ws.sred[0][n] + ws.sred[1][n] + ws.sred[2][n] + ws.sred[3][n];
     asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");           // sred is reused by the next tile
   }
+  if (ws.prof) { const long long t = clock64(); ws.t_p1 += t - tp; tp = t; }
   // ---------------- pass 2: LayerNorm of the row (eps 1e-5), bf16 output, 16-channel head ----------------
   if (do_ln) {
     if (ws.share_stg) { if (elect_one()) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
@@ -377,27 +435,25 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     const float var = fmaxf(s2 * inv_n - mean_d * mean_d, 0.f);
     const float rstd = rsqrtf(var + 1e-5f);
     const float nmr = -(ln_k + mean_d) * rstd;    // (x - mean) * rstd = x * rstd + nmr
-    tmem_ld16(trow, r);
-    for (int ci = 0; ci < nch; ci++) {
+    const bool head = F::HEAD && ep.ln_head != nullptr;
+    auto pass2 = [&](const int ci, uint32_t (&rc)[CW], uint32_t (&rn)[CW]) __attribute__((always_inline)) {
       const int nb = ci * CW;
-      float ga[CW], be[CW], v[CW], acc[CW];
+      float ga[CW], be[CW], v[CW];
       tab_read(ws.tab_gamma + nb, ga);
       tab_read(ws.tab_beta + nb, be);
       tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < CW; j++) acc[j] = __uint_as_float(r[j]);
-      if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), r);
+      if (ci + 1 < nch) tmem_ld16(trow + (uint32_t)(nb + CW), rn);
 #pragma unroll
       for (int j = 0; j < CW; j += 2) {
         float t0, t1;
-        fma2(t0, t1, acc[j], acc[j + 1], rstd, rstd, nmr, nmr);
+        fma2(t0, t1, __uint_as_float(rc[j]), __uint_as_float(rc[j + 1]), rstd, rstd, nmr, nmr);
         fma2(v[j], v[j + 1], t0, t1, ga[j], ga[j + 1], be[j], be[j + 1]);
       }
       const int slot = ci % GW16;
       if (slot == 0) ws.st16.begin(lane);
       ws.st16.put_bf16(lane, slot, v);
       if (slot == GW16 - 1 || ci == nch - 1) ws.st16.flush(tmLN, lane, (ci - slot) * CW, ts, quarter);
-      if (ci == 0 && ep.ln_head) {    // compact / x-padded copies of the first channels + their column sums
+      if (ci == 0 && head) {          // compact / x-padded copies of the first channels + their column sums
         uint4 q[2];
         __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(q);
 #pragma unroll
@@ -424,13 +480,19 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
           }
         }
       }
+    };
+    tmem_ld16(trow, ra);
+    pass2(0, ra, rb);                 // chunk 0 carries the head: kept out of the steady-state loop
+    for (int ci = 1; ci < nch; ci += 2) {
+      pass2(ci, rb, ra);
+      if (ci + 1 < nch) pass2(ci + 1, ra, rb);
     }
     for (int nb = ws.BN; nb < ep.ln_pitch; nb += CW * GW16) {   // pad columns beyond the (single) n-tile
       ws.st16.begin(lane);
       ws.st16.put_zero(lane);
       ws.st16.flush(tmLN, lane, nb, ts, quarter);
     }
-    if (ep.ln_head_colsum) {
+    if (head && ep.ln_head_colsum) {
       asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
       if (ws.wg_tid < ep.ln_head_c && ws.wg_tid < 16) {
         // warps of this warpgroup in row order: quarter q is warp ((q + 2) & 3) of the group
@@ -441,14 +503,29 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
       asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");       // hsum is reused by the next tile
     }
   }
+  if (ws.prof) ws.t_p2 += clock64() - tp;
 }
 
 // Operand-ring producer of one warpgroup for one tile (one elected thread): residual / CAB-branch chunks.
+// The ring is shallow (2-4 chunks of 8-12 KB per warpgroup), so what a load waits for is one memory latency per
+// `ops` chunks: the warpgroup's NEXT tile (`nx`, when `has_next`) is therefore pulled into L2 while this one is
+// consumed, and the ring loads of the next tile find their lines there instead of in DRAM.
 template <class TS>
-__device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tmR, const CUtensorMap* tmU, uint8_t* ring,
+__device__ __forceinline__ void produce_tile(const TS& ts, const TS& nx, bool first, bool has_next, const CUtensorMap* tmR,
+                                             const CUtensorMap* tmU, uint8_t* ring,
                                              uint64_t* op_full, uint64_t* op_empty, int ops, int op_stage_bytes,
                                              int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k) {
   const uint32_t bytes = (uint32_t)((has_resid ? 128 * CW * 4 : 0) + (has_u ? 128 * CW * 2 : 0));
+  if (first)                                       // the warpgroup's first tile: everything the ring cannot hold yet
+    for (int ci = ops; ci < nch; ci++) {
+      if (has_resid) ts.prefetch(tmR, n0 + ci * CW);
+      if (has_u) ts.prefetch(tmU, n0 + ci * CW);
+    }
+  if (has_next)
+    for (int ci = 0; ci < nch; ci++) {
+      if (has_resid) nx.prefetch(tmR, n0 + ci * CW);
+      if (has_u) nx.prefetch(tmU, n0 + ci * CW);
+    }
   for (int ci = 0; ci < nch; ci++, k.next(ops)) {
     const int s = k.s;
     mbar_wait(&op_empty[s], k.ph ^ 1u);

@@ -71,7 +71,7 @@ struct G3Params {
 }  // namespace
 
 // ---- the kernel ----------------------------------------------------------------------------------------
-template <bool RING, bool GROUPED>
+template <class F, bool GROUPED>
 __global__ void __launch_bounds__(G3_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU,
@@ -185,7 +185,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 10) {
     // ===== operand-ring producer of warpgroup g: residual / CAB-branch chunks, as far ahead as the ring allows =====
     const int g = warp - 10;
-    if (RING && elect_one()) {
+    if (feat_ring<F>() && (p.has_resid || p.has_u) && elect_one()) {
       if (p.has_resid) prefetch_tmap(&tmR);
       if (p.has_u) prefetch_tmap(&tmU);
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
@@ -193,8 +193,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
-        const Tile2D ts{t * G3_TILE_M};
-        produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
+        const Tile2D ts{t * G3_TILE_M}, nx{(t + 2 * (int)gridDim.x) * G3_TILE_M};
+        produce_tile(ts, nx, i < 2, t + 2 * (int)gridDim.x < p.m_tiles, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
                      p.has_u, n0, p.BN / CW, k);
       }
     }
@@ -212,6 +212,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
     ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
     ws.has_resid = p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
+    ws.prof = p.trace != nullptr;
     ws.hsum = hsum; ws.sred = nullptr;                   // no tile column sums in the 1x1 layers
     ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
     ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
@@ -238,12 +239,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       if (tr) G3_TRACE(25 + g * 16 + 4 * (i >> 1));
       const Tile2D ts{m0};
-      run_tile<RING, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+      run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
     }
     if (elect_one()) bulk_wait_all();       // staging buffers must outlive the last stores
+    if (ws.prof && ws.wg_tid == 0) {
+      unsigned long long* tr = p.trace + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 64 + 56 + 4 * g;
+      tr[0] = (unsigned long long)ws.t_ring; tr[1] = (unsigned long long)ws.t_stg;
+      tr[2] = (unsigned long long)ws.t_p1; tr[3] = (unsigned long long)ws.t_p2;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -423,10 +429,11 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   static bool attr_set = false;
   if (!attr_set) {
     const int lim = G3_SMEM_LIMIT + 1024;
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
-    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+#define G3_ATTR(F_) \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim)); \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
+    G3_ATTR(FeatAll); G3_ATTR(FeatPlain); G3_ATTR(FeatResLn); G3_ATTR(FeatResULn);
+#undef G3_ATTR
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
@@ -435,9 +442,19 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   if (per_n > p.m_tiles) per_n = p.m_tiles;
   dim3 grid(per_n, n_tiles);
   const bool ring = p.has_resid || p.has_u;
-#define G3_LAUNCH(R_, G_) gemm_tc_kernel<R_, G_><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep)
-  if (ring) { if (grouped) G3_LAUNCH(true, true); else G3_LAUNCH(true, false); }
-  else { if (grouped) G3_LAUNCH(false, true); else G3_LAUNCH(false, false); }
+  // epilogue specialisation: the first compile-time feature set that covers this layer exactly, else the generic one
+#define G3_LAUNCH(F_)                                                                                                \
+  do {                                                                                                               \
+    if (grouped) gemm_tc_kernel<F_, true><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
+    else gemm_tc_kernel<F_, false><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);       \
+  } while (0)
+  static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;     // engineering: A/B the specialisation
+  switch (generic_only ? FEAT_ALL : feat_select(ep)) {
+    case FEAT_PLAIN: G3_LAUNCH(FeatPlain); break;
+    case FEAT_RESLN: G3_LAUNCH(FeatResLn); break;
+    case FEAT_RESULN: G3_LAUNCH(FeatResULn); break;
+    default: G3_LAUNCH(FeatAll); break;
+  }
 #undef G3_LAUNCH
   HB_CHECK_LAUNCH();
   return 0;

@@ -5,7 +5,9 @@ committed; 24+16g+4k+{0,1,3,2}: epilogue warpgroup g, its k-th tile: waiting, ac
 """
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ["HATB200_GEMM_TRACE"] = "1"
+NO_TRACE = bool(os.environ.get("HATB200_NO_TRACE"))      # plain run of the same launch (ncu target)
+if not NO_TRACE:
+    os.environ["HATB200_GEMM_TRACE"] = "1"
 import numpy as np, torch
 from super_resolution_b200 import _lib
 lib = C.CDLL(_lib.LIB_PATH)
@@ -40,6 +42,9 @@ for _ in range(3):
     flush.zero_()
     run()
 torch.cuda.synchronize()
+if NO_TRACE:
+    print("ran", mode, Cin, N)
+    sys.exit(0)
 buf = np.zeros((1024, 64), dtype=np.uint64)
 lib.hatb200_debug_gemm_trace.argtypes = [C.c_void_p, C.c_void_p]
 rc = lib.hatb200_debug_gemm_trace(buf.ctypes.data, None)
@@ -49,5 +54,8 @@ t0 = t[live, 0].min()
 print(mode, Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
     r_ = t[cta]
-    ev = {k: int(r_[k] - t0) for k in range(64) if r_[k] > 0}
+    ev = {k: int(r_[k] - t0) for k in range(56) if r_[k] > 0}
     print("cta", cta, {k: round(v / 1000, 2) for k, v in sorted(ev.items())})
+    for g in range(2):   # epilogue warpgroup totals over its tiles, cycles of SM clock -> us at 1.965 GHz
+        ring, stg, p1, p2 = (float(r_[56 + 4 * g + j]) / 1965.0 for j in range(4))
+        print("   wg%d: pass1 %.2f us (ring wait %.2f, staging wait %.2f)  pass2 %.2f us" % (g, p1, ring, stg, p2))
