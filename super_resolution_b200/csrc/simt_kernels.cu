@@ -282,17 +282,27 @@ int launch_colsum(const void* in, int dt, int pitch, int B, int HW, int nc, floa
   return 0;
 }
 
+// Sum of `n` per-tile partials `stride` floats apart, in index order (deterministic), with 16 loads in flight:
+// these finish kernels are one small block per sample and nothing but the latency of this dependent chain.
+__device__ __forceinline__ float chunk_sum(const float* __restrict__ p, int n, int stride) {
+  float s = 0.f;
+  for (int k0 = 0; k0 < n; k0 += 16) {
+    float t[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) t[j] = k0 + j < n ? __ldg(p + (size_t)(k0 + j) * stride) : 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s += t[j];
+  }
+  return s;
+}
+
 // ECA gate: sigmoid(conv1d_k5(mean over HW)) across the channel axis, zero padded
 // ends, no bias (hat_arch.py:66-77).  One block per sample.
 __global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk, int C, float inv_hw,
                                   const float* __restrict__ w5, float* __restrict__ scale) {
   extern __shared__ float mean[];  // C
   int b = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float s = 0.f;
-    for (int k = 0; k < nchunk; k++) s += partial[((size_t)b * nchunk + k) * C + c];
-    mean[c] = s * inv_hw;
-  }
+  for (int c = threadIdx.x; c < C; c += blockDim.x) mean[c] = chunk_sum(partial + (size_t)b * nchunk * C + c, nchunk, C) * inv_hw;
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float a = 0.f;
@@ -321,11 +331,8 @@ __global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk,
   __shared__ float mean[64];
   __shared__ float hid[32];
   int b = blockIdx.x, half = pdim / 2;
-  for (int c = threadIdx.x; c < pdim; c += blockDim.x) {
-    float s = 0.f;
-    for (int k = 0; k < nchunk; k++) s += partial[((size_t)b * nchunk + k) * pdim + c];
-    mean[c] = s * inv_hw;
-  }
+  for (int c = threadIdx.x; c < pdim; c += blockDim.x)
+    mean[c] = chunk_sum(partial + (size_t)b * nchunk * pdim + c, nchunk, pdim) * inv_hw;
   __syncthreads();
   for (int o = threadIdx.x; o < half; o += blockDim.x) {
     float a = b1[o];

@@ -59,6 +59,7 @@ struct C3Params {
   int off_halo, off_w, off_op, off_stg32, off_stg16, off_tab, off_sred, smem_bytes;
   int stg_bufs, share_stg;
   unsigned long long* trace;     // engineering: per-CTA timestamps (HATB200_GEMM_TRACE)
+  int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
   int dbg_aligned;               // engineering: 1024-aligned A descriptors (wrong results; timing experiment)
 };
 
@@ -120,13 +121,18 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  // All CTAs stream the same 9 * kblocks weight slices per tile; each starts at a different tap (and wraps) so that
+  // 148 SMs do not ask the same L2 lines for the same slice at the same moment.  The accumulation order of a tile
+  // then depends on its CTA: results stay deterministic, sums differ in the last fp32 bit between tiles.
+  const int nsl = 9 * p.kblocks;
+  const int tap0 = p.rot ? (int)(blockIdx.x % 9u) : 0;
   if (warp == 0) {
     // ===== TMA producer: one halo per tile (kblocks boxes), 9 * kblocks weight slices per tile =====
     // (the single issuing thread is picked with elect.sync, not `lane == 0`: ptxas then knows the region is
     //  one-thread and emits UTMALDG / UTCHMMA straight from uniform registers instead of a per-lane waterfall loop)
     if (elect_one()) {
       RingPos hp, wp;
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, hp.next(p.hst)) {
+      auto issue_halo = [&](int t) {
         int x0, y0, b;
         tile_coords(p, t, x0, y0, b);
         const int hs = hp.s;
@@ -135,13 +141,28 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_arrive_expect_tx(&halo_full[hs], (uint32_t)(p.kblocks * C3_HH * C3_HW * 128));
         for (int kb = 0; kb < p.kblocks; kb++)
           tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
-        for (int tap = 0; tap < 9; tap++)
-          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst)) {
+        hp.next(p.hst);
+      };
+      // The next tile's halo is requested once `early` weight slices of this tile are on their way: by then the
+      // previous tile has released the other halo stage, and the load has most of a tile's MMAs to land.  (Issued
+      // after the last slice instead, it costs ~1 us of idle tensor pipe per tile; with a single halo stage it
+      // has to wait for this tile's MMAs and can only go last.)
+      const int early = p.hst > 1 ? (p.wst < nsl - 1 ? p.wst : nsl - 1) : nsl;
+      if ((int)blockIdx.x < p.tiles) issue_halo(blockIdx.x);
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+        const int tn = t + gridDim.x;
+        int cnt = 0, tap = tap0;
+        for (int j = 0; j < 9; j++) {
+          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst), cnt++) {
+            if (cnt == early && tn < p.tiles) issue_halo(tn);
             const int s = wp.s;
             mbar_wait(&w_empty[s], wp.ph ^ 1u);
             mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
             tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
           }
+          if (++tap == 9) tap = 0;
+        }
+        if (early >= nsl && tn < p.tiles) issue_halo(tn);
       }
     }
   } else if (warp == 1) {
@@ -166,7 +187,8 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                                 ((uint64_t)((p.dbg_aligned ? 1024 : C3_HROW) >> 4) << 32);
         const uint64_t b_tmpl = make_smem_desc(0, 128);
         uint32_t first = 0;
-        for (int tap = 0; tap < 9; tap++) {
+        int tap = tap0;
+        for (int j = 0; j < 9; j++, tap = tap == 8 ? 0 : tap + 1) {
           const int ky = tap / 3, kx = tap - ky * 3;
           for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst)) {
             const int s = wp.s;
@@ -199,11 +221,9 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int i = 0;
       for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
-        Tile4D ts, nx;
+        Tile4D ts;
         tile_coords(p, t, ts.x0, ts.y0, ts.b);
-        const int tn = t + 2 * (int)gridDim.x;
-        tile_coords(p, tn < p.tiles ? tn : t, nx.x0, nx.y0, nx.b);
-        produce_tile(ts, nx, i < 2, tn < p.tiles, &tmR, &tmR, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid, 0,
+        produce_tile(ts, &tmR, &tmR, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid, 0,
                      n0, p.BN / CW, k);
       }
     }
@@ -391,6 +411,7 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
   p.trace = gemm_trace_arm(st);
   p.dbg_aligned = getenv("HATB200_C3_ALIGNED") ? atoi(getenv("HATB200_C3_ALIGNED")) : 0;
+  p.rot = getenv("HATB200_C3_ROT") ? atoi(getenv("HATB200_C3_ROT")) : 1;
   const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {

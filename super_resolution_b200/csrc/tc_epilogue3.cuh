@@ -507,25 +507,15 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
 }
 
 // Operand-ring producer of one warpgroup for one tile (one elected thread): residual / CAB-branch chunks.
-// The ring is shallow (2-4 chunks of 8-12 KB per warpgroup), so what a load waits for is one memory latency per
-// `ops` chunks: the warpgroup's NEXT tile (`nx`, when `has_next`) is therefore pulled into L2 while this one is
-// consumed, and the ring loads of the next tile find their lines there instead of in DRAM.
+// (Measured and dropped: L2-prefetching the warpgroup's next tile, and everything of its first tile the ring
+//  cannot hold yet -- 27 MB of prefetch at kernel start delays the first A/B stages by 3-4 us and ring depth
+//  2 -> 4 moves a launch by < 5 %; the epilogue warps wait for accumulators, not for the ring.)
 template <class TS>
-__device__ __forceinline__ void produce_tile(const TS& ts, const TS& nx, bool first, bool has_next, const CUtensorMap* tmR,
+__device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tmR,
                                              const CUtensorMap* tmU, uint8_t* ring,
                                              uint64_t* op_full, uint64_t* op_empty, int ops, int op_stage_bytes,
                                              int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k) {
   const uint32_t bytes = (uint32_t)((has_resid ? 128 * CW * 4 : 0) + (has_u ? 128 * CW * 2 : 0));
-  if (first)                                       // the warpgroup's first tile: everything the ring cannot hold yet
-    for (int ci = ops; ci < nch; ci++) {
-      if (has_resid) ts.prefetch(tmR, n0 + ci * CW);
-      if (has_u) ts.prefetch(tmU, n0 + ci * CW);
-    }
-  if (has_next)
-    for (int ci = 0; ci < nch; ci++) {
-      if (has_resid) nx.prefetch(tmR, n0 + ci * CW);
-      if (has_u) nx.prefetch(tmU, n0 + ci * CW);
-    }
   for (int ci = 0; ci < nch; ci++, k.next(ops)) {
     const int s = k.s;
     mbar_wait(&op_empty[s], k.ph ^ 1u);

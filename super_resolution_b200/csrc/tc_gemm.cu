@@ -65,6 +65,7 @@ struct G3Params {
   int off_b, off_a, off_op, off_stg32, off_stg16, off_tab, smem_bytes;
   int stg_bufs;             // staging buffers per warp and element type (2, or 1 when both types stage in pass 1)
   int share_stg;            // fp32 and bf16 staging alias (pass 1 writes only fp32, pass 2 only bf16)
+  int prof;                      // engineering: epilogue wait-cycle counters on top of the timestamps
   unsigned long long* trace;
 };
 
@@ -193,8 +194,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
-        const Tile2D ts{t * G3_TILE_M}, nx{(t + 2 * (int)gridDim.x) * G3_TILE_M};
-        produce_tile(ts, nx, i < 2, t + 2 * (int)gridDim.x < p.m_tiles, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
+        const Tile2D ts{t * G3_TILE_M};
+        produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
                      p.has_u, n0, p.BN / CW, k);
       }
     }
@@ -212,7 +213,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
     ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
     ws.has_resid = p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
-    ws.prof = p.trace != nullptr;
+    ws.prof = p.trace != nullptr && p.prof;
     ws.hsum = hsum; ws.sred = nullptr;                   // no tile column sums in the 1x1 layers
     ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
     ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
@@ -324,39 +325,59 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   const int rb = p.has_resid ? G3_TILE_M * CW * 4 : 0, ub = p.has_u ? G3_TILE_M * CW * 2 : 0;
   p.op_u_off = rb;
   p.op_stage_bytes = round_up(rb + ub, 1024);
-  // weights resident when the pipeline still gets >= 3 activation stages (>= 2 for short K), else streamed
-  for (int pass = 0; pass < 4; pass++) {
-    const int resident = pass < 2 ? 1 : 0;
-    const int want = (pass & 1) ? 2 : 3;
-    const int stage = G3_TILE_M * G3_BK * 2 + (resident ? 0 : p.BN * 128);
-    const int fixed = tab + stg32 + stg16 + (resident ? round_up(b_bytes, 1024) : 0);
-    int best_ops = -1, best_st = 0;
-    for (int ops = ring ? 3 : 0; ops >= (ring ? 2 : 0); ops--) {
-      const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes;
-      const int st = avail > 0 ? avail / stage : 0;
-      if (st >= want) { best_ops = ops; best_st = st; break; }
+  // Shared-memory plan.  Candidates: weights resident or streamed, staging double or single buffered, operand
+  // ring depth; each leaves some number of activation stages.  The epilogue -- not the MMA -- is the long pole of
+  // the ring kernels (one tile's MMAs take 1-3 us, its epilogue 8-10 us), and what the ring waits for is one
+  // memory latency per `ops` chunks, so ring depth is bought before activation stages beyond 2.
+  static const int force_ops = getenv("HATB200_G3_OPS") ? atoi(getenv("HATB200_G3_OPS")) : 0;          // engineering
+  static const int force_bufs = getenv("HATB200_G3_STGBUFS") ? atoi(getenv("HATB200_G3_STGBUFS")) : 0;
+  static const int force_res = getenv("HATB200_G3_RESIDENT") ? atoi(getenv("HATB200_G3_RESIDENT")) : -1;
+  int best_score = -1;
+  G3Params best = p;
+  for (int resident = 1; resident >= 0; resident--) {
+    if (force_res >= 0 && resident != force_res) continue;
+    for (int bufs = p.stg_bufs; bufs >= 1; bufs--) {
+      if (force_bufs && bufs != force_bufs) continue;
+      const int s32 = stg32 / p.stg_bufs * bufs, s16 = stg16 / p.stg_bufs * bufs;
+      const int stage = G3_TILE_M * G3_BK * 2 + (resident ? 0 : p.BN * 128);
+      const int fixed = tab + s32 + s16 + (resident ? round_up(b_bytes, 1024) : 0);
+      for (int ops = ring ? G3_MAX_OPS : 0; ops >= (ring ? 2 : 0); ops--) {
+        if (force_ops && ring && ops != force_ops) continue;
+        const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes;
+        int st = avail > 0 ? avail / stage : 0;
+        if (st > G3_MAX_STAGES) st = G3_MAX_STAGES;
+        if (st > p.kblocks * 2 && st > 4) st = p.kblocks * 2 > 4 ? p.kblocks * 2 : 4;
+        if (st < 2) continue;
+        // score: ring depth first (x4), then activation stages (capped at 4), resident weights (+3 when K is
+        // short enough that the panel load is not a long prologue), double-buffered staging (+2)
+        const int score = (ring ? 4 * ops : 0) + (st > 4 ? 4 : st) + (resident ? (p.kblocks <= 3 ? 3 : 1) : 0) + 2 * (bufs - 1);
+        if (score > best_score) {
+          best_score = score;
+          best = p;
+          best.b_resident = resident; best.stage_bytes = stage; best.stages = st; best.ops = ops; best.stg_bufs = bufs;
+        }
+      }
     }
-    if (best_ops < 0) continue;
-    if (resident && want == 2 && p.kblocks >= 4) continue;     // long K with a starved ring: stream the weights instead
-    p.b_resident = resident;
-    p.stage_bytes = stage;
-    p.stages = best_st > G3_MAX_STAGES ? G3_MAX_STAGES : best_st;
-    p.ops = best_ops;
-    if (ring) {                                                 // spend what is left on a deeper operand ring
-      int left = G3_SMEM_LIMIT - fixed - 2 * p.ops * p.op_stage_bytes - p.stages * stage;
-      while (p.ops < G3_MAX_OPS && left >= 2 * p.op_stage_bytes) { p.ops++; left -= 2 * p.op_stage_bytes; }
-    }
+  }
+  if (best_score < 0) return false;
+  {
+    const int bufs0 = p.stg_bufs;
+    p = best;
+    const int s32 = stg32 / bufs0 * p.stg_bufs, s16 = stg16 / bufs0 * p.stg_bufs;
+    const int resident = p.b_resident, stage = p.stage_bytes;
+    if (getenv("HATB200_TRACE"))
+      fprintf(stderr, "[gemm_tc] N=%d K=%d BN=%d resident=%d stages=%d ops=%d stg_bufs=%d share=%d\n", p.N, Kpad, p.BN,
+              resident, p.stages, p.ops, p.stg_bufs, p.share_stg);
     int off = 0;
     p.off_b = off; off += resident ? round_up(b_bytes, 1024) : 0;
     p.off_a = off; off += p.stages * stage;
     p.off_op = off; off += 2 * p.ops * p.op_stage_bytes;
-    p.off_stg32 = off; off += stg32;
-    p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += stg16;
+    p.off_stg32 = off; off += s32;
+    p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += s16;
     p.off_tab = off; off += tab;
     p.smem_bytes = off;
     return off <= G3_SMEM_LIMIT;
   }
-  return false;
 }
 
 bool gemm_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
@@ -419,11 +440,12 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     uint32_t box[2] = {w16, 32};
     HB_TRY(tc::make_tmap_bf16(&tmLN, ep.ln_out, 2, dims, str, box, w16 * 2));
   }
-  p.trace = nullptr;
+  p.trace = nullptr; p.prof = 0;
   if (getenv("HATB200_GEMM_TRACE")) {
     if (!g_gemm_trace) HB_CHECK_CUDA(cudaMalloc(&g_gemm_trace, 1024 * 64 * 8));
     HB_CHECK_CUDA(cudaMemsetAsync(g_gemm_trace, 0, 1024 * 64 * 8, st));
     p.trace = g_gemm_trace;
+    p.prof = getenv("HATB200_GEMM_PROF") != nullptr;
   }
   const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;

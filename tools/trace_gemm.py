@@ -37,7 +37,7 @@ else:
     eca = mode == "aggr"
     run = lambda: _lib.check(L.hatb200_linear_fused(p(x), pitch, Cin, B, H, W, p(w), p(b), N, 0, p(r), p(u) if eca else None,
                                                     opitch, p(sc) if eca else None, 0.01, p(o32), None, 0, 0, p(g), p(be),
-                                                    p(lo), opitch, p(hd), p(cs), st))
+                                                    p(lo), opitch, None if eca else p(hd), None if eca else p(cs), st))
 for _ in range(3):
     flush.zero_()
     run()
@@ -51,7 +51,10 @@ rc = lib.hatb200_debug_gemm_trace(buf.ctypes.data, None)
 t = buf.astype(np.int64)
 live = t[:, 0] > 0
 t0 = t[live, 0].min()
-print(mode, Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
+knobs = " ".join(f"{k[8:]}={v}" for k, v in os.environ.items() if k.startswith("HATB200_G3") or k.startswith("HATB200_EPI"))
+print(mode, Cin, N, "ctas", live.sum(), "span us", (t[live, :56].max() - t0) / 1000, "[" + knobs + "]")
+if not os.environ.get("VERBOSE"):
+    sys.exit(0)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
     r_ = t[cta]
     ev = {k: int(r_[k] - t0) for k in range(56) if r_[k] > 0}
