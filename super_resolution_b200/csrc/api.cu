@@ -1,6 +1,7 @@
 // api.cu -- C ABI of libhatb200: handle lifetime, state_dict registry, weight packing.
 // (forward orchestration lives in forward.cu.)
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "model.cuh"
@@ -9,6 +10,12 @@ namespace hb {
 
 static thread_local char g_err[1024] = "";
 thread_local int g_launches = 0;
+
+// HATB200_PDL=0 launches every kernel fully serialised (bisecting aid); default on
+bool pdl_enabled() {
+  static const bool on = !(getenv("HATB200_PDL") && getenv("HATB200_PDL")[0] == '0');
+  return on;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;

@@ -49,6 +49,28 @@ extern thread_local int g_launches;   // kernels launched since last reset
     if (_r != 0) return _r;                                                        \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------------------
+// The forward is ~290 dependent launches of 10-50 us kernels.  A kernel launched through launch_pdl() may start
+// while its predecessor in the stream is still draining: its prologue (barrier init, TMEM allocation, tensor-map
+// prefetch, parameter tables, resident weight panels -- nothing a predecessor writes) overlaps that tail.
+// Contract for every kernel launched this way: pdl_wait() before the first access to memory another kernel of
+// the forward produces and before the first global store; pdl_trigger() right after it, so at most one
+// successor is in flight.  Launched without the attribute (HATB200_PDL=0) both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline int round_up(int a, int b) { return cdiv(a, b) * b; }
 

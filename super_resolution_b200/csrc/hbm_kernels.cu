@@ -76,6 +76,8 @@ dwgate_bf16_kernel(const __grid_constant__ CUtensorMap tmIn, int H, int W, int h
   if (threadIdx.x == 0) {
     tc::mbar_init(&bar, 1);
     tc::fence_barrier_init();
+    pdl_wait();                     // fc1's output; the weight registers below load meanwhile
+    pdl_trigger();
     tc::mbar_arrive_expect_tx(&bar, 2 * DW_HALF_BYTES);
     tc::tma_load_4d(sp, &tmIn, &bar, c0, x0 - 1, y0 - 1, b);
     tc::tma_load_4d(sg, &tmIn, &bar, hid + c0, x0 - 1, y0 - 1, b);
@@ -105,6 +107,7 @@ dwgate_bf16_kernel(const __grid_constant__ CUtensorMap tmIn, int H, int W, int h
 #pragma unroll
     for (int p = 0; p < DW_PX; p++) { ap[s][p] = bp; ag[s][p] = bg; }
   __syncthreads();                                                // barrier initialised and armed (block-uniform point)
+  pdl_wait();                                                     // every thread stores: the previous kernel must be done
   tc::mbar_wait(&bar, 0);
   if (!active) {
     if (c < out_pitch)
@@ -178,7 +181,7 @@ int launch_dwgate_bf16(const bf16* in, int in_pitch, int B, int H, int W, int hi
     attr = true;
   }
   dim3 grid((W / DW_TW) * (H / DW_TH), cdiv(out_pitch, DW_CC), B);
-  dwgate_bf16_kernel<<<grid, DW_THREADS, DW_SMEM, st>>>(tm, H, W, hid, w, b, out, out_pitch);
+  launch_pdl(dwgate_bf16_kernel, grid, dim3(DW_THREADS), DW_SMEM, st, tm, H, W, hid, w, b, out, out_pitch);
   HB_CHECK_LAUNCH();
   return 0;
 }

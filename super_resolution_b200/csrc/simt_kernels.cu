@@ -302,6 +302,8 @@ __global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk,
                                   const float* __restrict__ w5, float* __restrict__ scale) {
   extern __shared__ float mean[];  // C
   int b = blockIdx.x;
+  pdl_wait();
+  pdl_trigger();
   for (int c = threadIdx.x; c < C; c += blockDim.x) mean[c] = chunk_sum(partial + (size_t)b * nchunk * C + c, nchunk, C) * inv_hw;
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -317,7 +319,7 @@ __global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk,
 
 int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
                       cudaStream_t st) {
-  eca_finish_kernel<<<B, 256, C * sizeof(float), st>>>(partial, nchunk, C, 1.0f / (float)HW, w5, scale);
+  launch_pdl(eca_finish_kernel, dim3(B), dim3(256), C * sizeof(float), st, partial, nchunk, C, 1.0f / (float)HW, w5, scale);
   HB_CHECK_LAUNCH();
   return 0;
 }
@@ -331,6 +333,8 @@ __global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk,
   __shared__ float mean[64];
   __shared__ float hid[32];
   int b = blockIdx.x, half = pdim / 2;
+  pdl_wait();
+  pdl_trigger();
   for (int c = threadIdx.x; c < pdim; c += blockDim.x)
     mean[c] = chunk_sum(partial + (size_t)b * nchunk * pdim + c, nchunk, pdim) * inv_hw;
   __syncthreads();
@@ -350,7 +354,7 @@ __global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk,
 int launch_dyn_finish(const float* partial, int nchunk, int B, int pdim, int HW, const float* w1, const float* b1,
                       const float* w2, const float* b2, float* dyn, cudaStream_t st) {
   HB_REQUIRE(pdim <= 64 && pdim % 2 == 0, HATB200_EUNSUPPORTED, "esc pdim=%d unsupported", pdim);
-  dyn_finish_kernel<<<B, 160, 0, st>>>(partial, nchunk, pdim, 1.0f / (float)HW, w1, b1, w2, b2, dyn);
+  launch_pdl(dyn_finish_kernel, dim3(B), dim3(160), 0, st, partial, nchunk, pdim, 1.0f / (float)HW, w1, b1, w2, b2, dyn);
   HB_CHECK_LAUNCH();
   return 0;
 }

@@ -97,6 +97,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();
+  pdl_trigger();
   const uint32_t tmem_base = tmem_slot;
   const int wins = p.nwx * p.nwy;
 
@@ -329,7 +331,7 @@ int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st) {
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   int grid = p.units < sms ? p.units : sms;
-  attn_tc_kernel<<<grid, AT_THREADS, SMEM_BYTES, st>>>(tmQ, tmKV, p);
+  launch_pdl(attn_tc_kernel, dim3(grid), dim3(AT_THREADS), SMEM_BYTES, st, tmQ, tmKV, p);
   HB_CHECK_LAUNCH();
   return 0;
 }

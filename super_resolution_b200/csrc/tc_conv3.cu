@@ -131,6 +131,8 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // (the single issuing thread is picked with elect.sync, not `lane == 0`: ptxas then knows the region is
     //  one-thread and emits UTMALDG / UTCHMMA straight from uniform registers instead of a per-lane waterfall loop)
     if (elect_one()) {
+      pdl_wait();        // halos are the previous kernel's output
+      pdl_trigger();
       RingPos hp, wp;
       auto issue_halo = [&](int t) {
         int x0, y0, b;
@@ -216,6 +218,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int g = warp - 10;
     if (feat_ring<F>() && p.has_resid && elect_one()) {
       prefetch_tmap(&tmR);
+      pdl_wait();
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       RingPos k;
       int i = 0;
@@ -251,6 +254,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (ep.out_t) prefetch_tmap(&tmOT);
       if (ep.ln_out) prefetch_tmap(&tmLN);
     }
+    pdl_wait();          // the epilogue writes the outputs (and reads the residual ring)
     int i = 0;
     for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
       if ((i & 1) != g) continue;
@@ -430,8 +434,8 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   dim3 grid(per_n, n_tiles);
 #define C3_LAUNCH(F_)                                                                                              \
   do {                                                                                                             \
-    if (grouped) conv3_tc_kernel<F_, true><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
-    else conv3_tc_kernel<F_, false><<<grid, C3_THREADS, smem, st>>>(tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
+    if (grouped) launch_pdl(conv3_tc_kernel<F_, true>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
+    else launch_pdl(conv3_tc_kernel<F_, false>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
   } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {

@@ -140,6 +140,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < p.kblocks; kb++)
           tma_load_2d(smem + p.off_b + (size_t)kb * p.BN * 128, &tmB, &b_bar, kb * G3_BK, n0);
       }
+      pdl_wait();        // weights are parameters; activations come from the previous kernel
+      pdl_trigger();
       const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
       RingPos rp;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
@@ -157,6 +159,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===== MMA issuer (one elected thread) =====
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(G3_TILE_M, p.BN);
+      pdl_wait();
       G3_TRACE(0);
       if (p.b_resident) mbar_wait(&b_bar, 0);
       G3_TRACE(1);
@@ -189,6 +192,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (feat_ring<F>() && (p.has_resid || p.has_u) && elect_one()) {
       if (p.has_resid) prefetch_tmap(&tmR);
       if (p.has_u) prefetch_tmap(&tmU);
+      pdl_wait();
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       RingPos k;
       int i = 0;
@@ -223,6 +227,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (ep.out_t) prefetch_tmap(&tmOT);
       if (ep.ln_out) prefetch_tmap(&tmLN);
     }
+    pdl_wait();          // the epilogue reads the ECA gate / ring operands and writes the outputs
     int i = 0;
     for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
       if ((i & 1) != g) continue;
@@ -467,8 +472,8 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   // epilogue specialisation: the first compile-time feature set that covers this layer exactly, else the generic one
 #define G3_LAUNCH(F_)                                                                                                \
   do {                                                                                                               \
-    if (grouped) gemm_tc_kernel<F_, true><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
-    else gemm_tc_kernel<F_, false><<<grid, G3_THREADS, smem, st>>>(tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);       \
+    if (grouped) launch_pdl(gemm_tc_kernel<F_, true>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
+    else launch_pdl(gemm_tc_kernel<F_, false>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);       \
   } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;     // engineering: A/B the specialisation
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {

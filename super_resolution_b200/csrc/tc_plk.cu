@@ -73,14 +73,20 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
 
   if (warp == 0) {
     if (elect_one()) {
-      mbar_arrive_expect_tx(&halo_bar, HALO_BYTES);
-      tma_load_4d(sm_h, &tmX, &halo_bar, 0, gx0, y0 - PH, b);
-      for (int dy = 0; dy < PK; dy++) {
+      // the first ring fill is weights only (parameters): it may run ahead of the previous kernel's completion
+      auto issue_w = [&](int dy) {
         const int s = dy % B_STAGES;
         mbar_wait(&empty_bar[s], (((uint32_t)(dy / B_STAGES)) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&full_bar[s], BST_BYTES);
         for (int kb = 0; kb < 4; kb++) tma_load_2d(sm_b + s * BST_BYTES + kb * 8192, &tmW, &full_bar[s], kb * 64, dy * 64);
-      }
+      };
+      const int pre = B_STAGES < PK ? B_STAGES : PK;
+      for (int dy = 0; dy < pre; dy++) issue_w(dy);
+      pdl_wait();
+      pdl_trigger();
+      mbar_arrive_expect_tx(&halo_bar, HALO_BYTES);
+      tma_load_4d(sm_h, &tmX, &halo_bar, 0, gx0, y0 - PH, b);
+      for (int dy = pre; dy < PK; dy++) issue_w(dy);
     }
   } else if (warp == 1) {
     if (elect_one()) {
@@ -115,6 +121,7 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     const int row = quarter * 32 + lane;
     const int y = y0 + row / TGX, x = (gx0 + row % TGX) * 4;
     const int WP = p.W + 2 * PH;
+    pdl_wait();          // reads the per-sample dynamic kernels and the padded head, writes the output
     mbar_wait(&done_bar, 0);
     tc_fence_after();
     const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
@@ -243,7 +250,7 @@ int launch_plk_tc(const bf16* xpad, int B, int H, int W, const bf16* wt, const f
     HB_CHECK_CUDA(cudaFuncSetAttribute(plk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PLK_SMEM));
     attr_set = true;
   }
-  plk_tc_kernel<<<B * p.tiles_x * p.tiles_y, PLK_THREADS, PLK_SMEM, st>>>(tmX, tmW, p);
+  launch_pdl(plk_tc_kernel, dim3(B * p.tiles_x * p.tiles_y), dim3(PLK_THREADS), PLK_SMEM, st, tmX, tmW, p);
   HB_CHECK_LAUNCH();
   return 0;
 }

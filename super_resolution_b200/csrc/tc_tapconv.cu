@@ -73,6 +73,8 @@ tapconv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();
+  pdl_trigger();
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
@@ -257,7 +259,7 @@ int launch_tapconv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, cons
     smem_attr = 227 * 1024;
   }
   dim3 grid(a.B * p.tiles_x * p.tiles_y, Npad / p.BN);
-  tapconv_tc_kernel<<<grid, TC_THREADS, smem, st>>>(tmA, tmB, p, ep);
+  launch_pdl(tapconv_tc_kernel, grid, dim3(TC_THREADS), smem, st, tmA, tmB, p, ep);
   HB_CHECK_LAUNCH();
   return 0;
 }
