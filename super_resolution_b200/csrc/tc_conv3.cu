@@ -19,6 +19,15 @@
 //     {cols, 8 x, 4 y}, pool partials, row-local LayerNorm + 16-channel head).
 // Warp roles (384 threads): 0 TMA producer (halos, weights), 1 MMA issuer + TMEM owner, 2-5 / 6-9 epilogue
 // warpgroups, 10 / 11 operand-ring producers.
+//
+// CTA pairs (template TWO, the default when the tile count is even): the one-CTA main loop is bound by shared-memory
+// bandwidth, not by the tensor pipe -- an M=128 x N MMA re-reads 4 KB of A and N*32 B of B per k-step while TMA writes
+// the next weight slice into the same banks (N=192: 107 + 64 B/clk of 128; N=64: 192 B/clk), measured as 330-370 ns
+// per 24 KB slice against 195 ns of tensor time.  With tcgen05 cta_group::2 the two SMs of a TPC run one M=256 MMA
+// over two tiles: each CTA keeps its own halo and accumulator rows but only HALF of every weight slice, so the
+// weight bytes written to and read from each SM's shared memory halve.  Rank 0 issues all MMAs; both producers load
+// into their own shared memory with the bytes completing on rank 0's full barriers; commits multicast to the
+// empty / accumulator-full barriers of both CTAs; both epilogues arrive on rank 0's accumulator-empty barrier.
 // Replaces F.conv2d at hat_arch.py:84-86 (CAB), :544 (RHAG conv), :854 (conv_after_body), :855 (conv_before_upsample).
 #include <stdlib.h>
 
@@ -38,7 +47,7 @@ __device__ __forceinline__ unsigned long long c3_time() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-#define C3_TRACE(slot) do { if (p.trace) p.trace[(size_t)blockIdx.x * 64 + (slot)] = c3_time(); } while (0)
+#define C3_TRACE(slot) do { if (p.trace) { p.trace[(size_t)blockIdx.x * 64 + (slot)] = c3_time(); p.trace[(size_t)blockIdx.x * 64 + 32 + (slot)] = (unsigned long long)clock64(); } } while (0)
 
 constexpr int C3_THREADS = 384;
 constexpr int C3_TW = 8, C3_TH = 16;                   // tile: 128 pixels = UMMA M
@@ -53,14 +62,13 @@ struct C3Params {
   int a_coff, kblocks;
   int N, BN, Npad;
   int hst, halo_stage_bytes;     // halo stages, kblocks * C3_HALO_KB
-  int wst, w_stage_bytes;        // weight ring, BN * 128
+  int wst, w_stage_bytes, grp;   // weight ring: stages of grp slices of BN (BN / 2 for a CTA pair) x 128 bytes
   int ops, op_stage_bytes, op_u_off, has_resid, has_u;
   uint32_t acc_stride, tmem_cols;
   int off_halo, off_w, off_op, off_stg32, off_stg16, off_tab, off_sred, smem_bytes;
   int stg_bufs, share_stg;
   unsigned long long* trace;     // engineering: per-CTA timestamps (HATB200_GEMM_TRACE)
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
-  int dbg_aligned;               // engineering: 1024-aligned A descriptors (wrong results; timing experiment)
 };
 
 __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
@@ -71,7 +79,7 @@ __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, i
 
 }  // namespace
 
-template <class F, bool GROUPED>
+template <class F, bool GROUPED, bool TWO>
 __global__ void __launch_bounds__(C3_THREADS, 1)
 conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmOF,
@@ -92,6 +100,10 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.y * p.BN;
+  // CTA pair: rank r of cluster q takes tile 2 * pair + r of every pair the cluster walks
+  const uint32_t rank = TWO ? cluster_ctarank() : 0u;
+  const int t_first = TWO ? (int)(blockIdx.x & ~1u) + (int)rank : (int)blockIdx.x;
+  const int t_step = (int)gridDim.x;
   float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);
   float* tab_gamma = tab_bias + p.BN;
   float* tab_beta = tab_gamma + p.BN;
@@ -104,7 +116,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int s = 0; s < p.wst; s++) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int g = 0; g < 2; g++) {
       mbar_init(&tmem_full_bar[g], 1);
-      mbar_init(&tmem_empty_bar[g], 128);
+      mbar_init(&tmem_empty_bar[g], TWO ? 256 : 128);
       for (int s = 0; s < MAX_OPS; s++) { mbar_init(&op_full[g][s], 1); mbar_init(&op_empty[g][s], 4); }
     }
     fence_barrier_init();
@@ -116,16 +128,20 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     tab_gamma[i] = (ok && ep.ln_gamma) ? __ldg(ep.ln_gamma + n) : 0.f;
     tab_beta[i] = (ok && ep.ln_beta) ? __ldg(ep.ln_beta + n) : 0.f;
   }
-  if (warp == 1) tmem_alloc(&tmem_slot, p.tmem_cols);
+  if (warp == 1) {
+    if (TWO) tmem_alloc2(&tmem_slot, p.tmem_cols);
+    else tmem_alloc(&tmem_slot, p.tmem_cols);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all();        // the peer's barriers are initialised before anything remote touches them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   // All CTAs stream the same 9 * kblocks weight slices per tile; each starts at a different tap (and wraps) so that
   // 148 SMs do not ask the same L2 lines for the same slice at the same moment.  The accumulation order of a tile
   // then depends on its CTA: results stay deterministic, sums differ in the last fp32 bit between tiles.
   const int nsl = 9 * p.kblocks;
-  const int tap0 = p.rot ? (int)(blockIdx.x % 9u) : 0;
+  const int tap0 = p.rot ? (int)((TWO ? blockIdx.x >> 1 : blockIdx.x) % 9u) : 0;
   if (warp == 0) {
     // ===== TMA producer: one halo per tile (kblocks boxes), 9 * kblocks weight slices per tile =====
     // (the single issuing thread is picked with elect.sync, not `lane == 0`: ptxas then knows the region is
@@ -140,27 +156,45 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int hs = hp.s;
         mbar_wait(&halo_empty[hs], hp.ph ^ 1u);
         uint8_t* hb_ = smem + p.off_halo + (size_t)hs * p.halo_stage_bytes;
-        mbar_arrive_expect_tx(&halo_full[hs], (uint32_t)(p.kblocks * C3_HH * C3_HW * 128));
-        for (int kb = 0; kb < p.kblocks; kb++)
-          tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
+        const uint32_t hbytes = (uint32_t)(p.kblocks * C3_HH * C3_HW * 128);
+        if (TWO) {       // both halos of the pair complete on rank 0's barrier
+          if (rank == 0) mbar_arrive_expect_tx(&halo_full[hs], 2 * hbytes);
+          const uint32_t bar0 = mapa_u32(&halo_full[hs], 0);
+          for (int kb = 0; kb < p.kblocks; kb++)
+            tma2_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, bar0, p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
+        } else {
+          mbar_arrive_expect_tx(&halo_full[hs], hbytes);
+          for (int kb = 0; kb < p.kblocks; kb++)
+            tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
+        }
         hp.next(p.hst);
       };
       // The next tile's halo is requested once `early` weight slices of this tile are on their way: by then the
       // previous tile has released the other halo stage, and the load has most of a tile's MMAs to land.  (Issued
       // after the last slice instead, it costs ~1 us of idle tensor pipe per tile; with a single halo stage it
       // has to wait for this tile's MMAs and can only go last.)
-      const int early = p.hst > 1 ? (p.wst < nsl - 1 ? p.wst : nsl - 1) : nsl;
-      if ((int)blockIdx.x < p.tiles) issue_halo(blockIdx.x);
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
-        const int tn = t + gridDim.x;
-        int cnt = 0, tap = tap0;
+      // A ring stage carries `grp` consecutive weight slices (one full barrier, one release): see the MMA issuer.
+      const int early = p.hst > 1 ? (p.wst * p.grp < nsl - 1 ? p.wst * p.grp : nsl - 1) : nsl;
+      const uint32_t slice_bytes = (uint32_t)(p.w_stage_bytes / p.grp);
+      if (t_first < p.tiles) issue_halo(t_first);
+      for (int t = t_first; t < p.tiles; t += t_step) {
+        const int tn = t + t_step;
+        int cnt = 0, tap = tap0, q = 0;
         for (int j = 0; j < 9; j++) {
-          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst), cnt++) {
+          for (int kb = 0; kb < p.kblocks; kb++, cnt++) {
             if (cnt == early && tn < p.tiles) issue_halo(tn);
             const int s = wp.s;
-            mbar_wait(&w_empty[s], wp.ph ^ 1u);
-            mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
-            tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
+            uint8_t* dst = smem + p.off_w + (size_t)s * p.w_stage_bytes + (size_t)q * slice_bytes;
+            if (q == 0) {
+              mbar_wait(&w_empty[s], wp.ph ^ 1u);
+              if (!TWO) mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+              else if (rank == 0) mbar_arrive_expect_tx(&w_full[s], 2u * (uint32_t)p.w_stage_bytes);
+            }
+            if (TWO)     // this CTA's half of the slice (rows [rank * BN/2, +BN/2)); both halves complete on rank 0
+              tma2_load_2d(dst, &tmB, mapa_u32(&w_full[s], 0), kb * 64, tap * p.Npad + n0 + (int)rank * (p.BN / 2));
+            else
+              tma_load_2d(dst, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
+            if (++q == p.grp) { q = 0; wp.next(p.wst); }
           }
           if (++tap == 9) tap = 0;
         }
@@ -168,49 +202,86 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (one elected thread) =====
-    if (elect_one()) {
-      const uint32_t idesc = make_idesc_bf16(128, p.BN);
-      RingPos hp, wp;
+    // ===== MMA issuer: the whole warp walks the loop so that ring cursors, descriptors and barrier addresses stay
+    // warp-uniform (uniform registers, no R2UR per operand); one elected lane issues each tcgen05 instruction =====
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_bf16(TWO ? 256 : 128, p.BN);
+      // The instructions this warp executes between two MMA groups are NOT hidden by the tensor pipe: tcgen05.mma
+      // issue blocks on a queue about two MMAs deep, and a per-slice iteration (barrier poll, fence, descriptor
+      // assembly, R2UR moves, commit, ring step) costs ~200 cycles against 4 x 48 (N = 64) / 4 x 96 (N = 192) cycles
+      // of MMAs -- B200 trace: 225 / 330 ns per slice, 95 / 110 cycles per MMA even with the ring removed.  So a ring
+      // stage carries `grp` slices (12 MMAs for grp = 3) behind ONE barrier poll and ONE commit, and everything else
+      // is stepped incrementally out of registers.
+      const uint32_t full0 = smem_u32(&w_full[0]), empty0 = smem_u32(&w_empty[0]);
+      const uint32_t wb0 = (smem_u32(smem + p.off_w) & 0x3FFFF) >> 4;
+      const int wst = p.wst, kblocks = p.kblocks, grp = p.grp;
+      const uint32_t wslice = (uint32_t)(p.w_stage_bytes / grp) >> 4;
+      // A descriptor template: 128-byte swizzled rows, 8-row groups one halo image row (C3_HROW bytes) apart
+      const uint64_t a_tmpl = (make_smem_desc(0, 128) & ~(0x3FFFull << 32)) | ((uint64_t)(C3_HROW >> 4) << 32);
+      const uint64_t b_tmpl = make_smem_desc(0, 128);
+      uint32_t full_a = full0, empty_a = empty0, wb = wb0, wph = 0;
+      int ws_i = 0;
+      RingPos hp;
       int i = 0;
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++, hp.next(p.hst)) {
+      for (int t = t_first; t < p.tiles; t += t_step, i++, hp.next(p.hst)) {
         const int g = i & 1;
-        if (i < 4) C3_TRACE(4 * i);
+        if (i < 4 && lane == 0) C3_TRACE(4 * i);
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
         const int hs = hp.s;
-        if (i < 4) C3_TRACE(4 * i + 1);
+        if (i < 4 && lane == 0) C3_TRACE(4 * i + 1);
         mbar_wait(&halo_full[hs], hp.ph);
         tc_fence_after();
-        if (i < 4) C3_TRACE(4 * i + 2);
+        if (i < 4 && lane == 0) C3_TRACE(4 * i + 2);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
-        const uint32_t h_addr = smem_u32(smem + p.off_halo + (size_t)hs * p.halo_stage_bytes);
-        // A descriptor template: 128-byte swizzled rows, 8-row groups one halo image row (C3_HROW bytes) apart
-        const uint64_t a_tmpl = (make_smem_desc(0, 128) & ~(0x3FFFull << 32)) |
-                                ((uint64_t)((p.dbg_aligned ? 1024 : C3_HROW) >> 4) << 32);
-        const uint64_t b_tmpl = make_smem_desc(0, 128);
+        const uint32_t ha = (smem_u32(smem + p.off_halo + (size_t)hs * p.halo_stage_bytes) & 0x3FFFF) >> 4;
         uint32_t first = 0;
-        int tap = tap0;
-        for (int j = 0; j < 9; j++, tap = tap == 8 ? 0 : tap + 1) {
-          const int ky = tap / 3, kx = tap - ky * 3;
-          for (int kb = 0; kb < p.kblocks; kb++, wp.next(p.wst)) {
-            const int s = wp.s;
-            mbar_wait(&w_full[s], wp.ph);
-            tc_fence_after();
-            // accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx
-            const uint32_t sa = p.dbg_aligned ? h_addr + (uint32_t)(kb * C3_HALO_KB + tap * 1024)
-                                              : h_addr + (uint32_t)(kb * C3_HALO_KB + (ky * C3_HW + kx) * 128);
-            const uint32_t sb = smem_u32(smem + p.off_w + (size_t)s * p.w_stage_bytes);
-            const uint64_t ad = a_tmpl | (uint64_t)((sa & 0x3FFFF) >> 4);
-            const uint64_t bd = b_tmpl | (uint64_t)((sb & 0x3FFFF) >> 4);
+        int ky = tap0 / 3, kx = tap0 - ky * 3, q = 0;
+        for (int j = 0; j < 9; j++) {
+          // accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx
+          uint32_t a_lo = ha + (uint32_t)((ky * C3_HW + kx) * (128 >> 4));
+          for (int kb = 0; kb < kblocks; kb++) {
+            if (q == 0) {
+              mbar_wait_a(full_a, wph);
+              tc_fence_after();
+            }
+            const uint64_t ad = a_tmpl | (uint64_t)a_lo, bd = b_tmpl | (uint64_t)wb;
+            const bool last = q == grp - 1;
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, first | (uint32_t)k);
+              for (int k = 0; k < 4; k++) {
+                if (TWO) umma2_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, first | (uint32_t)k);
+                else umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, first | (uint32_t)k);
+              }
+              if (last) {                              // frees the ring stage once its MMAs have read it
+                if (TWO) umma2_commit_a(empty_a);
+                else umma_commit_a(empty_a);
+              }
+            }
+            __syncwarp();
             first = 1;
-            umma_commit(&w_empty[s]);         // frees the weight slot once these MMAs have read it
+            a_lo += (uint32_t)(C3_HALO_KB >> 4);
+            wb += wslice;
+            if (last) {
+              q = 0;
+              full_a += 8; empty_a += 8;
+              if (++ws_i == wst) { ws_i = 0; full_a = full0; empty_a = empty0; wb = wb0; wph ^= 1u; }
+            } else {
+              q++;
+            }
+          }
+          if (++kx == 3) { kx = 0; if (++ky == 3) ky = 0; }
+        }
+        if (i < 4 && lane == 0) C3_TRACE(4 * i + 3);
+        if (elect_one()) {
+          if (TWO) {
+            umma2_commit(&halo_empty[hs]);
+            umma2_commit(&tmem_full_bar[g]);
+          } else {
+            umma_commit(&halo_empty[hs]);     // halo may be overwritten
+            umma_commit(&tmem_full_bar[g]);   // accumulator of tile i complete
           }
         }
-        if (i < 4) C3_TRACE(4 * i + 3);
-        umma_commit(&halo_empty[hs]);         // halo may be overwritten
-        umma_commit(&tmem_full_bar[g]);       // accumulator of tile i complete
+        __syncwarp();
       }
     }
   } else if (warp >= 10) {
@@ -222,7 +293,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       RingPos k;
       int i = 0;
-      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+      for (int t = t_first; t < p.tiles; t += t_step, i++) {
         if ((i & 1) != g) continue;
         Tile4D ts;
         tile_coords(p, t, ts.x0, ts.y0, ts.b);
@@ -255,8 +326,9 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (ep.ln_out) prefetch_tmap(&tmLN);
     }
     pdl_wait();          // the epilogue writes the outputs (and reads the residual ring)
+    const uint32_t empty0[2] = {TWO ? mapa_u32(&tmem_empty_bar[0], 0) : 0u, TWO ? mapa_u32(&tmem_empty_bar[1], 0) : 0u};
     int i = 0;
-    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x, i++) {
+    for (int t = t_first; t < p.tiles; t += t_step, i++) {
       if ((i & 1) != g) continue;
       Tile4D ts;
       tile_coords(p, t, ts.x0, ts.y0, ts.b);
@@ -274,20 +346,26 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (tr) C3_TRACE(17 + 4 * i);
       run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[g]);
+      if (TWO) mbar_arrive_cluster(empty0[g]);      // rank 0 issues the next MMAs into both CTAs' stage g
+      else mbar_arrive(&tmem_empty_bar[g]);
       if (tr) C3_TRACE(18 + 4 * i);
     }
     if (elect_one()) bulk_wait_all();
   }
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all();        // the peer may still read this CTA's operands / arrive on its barriers
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if (TWO) tmem_dealloc2(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
 // ---- host ------------------------------------------------------------------------------------------
+// set when a cluster launch was refused (no co-schedulable SM pairs, e.g. a partitioned GPU): one-CTA kernels from then on
+static bool g_c3_pairs_failed = false;
+
 static int c3_sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -299,7 +377,8 @@ static int c3_sm_count() {
   return n;
 }
 
-static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep, C3Params& p, bool& grouped) {
+static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep, C3Params& p, bool& grouped,
+                           bool& two) {
   if (a.KH != 3 || a.KW != 3) return false;
   if (a.W % C3_TW || a.H % C3_TH) return false;
   if (Kpad % 64 || Kpad < a.Cin) return false;
@@ -319,6 +398,9 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
   p.tiles_x = a.W / C3_TW; p.tiles_y = a.H / C3_TH; p.tiles = a.B * p.tiles_x * p.tiles_y;
   p.a_coff = a.a_coff; p.kblocks = Kpad / 64;
   p.N = a.N; p.Npad = Npad;
+  // CTA pairs need an even tile count (both ranks walk the same number of tiles) and an even number of CTAs per n-tile
+  static const bool two_off = getenv("HATB200_C3_TWO") && getenv("HATB200_C3_TWO")[0] == '0';
+  two = !two_off && !g_c3_pairs_failed && p.tiles % 2 == 0 && p.tiles >= 2 && c3_sm_count() / (Npad / p.BN) >= 2;
   p.acc_stride = (uint32_t)round_up(p.BN, 32);
   uint32_t cols = 32;
   while (cols < 2 * p.acc_stride) cols <<= 1;
@@ -334,22 +416,29 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
   p.op_u_off = 128 * CW * 4;
   p.op_stage_bytes = ring ? 128 * CW * 4 : 0;
   p.halo_stage_bytes = p.kblocks * C3_HALO_KB;
-  p.w_stage_bytes = p.BN * 128;
+  const int slice_bytes = (two ? p.BN / 2 : p.BN) * 128;     // a CTA of a pair holds half of every weight slice
   p.ops = ring ? 2 : 0;
-  // prefer double-buffered halos and double-buffered staging; give what is left to the weight ring (>= 3 slices)
-  for (int pass = 0; pass < 8; pass++) {
+  // Prefer ring stages of 3 slices (>= 2 of them: one barrier round trip per 12 MMAs), double-buffered halos and
+  // double-buffered staging; fall back to single-slice stages (>= 3) before giving up the second halo buffer.
+  static const int force_grp = getenv("HATB200_C3_GRP") ? atoi(getenv("HATB200_C3_GRP")) : 0;
+  for (int pass = 0; pass < 16; pass++) {
     static const int force_hst = getenv("HATB200_C3_HST") ? atoi(getenv("HATB200_C3_HST")) : 0;
     static const int force_bufs = getenv("HATB200_C3_BUFS") ? atoi(getenv("HATB200_C3_BUFS")) : 0;
-    int hst = (pass & 2) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2;
-    const int want = pass < 4 ? 3 : 2;
+    // pass order: (grp 3, hst 2, bufs 2/1), (grp 1, hst 2, bufs 2/1), (grp 3, hst 1, ..), (grp 1, hst 1, ..), then want - 1
+    int grp = (pass & 2) ? 1 : 3;
+    int hst = (pass & 4) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2;
+    if (force_grp) grp = force_grp;
+    const int want = (grp == 3 ? 2 : 3) - (pass >= 8 ? 1 : 0);
     if (force_hst) hst = force_hst;
     if (force_bufs) bufs = force_bufs;
+    p.grp = grp;
+    p.w_stage_bytes = grp * slice_bytes;
     const int stg32 = f32o ? 8 * bufs * 32 * (grouped ? 128 : 64) : 0;
     const int stg16 = bf16o && !p.share_stg ? 8 * bufs * 32 * (grouped ? 128 : 32) : 0;
     const int fixed = tab + sred + stg32 + stg16 + 2 * p.ops * p.op_stage_bytes + hst * p.halo_stage_bytes;
     const int avail = C3_SMEM_LIMIT - fixed;
     const int wst = avail > 0 ? avail / p.w_stage_bytes : 0;
-    if (wst < want) continue;
+    if (wst < want || wst < 1) continue;
     p.hst = hst; p.stg_bufs = bufs;
     p.wst = wst > C3_MAX_WST ? C3_MAX_WST : wst;
     if (ring) {                      // spend what is left on a deeper operand ring
@@ -365,6 +454,9 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
     p.off_tab = off; off += tab;
     p.off_sred = off; off += sred;
     p.smem_bytes = off;
+    if (getenv("HATB200_TRACE"))
+      fprintf(stderr, "[conv3_tc] N=%d K=%d BN=%d two=%d grp=%d wst=%d hst=%d stg_bufs=%d ops=%d smem=%d\n", p.N, Kpad, p.BN,
+              (int)two, p.grp, p.wst, p.hst, p.stg_bufs, p.ops, p.smem_bytes);
     return off <= C3_SMEM_LIMIT;
   }
   return false;
@@ -372,8 +464,8 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
 
 bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
   C3Params p;
-  bool grouped;
-  if (!conv3_geometry(a, Npad, Kpad, ep, p, grouped)) return false;
+  bool grouped, two;
+  if (!conv3_geometry(a, Npad, Kpad, ep, p, grouped, two)) return false;
   if (tc::encode_tiled_fn() == nullptr) return false;
   const char* v = getenv("HATB200_CONV3");
   if (v && *v == '0') return false;
@@ -382,8 +474,8 @@ bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& e
 
 int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
   C3Params p;
-  bool grouped;
-  HB_REQUIRE(conv3_geometry(a, Npad, Kpad, ep, p, grouped), HATB200_EUNSUPPORTED, "conv3_tc: unsupported shape");
+  bool grouped, two;
+  HB_REQUIRE(conv3_geometry(a, Npad, Kpad, ep, p, grouped, two), HATB200_EUNSUPPORTED, "conv3_tc: unsupported shape");
   CUtensorMap tmA, tmB, tmR, tmOF, tmOT, tmLN;
   {
     uint64_t dims[4] = {(uint64_t)a.a_pitch, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
@@ -394,7 +486,7 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   {
     uint64_t dims[2] = {(uint64_t)Kpad, (uint64_t)9 * Npad};
     uint64_t str[1] = {(uint64_t)Kpad * 2};
-    uint32_t box[2] = {64, (uint32_t)p.BN};
+    uint32_t box[2] = {64, (uint32_t)(two ? p.BN / 2 : p.BN)};
     HB_TRY(tc::make_tmap_bf16(&tmB, w, 2, dims, str, box, 128));
   }
   tmR = tmA; tmOF = tmA; tmOT = tmA; tmLN = tmA;      // placeholders for absent operands (never dereferenced)
@@ -414,28 +506,35 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   }
   if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
   p.trace = gemm_trace_arm(st);
-  p.dbg_aligned = getenv("HATB200_C3_ALIGNED") ? atoi(getenv("HATB200_C3_ALIGNED")) : 0;
   p.rot = getenv("HATB200_C3_ROT") ? atoi(getenv("HATB200_C3_ROT")) : 1;
   const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     const int lim = C3_SMEM_LIMIT + 1024;
+#define C3_ATTR1(F_, G_, T_) \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, G_, T_>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
 #define C3_ATTR(F_) \
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim)); \
-    HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
+    C3_ATTR1(F_, false, false); C3_ATTR1(F_, true, false); C3_ATTR1(F_, false, true); C3_ATTR1(F_, true, true)
     C3_ATTR(FeatAll); C3_ATTR(FeatPlain); C3_ATTR(FeatColsum); C3_ATTR(FeatResLn);
 #undef C3_ATTR
+#undef C3_ATTR1
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
   int per_n = c3_sm_count() / n_tiles;
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles) per_n = p.tiles;
+  if (two) per_n &= ~1;
   dim3 grid(per_n, n_tiles);
 #define C3_LAUNCH(F_)                                                                                              \
   do {                                                                                                             \
-    if (grouped) launch_pdl(conv3_tc_kernel<F_, true>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
-    else launch_pdl(conv3_tc_kernel<F_, false>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
+    if (two) {                                                                                                     \
+      if (grouped) launch_pdl_cluster(conv3_tc_kernel<F_, true, true>, 2, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
+      else launch_pdl_cluster(conv3_tc_kernel<F_, false, true>, 2, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
+    } else {                                                                                                       \
+      if (grouped) launch_pdl(conv3_tc_kernel<F_, true, false>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);  \
+      else launch_pdl(conv3_tc_kernel<F_, false, false>, grid, dim3(C3_THREADS), smem, st, tmA, tmB, tmR, tmOF, tmOT, tmLN, p, ep);        \
+    }                                                                                                              \
   } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {
@@ -445,6 +544,11 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     default: C3_LAUNCH(FeatAll); break;
   }
 #undef C3_LAUNCH
+  if (two && cudaPeekAtLastError() != cudaSuccess) {     // pairs cannot be scheduled here: retry as single CTAs
+    cudaGetLastError();
+    g_c3_pairs_failed = true;
+    return launch_conv3_tc(a, w, Npad, Kpad, ep, st);
+  }
   HB_CHECK_LAUNCH();
   return 0;
 }

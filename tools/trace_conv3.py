@@ -32,9 +32,12 @@ lib.hatb200_debug_gemm_trace.argtypes = [C.c_void_p, C.c_void_p]
 lib.hatb200_debug_gemm_trace(buf.ctypes.data, None)
 t = buf.astype(np.int64)
 live = t[:, 0] > 0
+clk = t[:, 32:].copy(); t = t[:, :32]
 t0 = t[live][t[live] > 0].min()
 print(Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
     r_ = t[cta]
-    ev = {k: int(r_[k] - t0) for k in range(64) if r_[k] > 0}
+    ev = {k: int(r_[k] - t0) for k in range(32) if r_[k] > 0}
+    if r_[3] > r_[2] > 0:
+        print("   SM clock during the first tile's MMAs: %.3f GHz" % ((clk[cta][3] - clk[cta][2]) / float(r_[3] - r_[2])))
     print("cta", cta, {k: round(v / 1000, 2) for k, v in sorted(ev.items())})

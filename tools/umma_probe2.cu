@@ -1,0 +1,92 @@
+// umma_probe2.cu -- what does the MMA issue loop cost when descriptors are assembled from per-thread (vector)
+// registers every group of 4 MMAs, as the conv / GEMM main loops do, against compile-time-constant descriptors?
+// Variants: 0 constant descriptors; 1 descriptors stepped in vector registers per group (R2UR per operand);
+// 2 same, but the whole warp runs the loop and one elected lane issues; 3 as 1 with an mbarrier poll per group.
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../super_resolution_b200/csrc/tc_common.cuh"
+using namespace hb::tc;
+struct Res { long long issue, total; };
+
+template <int VAR, int N>
+__global__ void __launch_bounds__(384) probe(int groups, volatile uint32_t* seed, Res* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar[4];
+  __shared__ uint32_t slot;
+  uint8_t* base = (uint8_t*)(((uintptr_t)smem + 1023) & ~(uintptr_t)1023);
+  for (int i = threadIdx.x; i < (96 * 1024) / 4; i += blockDim.x) ((uint32_t*)base)[i] = 0x3c003c00u * (i & 1);
+  if (threadIdx.x == 0) { for (int i = 0; i < 4; i++) mbar_init(&bar[i], 1); fence_barrier_init(); }
+  if (threadIdx.x < 32) tmem_alloc(&slot, 512);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = slot;
+  if (threadIdx.x == 0) { mbar_arrive(&bar[2]); if (VAR < 4) mbar_arrive(&bar[3]); }     // bar[2] phase 0 complete: polls succeed at once
+  __syncthreads();
+  if (threadIdx.x >= 64) {           // VAR 4 / 5: pollers, as the epilogue warps waiting for an accumulator
+    if (VAR == 4) mbar_wait(&bar[3], 0);
+    if (VAR == 5) { while (!mbar_try_wait(&bar[3], 0)) __nanosleep(200); }
+  }
+  if (threadIdx.x < 32) {
+    const uint32_t idesc = make_idesc_bf16(128, N);
+    const uint32_t a0 = (smem_u32(base) & 0x3FFFF) >> 4, b0 = (smem_u32(base + 64 * 1024) & 0x3FFFF) >> 4;
+    const uint64_t tmpl = make_smem_desc(0, 128);
+    const uint32_t step = seed[0];      // run-time 0x40 (1 KB): keeps the loop honest
+    const bool whole_warp = VAR == 2;
+    if (whole_warp || elect_one()) {
+      uint32_t a_lo = a0, b_lo = b0;
+      int wrap = 0;
+      const long long t0 = clock64();
+      for (int g = 0; g < groups; ++g) {
+        if (VAR == 3) { mbar_wait(&bar[2], 0); tc_fence_after(); }
+        uint64_t ad, bd;
+        if (VAR == 0) { ad = tmpl | a0; bd = tmpl | b0; }
+        else { ad = tmpl | (uint64_t)a_lo; bd = tmpl | (uint64_t)b_lo; }
+        if (!whole_warp || elect_one()) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16(tm, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)(g | k));
+          umma_commit(&bar[1]);
+        }
+        if (whole_warp) __syncwarp();
+        a_lo += step; b_lo += step;
+        if (++wrap == 8) { wrap = 0; a_lo = a0; b_lo = b0; }
+      }
+      const long long t1 = clock64();
+      if (!whole_warp || elect_one()) {
+        umma_commit(&bar[0]);
+        mbar_wait(&bar[0], 0);
+        const long long t2 = clock64();
+        out[blockIdx.x].issue = t1 - t0;
+        out[blockIdx.x].total = t2 - t0;
+        mbar_arrive(&bar[3]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) tmem_dealloc(tm, 512);
+}
+
+static Res* d; static uint32_t* seed;
+template <int VAR, int N> void run() {
+  const int groups = 256;
+  cudaFuncSetAttribute(probe<VAR, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  probe<VAR, N><<<148, VAR >= 4 ? 384 : 128, 100 * 1024>>>(2, seed, d);
+  probe<VAR, N><<<148, VAR >= 4 ? 384 : 128, 100 * 1024>>>(groups, seed, d);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); exit(1); }
+  Res h[148];
+  cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  double si = 0, st = 0;
+  for (int i = 0; i < 148; ++i) { si += h[i].issue; st += h[i].total; }
+  printf("var %d N %3d | issue/mma %7.1f total/mma %7.1f ideal %5.1f\n", VAR, N, si / (148.0 * groups * 4), st / (148.0 * groups * 4), N / 2.0);
+}
+int main() {
+  cudaMalloc(&d, 148 * sizeof(Res)); cudaMalloc(&seed, 4);
+  uint32_t s = 0x40; cudaMemcpy(seed, &s, 4, cudaMemcpyHostToDevice);
+  run<0, 64>(); run<1, 64>(); run<2, 64>(); run<3, 64>(); run<4, 64>(); run<5, 64>();
+  run<0, 192>(); run<1, 192>(); run<4, 192>(); run<5, 192>();
+  return 0;
+}
