@@ -158,6 +158,28 @@ KERNEL_OF_TAG = {"ocab_attention": "ocab_attention", "ffn_dwconv_gate": "dwconv_
                  "conv_last": "conv_last"}
 
 
+def ncu_traffic(name_parts):
+    """Mean dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) of the kernels whose name contains one of
+    `name_parts`, from the newest profiles/r*_ncu_full_*_summary.csv; (None, None) when there is no capture."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")), key=os.path.getmtime)
+    if not files:
+        return None, None
+    try:
+        rows = list(csv.reader(open(files[-1])))
+        hdr, units = rows[0], rows[1]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+                for r in rows[2:] if any(n in r[0] for n in name_parts)]
+        if not vals:
+            return None, None
+        return sum(vals) / len(vals), f"profiles/{os.path.basename(files[-1])} ({len(vals)} launches, ncu --set full)"
+    except Exception:      # a malformed capture must not take the bench down
+        return None, None
+
+
 def summarize_profile(prof, peaks, tc_on):
     groups = {}
     for tag, r in prof.items():
@@ -176,6 +198,13 @@ def summarize_profile(prof, peaks, tc_on):
         achieved = g["bytes"] / (g["ms"] * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm"], "traffic": None}
+    # DRAM traffic per launch of the dominant family from the committed `ncu --set full` capture (cold cache: ncu
+    # flushes L2 between replays), next to the algorithmic bytes per launch of the same family
+    traffic, traffic_src = ncu_traffic({"tapconv": ("gemm_tc", "conv3_tc", "tapconv_tc"), "ocab_attention": ("attn_tc",),
+                                        "dwgate": ("dwgate",)}.get(dom, (dom,)))
+    roof["traffic"] = traffic
+    roof["traffic_source"] = traffic_src
+    roof["algorithmic_bytes_per_launch"] = g["bytes"] / max(1, g["launches"])
     roof.update({"kernel": dom + ("_tcgen05" if tc_on and dom in ("tapconv", "ocab_attention") else ""),
                  "launches": g["launches"], "avg_launch_us": g["ms"] * 1e3 / max(1, g["launches"]),
                  "share_of_step": g["ms"] / total_ms if total_ms else None,

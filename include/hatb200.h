@@ -120,6 +120,23 @@ int hatb200_crop_place(const void* src, int dtype, int B, int C, int src_h, int 
 int hatb200_reflect_pad(const void* src, int dtype, int B, int C, int h, int w,
                         void* dst, int ph, int pw, void* stream);
 
+/* ---- output post-processing right after the path -------- */
+
+/* basicsr.utils.tensor2img (basicsr/utils/img_util.py:38-95) for a (B,C,H,W) device tensor:
+ * clamp to [min_v,max_v], rescale to [0,1], x255, round half to even, uint8, NHWC; channel
+ * order reversed when rgb2bgr and C == 3 (cv2.COLOR_RGB2BGR).  out: device (B,H,W,C) bytes --
+ * the device-to-host copy shrinks 4x (fp32) / 2x (bf16) and the numpy / cv2 pass disappears. */
+int hatb200_tensor2img(const void* x, int dtype, int B, int C, int H, int W, float min_v,
+                       float max_v, int rgb2bgr, uint8_t* out, void* stream);
+/* basicsr.metrics.calculate_psnr (basicsr/metrics/psnr_ssim.py:12-50) on two device uint8 HWC
+ * images (BGR when C == 3): crop_border, optional Y channel (metric_util.py:32-45,
+ * color_util.py:60-68).  workspace: HATB200_PSNR_MAX_BLOCKS doubles on device.
+ * out (device, 2 doubles): {sum of squared differences, element count};
+ * psnr = 10 log10(255^2 * count / sum), +inf when sum == 0. */
+#define HATB200_PSNR_MAX_BLOCKS 1024
+int hatb200_psnr_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C, int crop_border,
+                    int test_y_channel, double* workspace, double* out, void* stream);
+
 /* ---- single-kernel entry points (unit tests, ncu) ------------------------ */
 
 /* nn.LayerNorm(C), eps 1e-5 (hat_arch.py:222,:237,:331,:392,:844).

@@ -166,6 +166,37 @@ def gen_tile_rects():
         json.dump(out, f)
 
 
+def postproc_inputs():
+    """Seeded inputs of the post-processing goldens: HR-like images with out-of-range values, exact .5 ties after
+    x255 (round half to even), a gray image and a pair for PSNR."""
+    g = torch.Generator().manual_seed(7)
+    a = torch.rand(1, 3, 40, 56, generator=g) * 1.3 - 0.15
+    a[0, :, 0, :8] = torch.tensor([0.5, 1.5, 2.5, 3.5, 126.5, 127.5, 253.5, 254.5]) / 255.0     # ties
+    b = (a + 0.02 * torch.randn(a.shape, generator=g)).contiguous()
+    gray = torch.rand(1, 24, 32, generator=g) * 1.2 - 0.1
+    wide = torch.rand(3, 16, 24, generator=g) * 300.0 - 20.0          # min_max = (0, 255)
+    return a, b, gray, wide
+
+
+def gen_postproc():
+    """tensor2img / calculate_psnr of the unmodified reference (basicsr/utils/img_util.py, basicsr/metrics/psnr_ssim.py)."""
+    load_ref.load_reference_hat()          # puts the reference's basicsr on sys.path
+    from basicsr.utils.img_util import tensor2img
+    from basicsr.metrics.psnr_ssim import calculate_psnr
+    a, b, gray, wide = postproc_inputs()
+    # the reference clamps its argument IN PLACE (`.clamp_` on a view, img_util.py:67): feed it copies
+    ia, ib = tensor2img([a.clone()]), tensor2img([b.clone()])
+    out = dict(a_bgr=ia, b_bgr=ib, a_rgb=tensor2img(a.clone(), rgb2bgr=False), gray=tensor2img(gray.clone()),
+               wide=tensor2img(wide.clone(), min_max=(0, 255)))
+    psnr = {}
+    for cb in (0, 4):
+        for ty in (False, True):
+            psnr[f"cb{cb}_y{int(ty)}"] = float(calculate_psnr(ia, ib, crop_border=cb, test_y_channel=ty))
+    psnr["gray_cb2_y1"] = float(calculate_psnr(out["gray"], tensor2img(gray * 0.97), crop_border=2, test_y_channel=True))
+    np.savez_compressed(os.path.join(GOLD, "postproc.npz"), psnr=json.dumps(psnr), **out)
+    print("postproc:", {k: v.shape for k, v in out.items()}, psnr)
+
+
 if __name__ == "__main__":
     if not load_ref.reference_available():
         sys.exit("reference not mounted; goldens can only be generated in the build container")
@@ -173,5 +204,6 @@ if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count())
     gen_index_tables()
     gen_tile_rects()
+    gen_postproc()
     gen_manifest()
     gen_forward_cases()

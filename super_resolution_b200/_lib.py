@@ -54,6 +54,10 @@ _SIGNATURES = {
     "hatb200_crop_place": (C.c_int, [C.c_void_p, C.c_int] + [C.c_int] * 6 + [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]),
     "hatb200_reflect_pad": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
                                       C.c_int, C.c_void_p]),
+    "hatb200_tensor2img": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
+                                     C.c_void_p, C.c_void_p]),
+    "hatb200_psnr_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                  C.c_void_p, C.c_void_p]),
     "hatb200_layernorm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                     C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "hatb200_conv_tokens": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

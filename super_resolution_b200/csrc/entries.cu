@@ -58,6 +58,18 @@ int hatb200_reflect_pad(const void* src, int dtype, int B, int C, int h, int w, 
   return launch_reflect_pad(src, dtype, B, C, h, w, dst, ph, pw, (cudaStream_t)stream);
 }
 
+int hatb200_tensor2img(const void* x, int dtype, int B, int C, int H, int W, float min_v, float max_v, int rgb2bgr,
+                       uint8_t* out, void* stream) {
+  HB_REQUIRE(x && out && B >= 1 && C >= 1 && H >= 1 && W >= 1, HATB200_EINVAL, "tensor2img: bad arguments");
+  return launch_tensor2img(x, dtype, B, C, H, W, min_v, max_v, rgb2bgr, out, (cudaStream_t)stream);
+}
+
+int hatb200_psnr_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C, int crop_border, int test_y_channel,
+                    double* workspace, double* out, void* stream) {
+  HB_REQUIRE(img && img2 && workspace && out && H >= 1 && W >= 1 && C >= 1, HATB200_EINVAL, "psnr_u8: bad arguments");
+  return launch_psnr_u8(img, img2, H, W, C, crop_border, test_y_channel, workspace, out, (cudaStream_t)stream);
+}
+
 int hatb200_layernorm(const float* x, int M, int C, const float* gamma, const float* beta, void* out, int out_dtype,
                       int out_pitch, void* out_head, int head_c, void* stream) {
   HB_REQUIRE(x && gamma && beta && out && out_pitch >= C, HATB200_EINVAL, "layernorm: bad arguments");

@@ -463,6 +463,104 @@ int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void
   return 0;
 }
 
+// tensor2img (basicsr/utils/img_util.py:38-95): clamp to [mn, mx], (v - mn) / (mx - mn), * 255, round half to even
+// (numpy .round()), uint8, NCHW -> NHWC with the channel order reversed when rgb2bgr (cv2.COLOR_RGB2BGR).
+// One thread per output pixel: reads C planes (coalesced along x), writes C consecutive bytes.
+template <typename T>
+__global__ void tensor2img_kernel(const T* __restrict__ x, int C, size_t hw, float mn, float mx, int flip,
+                                  uint8_t* __restrict__ out, size_t total) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;     // (b, y, x)
+  if (i >= total) return;
+  size_t b = i / hw, pix = i - b * hw;
+  const float span = mx - mn;
+  for (int c = 0; c < C; c++) {
+    float v = to_f(x[(b * C + (flip ? C - 1 - c : c)) * hw + pix]);
+    v = fminf(fmaxf(v, mn), mx);             // Tensor.clamp_: NaN propagates in torch; images are finite
+    v = __fdiv_rn(__fsub_rn(v, mn), span);
+    v = rintf(__fmul_rn(v, 255.0f));
+    out[i * C + c] = (uint8_t)v;
+  }
+}
+
+int launch_tensor2img(const void* x, int dt, int B, int C, int H, int W, float mn, float mx, int rgb2bgr, uint8_t* out,
+                      cudaStream_t st) {
+  HB_REQUIRE(mx > mn, HATB200_EINVAL, "tensor2img: min_max (%g, %g)", mn, mx);
+  size_t hw = (size_t)H * W, total = (size_t)B * hw;
+  if (total == 0) return 0;
+  const int flip = rgb2bgr && C == 3;
+  HB_DISPATCH_T(dt, T, {
+    tensor2img_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, C, hw, mn, mx, flip, out, total);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// calculate_psnr (basicsr/metrics/psnr_ssim.py:12-50) on two uint8 HWC images: crop_border, optional Y channel of
+// BGR input (metric_util.py:32-45 -> color_util.py:60-68: float32(u8) / 255, dot with float64 weights + 16, / 255,
+// float32, * 255 in float32), squared difference in float64.  Deterministic two-stage sum: per-block partials in a
+// fixed tree, then one block adds them in index order.  out[0] = sum of squared differences, out[1] = element count.
+__device__ __forceinline__ double y_of_bgr(const uint8_t* p) {
+  const float b = __fdiv_rn((float)p[0], 255.f), g = __fdiv_rn((float)p[1], 255.f), r = __fdiv_rn((float)p[2], 255.f);
+  double y = __dadd_rn(__dadd_rn(__dmul_rn((double)b, 24.966), __dmul_rn((double)g, 128.553)), __dmul_rn((double)r, 65.481));
+  y = __dadd_rn(y, 16.0);
+  const float y32 = (float)(y / 255.0);
+  return (double)__fmul_rn(y32, 255.f);
+}
+
+__global__ void psnr_partial_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int W, int C, int cb,
+                                    int h2, int w2, int test_y, double* __restrict__ partial) {
+  __shared__ double red[256];
+  const size_t npix = (size_t)h2 * w2;
+  double acc = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+    const int y = (int)(i / w2) + cb, x = (int)(i % w2) + cb;
+    const uint8_t* pa = a + ((size_t)y * W + x) * C;
+    const uint8_t* pb = b + ((size_t)y * W + x) * C;
+    if (test_y && C == 3) {
+      const double d = y_of_bgr(pa) - y_of_bgr(pb);
+      acc += d * d;
+    } else {
+      for (int c = 0; c < C; c++) {
+        // to_y_channel on a 1-channel image: float32(u8) / 255 * 255 in float32 (metric_util.py:41-45)
+        const double va = test_y ? (double)__fmul_rn(__fdiv_rn((float)pa[c], 255.f), 255.f) : (double)pa[c];
+        const double vb = test_y ? (double)__fmul_rn(__fdiv_rn((float)pb[c], 255.f), 255.f) : (double)pb[c];
+        const double d = va - vb;
+        acc += d * d;
+      }
+    }
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = red[0];
+}
+
+__global__ void psnr_finish_kernel(const double* __restrict__ partial, int n, double count, double* __restrict__ out) {
+  double s = 0.0;
+  for (int i = 0; i < n; i++) s += partial[i];
+  out[0] = s;
+  out[1] = count;
+}
+
+int launch_psnr_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int crop_border, int test_y, double* ws,
+                   double* out, cudaStream_t st) {
+  HB_REQUIRE(crop_border >= 0 && 2 * crop_border < H && 2 * crop_border < W, HATB200_EINVAL,
+             "psnr: crop_border %d leaves nothing of a %dx%d image", crop_border, H, W);
+  const int h2 = H - 2 * crop_border, w2 = W - 2 * crop_border;
+  const size_t npix = (size_t)h2 * w2;
+  int blocks = (int)((npix + 1023) / 1024);
+  if (blocks > HATB200_PSNR_MAX_BLOCKS) blocks = HATB200_PSNR_MAX_BLOCKS;
+  psnr_partial_kernel<<<blocks, 256, 0, st>>>(a, b, W, C, crop_border, h2, w2, test_y, ws);
+  HB_CHECK_LAUNCH();
+  const double count = (double)npix * ((test_y && C == 3) ? 1 : C);
+  psnr_finish_kernel<<<1, 1, 0, st>>>(ws, blocks, count, out);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
 }  // namespace hb
 
 namespace hb {

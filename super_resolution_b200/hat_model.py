@@ -141,6 +141,102 @@ def crop_place(src, cy, cx, dst, oy, ox, rh, rw):
                                              dst.shape[2], dst.shape[3], oy, ox, rh, rw, _stream(src)))
 
 
+def tensor2img(tensor, rgb2bgr=True, out_type=None, min_max=(0, 1), to_numpy=True):
+    """Device-side `basicsr.utils.tensor2img` (basicsr/utils/img_util.py:38-95): clamp, rescale, x255, round, uint8,
+    CHW -> HWC, RGB -> BGR in ONE kernel (`hatb200_tensor2img`) before the device-to-host copy -- the reference copies the
+    fp32 image to the host first and does this in numpy / cv2.
+
+    tensor: CUDA tensor (1,C,H,W), (C,H,W) or (H,W), or a list of them (a list returns a list, as the reference).
+    out_type: None / numpy.uint8 only (the float output of the reference is its input rescaled; no kernel needed).
+    Returns a numpy (H,W,C) / (H,W) uint8 array, or the device uint8 tensor when to_numpy=False."""
+    import numpy as np
+    if out_type is not None and out_type is not np.uint8:
+        raise NotImplementedError("tensor2img on device produces uint8 only")
+    if not (torch.is_tensor(tensor) or (isinstance(tensor, (list, tuple)) and all(torch.is_tensor(t) for t in tensor))):
+        raise TypeError(f'tensor or list of tensors expected, got {type(tensor)}')      # the reference's wording
+    many = not torch.is_tensor(tensor)
+    result = []
+    for t in (tensor if many else [tensor]):
+        if not t.is_cuda:
+            raise RuntimeError("super_resolution_b200.tensor2img: CUDA tensor required (there is no CPU path)")
+        t = t.squeeze(0)
+        if t.dim() == 4:
+            raise NotImplementedError("tensor2img: 4-D mini-batches go through torchvision make_grid in the reference")
+        if t.dim() not in (2, 3):
+            raise TypeError(f'Only support 4D, 3D or 2D tensor. But received with dimension: {t.dim()}')
+        if t.dtype not in (torch.float32, torch.bfloat16):
+            t = t.float()
+        t = t.contiguous()
+        Cn, H, W = (1, *t.shape) if t.dim() == 2 else t.shape
+        out = torch.empty((H, W, Cn), dtype=torch.uint8, device=t.device)
+        _lib.check(_lib.lib().hatb200_tensor2img(_ptr(t), _lib.dtype_code(t.dtype), 1, Cn, H, W, float(min_max[0]),
+                                                 float(min_max[1]), int(bool(rgb2bgr)), _ptr(out), _stream(t)))
+        if Cn == 1:
+            out = out[:, :, 0]                      # gray image: (H, W), as np.squeeze(axis=2) in the reference
+        result.append(out.cpu().numpy() if to_numpy else out)
+    return result if many else result[0]
+
+
+def calculate_psnr(img, img2, crop_border, input_order='HWC', test_y_channel=False):
+    """Device-side `basicsr.metrics.calculate_psnr` (basicsr/metrics/psnr_ssim.py:12-50) for two uint8 CUDA images
+    with range [0, 255] (HWC, BGR when 3 channels -- what `tensor2img` returns).  One reduction kernel + a fixed-order
+    finish; only two doubles cross to the host."""
+    import math
+    assert img.shape == img2.shape, (f'Image shapes are different: {img.shape}, {img2.shape}.')
+    if input_order not in ['HWC', 'CHW']:
+        raise ValueError(f'Wrong input_order {input_order}. Supported input_orders are "HWC" and "CHW"')
+    if not (img.is_cuda and img2.is_cuda and img.dtype == torch.uint8 and img2.dtype == torch.uint8):
+        raise RuntimeError("super_resolution_b200.calculate_psnr: uint8 CUDA tensors required")
+    if img.dim() == 2:
+        img, img2 = img[..., None], img2[..., None]
+    elif input_order == 'CHW':
+        img, img2 = img.permute(1, 2, 0), img2.permute(1, 2, 0)
+    img, img2 = img.contiguous(), img2.contiguous()
+    H, W, Cn = img.shape
+    ws = torch.empty(1024, dtype=torch.float64, device=img.device)
+    out = torch.empty(2, dtype=torch.float64, device=img.device)
+    _lib.check(_lib.lib().hatb200_psnr_u8(_ptr(img), _ptr(img2), H, W, Cn, int(crop_border), int(bool(test_y_channel)),
+                                          _ptr(ws), _ptr(out), _stream(img)))
+    sse, count = out.cpu().tolist()
+    if sse == 0:
+        return float('inf')
+    return 10. * math.log10(255. * 255. / (sse / count))
+
+
+def save_network(net, save_path, param_key='params'):
+    """Checkpoint file in the reference's on-disk format (`BaseModel.save_network`, basicsr/models/base_model.py:207-252):
+    `{param_key: state_dict}` with CPU tensors, `module.` prefixes (DataParallel / DDP wrappers) stripped.  `net` and
+    `param_key` may be parallel lists, as in the reference (`['params', 'params_ema']`)."""
+    nets = net if isinstance(net, list) else [net]
+    keys = param_key if isinstance(param_key, list) else [param_key]
+    assert len(nets) == len(keys), 'The lengths of net and param_key should be the same.'
+    save_dict = {}
+    for net_, key_ in zip(nets, keys):
+        net_ = getattr(net_, 'module', net_)              # get_bare_model
+        save_dict[key_] = {(k[7:] if k.startswith('module.') else k): v.cpu() for k, v in net_.state_dict().items()}
+    torch.save(save_dict, save_path)
+
+
+def load_network(net, load_path, strict=True, param_key='params'):
+    """`BaseModel.load_network` (basicsr/models/base_model.py:289-315): reads a `.pth` written by the reference's
+    `save_network`, falls back from a missing `params_ema` to `params`, strips `module.` prefixes and loads with
+    `load_state_dict` -- so checkpoints trained with the reference drop into the B200 `HAT` unchanged.  With
+    strict=False, keys whose sizes differ are skipped (base_model.py:281-287)."""
+    net = getattr(net, 'module', net)
+    load_net = torch.load(load_path, map_location=lambda storage, loc: storage, weights_only=True)
+    if param_key is not None:
+        if param_key not in load_net and 'params' in load_net:
+            param_key = 'params'
+        load_net = load_net[param_key]
+    load_net = {(k[7:] if k.startswith('module.') else k): v for k, v in load_net.items()}
+    if not strict:
+        crt = net.state_dict()
+        for k in list(load_net.keys()):
+            if k in crt and crt[k].size() != load_net[k].size():
+                load_net[k + '.ignore'] = load_net.pop(k)
+    return net.load_state_dict(load_net, strict=strict)
+
+
 class HATModel:
     """Inference half of the reference `HATModel` (hat_model.py:13-112) around a B200-native `HAT`.
 
