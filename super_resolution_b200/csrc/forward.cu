@@ -186,9 +186,9 @@ struct Fwd {
 
   // ESC ConvAttn core on xn (esc_arch.py:119-123): writes the mixed first-pdim channels into
   // dst[:, :pdim] (dst already holds xn elsewhere).  Needs X16 + part16 from the preceding LN.
-  int esc_mix(const EscW& e, void* dst) {
+  int esc_mix(const EscW& e, void* dst, bool dyn_done = false) {
     int nchunk = colsum_chunks(d.H * d.W);
-    HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
+    if (!dyn_done) HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
     if (e.plk_wt && plk_tc(e.pdim)) {
       double Mt = (double)d.M;
       int tid = t_begin("esc_plk13", 2.0 * Mt * e.pdim * e.pdim * (e.plk.taps() + 9.0 / e.pdim), Mt * 2 * e.pdim * d.es);
@@ -215,9 +215,11 @@ struct Fwd {
     {  // CAB conv2 -> U, with GAP partials for ECA
       Epilogue ep; ep.out_t = w.U; ep.out_t_pitch = d.Cp; ep.colsum = w.part;
       HB_TRY(conv("cab_conv2", b.cab2, w.T1, d.midp, 0, d.H, d.W, ep));
-      HB_TRY(launch_eca_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, st));
+      // ECA gate of this branch and the ESC branch's per-sample dynamic kernel in one launch
+      HB_TRY(launch_hab_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, w.part16, b.esc.pdim, b.esc.w1,
+                               b.esc.b1, b.esc.w2, b.esc.b2, w.dyn, st));
     }
-    HB_TRY(esc_mix(b.esc, w.XN));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
+    HB_TRY(esc_mix(b.esc, w.XN, true));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
     {  // aggr 1x1 + HAB combine (hat_arch.py:236) [+ norm2]
       Epilogue ep;
       ep.eca_u = w.U; ep.eca_pitch = d.Cp; ep.eca_scale = w.eca_s; ep.eca_coef = c.conv_scale;

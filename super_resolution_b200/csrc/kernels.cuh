@@ -37,6 +37,9 @@ int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, co
 // ESC dynamic kernel (esc_arch.py:95-100,:121): GAP(pdim) -> 1x1 (pdim->pdim/2) -> GELU -> 1x1 (->pdim*9)
 int launch_dyn_finish(const float* partial, int nchunk, int B, int pdim, int HW, const float* w1, const float* b1,
                       const float* w2, const float* b2, float* dyn /*(B,pdim,9)*/, cudaStream_t st);
+int launch_hab_finish(const float* eca_partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
+                      const float* dyn_partial, int pdim, const float* w1, const float* b1, const float* w2,
+                      const float* b2, float* dyn, cudaStream_t st);
 // GatedDconvFFN middle (hat_arch.py:112-116)
 int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w /*(2hid,9)*/,
                   const float* b, void* out, int out_pitch, int zero_to, cudaStream_t st);

@@ -298,12 +298,8 @@ __device__ __forceinline__ float chunk_sum(const float* __restrict__ p, int n, i
 
 // ECA gate: sigmoid(conv1d_k5(mean over HW)) across the channel axis, zero padded
 // ends, no bias (hat_arch.py:66-77).  One block per sample.
-__global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk, int C, float inv_hw,
-                                  const float* __restrict__ w5, float* __restrict__ scale) {
-  extern __shared__ float mean[];  // C
-  int b = blockIdx.x;
-  pdl_wait();
-  pdl_trigger();
+__device__ __forceinline__ void eca_finish_body(int b, const float* __restrict__ partial, int nchunk, int C, float inv_hw,
+                                                const float* __restrict__ w5, float* __restrict__ scale, float* mean) {
   for (int c = threadIdx.x; c < C; c += blockDim.x) mean[c] = chunk_sum(partial + (size_t)b * nchunk * C + c, nchunk, C) * inv_hw;
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -317,6 +313,14 @@ __global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk,
   }
 }
 
+__global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk, int C, float inv_hw,
+                                  const float* __restrict__ w5, float* __restrict__ scale) {
+  extern __shared__ float mean[];  // C
+  pdl_wait();
+  pdl_trigger();
+  eca_finish_body(blockIdx.x, partial, nchunk, C, inv_hw, w5, scale, mean);
+}
+
 int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
                       cudaStream_t st) {
   launch_pdl(eca_finish_kernel, dim3(B), dim3(256), C * sizeof(float), st, partial, nchunk, C, 1.0f / (float)HW, w5, scale);
@@ -326,15 +330,11 @@ int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, co
 
 // ESC dynamic depthwise kernel per sample (esc_arch.py:95-100, :121):
 // dyn = W2 . gelu(W1 . GAP(x[:, :pdim]) + b1) + b2, reshaped (pdim, 3, 3).
-__global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,
-                                  const float* __restrict__ w1, const float* __restrict__ b1,
-                                  const float* __restrict__ w2, const float* __restrict__ b2,
-                                  float* __restrict__ dyn) {
-  __shared__ float mean[64];
-  __shared__ float hid[32];
-  int b = blockIdx.x, half = pdim / 2;
-  pdl_wait();
-  pdl_trigger();
+__device__ __forceinline__ void dyn_finish_body(int b, const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,
+                                                const float* __restrict__ w1, const float* __restrict__ b1,
+                                                const float* __restrict__ w2, const float* __restrict__ b2,
+                                                float* __restrict__ dyn, float* mean, float* hid) {
+  const int half = pdim / 2;
   for (int c = threadIdx.x; c < pdim; c += blockDim.x)
     mean[c] = chunk_sum(partial + (size_t)b * nchunk * pdim + c, nchunk, pdim) * inv_hw;
   __syncthreads();
@@ -349,6 +349,44 @@ __global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk,
     for (int i = 0; i < half; i++) a = fmaf(w2[j * half + i], hid[i], a);
     dyn[(size_t)b * pdim * 9 + j] = a;
   }
+}
+
+__global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,
+                                  const float* __restrict__ w1, const float* __restrict__ b1,
+                                  const float* __restrict__ w2, const float* __restrict__ b2,
+                                  float* __restrict__ dyn) {
+  __shared__ float mean[64];
+  __shared__ float hid[32];
+  pdl_wait();
+  pdl_trigger();
+  dyn_finish_body(blockIdx.x, partial, nchunk, pdim, inv_hw, w1, b1, w2, b2, dyn, mean, hid);
+}
+
+// One launch for the two per-sample "finish" steps of a HAB (ECA gate of the CAB branch, dynamic depthwise kernel of
+// the ESC branch): blocks [0, B) run the former, [B, 2B) the latter.  They are independent of each other and both
+// only need the partial sums written by earlier kernels; a launch of their own each cost ~4 us of an otherwise idle GPU.
+struct HabFinishArgs {
+  const float* eca_partial; int nchunk, C; const float* w5; float* scale;
+  const float* dyn_partial; int pdim; const float* w1; const float* b1; const float* w2; const float* b2; float* dyn;
+  float inv_hw; int B;
+};
+__global__ void hab_finish_kernel(const HabFinishArgs a) {
+  extern __shared__ float mean[];  // max(C, 64) + 32
+  pdl_wait();
+  pdl_trigger();
+  if ((int)blockIdx.x < a.B) eca_finish_body(blockIdx.x, a.eca_partial, a.nchunk, a.C, a.inv_hw, a.w5, a.scale, mean);
+  else dyn_finish_body(blockIdx.x - a.B, a.dyn_partial, a.nchunk, a.pdim, a.inv_hw, a.w1, a.b1, a.w2, a.b2, a.dyn, mean,
+                       mean + (a.C > 64 ? a.C : 64));
+}
+
+int launch_hab_finish(const float* eca_partial, int nchunk, int B, int C, int HW, const float* w5, float* scale,
+                      const float* dyn_partial, int pdim, const float* w1, const float* b1, const float* w2,
+                      const float* b2, float* dyn, cudaStream_t st) {
+  HB_REQUIRE(pdim <= 64 && pdim % 2 == 0, HATB200_EUNSUPPORTED, "esc pdim=%d unsupported", pdim);
+  HabFinishArgs a{eca_partial, nchunk, C, w5, scale, dyn_partial, pdim, w1, b1, w2, b2, dyn, 1.0f / (float)HW, B};
+  launch_pdl(hab_finish_kernel, dim3(2 * B), dim3(256), ((C > 64 ? C : 64) + 32) * sizeof(float), st, a);
+  HB_CHECK_LAUNCH();
+  return 0;
 }
 
 int launch_dyn_finish(const float* partial, int nchunk, int B, int pdim, int HW, const float* w1, const float* b1,

@@ -46,6 +46,7 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t halo_bar, full_bar[B_STAGES], empty_bar[B_STAGES], done_bar;
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float sdk[9 * PD];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sm_b = smem;
   uint8_t* sm_h = smem + B_STAGES * BST_BYTES;
@@ -122,11 +123,17 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     const int y = y0 + row / TGX, x = (gx0 + row % TGX) * 4;
     const int WP = p.W + 2 * PH;
     pdl_wait();          // reads the per-sample dynamic kernels and the padded head, writes the output
+    // this sample's dynamic 3x3 kernels, tap-major, staged once: the loop below reads them as broadcast float4s
+    // (144 scalar read-only loads per pixel before)
+    if (p.dyn) {
+      for (int j = threadIdx.x - 64; j < PD * 9; j += 128) sdk[(j % 9) * PD + j / 9] = p.dyn[(size_t)b * PD * 9 + j];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     mbar_wait(&done_bar, 0);
     tc_fence_after();
     const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16);
     {
-      const float* dk = p.dyn ? p.dyn + (size_t)b * PD * 9 : nullptr;
+      const bool dk = p.dyn != nullptr;
       const bool live = x < p.W;          // half-empty tiles at the right image edge (W % 32 == 16)
 #pragma unroll
       for (int px = 0; px < 4; px++) {
@@ -148,13 +155,17 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
               const uint4 t0 = *reinterpret_cast<const uint4*>(src), t1 = *reinterpret_cast<const uint4*>(src + 8);
               const __nv_bfloat162* h0 = reinterpret_cast<const __nv_bfloat162*>(&t0);
               const __nv_bfloat162* h1 = reinterpret_cast<const __nv_bfloat162*>(&t1);
+              const float4* wk = reinterpret_cast<const float4*>(sdk + (ky * 3 + kx) * PD);
+              const float4 w0 = wk[0], w1 = wk[1], w2 = wk[2], w3 = wk[3];
+              const float wv[16] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w,
+                                    w2.x, w2.y, w2.z, w2.w, w3.x, w3.y, w3.z, w3.w};
 #pragma unroll
               for (int j = 0; j < 4; j++) {
                 const float2 f0 = __bfloat1622float2(h0[j]), f1 = __bfloat1622float2(h1[j]);
-                v[2 * j] = fmaf(f0.x, __ldg(dk + (2 * j) * 9 + ky * 3 + kx), v[2 * j]);
-                v[2 * j + 1] = fmaf(f0.y, __ldg(dk + (2 * j + 1) * 9 + ky * 3 + kx), v[2 * j + 1]);
-                v[8 + 2 * j] = fmaf(f1.x, __ldg(dk + (8 + 2 * j) * 9 + ky * 3 + kx), v[8 + 2 * j]);
-                v[9 + 2 * j] = fmaf(f1.y, __ldg(dk + (9 + 2 * j) * 9 + ky * 3 + kx), v[9 + 2 * j]);
+                v[2 * j] = fmaf(f0.x, wv[2 * j], v[2 * j]);
+                v[2 * j + 1] = fmaf(f0.y, wv[2 * j + 1], v[2 * j + 1]);
+                v[8 + 2 * j] = fmaf(f1.x, wv[8 + 2 * j], v[8 + 2 * j]);
+                v[9 + 2 * j] = fmaf(f1.y, wv[9 + 2 * j], v[9 + 2 * j]);
               }
             }
           }
