@@ -328,6 +328,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     float v[CW], tb[CW];
     tab_read(ws.tab_bias + nb, tb);
     float u[CW], rs[CW], cf[CW];
+    int rel_s = -1;
     if (RING && (has_u || has_resid)) {
       const int s = ws.k.s;
       long long tw = 0;
@@ -337,8 +338,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
       const uint8_t* st = ws.ring + (size_t)s * ws.op_stage_bytes;
       if (has_u) { row_read_bf16(st + ws.op_u_off, row, u); tab_read(ws.coef + nb, cf); }
       if (has_resid) row_read_f32(st, row, rs);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ws.op_empty[s]);      // this warp's rows are in registers
+      rel_s = s;
       ws.k.next(ws.ops);
     }
     tmem_ld_wait();
@@ -364,6 +364,15 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     if (has_resid) {
 #pragma unroll
       for (int j = 0; j < CW; j += 2) add2(v[j], v[j + 1], v[j], v[j + 1], rs[j], rs[j + 1]);
+    }
+    if (RING && rel_s >= 0) {
+      // Release the ring stage only AFTER its values have been consumed: the shared-memory loads above are
+      // asynchronous, and an arrive issued right behind them let the producer's next TMA box land in the stage while
+      // loads of the slower warps were still outstanding (B200, M = 65536: ~0.3 % of the rows, always TMEM lanes
+      // 0-63 = the two warps that share their schedulers with the TMA / MMA warps, picked up a later chunk's
+      // residual -- errors of +-5 in the fp32 stream that the small-M parity tests never reached).
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ws.op_empty[rel_s]);
     }
     if (do_ln) {
       if (ci == 0) ln_k = v[0];

@@ -282,6 +282,21 @@ def test_linear_fused_tcgen05(shape):
     _linear_fused_case(*shape)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [
+    # BASELINE configs[1] sizes: 512 token tiles over 148 persistent CTAs (3-4 tiles each, operand ring wraps ~12x per
+    # CTA).  The small shapes above give every CTA at most one tile and never caught a ring stage released before its
+    # shared-memory loads had landed (0.3 % of the rows took a later chunk's residual at this size).
+    (16, 64, 64, 360, 180, True, False, True, True, False, 0),      # ffn fc2 at bench size
+    (16, 64, 64, 180, 180, True, True, True, False, False, 0),      # ESC aggr + HAB combine at bench size
+    (1, 256, 256, 360, 180, True, False, True, True, False, 0),     # one 256x256 sample (configs[2])
+    (16, 64, 64, 180, 720, False, False, False, False, True, 0),    # ffn fc1 at bench size
+])
+def test_linear_fused_tcgen05_full_size(shape):
+    _linear_fused_case(*shape, seed=3)
+    _linear_fused_case(*shape, seed=4)      # run to run: the failure was timing dependent
+
+
 # ---- persistent halo-resident tcgen05 3x3 conv with the fused epilogue (csrc/tc_conv3.cu) ---------------------
 def _conv3_fused_case(B, H, W, Cin, N, resid, ln, head, out_t, colsum, act=0, seed=0):
     g = torch.Generator().manual_seed(seed)
@@ -359,3 +374,16 @@ def _conv3_fused_case(B, H, W, Cin, N, resid, ln, head, out_t, colsum, act=0, se
 ])
 def test_conv3_fused_tcgen05(shape):
     _conv3_fused_case(*shape)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [
+    # bench-size launches: 512 pixel tiles over 74 CTA pairs (cta_group::2), 3-4 pair iterations each
+    (16, 64, 64, 180, 180, True, True, True, False, False, 0),      # RHAG conv + residual ring + LayerNorm + head
+    (16, 64, 64, 180, 60, False, False, False, True, False, 1),     # CAB conv1 + GELU
+    (16, 64, 64, 60, 180, False, False, False, True, True, 0),      # CAB conv2 + pool partials
+    (3, 48, 80, 180, 180, True, True, True, False, False, 0),       # 3 * 3 * 10 = 90 tiles: ragged pair waves
+    (1, 16, 24, 180, 60, False, False, False, True, False, 1),      # 3 tiles: odd count -> single-CTA kernel
+])
+def test_conv3_fused_tcgen05_full_size(shape):
+    _conv3_fused_case(*shape, seed=5)
