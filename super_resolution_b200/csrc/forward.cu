@@ -153,6 +153,8 @@ struct Fwd {
                               ep.ln_pitch, ep.ln_head, ep.ln_head_c, st));
       if (ep.ln_head_colsum)
         HB_TRY(launch_colsum(ep.ln_head, d.dt, ep.ln_head_c, d.B, hw, ep.ln_head_c, ep.ln_head_colsum, st));
+      if (ep.ln_head_pad)     // the x-padded copy the Toeplitz 13x13 kernel reads (written by the fused epilogue otherwise)
+        HB_TRY(launch_plk_pad_copy((const bf16*)ep.ln_head, d.B, H, W, (bf16*)ep.ln_head_pad, st));
     }
     if (ep.colsum) HB_TRY(launch_colsum(ep.out_t, d.dt, ep.out_t_pitch, d.B, hw, cw.O, ep.colsum, st));
     return dbg("conv tail");

@@ -523,10 +523,17 @@ template <class TS>
 __device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tmR,
                                              const CUtensorMap* tmU, uint8_t* ring,
                                              uint64_t* op_full, uint64_t* op_empty, int ops, int op_stage_bytes,
-                                             int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k) {
+                                             int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k,
+                                             const TS* next = nullptr) {
   const uint32_t bytes = (uint32_t)((has_resid ? 128 * CW * 4 : 0) + (has_u ? 128 * CW * 2 : 0));
   for (int ci = 0; ci < nch; ci++, k.next(ops)) {
     const int s = k.s;
+    // one tile ahead, chunk by chunk: the warpgroup's NEXT tile's operands start towards L2 while this tile's chunks
+    // go through the ring (a ring stage then waits for an L2 hit, not for HBM)
+    if (next) {
+      if (has_resid) next->prefetch(tmR, n0 + ci * CW);
+      if (has_u) next->prefetch(tmU, n0 + ci * CW);
+    }
     mbar_wait(&op_empty[s], k.ph ^ 1u);
     uint8_t* st = ring + (size_t)s * op_stage_bytes;
     mbar_arrive_expect_tx(&op_full[s], bytes);

@@ -66,6 +66,7 @@ struct G3Params {
   int stg_bufs;             // staging buffers per warp and element type (2, or 1 when both types stage in pass 1)
   int share_stg;            // fp32 and bf16 staging alias (pass 1 writes only fp32, pass 2 only bf16)
   int prof;                      // engineering: epilogue wait-cycle counters on top of the timestamps
+  int l2_ahead;                  // L2-prefetch the warpgroup's next tile's ring operands (HATB200_G3_L2AHEAD=1; measured slower: 10.82 vs 10.60 ms/step)
   unsigned long long* trace;
 };
 
@@ -199,8 +200,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         if ((i & 1) != g) continue;
         const Tile2D ts{t * G3_TILE_M};
+        const int tn = t + 2 * (int)gridDim.x;          // this warpgroup's next tile
+        const Tile2D nx{tn * G3_TILE_M};
         produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
-                     p.has_u, n0, p.BN / CW, k);
+                     p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr);
       }
     }
   } else {
@@ -446,6 +449,7 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     HB_TRY(tc::make_tmap_bf16(&tmLN, ep.ln_out, 2, dims, str, box, w16 * 2));
   }
   p.trace = nullptr; p.prof = 0;
+  p.l2_ahead = getenv("HATB200_G3_L2AHEAD") ? atoi(getenv("HATB200_G3_L2AHEAD")) : 0;
   if (getenv("HATB200_GEMM_TRACE")) {
     if (!g_gemm_trace) HB_CHECK_CUDA(cudaMalloc(&g_gemm_trace, 1024 * 64 * 8));
     HB_CHECK_CUDA(cudaMemsetAsync(g_gemm_trace, 0, 1024 * 64 * 8, st));
