@@ -74,41 +74,56 @@ int launch_layernorm(const float* x, int M, int C, const float* gamma, const flo
 // conv_first with the input normalisation folded in (hat_arch.py:849-853).
 // One thread per (token, channel); the 9*IC inputs are warp-broadcast loads.
 // ---------------------------------------------------------------------------
-// One thread per (token, 4 consecutive channels): the 9*IC normalised inputs are loaded once per thread
-// (warp-broadcast when the lanes share a token) and the weights as float4.
+// A warp owns 32 consecutive tokens and one group of CF_G * 4 consecutive channels: the 9*IC normalised inputs of a
+// lane's token are loaded once (coalesced along x) and kept in registers; every weight is a float4 at a warp-uniform
+// address (one broadcast transaction), reused by the 32 tokens.  0.3 loads per FMA instead of 0.5 with all 27 inputs
+// re-read by each of a token's 45 threads (B200: 131 us for 65 536 tokens x 180 channels before).
+constexpr int CF_G = 5;                // float4 groups per thread (20 channels)
 template <typename T>
 __global__ void __launch_bounds__(256) conv_first_kernel(const T* __restrict__ x, int B, int IC, int H, int W,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          int C, float4 mean, float range, float* __restrict__ out) {
-  const int C4 = C >> 2;
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t total = (size_t)B * H * W * C4;
-  if (idx >= total) return;
-  const int c = (int)(idx % C4) * 4;
-  const size_t m = idx / C4;
+  const int groups = (C + CF_G * 4 - 1) / (CF_G * 4);
+  const size_t M = (size_t)B * H * W;
+  const int lane = threadIdx.x & 31;
+  const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;     // warp index: (token block, group)
+  const int grp = (int)(wid % groups);
+  const size_t m = (wid / groups) * 32 + lane;
+  if (m >= M) return;
+  const int c0 = grp * CF_G * 4;
   const int px = (int)(m % W);
   const int py = (int)((m / W) % H);
   const int b = (int)(m / ((size_t)W * H));
   const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
-  float4 acc = bias ? __ldg(reinterpret_cast<const float4*>(bias + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 acc[CF_G];
+#pragma unroll
+  for (int q = 0; q < CF_G; q++)
+    acc[q] = (bias && c0 + 4 * q < C) ? __ldg(reinterpret_cast<const float4*>(bias + c0 + 4 * q)) : make_float4(0.f, 0.f, 0.f, 0.f);
   const T* xb = x + (size_t)b * IC * H * W;
 #pragma unroll
   for (int ky = 0; ky < 3; ky++) {
     const int yy = py + ky - 1;
-    if (yy < 0 || yy >= H) continue;
 #pragma unroll
     for (int kx = 0; kx < 3; kx++) {
       const int xx = px + kx - 1;
-      if (xx < 0 || xx >= W) continue;
+      const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
       for (int i = 0; i < IC; i++) {
-        const float v = (to_f(xb[((size_t)i * H + yy) * W + xx]) - mean_a[i]) * range;
-        const float4 wv = __ldg(reinterpret_cast<const float4*>(w + ((ky * 3 + kx) * IC + i) * C + c));
-        acc.x = fmaf(v, wv.x, acc.x); acc.y = fmaf(v, wv.y, acc.y);
-        acc.z = fmaf(v, wv.z, acc.z); acc.w = fmaf(v, wv.w, acc.w);
+        // zero padding applies to the NORMALISED image (hat_arch.py:849-853): a pad pixel contributes nothing
+        const float v = in ? (to_f(xb[((size_t)i * H + yy) * W + xx]) - mean_a[i]) * range : 0.f;
+        const float* wr = w + ((ky * 3 + kx) * IC + i) * C + c0;
+#pragma unroll
+        for (int q = 0; q < CF_G; q++) {
+          if (c0 + 4 * q >= C) break;
+          const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + 4 * q));
+          acc[q].x = fmaf(v, wv.x, acc[q].x); acc[q].y = fmaf(v, wv.y, acc[q].y);
+          acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
+        }
       }
     }
   }
-  *reinterpret_cast<float4*>(out + m * C + c) = acc;
+#pragma unroll
+  for (int q = 0; q < CF_G; q++)
+    if (c0 + 4 * q < C) *reinterpret_cast<float4*>(out + m * C + c0 + 4 * q) = acc[q];
 }
 
 // generic channel count (C % 4 != 0): one thread per (token, channel)
@@ -146,7 +161,9 @@ int launch_conv_first(const void* x, int x_dt, int B, int IC, int H, int W, cons
   HB_REQUIRE(IC >= 1 && IC <= 4, HATB200_EUNSUPPORTED, "conv_first: in_chans=%d not in 1..4", IC);
   float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
   const bool v4 = C % 4 == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)out & 15) == 0 && (!bias || ((uintptr_t)bias & 15) == 0);
-  size_t total = (size_t)B * H * W * (v4 ? C / 4 : C);
+  // vector kernel: one warp per (32 tokens, 20-channel group); scalar kernel: one thread per (token, channel)
+  const size_t M = (size_t)B * H * W;
+  size_t total = v4 ? ((M + 31) / 32) * (size_t)((C + CF_G * 4 - 1) / (CF_G * 4)) * 32 : M * C;
   HB_DISPATCH_T(x_dt, T, {
     if (v4)
       conv_first_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
