@@ -136,6 +136,8 @@ struct Epilogue {
   int out_t_coff = 0;
   int out_t_zero_to = 0;             // columns [N, out_t_zero_to) are written as zero (K padding of the consumer)
   int shuffle_r = 1;                 // PixelShuffle factor folded into the store (hat_arch.py:593-605)
+  int shuffle_perm = 0;              // weights / bias rows are pre-permuted to n' = (i*r + j)*64 + c (tc_conv3.cu: each
+                                     // 64-column block is then one (i, j) sub-pixel and leaves as one TMA store)
   // fused LayerNorm of the fp32 result row (tcgen05 kernel only; the CUDA-core path runs layernorm separately)
   const float* ln_gamma = nullptr;
   const float* ln_beta = nullptr;

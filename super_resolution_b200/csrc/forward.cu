@@ -120,6 +120,25 @@ struct Fwd {
     return r;
   }
 
+  // conv + PixelShuffle (hat_arch.py:593-605): the persistent conv3 kernel with (i, j, c)-ordered weight rows when it
+  // takes the shape (each 64-column block = one sub-pixel = one TMA store), else the generic route
+  int conv_shuffle(const char* tag, const ConvW& cw, const void* A, int H, int W, Epilogue ep) {
+    if (tc() && cw.w16s && cw.shuffle_r == ep.shuffle_r && !tc_disabled(tag)) {
+      ConvArgs a{A, 64, 0, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
+      Epilogue e2 = ep;
+      e2.shuffle_perm = 1; e2.bias = cw.bias_s;
+      if (conv3_tc_supported(a, cw.Npad, cw.Kpad, e2)) {
+        double Mt = (double)d.B * H * W;
+        int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), Mt * (cw.I + cw.O) * d.es);
+        int r = launch_conv3_tc(a, cw.w16s, cw.Npad, cw.Kpad, e2, st);
+        t_end(tid);
+        HB_TRY(r);
+        return dbg("conv3_tc shuffle");
+      }
+    }
+    return conv(tag, cw, A, 64, 0, H, W, ep);
+  }
+
   // engineering switch: HATB200_TC_DISABLE=tag1,tag2 keeps the named ops on the CUDA-core kernel (bisecting)
   static bool tc_disabled(const char* tag) {
     const char* v = getenv("HATB200_TC_DISABLE");
@@ -366,17 +385,17 @@ struct Fwd {
     int hh = d.H, hw = d.W;
     if (c.upscale == 3) {
       Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 3;
-      HB_TRY(conv("upsample_conv", h->up0, w.F64, 64, 0, hh, hw, ep));
+      HB_TRY(conv_shuffle("upsample_conv", h->up0, w.F64, hh, hw, ep));
       hr = w.UP1; hh *= 3; hw *= 3;
     } else {
       if (c.upscale >= 2) {
         Epilogue ep; ep.out_t = w.UP1; ep.out_t_pitch = 64; ep.shuffle_r = 2;
-        HB_TRY(conv("upsample_conv", h->up0, w.F64, 64, 0, hh, hw, ep));
+        HB_TRY(conv_shuffle("upsample_conv", h->up0, w.F64, hh, hw, ep));
         hr = w.UP1; hh *= 2; hw *= 2;
       }
       if (c.upscale >= 4) {
         Epilogue ep; ep.out_t = w.UP2; ep.out_t_pitch = 64; ep.shuffle_r = 2;
-        HB_TRY(conv("upsample_conv", h->up1, w.UP1, 64, 0, hh, hw, ep));
+        HB_TRY(conv_shuffle("upsample_conv", h->up1, w.UP1, hh, hw, ep));
         hr = w.UP2; hh *= 2; hw *= 2;
       }
     }

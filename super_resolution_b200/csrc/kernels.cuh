@@ -11,6 +11,8 @@ namespace hb {
 int launch_pack_w_f32(const void* src, int src_dt, int O, int I, int taps, float* dst, int Np, int ncols,
                       cudaStream_t st);
 // bf16 K-major layout for tcgen05: dst[tap][n][k], n < Npad, k < Kpad (zero padded).
+int launch_pack_w_bf16_shuffle(const void* src, int src_dt, int O, int I, int taps, int r, bf16* dst, int Npad, int Kpad,
+                               const float* bias, float* bias_dst, cudaStream_t st);
 int launch_pack_w_bf16(const void* src, int src_dt, int O, int I, int taps, bf16* dst, int Npad, int Kpad,
                        int src_i_off, int src_i_total, cudaStream_t st);
 // any float dtype vector -> fp32

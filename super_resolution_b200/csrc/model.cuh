@@ -22,6 +22,7 @@ struct ConvW {               // dense conv / Linear weight in both kernel layout
   float* w32 = nullptr; int Np = 0;            // fp32 [taps][I][Np]        (CUDA-core kernels)
   bf16* w16 = nullptr; int Npad = 0, Kpad = 0;  // bf16 [taps][Npad][Kpad]   (tcgen05 kernels)
   float* bias = nullptr;                        // fp32 [O] (zeros when the layer has no bias)
+  bf16* w16s = nullptr; float* bias_s = nullptr; int shuffle_r = 0;   // pixel-shuffle layers: rows permuted to (i, j, c)
   int algoO = 0, algoI = 0;                     // un-padded sizes for FLOP accounting when O / I include layout padding
   int taps() const { return KH * KW; }
 };

@@ -63,6 +63,15 @@ struct Packer {
   int conv(const std::string& prefix, ConvW& w, int O, int I, int KH, int KW) {
     return conv(prefix + ".weight", prefix + ".bias", w, O, I, KH, KW);
   }
+  // second bf16 copy of a conv + PixelShuffle(r) layer with rows ordered (i, j, c) for tc_conv3.cu
+  int shuffle_copy(const std::string& prefix, ConvW& w, int r) {
+    const ParamRef* p;
+    HB_TRY(get(prefix + ".weight", &p));
+    HB_TRY(alloc((void**)&w.w16s, (size_t)w.taps() * w.Npad * w.Kpad * sizeof(bf16)));
+    HB_TRY(alloc((void**)&w.bias_s, (size_t)w.O * sizeof(float)));
+    w.shuffle_r = r;
+    return launch_pack_w_bf16_shuffle(p->ptr, p->dtype, w.O, w.I, w.taps(), r, w.w16s, w.Npad, w.Kpad, w.bias, w.bias_s, st);
+  }
 
   int esc(const std::string& core, const std::string& plk_key, EscW& e, int C, int pdim, int k) {
     e.pdim = pdim;
@@ -203,9 +212,10 @@ struct Packer {
       HB_TRY(conv("conv_before_upsample.0", h->conv_before_up, 64, C, 3, 3));
       if (c.upscale == 3) {
         HB_TRY(conv("upsample.0", h->up0, 576, 64, 3, 3));
+        HB_TRY(shuffle_copy("upsample.0", h->up0, 3));
       } else {
-        if (c.upscale >= 2) HB_TRY(conv("upsample.0", h->up0, 256, 64, 3, 3));
-        if (c.upscale >= 4) HB_TRY(conv("upsample.2", h->up1, 256, 64, 3, 3));
+        if (c.upscale >= 2) { HB_TRY(conv("upsample.0", h->up0, 256, 64, 3, 3)); HB_TRY(shuffle_copy("upsample.0", h->up0, 2)); }
+        if (c.upscale >= 4) { HB_TRY(conv("upsample.2", h->up1, 256, 64, 3, 3)); HB_TRY(shuffle_copy("upsample.2", h->up1, 2)); }
         HB_REQUIRE(c.upscale <= 4, HATB200_EUNSUPPORTED, "upscale=%d: only 1, 2, 3, 4 are implemented", c.upscale);
       }
       HB_TRY(get("conv_last.weight", &p));

@@ -69,6 +69,7 @@ struct C3Params {
   int stg_bufs, share_stg;
   unsigned long long* trace;     // engineering: per-CTA timestamps (HATB200_GEMM_TRACE)
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
+  int shuf_r;                    // > 1: pixel-shuffle store (columns pre-permuted to (i, j, c))
 };
 
 __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
@@ -332,6 +333,7 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if ((i & 1) != g) continue;
       Tile4D ts;
       tile_coords(p, t, ts.x0, ts.y0, ts.b);
+      ts.r = p.shuf_r; ts.H = p.H;
       RowInfo ri;
       ri.b = ts.b;
       ri.py = ts.y0 + ws.row / C3_TW; ri.px = ts.x0 + ws.row % C3_TW;
@@ -385,10 +387,20 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
   if ((a.a_pitch * 2) % 16 || (a.a_coff * 2) % 16) return false;
   p.BN = tc_bn(a.N);
   if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
-  if (ep.dyn_k || ep.shuffle_r != 1 || ep.eca_u || ep.scale_ncols) return false;      // tc_tapconv.cu keeps those layers
+  if (ep.dyn_k || ep.eca_u || ep.scale_ncols) return false;      // tc_tapconv.cu keeps those layers
+  if (ep.shuffle_r != 1) {      // conv + PixelShuffle: only with (i, j, c)-ordered rows, plain bf16 output of 64 channels
+    const int r = ep.shuffle_r;
+    if (!ep.shuffle_perm || (r != 2 && r != 3) || a.N != 64 * r * r || p.BN % 64) return false;
+    if (!ep.out_t || ep.out_f32 || ep.ln_out || ep.colsum || ep.resid || ep.out_t_pitch != 64 || ep.out_t_coff ||
+        ep.out_t_zero_to > a.N)
+      return false;
+  } else if (ep.shuffle_perm) {
+    return false;
+  }
+  p.shuf_r = ep.shuffle_r;
   if (ep.out_f32 && ((ep.out_f32_pitch * 4) % 16 || ((uintptr_t)ep.out_f32 & 15))) return false;
   if (ep.out_t && ((ep.out_t_pitch * 2) % 16 || (ep.out_t_coff * 2) % 16 || ((uintptr_t)ep.out_t & 15))) return false;
-  if (ep.out_t && ep.out_t_pitch - ep.out_t_coff < (ep.out_t_zero_to > a.N ? ep.out_t_zero_to : a.N)) return false;
+  if (ep.out_t && ep.shuffle_r == 1 && ep.out_t_pitch - ep.out_t_coff < (ep.out_t_zero_to > a.N ? ep.out_t_zero_to : a.N)) return false;
   if (ep.ln_out && ((ep.ln_pitch * 2) % 16 || ((uintptr_t)ep.ln_out & 15) || ep.ln_pitch < a.N)) return false;
   if (ep.resid && ((ep.resid_pitch * 4) % 16 || ((uintptr_t)ep.resid & 15))) return false;
   if (ep.ln_out && Npad != p.BN) return false;
@@ -500,7 +512,13 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   };
   if (p.has_resid) HB_TRY(map4(&tmR, true, ep.resid, p.N, ep.resid_pitch, CW, C3_TW, C3_TH));
   if (ep.out_f32) HB_TRY(map4(&tmOF, true, ep.out_f32, p.N, ep.out_f32_pitch, w32, C3_TW, 4));
-  if (ep.out_t) {
+  if (ep.out_t && p.shuf_r > 1) {     // (B, H*r, W*r, 64) output as {c, j, x, i, b*H + y}: one (i, j) sub-pixel per store
+    const uint64_t r = (uint64_t)p.shuf_r, W = (uint64_t)a.W;
+    uint64_t dims[5] = {64, r, W, r, (uint64_t)a.B * a.H};
+    uint64_t str[4] = {64 * 2, r * 64 * 2, W * r * 64 * 2, r * W * r * 64 * 2};
+    uint32_t box[5] = {64, 1, C3_TW, 1, 4};
+    HB_TRY(tc::make_tmap_bf16(&tmOT, ep.out_t, 5, dims, str, box, 128));
+  } else if (ep.out_t) {
     const int width = ep.out_t_zero_to > p.N ? ep.out_t_zero_to : p.N;
     HB_TRY(map4(&tmOT, false, (const bf16*)ep.out_t + ep.out_t_coff, width, ep.out_t_pitch, w16, C3_TW, 4));
   }

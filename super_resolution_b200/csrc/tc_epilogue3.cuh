@@ -30,6 +30,11 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* s
                "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3, int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
 // ---- small PTX helpers -------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m),
@@ -186,8 +191,16 @@ struct Tile2D {
 // maps are 4-D (col, x, y, b): store box {w, 8, 4, 1} (one warp = 4 image rows), load box {CW, 8, 16, 1}.
 struct Tile4D {
   int x0, y0, b;
+  int r = 1, H = 0;      // r > 1: conv + PixelShuffle(r) with (i, j, c)-ordered columns: the 64-column block starting at
+                         // `col` is sub-pixel (i, j) = (col/64 / r, col/64 % r) of every pixel of the tile; the store map
+                         // is 5-D {c, j, x, i, b*H + y} over the (B, H*r, W*r, 64) output
   __device__ __forceinline__ void store(const CUtensorMap* tm, const void* src, int col, int quarter) const {
-    tma_store_4d(tm, src, col, x0, y0 + quarter * 4, b);
+    if (r > 1) {
+      const int blk = col >> 6, i = blk / r, j = blk - i * r;
+      tma_store_5d(tm, src, 0, j, x0, i, b * H + y0 + quarter * 4);
+    } else {
+      tma_store_4d(tm, src, col, x0, y0 + quarter * 4, b);
+    }
   }
   __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col) const {
     tma_load_4d(dst, tm, bar, col, x0, y0, b);

@@ -232,6 +232,7 @@ bool tapconv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   if (ep.ln_out && (Npad != p.BN || ep.ln_pitch > 512)) return false;     // LN needs the whole row in one CTA
   if (ep.ln_head && ep.ln_head_c > 16) return false;
   if (ep.dyn_k && a.N > 16) return false;
+  if (ep.shuffle_perm) return false;                 // pre-permuted rows: tc_conv3.cu only
   if (tc::encode_tiled_fn() == nullptr) return false;
   return true;
 }
