@@ -64,6 +64,7 @@ static void plan(const hatb200_config& c, const Dims& d, char* base, Workspace& 
     if (s == 3) w.UP1 = take(M * 9 * 64 * d.es);
     if (s == 2 || s == 4) w.UP1 = take(M * 4 * 64 * d.es);
     if (s == 4) w.UP2 = take(M * 16 * 64 * d.es);
+    w.CL32 = d.dt == HATB200_BF16 ? (float*)take(M * s * s * 4 * sizeof(float)) : nullptr;   // conv_last, pixels-last fp32
   }
   int nchunk = colsum_chunks(d.H * d.W);
   w.part = (float*)take((size_t)d.B * nchunk * d.C * 4);
@@ -401,6 +402,20 @@ struct Fwd {
     }
     int tid = t_begin("conv_last", 2.0 * d.B * hh * hw * 64 * 9 * c.in_chans,
                       (double)d.B * hh * hw * (64 * d.es + c.in_chans * (y_dt == HATB200_F32 ? 4 : 2)));
+    // tensor-core route: N = 3 padded to a 16-column MMA tile on the persistent conv3 kernel (fp32 pixels-last out),
+    // then one pass that applies "/ img_range + mean" and writes the NCHW planes.  (The CUDA-core kernel below spends
+    // one shared-memory weight load per FMA: 172 us for 16 x 256 x 256 pixels.)
+    if (tc() && w.CL32 && h->conv_last_tc.w16 && c.in_chans <= 4 && !tc_disabled("conv_last")) {
+      const ConvW& cw = h->conv_last_tc;
+      ConvArgs a{hr, 64, 0, 64, d.B, hh, hw, 3, 3, cw.O};
+      Epilogue ep; ep.bias = cw.bias; ep.out_f32 = w.CL32; ep.out_f32_pitch = 4;
+      if (conv3_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
+        HB_TRY(launch_conv3_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
+        HB_TRY(launch_nhwc_to_nchw_affine(w.CL32, 4, d.B, c.in_chans, hh, hw, c.mean, c.img_range, y, y_dt, st));
+        t_end(tid);
+        return dbg("conv_last tc");
+      }
+    }
     HB_TRY(launch_conv_last(hr, d.dt, 64, 64, d.B, hh, hw, h->conv_last_w, h->conv_last_b, c.in_chans, c.mean,
                             c.img_range, y, y_dt, st));
     t_end(tid);

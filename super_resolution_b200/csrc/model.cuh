@@ -74,6 +74,7 @@ struct Workspace {           // carved from the caller's scratch buffer
   void *H1 = nullptr;                                    // T (M, max(hp4, qkvp))
   void *G = nullptr;                                     // T (M, hp2)
   void *F64 = nullptr, *UP1 = nullptr, *UP2 = nullptr;   // tail
+  float* CL32 = nullptr;                                 // conv_last output, pixels-last fp32 (B*Hr*Wr, 4), bf16 path
   float *part = nullptr, *part16 = nullptr, *eca_s = nullptr, *dyn = nullptr;
   size_t bytes = 0;
 };
@@ -105,5 +106,6 @@ struct hatb200_handle {
   std::vector<hb::LayerW> layers;
   hb::ConvW conv_after_body, conv_before_up, up0, up1;
   float *conv_last_w = nullptr, *conv_last_b = nullptr;     // [9][64][OC]
+  hb::ConvW conv_last_tc;                                        // the same layer for tc_conv3.cu (N padded to 16)
   float* mean_dev = nullptr;
 };

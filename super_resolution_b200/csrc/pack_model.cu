@@ -222,6 +222,7 @@ struct Packer {
       HB_TRY(alloc((void**)&h->conv_last_w, (size_t)9 * 64 * c.in_chans * sizeof(float)));
       HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, c.in_chans, 64, 9, h->conv_last_w, c.in_chans, c.in_chans, st));
       HB_TRY(vec("conv_last.bias", &h->conv_last_b));
+      HB_TRY(conv("conv_last", h->conv_last_tc, c.in_chans, 64, 3, 3));
     }
     int flag = 0;
     HB_CHECK_CUDA(cudaMemcpyAsync(&flag, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -518,6 +518,38 @@ int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void
   return 0;
 }
 
+// conv_last tail on the tensor-core route: (B*H*W, pitch) fp32 pixels-last -> (B, OC, H, W) with "/ img_range + mean"
+// (hat_arch.py:858).  One thread per pixel: a 16-byte read, OC coalesced plane writes.
+template <typename TY>
+__global__ void nhwc_to_nchw_affine_kernel(const float* __restrict__ in, int pitch, int OC, size_t hw, float4 mean,
+                                           float range, TY* __restrict__ y, size_t total) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const size_t b = i / hw, pix = i - b * hw;
+  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+  float v[4];
+  if (pitch == 4) {
+    const float4 t = *reinterpret_cast<const float4*>(in + i * 4);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  } else {
+    for (int o = 0; o < OC; o++) v[o] = in[i * pitch + o];
+  }
+  for (int o = 0; o < OC; o++) y[(b * OC + o) * hw + pix] = from_f<TY>(v[o] / range + mean_a[o]);
+}
+
+int launch_nhwc_to_nchw_affine(const float* in, int pitch, int B, int OC, int H, int W, const float* mean, float range,
+                               void* y, int y_dt, cudaStream_t st) {
+  HB_REQUIRE(OC >= 1 && OC <= 4 && pitch >= OC, HATB200_EINVAL, "nhwc_to_nchw: OC=%d pitch=%d", OC, pitch);
+  const size_t hw = (size_t)H * W, total = (size_t)B * hw;
+  const float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  if (y_dt == HATB200_F32) nhwc_to_nchw_affine_kernel<float><<<blocks, 256, 0, st>>>(in, pitch, OC, hw, m4, range, (float*)y, total);
+  else if (y_dt == HATB200_BF16) nhwc_to_nchw_affine_kernel<bf16><<<blocks, 256, 0, st>>>(in, pitch, OC, hw, m4, range, (bf16*)y, total);
+  else { set_error("nhwc_to_nchw: output dtype %d unsupported", y_dt); return HATB200_EINVAL; }
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
 // tensor2img (basicsr/utils/img_util.py:38-95): clamp to [mn, mx], (v - mn) / (mx - mn), * 255, round half to even
 // (numpy .round()), uint8, NCHW -> NHWC with the channel order reversed when rgb2bgr (cv2.COLOR_RGB2BGR).
 // One thread per output pixel: reads C planes (coalesced along x), writes C consecutive bytes.
