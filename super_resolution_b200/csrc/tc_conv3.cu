@@ -70,7 +70,77 @@ struct C3Params {
   unsigned long long* trace;     // engineering: per-CTA timestamps (HATB200_GEMM_TRACE)
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
   int shuf_r;                    // > 1: pixel-shuffle store (columns pre-permuted to (i, j, c))
+  int lean;                      // MMA issue through the unrolled c3_issue_tiles (grp == 3, kblocks 1 or 3, no tap rotation)
+  int probe;                     // engineering (HATB200_C3_PROBE, with tracing): 1 = time 64 back-to-back MMAs before the
+                                 // tile loop; 8 = weight slices are loaded for the first ring pass only (timing experiment)
 };
+
+// Everything the unrolled MMA issuer needs, as shared-window addresses (descriptor fields are address >> 4).
+struct C3Issue {
+  int tiles, t_first, t_step, hst, wst;
+  uint32_t idesc, tmem_base, acc_stride;
+  uint32_t halo16, halo_stage16;         // halo stage 0, stage stride
+  uint32_t w16, wslice16;                // weight ring stage 0, one slice
+  uint32_t w_full, w_empty, halo_full, halo_empty, tmem_full, tmem_empty;   // barrier arrays (8 bytes per entry)
+  unsigned long long* trace;
+};
+
+// One thread issues every tile's 36 * KB MMAs as straight-line code: all 9 taps x KB k-blocks unrolled, each operand
+// descriptor the tile's (A) or ring stage's (B) base plus an immediate, so that an MMA costs one UIADD3.64 + UTCHMMA
+// instead of the looped form's ~70 instructions per group of four (ring cursor, tap stepping, R2UR moves, elect /
+// reconvergence).  A ring stage holds 3 slices (producer: grp == 3).
+template <int KB, bool TWO>
+__device__ __noinline__ void c3_issue_tiles(const C3Issue a) {
+  const uint64_t a_tmpl = (make_smem_desc(0, 128) & ~(0x3FFFull << 32)) | ((uint64_t)(C3_HROW >> 4) << 32);
+  const uint64_t b_tmpl = make_smem_desc(0, 128);
+  uint32_t full_a = a.w_full, empty_a = a.w_empty, wb = a.w16, wph = 0;
+  int ws_i = 0;
+  uint32_t hs = 0, hph = 0;
+  int i = 0;
+  unsigned long long* tr = a.trace ? a.trace + (size_t)blockIdx.x * 64 : nullptr;
+  for (int t = a.t_first; t < a.tiles; t += a.t_step, i++) {
+    const uint32_t g = (uint32_t)i & 1u;
+    if (tr && i < 4) tr[4 * i] = c3_time();
+    mbar_wait_a(a.tmem_empty + 8 * g, (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
+    if (tr && i < 4) tr[4 * i + 1] = c3_time();
+    mbar_wait_a(a.halo_full + 8 * hs, hph);
+    tc_fence_after();
+    if (tr && i < 4) { tr[4 * i + 2] = c3_time(); tr[32 + 4 * i + 2] = (unsigned long long)clock64(); }
+    const uint32_t acc = a.tmem_base + g * a.acc_stride;
+    const uint64_t ad0 = a_tmpl | (uint64_t)(a.halo16 + hs * a.halo_stage16);
+#pragma unroll
+    for (int st = 0; st < 3 * KB; st++) {
+      mbar_wait_a(full_a, wph);
+      tc_fence_after();
+      const uint64_t bd0 = b_tmpl | (uint64_t)wb;
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const int n = st * 3 + q, tap = n / KB, kb = n % KB, ky = tap / 3, kx = tap % 3;
+        // accumulator row (y, x) reads halo row (y + ky) * 10 + x + kx of k-block kb
+        const uint64_t ad = ad0 + (uint64_t)((ky * C3_HW + kx) * (128 >> 4) + kb * (C3_HALO_KB >> 4));
+        const uint64_t bd = bd0 + (uint64_t)((uint32_t)q * a.wslice16);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          if (TWO) umma2_bf16(acc, ad + 2 * k, bd + 2 * k, a.idesc, (n | k) ? 1u : 0u);
+          else umma_bf16(acc, ad + 2 * k, bd + 2 * k, a.idesc, (n | k) ? 1u : 0u);
+        }
+      }
+      if (TWO) umma2_commit_a(empty_a);          // frees the ring stage once its MMAs have read it
+      else umma_commit_a(empty_a);
+      full_a += 8; empty_a += 8; wb += 3 * a.wslice16;
+      if (++ws_i == a.wst) { ws_i = 0; full_a = a.w_full; empty_a = a.w_empty; wb = a.w16; wph ^= 1u; }
+    }
+    if (tr && i < 4) { tr[4 * i + 3] = c3_time(); tr[32 + 4 * i + 3] = (unsigned long long)clock64(); }
+    if (TWO) {
+      umma2_commit_a(a.halo_empty + 8 * hs);
+      umma2_commit_a(a.tmem_full + 8 * g);
+    } else {
+      umma_commit_a(a.halo_empty + 8 * hs);      // halo may be overwritten
+      umma_commit_a(a.tmem_full + 8 * g);        // accumulator of tile i complete
+    }
+    if (++hs == (uint32_t)a.hst) { hs = 0; hph ^= 1u; }
+  }
+}
 
 __device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
   const int tx = t % p.tiles_x, ty = (t / p.tiles_x) % p.tiles_y;
@@ -186,12 +256,15 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (cnt == early && tn < p.tiles) issue_halo(tn);
             const int s = wp.s;
             uint8_t* dst = smem + p.off_w + (size_t)s * p.w_stage_bytes + (size_t)q * slice_bytes;
+            const bool skip = (p.probe & 8) && wp.ph != 0;
             if (q == 0) {
               mbar_wait(&w_empty[s], wp.ph ^ 1u);
-              if (!TWO) mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+              if (skip) { if (rank == 0) mbar_arrive(&w_full[s]); }
+              else if (!TWO) mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
               else if (rank == 0) mbar_arrive_expect_tx(&w_full[s], 2u * (uint32_t)p.w_stage_bytes);
             }
-            if (TWO)     // this CTA's half of the slice (rows [rank * BN/2, +BN/2)); both halves complete on rank 0
+            if (skip) {
+            } else if (TWO)     // this CTA's half of the slice (rows [rank * BN/2, +BN/2)); both halves complete on rank 0
               tma2_load_2d(dst, &tmB, mapa_u32(&w_full[s], 0), kb * 64, tap * p.Npad + n0 + (int)rank * (p.BN / 2));
             else
               tma_load_2d(dst, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
@@ -224,6 +297,38 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int ws_i = 0;
       RingPos hp;
       int i = 0;
+      if ((p.probe & 1) && p.trace) {    // MMA issue rate in this kernel's environment, nothing else running on the pipe
+        const uint32_t ha = (smem_u32(smem + p.off_halo) & 0x3FFFF) >> 4;
+        if (elect_one()) {
+          const long long c0 = clock64();
+          for (int n = 0; n < 16; n++) {
+            const uint64_t ad = a_tmpl | (uint64_t)(ha + (uint32_t)((n % 9) * 8)), bd = b_tmpl | (uint64_t)wb0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              if (TWO) umma2_bf16(tmem_base, ad + 2 * k, bd + 2 * k, idesc, 1u);
+              else umma_bf16(tmem_base, ad + 2 * k, bd + 2 * k, idesc, 1u);
+            }
+          }
+          p.trace[(size_t)blockIdx.x * 64 + 31] = (unsigned long long)(clock64() - c0);
+        }
+        __syncwarp();
+      }
+      if (p.lean) {
+        if (elect_one()) {
+          C3Issue ia;
+          ia.tiles = p.tiles; ia.t_first = t_first; ia.t_step = t_step; ia.hst = p.hst; ia.wst = wst;
+          ia.idesc = idesc; ia.tmem_base = tmem_base; ia.acc_stride = p.acc_stride;
+          ia.halo16 = (smem_u32(smem + p.off_halo) & 0x3FFFF) >> 4; ia.halo_stage16 = (uint32_t)p.halo_stage_bytes >> 4;
+          ia.w16 = wb0; ia.wslice16 = wslice;
+          ia.w_full = full0; ia.w_empty = empty0;
+          ia.halo_full = smem_u32(&halo_full[0]); ia.halo_empty = smem_u32(&halo_empty[0]);
+          ia.tmem_full = smem_u32(&tmem_full_bar[0]); ia.tmem_empty = smem_u32(&tmem_empty_bar[0]);
+          ia.trace = p.trace;
+          if (p.kblocks == 3) c3_issue_tiles<3, TWO>(ia);
+          else c3_issue_tiles<1, TWO>(ia);
+        }
+        __syncwarp();
+      } else
       for (int t = t_first; t < p.tiles; t += t_step, i++, hp.next(p.hst)) {
         const int g = i & 1;
         if (i < 4 && lane == 0) C3_TRACE(4 * i);
@@ -444,6 +549,8 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
     if (force_hst) hst = force_hst;
     if (force_bufs) bufs = force_bufs;
     p.grp = grp;
+    static const bool lean_off = getenv("HATB200_C3_LEAN") && getenv("HATB200_C3_LEAN")[0] == '0';
+    p.lean = !lean_off && grp == 3 && (p.kblocks == 1 || p.kblocks == 3);
     p.w_stage_bytes = grp * slice_bytes;
     const int stg32 = f32o ? 8 * bufs * 32 * (grouped ? 128 : 64) : 0;
     const int stg16 = bf16o && !p.share_stg ? 8 * bufs * 32 * (grouped ? 128 : 32) : 0;
@@ -525,6 +632,8 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
   p.trace = gemm_trace_arm(st);
   p.rot = getenv("HATB200_C3_ROT") ? atoi(getenv("HATB200_C3_ROT")) : 1;
+  if (p.lean) p.rot = 0;         // the unrolled issuer walks the taps in order
+  p.probe = getenv("HATB200_C3_PROBE") ? atoi(getenv("HATB200_C3_PROBE")) : 0;
   const size_t smem = (size_t)p.smem_bytes + 1024;
   static bool attr_set = false;
   if (!attr_set) {

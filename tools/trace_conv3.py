@@ -32,7 +32,11 @@ lib.hatb200_debug_gemm_trace.argtypes = [C.c_void_p, C.c_void_p]
 lib.hatb200_debug_gemm_trace(buf.ctypes.data, None)
 t = buf.astype(np.int64)
 live = t[:, 0] > 0
-clk = t[:, 32:].copy(); t = t[:, :32]
+clk = t[:, 32:].copy(); t = t[:, :32].copy()
+if int(os.environ.get("HATB200_C3_PROBE", "0")) & 1:
+    pr = t[:, 31][t[:, 31] > 0]
+    print("in-kernel probe: cycles per MMA over 64 back-to-back issues: median %.1f min %.1f max %.1f" % (np.median(pr) / 64, pr.min() / 64, pr.max() / 64))
+t[:, 31] = 0
 t0 = t[live][t[live] > 0].min()
 print(Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
