@@ -71,8 +71,7 @@ struct C3Params {
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
   int shuf_r;                    // > 1: pixel-shuffle store (columns pre-permuted to (i, j, c))
   int lean;                      // MMA issue through the unrolled c3_issue_tiles (grp == 3, kblocks 1 or 3, no tap rotation)
-  int probe;                     // engineering (HATB200_C3_PROBE, with tracing): 1 = time 64 back-to-back MMAs before the
-                                 // tile loop; 8 = weight slices are loaded for the first ring pass only (timing experiment)
+  int probe;                     // engineering (HATB200_C3_PROBE=1, with tracing): time 64 back-to-back MMAs before the tile loop
 };
 
 // Everything the unrolled MMA issuer needs, as shared-window addresses (descriptor fields are address >> 4).
@@ -221,11 +220,19 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       pdl_wait();        // halos are the previous kernel's output
       pdl_trigger();
       RingPos hp, wp;
-      auto issue_halo = [&](int t) {
-        int x0, y0, b;
-        tile_coords(p, t, x0, y0, b);
+      // Halos never block the weight stream: the next halo goes out as soon as its stage is free, polled between
+      // weight slices and inside the wait for a free ring stage.  (Issued at a fixed point of the slice sequence, a
+      // halo that had to wait for the previous tile's MMAs held back every weight slice behind it, and each tile then
+      // paid an L2 round trip for its last slices: B200 trace 0.24 us per slice whatever N, 2.2 us per K = 64 tile
+      // whose MMAs take 0.5 us.)
+      int halo_t = t_first;
+      auto try_halo = [&](bool block) {
+        if (halo_t >= p.tiles) return;
         const int hs = hp.s;
-        mbar_wait(&halo_empty[hs], hp.ph ^ 1u);
+        if (block) mbar_wait(&halo_empty[hs], hp.ph ^ 1u);
+        else if (!mbar_try_wait(&halo_empty[hs], hp.ph ^ 1u)) return;
+        int x0, y0, b;
+        tile_coords(p, halo_t, x0, y0, b);
         uint8_t* hb_ = smem + p.off_halo + (size_t)hs * p.halo_stage_bytes;
         const uint32_t hbytes = (uint32_t)(p.kblocks * C3_HH * C3_HW * 128);
         if (TWO) {       // both halos of the pair complete on rank 0's barrier
@@ -239,32 +246,66 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             tma_load_4d(hb_ + (size_t)kb * C3_HALO_KB, &tmA, &halo_full[hs], p.a_coff + kb * 64, x0 - 1, y0 - 1, b);
         }
         hp.next(p.hst);
+        halo_t += t_step;
       };
-      // The next tile's halo is requested once `early` weight slices of this tile are on their way: by then the
-      // previous tile has released the other halo stage, and the load has most of a tile's MMAs to land.  (Issued
-      // after the last slice instead, it costs ~1 us of idle tensor pipe per tile; with a single halo stage it
-      // has to wait for this tile's MMAs and can only go last.)
       // A ring stage carries `grp` consecutive weight slices (one full barrier, one release): see the MMA issuer.
-      const int early = p.hst > 1 ? (p.wst * p.grp < nsl - 1 ? p.wst * p.grp : nsl - 1) : nsl;
       const uint32_t slice_bytes = (uint32_t)(p.w_stage_bytes / p.grp);
-      if (t_first < p.tiles) issue_halo(t_first);
+      try_halo(true);
+      if (p.lean) {
+        // One 4-D box per ring stage ([tap][k-block][row][64] view of the weights: 3 k-blocks of a tap, or 3 taps of
+        // a one-block layer): this thread runs alone on its scheduler slot at ~10 cycles per dependent instruction,
+        // and a per-slice loop (~45 instructions + 1 TMA each) fed the ring slower than the MMAs drain it.
+        const uint32_t full0 = smem_u32(&w_full[0]), empty0 = smem_u32(&w_empty[0]);
+        const uint32_t full0c = TWO ? mapa_u32(&w_full[0], 0) : full0;
+        const uint32_t dst0 = smem_u32(smem + p.off_w), stage_b = (uint32_t)p.w_stage_bytes;
+        const uint32_t tx = (TWO ? 2u : 1u) * stage_b;
+        const int row0 = n0 + (int)rank * (p.BN / 2) * (TWO ? 1 : 0);
+        const int nst = 3 * p.kblocks, dtap = p.kblocks == 3 ? 1 : 3;
+        uint32_t full_a = full0, full_c = full0c, empty_a = empty0, dst = dst0, ph = 1u;
+        int ws_i = 0;
+        for (int t = t_first; t < p.tiles; t += t_step) {
+          for (int st = 0, tap = 0; st < nst; st++, tap += dtap) {
+            try_halo(false);
+            if (!mbar_try_wait_a(empty_a, ph)) {
+              const long long t0 = clock64();
+              while (!mbar_try_wait_a(empty_a, ph)) {
+                try_halo(false);
+                if (clock64() - t0 > 4000000000ll) {
+                  printf("libhatb200: conv3 weight ring wait timed out (block %d,%d)\n", blockIdx.x, blockIdx.y);
+                  __trap();
+                }
+              }
+            }
+            if (!TWO || rank == 0) mbar_arrive_expect_tx_a(full_a, tx);
+            if (TWO) tma2_load_4d_a(dst, &tmB, full_c, 0, row0, 0, tap);
+            else tma_load_4d_a(dst, &tmB, full_a, 0, row0, 0, tap);
+            full_a += 8; full_c += 8; empty_a += 8; dst += stage_b;
+            if (++ws_i == p.wst) { ws_i = 0; full_a = full0; full_c = full0c; empty_a = empty0; dst = dst0; ph ^= 1u; }
+          }
+        }
+      } else
       for (int t = t_first; t < p.tiles; t += t_step) {
-        const int tn = t + t_step;
-        int cnt = 0, tap = tap0, q = 0;
+        int tap = tap0, q = 0;
         for (int j = 0; j < 9; j++) {
-          for (int kb = 0; kb < p.kblocks; kb++, cnt++) {
-            if (cnt == early && tn < p.tiles) issue_halo(tn);
+          for (int kb = 0; kb < p.kblocks; kb++) {
+            try_halo(false);
             const int s = wp.s;
             uint8_t* dst = smem + p.off_w + (size_t)s * p.w_stage_bytes + (size_t)q * slice_bytes;
-            const bool skip = (p.probe & 8) && wp.ph != 0;
             if (q == 0) {
-              mbar_wait(&w_empty[s], wp.ph ^ 1u);
-              if (skip) { if (rank == 0) mbar_arrive(&w_full[s]); }
-              else if (!TWO) mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
+              if (!mbar_try_wait(&w_empty[s], wp.ph ^ 1u)) {
+                const long long t0 = clock64();
+                while (!mbar_try_wait(&w_empty[s], wp.ph ^ 1u)) {
+                  try_halo(false);
+                  if (clock64() - t0 > 4000000000ll) {
+                    printf("libhatb200: conv3 weight ring wait timed out (block %d,%d)\n", blockIdx.x, blockIdx.y);
+                    __trap();
+                  }
+                }
+              }
+              if (!TWO) mbar_arrive_expect_tx(&w_full[s], (uint32_t)p.w_stage_bytes);
               else if (rank == 0) mbar_arrive_expect_tx(&w_full[s], 2u * (uint32_t)p.w_stage_bytes);
             }
-            if (skip) {
-            } else if (TWO)     // this CTA's half of the slice (rows [rank * BN/2, +BN/2)); both halves complete on rank 0
+            if (TWO)            // this CTA's half of the slice (rows [rank * BN/2, +BN/2)); both halves complete on rank 0
               tma2_load_2d(dst, &tmB, mapa_u32(&w_full[s], 0), kb * 64, tap * p.Npad + n0 + (int)rank * (p.BN / 2));
             else
               tma_load_2d(dst, &tmB, &w_full[s], kb * 64, tap * p.Npad + n0);
@@ -272,8 +313,8 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
           if (++tap == 9) tap = 0;
         }
-        if (early >= nsl && tn < p.tiles) issue_halo(tn);
       }
+      while (halo_t < p.tiles) try_halo(true);
     }
   } else if (warp == 1) {
     // ===== MMA issuer: the whole warp walks the loop so that ring cursors, descriptors and barrier addresses stay
@@ -602,7 +643,12 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     uint32_t box[4] = {64, C3_HW, C3_HH, 1};
     HB_TRY(tc::make_tmap_bf16(&tmA, a.A, 4, dims, str, box, 128));
   }
-  {
+  if (p.lean) {      // [tap][k-block][row][64]: a ring stage (3 k-blocks of one tap, or 3 taps of a one-block layer) is one box
+    uint64_t dims[4] = {64, (uint64_t)Npad, (uint64_t)p.kblocks, 9};
+    uint64_t str[3] = {(uint64_t)Kpad * 2, 128, (uint64_t)Npad * Kpad * 2};
+    uint32_t box[4] = {64, (uint32_t)(two ? p.BN / 2 : p.BN), p.kblocks == 3 ? 3u : 1u, p.kblocks == 3 ? 1u : 3u};
+    HB_TRY(tc::make_tmap_bf16(&tmB, w, 4, dims, str, box, 128));
+  } else {
     uint64_t dims[2] = {(uint64_t)Kpad, (uint64_t)9 * Npad};
     uint64_t str[1] = {(uint64_t)Kpad * 2};
     uint32_t box[2] = {64, (uint32_t)(two ? p.BN / 2 : p.BN)};

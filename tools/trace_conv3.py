@@ -44,4 +44,5 @@ for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
     ev = {k: int(r_[k] - t0) for k in range(32) if r_[k] > 0}
     if r_[3] > r_[2] > 0:
         print("   SM clock during the first tile's MMAs: %.3f GHz" % ((clk[cta][3] - clk[cta][2]) / float(r_[3] - r_[2])))
+    print("cta", cta, "MMA issue us per tile:", [round((r_[4 * i + 3] - r_[4 * i + 2]) / 1000, 2) for i in range(4) if r_[4 * i + 3] > 0])
     print("cta", cta, {k: round(v / 1000, 2) for k, v in sorted(ev.items())})
