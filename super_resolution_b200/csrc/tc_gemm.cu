@@ -65,6 +65,7 @@ struct G3Params {
   int off_b, off_a, off_op, off_stg32, off_stg16, off_tab, smem_bytes;
   int stg_bufs;             // staging buffers per warp and element type (2, or 1 when both types stage in pass 1)
   int share_stg;            // fp32 and bf16 staging alias (pass 1 writes only fp32, pass 2 only bf16)
+  int nwg;                  // epilogue warpgroups: 2 (one per accumulator stage) or 4 (two per stage, each half of the columns)
   int prof;                      // engineering: epilogue wait-cycle counters on top of the timestamps
   int l2_ahead;                  // L2-prefetch the warpgroup's next tile's ring operands (HATB200_G3_L2AHEAD=1; measured slower: 10.82 vs 10.60 ms/step)
   unsigned long long* trace;
@@ -73,8 +74,12 @@ struct G3Params {
 }  // namespace
 
 // ---- the kernel ----------------------------------------------------------------------------------------
-template <class F, bool GROUPED>
-__global__ void __launch_bounds__(G3_THREADS, 1)
+// NWG = 4: the epilogue warps are latency bound at two per scheduler (ncu: 18-33 % issue-slot utilisation), and a warp
+// can only read its own 32 TMEM lanes, so the extra parallelism comes from the columns: two warpgroups per accumulator
+// stage, each running the unchanged per-tile epilogue on one half of the n-tile (plain bf16 layers only: no row
+// statistics, no operand ring; 576 threads, no ring-producer warps).
+template <class F, bool GROUPED, int NWG = 2>
+__global__ void __launch_bounds__(NWG == 4 ? 64 + 128 * 4 : G3_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU,
                const __grid_constant__ CUtensorMap tmOF, const __grid_constant__ CUtensorMap tmOT,
@@ -109,7 +114,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     mbar_init(&b_bar, 1);
     for (int g = 0; g < 2; g++) {
       mbar_init(&tmem_full_bar[g], 1);
-      mbar_init(&tmem_empty_bar[g], 128);
+      mbar_init(&tmem_empty_bar[g], 64 * NWG);
       for (int s = 0; s < G3_MAX_OPS; s++) {
         mbar_init(&op_full[g][s], 1);
         mbar_init(&op_empty[g][s], 4);
@@ -118,7 +123,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_barrier_init();
   }
   // tables: zero padded beyond N, so pad columns come out as exact zeros with no predicate
-  for (int i = threadIdx.x; i < p.BN; i += G3_THREADS) {
+  for (int i = threadIdx.x; i < p.BN; i += (int)blockDim.x) {
     const int n = n0 + i;
     const bool ok = n < p.N;
     tab_bias[i] = (ok && ep.bias) ? __ldg(ep.bias + n) : 0.f;
@@ -187,7 +192,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (i < 6) G3_TRACE(9 + 2 * i);
       }
     }
-  } else if (warp >= 10) {
+  } else if (warp >= 2 + 4 * NWG) {
     // ===== operand-ring producer of warpgroup g: residual / CAB-branch chunks, as far ahead as the ring allows =====
     const int g = warp - 10;
     if (feat_ring<F>() && (p.has_resid || p.has_u) && elect_one()) {
@@ -208,14 +213,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else {
     // ===== epilogue warps: warpgroup g = (warp - 2) / 4 takes local tiles i with (i & 1) == g =====
-    const int g = (warp - 2) >> 2;
+    const int wgi = (warp - 2) >> 2;
+    const int g = wgi & 1, half = NWG == 4 ? wgi >> 1 : 0;      // accumulator stage, column half of the n-tile
+    const int HB = NWG == 4 ? p.BN / 2 : p.BN, hoff = half * HB;
     WarpState<GROUPED> ws;
     ws.g = g; ws.ew = warp - 2; ws.quarter = warp & 3; ws.lane = lane;
     ws.row = ws.quarter * 32 + lane;                     // row of the tile owned by this thread (TMEM lane)
     ws.wg_tid = ((warp - 2) & 3) * 32 + lane;            // 0..127 inside the warpgroup
-    ws.BN = p.BN; ws.N = p.N; ws.n0 = n0; ws.nch = p.BN / CW; ws.H = p.H; ws.W = p.W; ws.hw = p.hw;
-    ws.last_ntile = blockIdx.y == gridDim.y - 1;
-    ws.tab_bias = tab_bias; ws.tab_gamma = tab_gamma; ws.tab_beta = tab_beta; ws.coef = tab_coef + g * p.BN;
+    ws.BN = HB; ws.N = p.N; ws.n0 = n0 + hoff; ws.nch = HB / CW; ws.H = p.H; ws.W = p.W; ws.hw = p.hw;
+    ws.last_ntile = blockIdx.y == gridDim.y - 1 && half == NWG / 2 - 1;
+    ws.tab_bias = tab_bias + hoff; ws.tab_gamma = tab_gamma + hoff; ws.tab_beta = tab_beta + hoff; ws.coef = tab_coef + g * p.BN;
     ws.ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
     ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
     ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
@@ -241,8 +248,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int rem = ri.m - ri.b * p.hw;
       ri.py = rem / p.W; ri.px = rem - ri.py * p.W;
       ri.chunk = (m0 - ri.b * p.hw) / G3_TILE_M; ri.nchunk = p.hw / G3_TILE_M;
-      ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
-      const bool tr = ws.wg_tid == 0 && (i >> 1) < 4;
+      ri.trow = tmem_base + (uint32_t)g * p.acc_stride + (uint32_t)hoff + ((uint32_t)(ws.quarter * 32) << 16);
+      const bool tr = ws.wg_tid == 0 && half == 0 && (i >> 1) < 4;
       if (tr) G3_TRACE(24 + g * 16 + 4 * (i >> 1));
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
@@ -254,7 +261,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
     }
     if (elect_one()) bulk_wait_all();       // staging buffers must outlive the last stores
-    if (ws.prof && ws.wg_tid == 0) {
+    if (ws.prof && ws.wg_tid == 0 && half == 0) {
       unsigned long long* tr = p.trace + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 64 + 56 + 4 * g;
       tr[0] = (unsigned long long)ws.t_ring; tr[1] = (unsigned long long)ws.t_stg;
       tr[2] = (unsigned long long)ws.t_p1; tr[3] = (unsigned long long)ws.t_p2;
@@ -328,8 +335,11 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   const int b_bytes = p.BN * Kpad * 2;
   const int tab = round_up(5 * p.BN * 4, 1024);
   p.stg_bufs = (f32o && ep.out_t != nullptr) ? 1 : 2;
-  const int stg32 = f32o ? 8 * p.stg_bufs * 32 * (grouped ? 128 : 64) : 0;
-  const int stg16 = bf16o && !p.share_stg ? 8 * p.stg_bufs * 32 * (grouped ? 128 : 32) : 0;
+  static const bool nwg2 = getenv("HATB200_G3_NWG") && getenv("HATB200_G3_NWG")[0] == '2';
+  p.nwg = (!nwg2 && grouped && p.BN % 128 == 0 && feat_select(ep) == FEAT_PLAIN) ? 4 : 2;
+  const int ewarps = 4 * p.nwg;
+  const int stg32 = f32o ? ewarps * p.stg_bufs * 32 * (grouped ? 128 : 64) : 0;
+  const int stg16 = bf16o && !p.share_stg ? ewarps * p.stg_bufs * 32 * (grouped ? 128 : 32) : 0;
   const int rb = p.has_resid ? G3_TILE_M * CW * 4 : 0, ub = p.has_u ? G3_TILE_M * CW * 2 : 0;
   p.op_u_off = rb;
   p.op_stage_bytes = round_up(rb + ub, 1024);
@@ -374,8 +384,8 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
     const int s32 = stg32 / bufs0 * p.stg_bufs, s16 = stg16 / bufs0 * p.stg_bufs;
     const int resident = p.b_resident, stage = p.stage_bytes;
     if (getenv("HATB200_TRACE"))
-      fprintf(stderr, "[gemm_tc] N=%d K=%d BN=%d resident=%d stages=%d ops=%d stg_bufs=%d share=%d\n", p.N, Kpad, p.BN,
-              resident, p.stages, p.ops, p.stg_bufs, p.share_stg);
+      fprintf(stderr, "[gemm_tc] N=%d K=%d BN=%d resident=%d stages=%d ops=%d stg_bufs=%d share=%d nwg=%d\n", p.N, Kpad, p.BN,
+              resident, p.stages, p.ops, p.stg_bufs, p.share_stg, p.nwg);
     int off = 0;
     p.off_b = off; off += resident ? round_up(b_bytes, 1024) : 0;
     p.off_a = off; off += p.stages * stage;
@@ -465,6 +475,7 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
     G3_ATTR(FeatAll); G3_ATTR(FeatPlain); G3_ATTR(FeatResLn); G3_ATTR(FeatResULn);
 #undef G3_ATTR
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<FeatPlain, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
@@ -481,7 +492,11 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;     // engineering: A/B the specialisation
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {
-    case FEAT_PLAIN: G3_LAUNCH(FeatPlain); break;
+    case FEAT_PLAIN:
+      if (p.nwg == 4)
+        launch_pdl(gemm_tc_kernel<FeatPlain, true, 4>, grid, dim3(64 + 128 * 4), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);
+      else G3_LAUNCH(FeatPlain);
+      break;
     case FEAT_RESLN: G3_LAUNCH(FeatResLn); break;
     case FEAT_RESULN: G3_LAUNCH(FeatResULn); break;
     default: G3_LAUNCH(FeatAll); break;
