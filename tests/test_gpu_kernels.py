@@ -277,6 +277,10 @@ def _linear_fused_case(B, H, W, Cin, N, resid, eca, ln, head, out_t, act=0, seed
     (1, 16, 16, 360, 180, True, False, False, False, True, 0),      # OCAB mlp.2 + residual + bf16 copy
     (2, 16, 16, 48, 48, True, True, True, True, False, 0),          # mini model width
     (5, 32, 32, 144, 144, True, False, True, True, False, 0),       # HAT-S width, many tiles per CTA
+    # plain bf16 layers with BN % 128 == 0 run four epilogue warpgroups (two per accumulator stage, half the columns each)
+    (2, 16, 16, 96, 128, False, False, False, False, True, 0),      # BN 128: halves of 64 columns
+    (4, 32, 32, 180, 250, False, False, False, False, True, 1),     # BN 256, ragged N: pad columns of the upper half are zeros
+    (3, 16, 32, 64, 512, False, False, False, False, True, 0),      # two n-tiles of 256
 ])
 def test_linear_fused_tcgen05(shape):
     _linear_fused_case(*shape)
