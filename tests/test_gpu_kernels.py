@@ -375,6 +375,8 @@ def _conv3_fused_case(B, H, W, Cin, N, resid, ln, head, out_t, colsum, act=0, se
     (1, 16, 16, 180, 64, False, False, False, True, False, 2),      # conv_before_upsample + LeakyReLU
     (5, 32, 32, 144, 144, True, True, True, False, False, 0),       # HAT-S width, several tiles per CTA
     (1, 64, 64, 64, 256, False, False, False, True, False, 0),      # upsample-sized n-tile (256 columns)
+    (2, 32, 32, 128, 96, False, False, False, True, False, 0),      # 2 k-blocks: the looped (non-unrolled) issuer / producer
+    (2, 32, 16, 256, 64, False, False, False, True, False, 1),      # 4 k-blocks, GELU
 ])
 def test_conv3_fused_tcgen05(shape):
     _conv3_fused_case(*shape)
