@@ -195,6 +195,20 @@ int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, i
                         const float* dw_w /* (2hid,1,3,3) */, const float* dw_b,
                         void* out, int out_pitch, void* stream);
 
+/* hatb200_dwconv_gate for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * Same arguments, arithmetic and results as hatb200_dwconv_gate, but the
+ * re-laid-out depthwise weight lives in a file-scope static __device__ array (csrc/noalloc.cu) instead
+ * of a per-call allocation: the call makes no cudaMalloc / cudaFree / allocating library call and does
+ * not synchronise.  Limit: hid <= HATB200_NOALLOC_MAX_HID (larger -> HATB200_EINVAL with a message);
+ * every GPU that loads the library holds 9 * 2 * HATB200_NOALLOC_MAX_HID floats (72 KiB) until exit.
+ * All calls share that array (the used part is cleared and rewritten on `stream` by each call):
+ * calls on one stream are ordered and safe, calls that overlap on the GPU race. */
+#define HATB200_NOALLOC_MAX_HID 1024
+int hatb200_dwconv_gate_noalloc(const void* in, int dtype, int in_pitch, int B, int H, int W, int hid,
+                                const float* dw_w /* (2hid,1,3,3) */, const float* dw_b,
+                                void* out, int out_pitch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
