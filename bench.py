@@ -154,8 +154,10 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-KERNEL_OF_TAG = {"ocab_attention": "ocab_attention", "ffn_dwconv_gate": "dwconv_gate", "layernorm": "layernorm",
-                 "conv_last": "conv_last"}
+# name fragments of each kernel family in an ncu launch list (profiles/r*_ncu_full_*_summary.csv)
+NCU_NAMES = {"gemm_tc": ("gemm_tc_kernel",), "conv3_tc": ("conv3_tc_kernel",), "tapconv_tc": ("tapconv_tc_kernel",),
+             "plk_tc": ("plk_tc_kernel",), "attn_tc": ("attn_tc_kernel",), "dwgate": ("dwgate",),
+             "ffn_tc": ("ffn_tc_kernel",), "layernorm": ("layernorm_kernel",)}
 
 
 def ncu_traffic(name_parts):
@@ -163,13 +165,14 @@ def ncu_traffic(name_parts):
     `name_parts`, from the newest profiles/r*_ncu_full_*_summary.csv; (None, None) when there is no capture."""
     import csv
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")), key=os.path.getmtime)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")))
     if not files:
         return None, None
     try:
         rows = list(csv.reader(open(files[-1])))
         hdr, units = rows[0], rows[1]
-        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        col = lambda suffix: next(i for i, h in enumerate(hdr) if h.endswith(suffix))
+        ir, iw = col("dram__bytes_read.sum"), col("dram__bytes_write.sum")
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
                 for r in rows[2:] if any(n in r[0] for n in name_parts)]
@@ -181,39 +184,52 @@ def ncu_traffic(name_parts):
 
 
 def summarize_profile(prof, peaks, tc_on):
+    """Group the per-op profile by the KERNEL that served each op (hatb200_op_profile names it), find the dominant
+    kernel by measured time inside the step, and state ITS roofline: the bound is whichever of (algorithmic flops /
+    bf16 peak) and (algorithmic bytes / copy bandwidth) is the larger time."""
     groups = {}
     for tag, r in prof.items():
-        k = KERNEL_OF_TAG.get(tag, "tapconv")
-        g = groups.setdefault(k, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
+        g = groups.setdefault(r.get("kernel", "?"), dict(launches=0, ms=0.0, flops=0.0, bytes=0.0, tags=[]))
         for f in ("launches", "ms", "flops", "bytes"):
             g[f] += r[f]
+        g["tags"].append(tag)
     total_ms = sum(g["ms"] for g in groups.values())
+
+    def roof_of(g):
+        t_tensor = g["flops"] / (peaks["tf"] * 1e12)
+        t_hbm = g["bytes"] / (peaks["hbm"] * 1e9)
+        sec = g["ms"] * 1e-3
+        if t_tensor >= t_hbm:
+            ach = g["flops"] / sec / 1e12
+            return {"bound": "tensor", "achieved": ach, "peak": peaks["tf"], "unit": "TFLOP/s", "frac": ach / peaks["tf"]}
+        ach = g["bytes"] / sec / 1e9
+        return {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s", "frac": ach / peaks["hbm"]}
+
     dom = max(groups, key=lambda k: groups[k]["ms"])
     g = groups[dom]
-    if dom in ("tapconv", "ocab_attention"):
-        achieved = g["flops"] / (g["ms"] * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tf"], "unit": "TFLOP/s",
-                "frac": achieved / peaks["tf"], "traffic": None}
-    else:
-        achieved = g["bytes"] / (g["ms"] * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm"], "traffic": None}
-    # DRAM traffic per launch of the dominant family from the committed `ncu --set full` capture (cold cache: ncu
-    # flushes L2 between replays), next to the algorithmic bytes per launch of the same family
-    traffic, traffic_src = ncu_traffic({"tapconv": ("gemm_tc", "conv3_tc", "tapconv_tc"), "ocab_attention": ("attn_tc",),
-                                        "dwgate": ("dwgate",)}.get(dom, (dom,)))
+    roof = roof_of(g)
+    # DRAM traffic per launch of the dominant kernel from the committed `ncu --set full` capture (cold cache: ncu
+    # flushes L2 between replays), next to the algorithmic bytes per launch of the same kernel
+    traffic, traffic_src = ncu_traffic(NCU_NAMES.get(dom, (dom,)))
     roof["traffic"] = traffic
     roof["traffic_source"] = traffic_src
     roof["algorithmic_bytes_per_launch"] = g["bytes"] / max(1, g["launches"])
-    roof.update({"kernel": dom + ("_tcgen05" if tc_on and dom in ("tapconv", "ocab_attention") else ""),
-                 "launches": g["launches"], "avg_launch_us": g["ms"] * 1e3 / max(1, g["launches"]),
+    roof["algorithmic_flops_per_launch"] = g["flops"] / max(1, g["launches"])
+    roof.update({"kernel": dom, "ops": g["tags"], "launches": g["launches"],
+                 "avg_launch_us": g["ms"] * 1e3 / max(1, g["launches"]),
                  "share_of_step": g["ms"] / total_ms if total_ms else None,
                  "peak_source": f"{peaks['src']} (sustained bf16 / copy bandwidth, MEASURED_PEAKS.json)"})
-    per_op = {t: {"launches": r["launches"], "ms": round(r["ms"], 4),
+    per_kernel = {}
+    for k, gk in sorted(groups.items(), key=lambda kv: -kv[1]["ms"]):
+        rk = roof_of(gk)
+        per_kernel[k] = {"launches": gk["launches"], "ms": round(gk["ms"], 4), "bound": rk["bound"],
+                         "achieved": round(rk["achieved"], 1), "unit": rk["unit"], "frac": round(rk["frac"], 4),
+                         "share_of_step": round(gk["ms"] / total_ms, 4) if total_ms else None}
+    per_op = {t: {"kernel": r.get("kernel"), "launches": r["launches"], "ms": round(r["ms"], 4),
                   "tflops": round(r["flops"] / (r["ms"] * 1e-3) / 1e12, 2) if r["ms"] > 0 else None,
                   "gbs": round(r["bytes"] / (r["ms"] * 1e-3) / 1e9, 1) if r["ms"] > 0 else None}
               for t, r in prof.items()}
-    return roof, per_op, total_ms
+    return roof, per_kernel, per_op, total_ms
 
 
 def run_ours(args):
@@ -289,7 +305,7 @@ def run_ours(args):
     if rank == 0:
         prof = eng.op_profile(x)
         torch.cuda.synchronize()
-        roof, per_op, prof_ms = summarize_profile(prof, peaks, tc_on)
+        roof, per_kernel, per_op, prof_ms = summarize_profile(prof, peaks, tc_on)
         lr_px = BATCH * LR * LR
         whole = MFLOP_PER_LR_PX * 1e6 * lr_px / (ms_step * 1e-3) / 1e12
         cpu = None
@@ -316,8 +332,10 @@ def run_ours(args):
                     "d2h_bytes_per_step": y_host.numel() * 2},
             "gpu_launches": launches * K,
             "roofline": roof,
-            "whole_forward_tflops": whole, "whole_forward_frac_of_peak": whole / peaks["tf"],
-            "per_op": per_op, "profiled_eager_step_ms": prof_ms,
+            "whole_forward": {"bound": "tensor", "achieved": whole, "peak": peaks["tf"], "unit": "TFLOP/s",
+                              "frac": whole / peaks["tf"], "gflop_per_step": MFLOP_PER_LR_PX * lr_px / 1e3},
+            "per_kernel": per_kernel, "per_op": per_op, "profiled_eager_step_ms": prof_ms,
+            "tcgen05_fallbacks": eng.last_fallback_count,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu

@@ -84,7 +84,9 @@ const char* hatb200_param_key(hatb200_handle* h, int i);
 /* Build the packed device copies (allocates; call outside stream capture). */
 int hatb200_pack(hatb200_handle* h, void* stream);
 
-/* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1), "op_timing" (0/1). */
+/* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1), "op_timing" (0/1), "strict_tc" (0/1: in the
+ * bf16 path a shape that no tcgen05 kernel takes fails with HATB200_EUNSUPPORTED instead of running the CUDA-core
+ * kernel). */
 int hatb200_set_option(hatb200_handle* h, const char* name, int value);
 
 /* Bytes of scratch needed by hatb200_forward for (B,H,W) in the given compute
@@ -98,11 +100,21 @@ int hatb200_workspace_bytes(hatb200_handle* h, int B, int H, int W, int compute_
  * from calculate_mask -> window_partition, hat_arch.py:124-128, :831). */
 int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W,
                     void* y, int y_dtype, void* workspace, size_t ws_bytes, void* stream);
+/* HAT.forward_features (hat_arch.py:828-846): x is the (B, embed_dim, H, W) output of conv_first, y the
+ * (B, embed_dim, H, W) output of the final LayerNorm (patch_embed + norm, the residual groups, norm, patch_unembed).
+ * Same arithmetic selection, geometry rules and workspace as hatb200_forward. */
+int hatb200_forward_features(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W,
+                             void* y, int y_dtype, void* workspace, size_t ws_bytes, void* stream);
 /* Number of kernels launched by the last hatb200_forward on this handle. */
 int hatb200_last_launch_count(hatb200_handle* h);
+/* Number of ops of the last bf16 hatb200_forward that ran on a CUDA-core kernel because no tcgen05 kernel takes their
+ * shape (0 for every published HAT variant at sizes that are multiples of 16). */
+int hatb200_last_fallback_count(hatb200_handle* h);
 
 /* Per-op device times (CUDA events) of the last forward run with option "op_timing"=1, as a JSON
- * object {"tag": {"launches","ms","flops","bytes"}} with ALGORITHMIC flops/bytes per tag. */
+ * object {"tag": {"kernel","launches","ms","flops","bytes"}} with ALGORITHMIC flops/bytes per tag (bytes: every
+ * stream the launch reads or writes -- activations, weights, fp32 residual in/out, CAB branch, LayerNorm copy --
+ * each counted once) and the name of the kernel that served the tag. */
 int hatb200_op_profile(hatb200_handle* h, char* json, size_t cap);
 
 /* HATModel.tile_process geometry (hat_model.py:52-108).  Fills up to `cap`
@@ -208,6 +220,15 @@ int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, i
 int hatb200_dwconv_gate_noalloc(const void* in, int dtype, int in_pitch, int B, int H, int W, int hid,
                                 const float* dw_w /* (2hid,1,3,3) */, const float* dw_b,
                                 void* out, int out_pitch, void* stream);
+
+#ifdef HATB200_ENGINEERING
+/* Engineering probes (csrc/tc_probe.cu), only in libraries built with HATB200_ENGINEERING=1; no reference counterpart.
+ * One tcgen05.mma with caller-chosen descriptor fields, and the per-CTA %globaltimer trace of the last persistent
+ * GEMM / conv3 launch made with HATB200_GEMM_TRACE set (tools/probe_umma.py, tools/trace_gemm.py, tools/trace_conv3.py). */
+int hatb200_probe_umma(const void* a, int R, const void* b, int r0, int sbo_bytes, int base_offset, void* out,
+                       void* stream);
+int hatb200_debug_gemm_trace(unsigned long long* host, void* stream);
+#endif
 
 #ifdef __cplusplus
 }

@@ -357,3 +357,30 @@ def randomized_state_dict(template: dict, seed: int):
         else:
             out[k] = 0.05 * r
     return out
+
+
+def scale_tail(sd: dict, tail_scale: float):
+    """`conv_last.{weight,bias}` x float32(tail_scale): y' = tail_scale * (y - mean) + mean, so a randomised
+    state_dict gives image-range outputs (the north_star's bars are stated at peak 1.0)."""
+    out = dict(sd)
+    s = torch.tensor(float(tail_scale), dtype=torch.float32)
+    for k in ("conv_last.weight", "conv_last.bias"):
+        out[k] = sd[k] * s
+    return out
+
+
+def fresh_state_dict(hat_cls, cfg: dict, seed: int):
+    """The reference-style initialisation (hat_arch.py:761-768 + PyTorch conv defaults) of `hat_cls(**cfg)`
+    under torch.manual_seed(seed), as a detached CPU state_dict."""
+    torch.manual_seed(seed)
+    net = hat_cls(**cfg)
+    return {k: v.detach().clone() for k, v in net.state_dict().items()}
+
+
+def state_dict_checksum(sd: dict) -> float:
+    """Order-dependent float64 checksum of the floating entries (pins seeded weights across machines)."""
+    tot = 0.0
+    for i, (k, v) in enumerate(sd.items()):
+        if v.is_floating_point():
+            tot += (i % 7 + 1) * v.double().abs().sum().item()
+    return tot

@@ -49,7 +49,10 @@ _SIGNATURES = {
     "hatb200_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "hatb200_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
                                   C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hatb200_forward_features": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                           C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "hatb200_last_launch_count": (C.c_int, [C.c_void_p]),
+    "hatb200_last_fallback_count": (C.c_int, [C.c_void_p]),
     "hatb200_op_profile": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "hatb200_tile_plan": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int32), C.c_int]),
     "hatb200_crop_place": (C.c_int, [C.c_void_p, C.c_int] + [C.c_int] * 6 + [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]),

@@ -8,11 +8,19 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libhatb200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "--expt-relaxed-constexpr"]
+         "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "--expt-relaxed-constexpr",
+         "-Wno-deprecated-gpu-targets"] + (["-DHATB200_ENGINEERING"] if os.environ.get("HATB200_ENGINEERING", "0") == "1" else [])
+
+
+# engineering probes (tcgen05 descriptor probe, per-CTA timestamp dump): compiled into the library only on demand
+# (HATB200_ENGINEERING=1 python super_resolution_b200/build.py --force); the product library does not export them
+ENGINEERING_ONLY = {"tc_probe.cu"}
+ENGINEERING = os.environ.get("HATB200_ENGINEERING", "0") == "1"
 
 
 def sources():
-    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
+    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)
+                  if f.endswith(".cu") and (ENGINEERING or f not in ENGINEERING_ONLY))
 
 
 def needs_build():

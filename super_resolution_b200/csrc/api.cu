@@ -200,17 +200,19 @@ int hatb200_set_option(hatb200_handle* h, const char* name, int value) {
   if (!strcmp(name, "tensor_cores")) h->use_tc = value != 0;
   else if (!strcmp(name, "sync_debug")) h->sync_debug = value != 0;
   else if (!strcmp(name, "op_timing")) h->op_timing = value != 0;
+  else if (!strcmp(name, "strict_tc")) h->strict_tc = value != 0;
   else { set_error("set_option: unknown option '%s'", name); return HATB200_EINVAL; }
   return 0;
 }
 
 int hatb200_last_launch_count(hatb200_handle* h) { return h ? h->last_launches : 0; }
+int hatb200_last_fallback_count(hatb200_handle* h) { return h ? h->last_fallbacks : 0; }
 
 // Per-op device times of the last forward run with option "op_timing" = 1, as JSON:
-// {"tag": {"launches": n, "ms": t, "flops": f, "bytes": b}, ...}.  Synchronises.
+// {"tag": {"kernel": name, "launches": n, "ms": t, "flops": f, "bytes": b}, ...}.  Synchronises.
 int hatb200_op_profile(hatb200_handle* h, char* json, size_t cap) {
   HB_REQUIRE(h && json && cap > 2, HATB200_EINVAL, "op_profile: bad arguments");
-  struct Agg { int n = 0; double ms = 0, flops = 0, bytes = 0; };
+  struct Agg { int n = 0; double ms = 0, flops = 0, bytes = 0; std::string kernel; };
   std::map<std::string, Agg> agg;
   std::vector<std::string> order;
   for (const OpRec& r : h->recs) {
@@ -220,13 +222,17 @@ int hatb200_op_profile(hatb200_handle* h, char* json, size_t cap) {
     if (!agg.count(r.tag)) order.push_back(r.tag);
     Agg& a = agg[r.tag];
     a.n++; a.ms += ms; a.flops += r.flops; a.bytes += r.bytes;
+    const std::string k = r.kernel ? r.kernel : "?";
+    if (a.kernel.empty()) a.kernel = k;
+    else if (a.kernel.find(k) == std::string::npos) a.kernel += "+" + k;     // a tag served by more than one kernel
   }
   std::string out = "{";
   for (size_t i = 0; i < order.size(); i++) {
     const Agg& a = agg[order[i]];
-    char line[256];
-    snprintf(line, sizeof(line), "%s\"%s\": {\"launches\": %d, \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
-             i ? ", " : "", order[i].c_str(), a.n, a.ms, a.flops, a.bytes);
+    char line[384];
+    snprintf(line, sizeof(line),
+             "%s\"%s\": {\"kernel\": \"%s\", \"launches\": %d, \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
+             i ? ", " : "", order[i].c_str(), a.kernel.c_str(), a.n, a.ms, a.flops, a.bytes);
     out += line;
   }
   out += "}";

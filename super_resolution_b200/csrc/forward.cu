@@ -83,20 +83,51 @@ struct Fwd {
   bool tc() const { return h->use_tc && d.dt == HATB200_BF16; }
 
   // op timing (bench roofline breakdown): CUDA events around each op on the launching stream
-  int t_begin(const char* tag, double flops, double bytes) {
+  int t_begin(const char* tag, double flops, double bytes, const char* kernel = nullptr) {
     if (!h->op_timing) return -1;
     while (h->ev_pool.size() < h->ev_used + 2) {
       cudaEvent_t e;
       if (cudaEventCreate(&e) != cudaSuccess) return -1;
       h->ev_pool.push_back(e);
     }
-    OpRec r{tag, h->ev_pool[h->ev_used], h->ev_pool[h->ev_used + 1], flops, bytes};
+    OpRec r{tag, kernel, h->ev_pool[h->ev_used], h->ev_pool[h->ev_used + 1], flops, bytes};
     h->ev_used += 2;
     cudaEventRecord(r.e0, st);
     h->recs.push_back(r);
     return (int)h->recs.size() - 1;
   }
   void t_end(int id) { if (id >= 0) cudaEventRecord(h->recs[id].e1, st); }
+
+  // the bf16 path met a shape no tcgen05 kernel takes: counted (hatb200_last_fallback_count), an error under
+  // the "strict_tc" option -- never silent (the CUDA-core kernels are 10-20x slower)
+  int fallback(const char* tag, const char* kernel) {
+    h->last_fallbacks++;
+    static const bool trace = getenv("HATB200_TRACE") != nullptr;
+    if (trace) fprintf(stderr, "[hatb200] %s: no tcgen05 kernel takes this shape -> %s\n", tag, kernel);
+    HB_REQUIRE(!h->strict_tc, HATB200_EUNSUPPORTED, "strict_tc: '%s' would run on the CUDA-core kernel %s", tag, kernel);
+    return 0;
+  }
+
+  // ALGORITHMIC bytes of one fused conv / GEMM launch: every stream the epilogue reads or writes, each once
+  double conv_bytes(const ConvW& cw, double Mt, const Epilogue& ep) const {
+    const double fo = cw.algoO ? cw.algoO : cw.O, fi = cw.algoI ? cw.algoI : cw.I;
+    double b = Mt * fi * d.es + (double)cw.taps() * fo * fi * d.es;          // activations in, weights
+    if (ep.out_t) b += Mt * fo * d.es * (ep.shuffle_r > 1 ? 1.0 : 1.0);
+    if (ep.out_f32) b += Mt * fo * 4;
+    if (ep.resid) b += Mt * fo * 4;
+    if (ep.eca_u) b += Mt * fo * d.es;
+    if (ep.ln_out) b += Mt * fo * d.es;
+    if (ep.ln_head) b += Mt * ep.ln_head_c * d.es * (ep.ln_head_pad ? 2 : 1);
+    return b;
+  }
+  const char* conv_kernel(const ConvW& cw, const ConvArgs& a, const Epilogue& ep, const char* tag) const {
+    if (tc() && !tc_disabled(tag)) {
+      if (gemm_tc_supported(a, cw.Npad, cw.Kpad, ep)) return "gemm_tc";
+      if (conv3_tc_supported(a, cw.Npad, cw.Kpad, ep)) return "conv3_tc";
+      if (tapconv_tc_supported(a, cw.Npad, cw.Kpad, ep)) return "tapconv_tc";
+    }
+    return "tapconv_simt";
+  }
 
   int dbg(const char* what) {
     if (!h->sync_debug) return 0;
@@ -115,7 +146,13 @@ struct Fwd {
   int conv(const char* tag, const ConvW& cw, const void* A, int a_pitch, int a_coff, int H, int W, Epilogue ep) {
     double Mt = (double)d.B * H * W;
     const double fo = cw.algoO ? cw.algoO : cw.O, fi = cw.algoI ? cw.algoI : cw.I;
-    int tid = t_begin(tag, 2.0 * Mt * fo * fi * cw.taps(), Mt * (fi + fo) * d.es);
+    int tid = -1;
+    if (h->op_timing) {
+      ConvArgs a{A, a_pitch, a_coff, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
+      Epilogue e2 = ep;
+      if (!e2.bias) e2.bias = cw.bias;
+      tid = t_begin(tag, 2.0 * Mt * fo * fi * cw.taps(), conv_bytes(cw, Mt, ep), conv_kernel(cw, a, e2, tag));
+    }
     int r = conv_impl(tag, cw, A, a_pitch, a_coff, H, W, ep);
     t_end(tid);
     return r;
@@ -130,7 +167,7 @@ struct Fwd {
       e2.shuffle_perm = 1; e2.bias = cw.bias_s;
       if (conv3_tc_supported(a, cw.Npad, cw.Kpad, e2)) {
         double Mt = (double)d.B * H * W;
-        int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), Mt * (cw.I + cw.O) * d.es);
+        int tid = t_begin(tag, 2.0 * Mt * cw.O * cw.I * cw.taps(), conv_bytes(cw, Mt, ep), "conv3_tc");
         int r = launch_conv3_tc(a, cw.w16s, cw.Npad, cw.Kpad, e2, st);
         t_end(tid);
         HB_TRY(r);
@@ -161,6 +198,7 @@ struct Fwd {
       return dbg("tapconv_tc");
     }
     // CUDA-core path: LayerNorm / column sums are separate kernels
+    if (tc()) HB_TRY(fallback(tag, "tapconv_simt"));
     Epilogue e2 = ep;
     e2.ln_gamma = e2.ln_beta = nullptr; e2.ln_out = e2.ln_head = nullptr;
     e2.ln_head_colsum = nullptr; e2.colsum = nullptr;
@@ -182,7 +220,7 @@ struct Fwd {
 
   // standalone LayerNorm of the fp32 stream (+ compact head and its column sums)
   int ln(const float* x, const LNW& n, void* out, int head_c) {
-    int tid = t_begin("layernorm", 8.0 * d.M * d.C, (double)d.M * d.C * (4 + d.es));
+    int tid = t_begin("layernorm", 8.0 * d.M * d.C, (double)d.M * d.C * (4 + d.es), "layernorm");
     int r = ln_impl(x, n, out, head_c);
     t_end(tid);
     return r;
@@ -213,7 +251,7 @@ struct Fwd {
     if (!dyn_done) HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
     if (e.plk_wt && plk_tc(e.pdim)) {
       double Mt = (double)d.M;
-      int tid = t_begin("esc_plk13", 2.0 * Mt * e.pdim * e.pdim * (e.plk.taps() + 9.0 / e.pdim), Mt * 2 * e.pdim * d.es);
+      int tid = t_begin("esc_plk13", 2.0 * Mt * e.pdim * e.pdim * (e.plk.taps() + 9.0 / e.pdim), Mt * 2 * e.pdim * d.es, "plk_tc");
       int r = launch_plk_tc((const bf16*)w.X16P, d.B, d.H, d.W, e.plk_wt, w.dyn, (bf16*)dst, d.Cp, st);
       t_end(tid);
       HB_TRY(r);
@@ -252,7 +290,7 @@ struct Fwd {
     {  // GatedDconvFFN (hat_arch.py:107-119)
       Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.hp4;
       HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
-      int tid = t_begin("ffn_dwconv_gate", 2.0 * d.M * 2 * d.hid * 9, (double)d.M * 3 * d.hid * d.es);
+      int tid = t_begin("ffn_dwconv_gate", 2.0 * d.M * 2 * d.hid * 9, (double)d.M * 3 * d.hid * d.es, "dwgate");
       HB_TRY(launch_dwgate(w.H1, d.dt, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, w.G, d.hp2, d.hp2, st));
       t_end(tid);
       HB_TRY(dbg("dwgate"));
@@ -272,17 +310,23 @@ struct Fwd {
     // tcgen05 attention (bf16 path, default geometry): head-padded qkv / proj weights
     const int hp = o.heads * ATTN_TC_DP;
     AttnTcArgs ta{w.H1, 3 * hp, d.B, d.H, d.W, o.heads, dh, c.window_size, c.overlap_win_size, o.bias_l2, w.G, hp};
-    const bool use_attn_tc = tc() && !c.ocab_esc_enable && o.bias_l2 != nullptr && !tc_disabled("ocab_attention") &&
-                             attn_tc_supported(ta);
+    const bool use_attn_tc = tc() && o.bias_l2 != nullptr && !tc_disabled("ocab_attention") && attn_tc_supported(ta);
     if (c.ocab_esc_enable) {   // K/V from y = ConvAttnWrapper(xn) (hat_arch.py:336-344)
       HB_CHECK_CUDA(cudaMemcpyAsync(w.XN2, w.XN, (size_t)d.M * d.Cp * d.es, cudaMemcpyDeviceToDevice, st));
       HB_TRY(esc_mix(o.esc, w.XN2));
       Epilogue ey; ey.out_t = w.U; ey.out_t_pitch = d.Cp; ey.out_t_zero_to = d.Cp;
       HB_TRY(conv("esc_aggr", o.esc.aggr, w.XN2, d.Cp, 0, d.H, d.W, ey));
-      Epilogue eq; eq.out_scale = scale; eq.scale_ncols = d.C; eq.out_t = w.H1; eq.out_t_pitch = d.qkvp;
-      HB_TRY(conv("ocab_qkv", o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
-      Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = d.qkvp; ek.out_t_coff = d.C;
-      HB_TRY(conv("ocab_qkv", o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
+      if (use_attn_tc) {       // head-padded layout of the tcgen05 attention: q at [0, hp), k / v at [hp, 3 hp)
+        Epilogue eq; eq.out_scale = scale; eq.scale_ncols = hp; eq.out_t = w.H1; eq.out_t_pitch = 3 * hp;
+        HB_TRY(conv("ocab_qkv", o.q_tc, w.XN, d.Cp, 0, d.H, d.W, eq));
+        Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = 3 * hp; ek.out_t_coff = hp;
+        HB_TRY(conv("ocab_qkv", o.kv_tc, w.U, d.Cp, 0, d.H, d.W, ek));
+      } else {
+        Epilogue eq; eq.out_scale = scale; eq.scale_ncols = d.C; eq.out_t = w.H1; eq.out_t_pitch = d.qkvp;
+        HB_TRY(conv("ocab_qkv", o.q, w.XN, d.Cp, 0, d.H, d.W, eq));
+        Epilogue ek; ek.out_t = w.H1; ek.out_t_pitch = d.qkvp; ek.out_t_coff = d.C;
+        HB_TRY(conv("ocab_qkv", o.kv, w.U, d.Cp, 0, d.H, d.W, ek));
+      }
     } else if (use_attn_tc) {
       Epilogue ep; ep.out_scale = scale; ep.scale_ncols = hp; ep.out_t = w.H1; ep.out_t_pitch = 3 * hp;
       HB_TRY(conv("ocab_qkv", o.qkv_tc, w.XN, d.Cp, 0, d.H, d.W, ep));
@@ -292,7 +336,9 @@ struct Fwd {
     }
     {
       double nk = (double)c.overlap_win_size * c.overlap_win_size;
-      int tid = t_begin("ocab_attention", 4.0 * d.M * nk * d.C, (double)d.M * 4 * d.C * d.es);
+      int tid = t_begin("ocab_attention", 4.0 * d.M * nk * d.C, (double)d.M * 4 * d.C * d.es,
+                        use_attn_tc ? "attn_tc" : "attn_simt");
+      if (tc() && !use_attn_tc) HB_TRY(fallback("ocab_attention", "attn_simt"));
       if (use_attn_tc) {
         HB_TRY(launch_attn_tc(ta, st));
       } else {
@@ -319,13 +365,19 @@ struct Fwd {
     return 0;
   }
 
-  int run(const void* x, int x_dt, void* y, int y_dt) {
+  // features_only: HAT.forward_features (hat_arch.py:828-846) -- x is the (B, C, H, W) output of conv_first, y the
+  // (B, C, H, W) output of the final LayerNorm; everything between is the same launch stream as the full forward
+  int run(const void* x, int x_dt, void* y, int y_dt, bool features_only = false) {
     const hatb200_config& c = h->cfg;
-    if (c.upsampler != 1)   // hat_arch.py:852: no tail -> only the (de)normalisation remains
+    if (c.upsampler != 1 && !features_only)   // hat_arch.py:852: no tail -> only the (de)normalisation remains
       return launch_affine_roundtrip(x, x_dt, d.B, c.in_chans, d.H * d.W, c.mean, c.img_range, y, y_dt, st);
     if (tc()) HB_CHECK_CUDA(cudaMemsetAsync(w.X16P, 0, (size_t)d.B * d.H * (d.W + 12) * 16 * 2, st));   // x pads stay zero
-    HB_TRY(launch_conv_first(x, x_dt, d.B, c.in_chans, d.H, d.W, h->conv_first_w, h->conv_first_b, d.C, c.mean,
-                             c.img_range, w.S, st));
+    if (features_only) {
+      HB_TRY(launch_nchw_to_tokens(x, x_dt, d.B, d.C, d.H * d.W, w.S, st));
+    } else {
+      HB_TRY(launch_conv_first(x, x_dt, d.B, c.in_chans, d.H, d.W, h->conv_first_w, h->conv_first_b, d.C, c.mean,
+                               c.img_range, w.S, st));
+    }
     HB_TRY(dbg("conv_first"));
     // patch_embed (+norm) -> XA: the running stream at the first group input (hat_arch.py:836)
     if (c.patch_norm) {
@@ -368,6 +420,11 @@ struct Fwd {
         HB_TRY(ln(w.XA, *nl, w.XN, nh));
       }
     }
+    if (features_only) {      // XN = norm(x) (hat_arch.py:844) -> patch_unembed: (B, C, H, W)
+      // (both the '1conv' and the 'identity' loop tails leave the final LayerNorm in XN)
+      HB_TRY(launch_tokens_to_nchw(w.XN, d.dt, d.Cp, d.B, d.C, d.H * d.W, y, y_dt, st));
+      return dbg("forward_features");
+    }
     // XN = norm(x) (hat_arch.py:844); conv_after_body + long skip (hat_arch.py:854) -> XN2 (T)
     if (c.resi_conv) {
       Epilogue ep; ep.resid = w.S; ep.resid_pitch = d.C; ep.out_t = w.XN2; ep.out_t_pitch = d.Cp; ep.out_t_zero_to = d.Cp;
@@ -401,7 +458,8 @@ struct Fwd {
       }
     }
     int tid = t_begin("conv_last", 2.0 * d.B * hh * hw * 64 * 9 * c.in_chans,
-                      (double)d.B * hh * hw * (64 * d.es + c.in_chans * (y_dt == HATB200_F32 ? 4 : 2)));
+                      (double)d.B * hh * hw * (64 * d.es + c.in_chans * (y_dt == HATB200_F32 ? 4 : 2)),
+                      tc() ? "conv3_tc+nhwc_to_nchw_affine" : "conv_last");
     // tensor-core route: N = 3 padded to a 16-column MMA tile on the persistent conv3 kernel (fp32 pixels-last out),
     // then one pass that applies "/ img_range + mean" and writes the NCHW planes.  (The CUDA-core kernel below spends
     // one shared-memory weight load per FMA: 172 us for 16 x 256 x 256 pixels.)
@@ -449,8 +507,21 @@ extern "C" int hatb200_workspace_bytes(hatb200_handle* h, int B, int H, int W, i
   return 0;
 }
 
+static int forward_common(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W, void* y, int y_dtype,
+                          void* workspace, size_t ws_bytes, void* stream, bool features_only);
+
 extern "C" int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W, void* y,
                                int y_dtype, void* workspace, size_t ws_bytes, void* stream) {
+  return forward_common(h, x, x_dtype, B, H, W, y, y_dtype, workspace, ws_bytes, stream, false);
+}
+
+extern "C" int hatb200_forward_features(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W, void* y,
+                                        int y_dtype, void* workspace, size_t ws_bytes, void* stream) {
+  return forward_common(h, x, x_dtype, B, H, W, y, y_dtype, workspace, ws_bytes, stream, true);
+}
+
+static int forward_common(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W, void* y, int y_dtype,
+                          void* workspace, size_t ws_bytes, void* stream, bool features_only) {
   HB_TRY(check_geometry(h, B, H, W));
   HB_REQUIRE(x && y, HATB200_EINVAL, "forward: null tensor");
   HB_REQUIRE(x_dtype == HATB200_F32 || x_dtype == HATB200_BF16, HATB200_EUNSUPPORTED,
@@ -468,9 +539,10 @@ extern "C" int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, in
   char* base = (char*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
   plan(h->cfg, f.d, base, f.w);
   g_launches = 0;
+  h->last_fallbacks = 0;
   h->recs.clear();
   h->ev_used = 0;
-  int r = f.run(x, x_dtype, y, y_dtype);
+  int r = f.run(x, x_dtype, y, y_dtype, features_only);
   h->last_launches = g_launches;
   return r;
 }

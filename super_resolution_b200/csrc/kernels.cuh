@@ -60,6 +60,8 @@ int launch_crop_place(const void* src, int dt, int B, int C, int sh, int sw, int
 int launch_reflect_pad(const void* src, int dt, int B, int C, int h, int w, void* dst, int ph, int pw, cudaStream_t st);
 int launch_nhwc_to_nchw_affine(const float* in, int pitch, int B, int OC, int H, int W, const float* mean, float range,
                                void* y, int y_dt, cudaStream_t st);
+int launch_nchw_to_tokens(const void* x, int x_dt, int B, int C, int hw, float* out, cudaStream_t st);
+int launch_tokens_to_nchw(const void* in, int dt, int pitch, int B, int C, int hw, void* y, int y_dt, cudaStream_t st);
 int launch_tensor2img(const void* x, int dt, int B, int C, int H, int W, float mn, float mx, int rgb2bgr, uint8_t* out,
                       cudaStream_t st);
 int launch_psnr_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int crop_border, int test_y, double* ws,

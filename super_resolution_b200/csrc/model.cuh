@@ -53,6 +53,7 @@ struct OcabW {
   float* bias_compact = nullptr;   // (heads, (ws+ows-1)^2)
   // tcgen05 attention path: head-padded (head_dim -> 32) qkv / proj weights and the log2e-scaled bias table
   ConvW qkv_tc, proj_tc;
+  ConvW q_tc, kv_tc;               // ocab_esc_enable: separate head-padded q / kv GEMMs (different inputs)
   float* bias_l2 = nullptr;        // (heads, 1536)
   ConvW proj, mlp0, mlp2;
   EscW esc;
@@ -82,7 +83,7 @@ struct Workspace {           // carved from the caller's scratch buffer
 }  // namespace hb
 
 namespace hb {
-struct OpRec { const char* tag; cudaEvent_t e0, e1; double flops, bytes; };
+struct OpRec { const char* tag; const char* kernel; cudaEvent_t e0, e1; double flops, bytes; };
 }
 
 struct hatb200_handle {
@@ -97,7 +98,9 @@ struct hatb200_handle {
   bool packed = false;
   bool use_tc = true;
   bool sync_debug = false;
+  bool strict_tc = false;            // bf16 path: a shape no tcgen05 kernel takes is an error instead of a CUDA-core launch
   int last_launches = 0;
+  int last_fallbacks = 0;            // ops of the last bf16 forward that ran on a CUDA-core kernel instead of tcgen05
   std::vector<void*> allocs;
   int* err_flag = nullptr;
   // packed weights

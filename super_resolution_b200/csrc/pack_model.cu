@@ -137,6 +137,25 @@ struct Packer {
       HB_TRY(launch_pack_vec_headpad(qb->ptr, qb->dtype, C, heads, 1, w.bias, 0, st));
       HB_TRY(launch_pack_vec_headpad(kvb->ptr, kvb->dtype, C, heads, 2, w.bias, HP, st));
     }
+    if (h->cfg.ocab_esc_enable) {    // q and k/v come from different inputs (hat_arch.py:336-351): two head-padded GEMMs
+      const ParamRef* srcs[2] = {q, kv};
+      ConvW* dst[2] = {&o.q_tc, &o.kv_tc};
+      const char* bkeys[2] = {".q_proj.bias", ".kv_proj.bias"};
+      for (int i = 0; i < 2; i++) {
+        ConvW& t = *dst[i];
+        const int nblk = i + 1;
+        t.O = nblk * HP; t.I = C; t.KH = t.KW = 1; t.algoO = nblk * C; t.algoI = C;
+        t.Npad = tc_npad(t.O); t.Kpad = kpad_of(C);
+        HB_TRY(alloc((void**)&t.w16, (size_t)t.Npad * t.Kpad * sizeof(bf16)));
+        HB_TRY(launch_pack_rows_headpad(srcs[i]->ptr, srcs[i]->dtype, C, heads, nblk, t.w16, t.Kpad, 0, st));
+        HB_TRY(alloc((void**)&t.bias, (size_t)t.O * sizeof(float)));
+        if (has(op + bkeys[i])) {
+          const ParamRef* b;
+          HB_TRY(get(op + bkeys[i], &b));
+          HB_TRY(launch_pack_vec_headpad(b->ptr, b->dtype, C, heads, nblk, t.bias, 0, st));
+        }
+      }
+    }
     ConvW& pj = o.proj_tc;
     pj.O = C; pj.I = HP; pj.KH = pj.KW = 1; pj.algoO = C; pj.algoI = C;
     pj.Npad = tc_npad(C); pj.Kpad = kpad_of(HP);
@@ -203,7 +222,7 @@ struct Packer {
       HB_TRY(alloc((void**)&o.bias_compact, (size_t)o.heads * T * T * sizeof(float)));
       HB_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
                                    h->err_flag, st));
-      if (ws == 16 && ows == 24 && !c.ocab_esc_enable) HB_TRY(ocab_tc(op, o, C, ws, ows));
+      if (ws == 16 && ows == 24) HB_TRY(ocab_tc(op, o, C, ws, ows));
       if (c.resi_conv) HB_TRY(conv(lp + ".conv", lw.conv, C, C, 3, 3));
     }
     HB_TRY(ln("norm", h->final_norm));

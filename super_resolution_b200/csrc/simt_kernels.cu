@@ -676,3 +676,61 @@ int launch_add_convert(const float* a, const float* b, int M, int C, float* out_
   return 0;
 }
 }  // namespace hb
+
+// ---------------------------------------------------------------------------
+// HAT.forward_features boundary (hat_arch.py:828-846): (B, C, H, W) feature maps <-> channels-last tokens.
+// 32 x 32 shared-memory tile transpose; both sides coalesced.
+// ---------------------------------------------------------------------------
+namespace hb {
+template <typename TX>
+__global__ void nchw_to_tokens_kernel(const TX* __restrict__ x, int C, int hw, float* __restrict__ out) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, p = p0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && p < hw) ? to_f(x[((size_t)b * C + c) * hw + p]) : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i, c = c0 + threadIdx.x;
+    if (p < hw && c < C) out[((size_t)b * hw + p) * C + c] = tile[threadIdx.x][i];
+  }
+}
+
+template <typename T, typename TY>
+__global__ void tokens_to_nchw_kernel(const T* __restrict__ in, int pitch, int C, int hw, TY* __restrict__ y) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (p < hw && c < C) ? to_f(in[((size_t)b * hw + p) * pitch + c]) : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, p = p0 + threadIdx.x;
+    if (c < C && p < hw) y[((size_t)b * C + c) * hw + p] = from_f<TY>(tile[threadIdx.x][i]);
+  }
+}
+
+int launch_nchw_to_tokens(const void* x, int x_dt, int B, int C, int hw, float* out, cudaStream_t st) {
+  dim3 grid(cdiv(hw, 32), cdiv(C, 32), B), block(32, 8);
+  if (x_dt == HATB200_F32) nchw_to_tokens_kernel<float><<<grid, block, 0, st>>>((const float*)x, C, hw, out);
+  else if (x_dt == HATB200_BF16) nchw_to_tokens_kernel<bf16><<<grid, block, 0, st>>>((const bf16*)x, C, hw, out);
+  else { set_error("nchw_to_tokens: dtype %d unsupported", x_dt); return HATB200_EINVAL; }
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_tokens_to_nchw(const void* in, int dt, int pitch, int B, int C, int hw, void* y, int y_dt, cudaStream_t st) {
+  dim3 grid(cdiv(hw, 32), cdiv(C, 32), B), block(32, 8);
+  if (dt == HATB200_F32 && y_dt == HATB200_F32)
+    tokens_to_nchw_kernel<float, float><<<grid, block, 0, st>>>((const float*)in, pitch, C, hw, (float*)y);
+  else if (dt == HATB200_BF16 && y_dt == HATB200_BF16)
+    tokens_to_nchw_kernel<bf16, bf16><<<grid, block, 0, st>>>((const bf16*)in, pitch, C, hw, (bf16*)y);
+  else if (dt == HATB200_BF16 && y_dt == HATB200_F32)
+    tokens_to_nchw_kernel<bf16, float><<<grid, block, 0, st>>>((const bf16*)in, pitch, C, hw, (float*)y);
+  else { set_error("tokens_to_nchw: dtypes %d -> %d unsupported", dt, y_dt); return HATB200_EINVAL; }
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+}  // namespace hb

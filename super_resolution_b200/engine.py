@@ -51,8 +51,11 @@ class Engine:
         self.handle = None
         self.device = None
         self._bound = None             # tensors borrowed by the handle (kept alive)
-        self._sample = None            # cheap staleness probe
+        self._sample = None            # staleness probe over every bound tensor
         self._probe_tensors = []
+        self.output_view = False       # True: graphed forwards return the graph's own output buffer (valid until the
+                                       # next forward of the same shape) instead of a fresh copy of it
+        self.last_fallback_count = 0
         self._ws = None
         self._graphs = {}
         self.use_cuda_graph = os.environ.get("HATB200_CUDA_GRAPH", "1") != "0"
@@ -88,9 +91,10 @@ class Engine:
 
     # -- binding ----------------------------------------------------------------
     def _probe(self):
-        # cheap staleness check on a few parameters (in-place updates bump _version, .to() moves data_ptr);
+        # staleness check on EVERY parameter / buffer (in-place updates bump _version, .to() / .data = ... move
+        # data_ptr): ~0.2 ms of host time for 912 tensors, hidden behind the asynchronous launch of the previous step.
         # load_state_dict / _apply also call invalidate() explicitly
-        return tuple((t.data_ptr(), t._version, t.dtype) for t in self._probe_tensors)
+        return tuple((t.data_ptr(), t._version) for t in self._probe_tensors)
 
     def _ensure_bound(self, device):
         m = self.module
@@ -124,8 +128,7 @@ class Engine:
         stream = torch.cuda.current_stream(device)
         _lib.check(self.lib.hatb200_pack(self.handle, C.c_void_p(stream.cuda_stream)))
         self._bound = bound
-        keys = list(sd.keys())
-        self._probe_tensors = [sd[k] for k in (keys[0], keys[len(keys) // 3], keys[2 * len(keys) // 3], keys[-1])]
+        self._probe_tensors = list(sd.values())
         self._sample = self._probe()
         self._graphs = {}
 
@@ -139,14 +142,16 @@ class Engine:
             self._ws = torch.empty(need.value, dtype=torch.uint8, device=device)
         return self._ws
 
-    def _launch(self, x, y, ws):
+    def _launch(self, x, y, ws, features=False):
         B, _, H, W = x.shape
         stream = torch.cuda.current_stream(x.device)
         code = _lib.dtype_code(x.dtype)
-        _lib.check(self.lib.hatb200_forward(self.handle, C.c_void_p(x.data_ptr()), code, B, H, W,
-                                            C.c_void_p(y.data_ptr()), _lib.dtype_code(y.dtype),
-                                            C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(stream.cuda_stream)))
+        fn = self.lib.hatb200_forward_features if features else self.lib.hatb200_forward
+        _lib.check(fn(self.handle, C.c_void_p(x.data_ptr()), code, B, H, W,
+                      C.c_void_p(y.data_ptr()), _lib.dtype_code(y.dtype),
+                      C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(stream.cuda_stream)))
         self.last_launch_count = self.lib.hatb200_last_launch_count(self.handle)
+        self.last_fallback_count = self.lib.hatb200_last_fallback_count(self.handle)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         m = self.module
@@ -176,6 +181,28 @@ class Engine:
                 return y
             return self._forward_graphed(x, ws, s)
 
+    def forward_features(self, x: torch.Tensor) -> torch.Tensor:
+        """HAT.forward_features (hat_arch.py:828-846): (B, embed_dim, H, W) -> (B, embed_dim, H, W), eager launches."""
+        m = self.module
+        if not isinstance(x, torch.Tensor) or x.dim() != 4 or x.shape[1] != m.embed_dim:
+            raise RuntimeError(f"HAT.forward_features expects a (B, {m.embed_dim}, H, W) tensor")
+        if not x.is_cuda:
+            raise RuntimeError("super_resolution_b200.HAT has no CPU path: the input must be a CUDA tensor")
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            raise NotImplementedError(f"input dtype {x.dtype}: float32 and bfloat16 are implemented")
+        B, _, H, W = x.shape
+        ws_ = m.window_size
+        if H % ws_ or W % ws_ or H < ws_ or W < ws_:
+            raise RuntimeError(f"shape '[{H}, {W}]' is invalid: height and width must be multiples of "
+                               f"window_size {ws_}")
+        x = x.contiguous()
+        with torch.cuda.device(x.device):
+            self._ensure_bound(x.device)
+            ws = self._workspace(B, H, W, _lib.dtype_code(x.dtype), x.device)
+            y = torch.empty_like(x)
+            self._launch(x, y, ws, features=True)
+            return y
+
     def _forward_graphed(self, x, ws, s):
         key = (tuple(x.shape), x.dtype)
         entry = self._graphs.get(key)
@@ -195,12 +222,12 @@ class Engine:
         g, xs, ys, _ = entry
         xs.copy_(x)
         g.replay()
-        return ys.clone()
+        return ys if self.output_view else ys.clone()
 
     # -- per-op profile (bench roofline breakdown) ----------------------------------
     def op_profile(self, x: torch.Tensor) -> dict:
         """Run one eager forward with CUDA events around every op and return
-        {tag: {launches, ms, flops, bytes}} (algorithmic flops / bytes per tag)."""
+        {tag: {kernel, launches, ms, flops, bytes}} (algorithmic flops / bytes per tag, serving kernel)."""
         import json
         graph, self.use_cuda_graph = self.use_cuda_graph, False
         try:

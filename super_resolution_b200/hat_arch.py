@@ -10,6 +10,8 @@ fallback -- `forward` raises if the input is not a CUDA tensor.
 """
 import math
 
+import warnings
+
 import torch
 import torch.nn as nn
 
@@ -238,6 +240,7 @@ class HAT(nn.Module):
 
         self.apply(self._init_weights)
         self._engine = None
+        self._warned_grad = False
 
     def _init_weights(self, m):              # hat_arch.py:761-768
         if isinstance(m, nn.Linear):
@@ -295,18 +298,27 @@ class HAT(nn.Module):
             self._engine = Engine(self)
         return self._engine
 
-    def forward_features(self, x):
-        raise NotImplementedError(
-            "forward_features is fused into the single native forward (csrc/forward.cu); call forward()")
-
-    def forward(self, x):                    # hat_arch.py:848-859
-        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
-            # forward-only build: refuse to return a graph-less tensor silently
+    def _forward_only_guard(self, x):
+        if torch.is_grad_enabled():
+            # forward-only build: never hand back a graph-less tensor silently
             if x.requires_grad:
                 raise RuntimeError("super_resolution_b200.HAT is forward-only: call it under torch.no_grad()")
+            if not self._warned_grad and any(p.requires_grad for p in self.parameters()):
+                self._warned_grad = True
+                warnings.warn("super_resolution_b200.HAT is forward-only: parameters require grad and grad mode is "
+                              "enabled, but the output carries no autograd graph (call under torch.no_grad())",
+                              RuntimeWarning, stacklevel=3)
         if self.training:
             raise RuntimeError("super_resolution_b200.HAT is inference-only: call .eval() first "
                                "(train mode of the reference uses stochastic depth, hat_arch.py:46-54)")
+
+    def forward_features(self, x):           # hat_arch.py:828-846: (B, embed_dim, H, W) -> (B, embed_dim, H, W)
+        self._forward_only_guard(x)
+        with torch.no_grad():
+            return self.engine().forward_features(x)
+
+    def forward(self, x):                    # hat_arch.py:848-859
+        self._forward_only_guard(x)
         self.mean = self.mean.type_as(x)
         with torch.no_grad():
             return self.engine().forward(x)

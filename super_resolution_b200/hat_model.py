@@ -59,6 +59,19 @@ def group_by_shape(rects, indices):
     return groups
 
 
+# hatb200_forward indexes tokens with 32 bits (csrc/forward.cu check_geometry: B*H*W*16*64 < 2^31); a stacked forward
+# also needs ~1 KB of workspace per token, so stacks are capped well below that limit by default
+MAX_FORWARD_TOKENS = (1 << 21) - 1
+DEFAULT_STACK_TOKENS = 1 << 20
+
+
+def split_stacks(idxs, th, tw, batch, max_tokens=DEFAULT_STACK_TOKENS):
+    """Cut one shape group into stacks of at most `max_tokens` LR pixels per forward (at least one tile each; the
+    reference runs one tile at a time and therefore handles any image size, hat_model.py:56-88)."""
+    per = max(1, min(max_tokens, MAX_FORWARD_TOKENS) // max(1, th * tw * batch))
+    return [idxs[k:k + per] for k in range(0, len(idxs), per)]
+
+
 def core_shape(rect, batch, channels):
     return (batch, channels, rect["out_y1"] - rect["out_y0"], rect["out_x1"] - rect["out_x0"])
 
@@ -244,6 +257,12 @@ class HATModel:
     `opt['network_g']['window_size']`, `opt['scale']`, and optionally `opt['tile']['tile_size']`,
     `opt['tile']['tile_pad']` (presence of `opt['tile']` selects tile mode, hat_model.py:139-141).
     group/dst: optional torch.distributed process group for tile sharding and the rank that receives the image.
+
+    Sharding is opt-in, as the reference validates on one rank (sr_model.py:180-182 dist_validation ->
+    nondist_validation on rank 0): tiles are spread over ranks only when a process group is passed or
+    `opt['tile']['shard']` is true -- then EVERY rank of the group must call `tile_process` with the SAME image.
+    With an initialised default group and neither of those, each caller computes all of its tiles itself.
+    `opt['tile']['max_stack_tokens']` (default 2^20 LR pixels) caps how many same-shape tiles share one forward.
     """
 
     def __init__(self, net, opt, group=None, dst=0):
@@ -278,14 +297,17 @@ class HATModel:
         ts, tp = self.opt['tile']['tile_size'], self.opt['tile']['tile_pad']
         rects = _lib.tile_plan(height, width, ts, tp, self.scale)
         world, rank = 1, 0
-        if self.group is not None or _dist_ready():
+        if self.group is not None or (self.opt['tile'].get('shard') and _dist_ready()):
             import torch.distributed as dist
             world, rank = dist.get_world_size(self.group), dist.get_rank(self.group)
         owners = shard_tiles(rects, world)
+        max_tokens = int(self.opt['tile'].get('max_stack_tokens', DEFAULT_STACK_TOKENS))
         self.net_g.eval()
         cores = {}
         with torch.no_grad():
-            for (th, tw), idxs in group_by_shape(rects, owners[rank]).items():
+            stacks = [((th, tw), part) for (th, tw), idxs in group_by_shape(rects, owners[rank]).items()
+                      for part in split_stacks(idxs, th, tw, batch, max_tokens)]
+            for (th, tw), idxs in stacks:
                 stack = torch.empty((len(idxs) * batch, channel, th, tw), dtype=img.dtype, device=img.device)
                 for k, i in enumerate(idxs):        # extract (hat_model.py:77): one strided copy kernel per tile
                     r = rects[i]

@@ -50,6 +50,37 @@ def load_case(name):
     return cfg, sd, x, torch.from_numpy(z["y"])
 
 
+# round 2: full-depth variants at BASELINE sizes with image-range outputs -- the north_star's bars asserted literally
+R2_CASES = [
+    "r2_hat_x4_b16_64x64", "r2_hatl_x4_64x64", "r2_hats_x4_64x64", "r2_hat_x2_64x64", "r2_hat_x3_64x64",
+    "r2_hat_x2_256x256", "r2_hat_x3_256x256", "r2_hat_x4_fresh_64x64", "r2_hatl_x4_fresh_64x64",
+    "r2_hat_x4_tiled_540x960",
+]
+
+
+def load_case_r2(name):
+    """-> dict(cfg, sd, x, y, tile, sub, y_shape, y_stats) for a round-2 golden (oracle/make_golden.py CASES_R2).
+    `y` is the reference output, stored every sub[0]-th row / sub[1]-th column when the full image is too big to
+    commit; y_stats = float64 (sum, sum of squares) of the FULL reference output."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False)
+    cfg = json.loads(str(z["cfg"]))
+    from super_resolution_b200.hat_arch import HAT
+    if str(z["weights"]) == "fresh":
+        sd = O.fresh_state_dict(HAT, cfg, int(z["sd_seed"]))
+        got, want = O.state_dict_checksum(sd), float(z["sd_checksum"])
+        assert abs(got - want) <= 1e-9 * abs(want), \
+            f"{name}: seeded fresh init differs from the one the golden was made with (torch {z['torch_version']})"
+    else:
+        sd = O.randomized_state_dict(HAT(**cfg).state_dict(), int(z["sd_seed"]))
+        sd = O.scale_tail(sd, float(z["tail_scale"]))
+    shape = tuple(int(v) for v in z["x_shape"])
+    x = torch.rand(shape, generator=torch.Generator().manual_seed(int(z["x_seed"])), dtype=torch.float32)
+    tile = tuple(int(v) for v in z["tile"])
+    return dict(cfg=cfg, sd=sd, x=x, y=torch.from_numpy(z["y"]), tile=tile if tile[0] else None,
+                sub=tuple(int(v) for v in z["sub"]), y_shape=tuple(int(v) for v in z["y_shape"]),
+                y_stats=z["y_stats"])
+
+
 def psnr(a, b, peak=1.0):
     mse = torch.mean((a.double() - b.double()) ** 2).item()
     return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)

@@ -74,11 +74,16 @@ def test_library_loads_and_exports_every_declared_symbol():
     l = _lib.lib()
     assert l.hatb200_version() == 100
     header = open(os.path.join(ROOT, "include", "hatb200.h")).read()
-    declared = sorted(set(re.findall(r"\b(hatb200_[a-z0-9_]+)\s*\(", header)))
+    product, eng = re.subn(r"#ifdef HATB200_ENGINEERING.*?#endif", "", header, flags=re.S)
+    assert eng == 1
+    declared = sorted(set(re.findall(r"\b(hatb200_[a-z0-9_]+)\s*\(", product)))
     assert declared == _lib.exported_symbols()
     nm = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
     for sym in declared:
         assert re.search(rf"\bT {sym}\b", nm), f"{sym} not exported by libhatb200.so"
+    # the engineering probes are declared under HATB200_ENGINEERING and are not part of the product library
+    exported = set(re.findall(r"\bT (hatb200_[a-z0-9_]+)\b", nm))
+    assert exported == set(declared), exported ^ set(declared)
     assert __import__("ctypes").sizeof(_lib.Config) == 356   # sizeof(hatb200_config); create() re-checks it
 
 

@@ -135,3 +135,74 @@ def test_no_upsampler_path():
     net = HAT(window_size=16, embed_dim=48, depths=[1], num_heads=[6], upsampler='').eval().to(DEV)
     x = torch.rand(1, 3, 16, 16, device=DEV)
     assert (net(x) - x).abs().max().item() <= 1e-6
+
+
+def test_forward_features_matches_oracle():
+    """HAT.forward_features (hat_arch.py:828-846): (B, C, H, W) conv_first output -> final LayerNorm, (B, C, H, W)."""
+    cfg, sd, x, _ = load_case("mini_x4_b3_32x32")
+    net = _net(cfg, sd)
+    f = torch.randn(2, cfg["embed_dim"], 32, 48, generator=torch.Generator().manual_seed(9))
+    ref = O.forward_features(f, sd, O.default_cfg(**cfg))
+    got = net.forward_features(f.to(DEV))
+    assert got.dtype == torch.float32 and tuple(got.shape) == tuple(ref.shape)
+    err = (got.cpu() - ref).abs().max().item()
+    assert err <= FP32_TOL * max(1.0, ref.abs().max().item()), err
+    got16 = net.forward_features(f.to(DEV).bfloat16())
+    assert got16.dtype == torch.bfloat16
+    assert psnr(got16.float().cpu(), ref, max(1.0, ref.abs().max().item())) >= 40.0    # LN output in bf16: 8 bits
+    # identity residual connection leaves the final LayerNorm in the same buffer
+    cfg2, sd2, _, _ = load_case("mini_x2_identity")
+    net2 = _net(cfg2, sd2)
+    ref2 = O.forward_features(f[:1], sd2, O.default_cfg(**cfg2))
+    assert (net2.forward_features(f[:1].to(DEV)).cpu() - ref2).abs().max().item() <= FP32_TOL * max(1.0, ref2.abs().max().item())
+    with pytest.raises(RuntimeError):
+        net.forward_features(torch.rand(1, 3, 32, 32, device=DEV))
+
+
+def test_no_silent_cuda_core_fallback_in_the_bf16_path():
+    """Every op of the published variants runs on a tcgen05 kernel at window-multiple sizes: the fallback counter of
+    the bf16 forward is zero, also with ocab_esc_enable; `strict_tc` turns a fallback into an error."""
+    for name in ("hat_dims_x4_32x32", "hats_dims_x4_32x32", "mini_x2_ocabesc", "mini_x3_48x32"):
+        cfg, sd, x, _ = load_case(name)
+        net = _net(cfg, sd)
+        net.engine().set_option("strict_tc", 1)
+        net(x.to(DEV).bfloat16())
+        assert net.engine().last_fallback_count == 0, name
+    cfg, sd, x, _ = load_case("mini_x4_32x32")
+    net = _net(cfg, sd)
+    net.engine().use_cuda_graph = False
+    import os
+    os.environ["HATB200_TC_DISABLE"] = "cab_conv1"
+    try:
+        net(x.to(DEV).bfloat16())
+        assert net.engine().last_fallback_count == cfg["depths"][0] * len(cfg["depths"])
+        net.engine().set_option("strict_tc", 1)
+        with pytest.raises(RuntimeError, match="strict_tc"):
+            net(x.to(DEV).bfloat16())
+    finally:
+        del os.environ["HATB200_TC_DISABLE"]
+
+
+def test_in_place_edit_of_any_parameter_repacks():
+    """The staleness probe covers every tensor: an in-place edit of one inner weight must change the output."""
+    cfg, sd, x, _ = load_case("mini_x4_32x32")
+    net = _net(cfg, sd)
+    y0 = net(x.to(DEV))
+    with torch.no_grad():
+        net.layers[1].residual_group.blocks[0].mlp.fc2.weight.mul_(1.5)
+    sd2 = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    y1 = net(x.to(DEV))
+    ref = O.hat_forward(x, sd2, cfg)
+    assert not torch.equal(y0, y1)
+    assert (y1.cpu() - ref).abs().max().item() <= FP32_TOL * max(1.0, ref.abs().max().item())
+
+
+def test_output_view_returns_the_graph_buffer():
+    cfg, sd, x, _ = load_case("mini_x4_32x32")
+    net = _net(cfg, sd)
+    xd = x.to(DEV)
+    y = net(xd).clone()
+    net.engine().output_view = True
+    a = net(xd)
+    b = net(xd)
+    assert a.data_ptr() == b.data_ptr() and torch.equal(a, y)

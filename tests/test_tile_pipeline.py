@@ -66,7 +66,6 @@ def test_mod_pad_matches_oracle():
         assert HM.mod_pad(h, w, 16) == O.mod_pad(h, w, 16)
 
 
-# ---- world_size-2 gather over gloo (host logic of the N>1 path) ---------------------------------------
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -75,6 +74,78 @@ def _free_port():
     return p
 
 
+def test_split_stacks_caps_the_stacked_forward():
+    """2048x2048 LR at tile 256 / pad 32 has 36 interior 320x320 tiles: one stack of 36 would exceed the 2^21-token
+    limit of hatb200_forward; the plan cuts it into forwards of at most max_tokens LR pixels."""
+    rects = O.tile_rects(2048, 2048, 256, 32, 4)
+    groups = HM.group_by_shape(rects, list(range(len(rects))))
+    assert len(groups[(320, 320)]) == 36
+    seen = []
+    for (th, tw), idxs in groups.items():
+        parts = HM.split_stacks(idxs, th, tw, 1)
+        assert [i for p in parts for i in p] == idxs                       # order kept, nothing lost
+        for p in parts:
+            assert len(p) * th * tw <= HM.DEFAULT_STACK_TOKENS < HM.MAX_FORWARD_TOKENS
+        seen += idxs
+    assert sorted(seen) == list(range(64))
+    assert [len(p) for p in HM.split_stacks(groups[(320, 320)], 320, 320, 1)] == [10, 10, 10, 6]
+    # a single tile that is larger than the cap still gets its own forward (the C library then checks the hard limit)
+    assert HM.split_stacks([0, 1], 1024, 1024, 2, max_tokens=1 << 20) == [[0], [1]]
+    # 2560x2560 at 512/32 (576x576 interior tiles, the shipped HAT_tile_example geometry): 3 per stack
+    assert [len(p) for p in HM.split_stacks(list(range(9)), 576, 576, 1)] == [3, 3, 3]
+
+
+def _rank0_only_worker(rank, world, port, q):
+    """The reference validates on rank 0 only (sr_model.py:180-182): with an initialised default group and no
+    group / shard option, tile_process must not wait for the other ranks."""
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        if rank == 0:
+            calls = []
+
+            class Net:
+                def eval(self):
+                    return self
+
+                def __call__(self, t):
+                    calls.append(tuple(t.shape))
+                    return t.repeat_interleave(2, 2).repeat_interleave(2, 3)
+
+            m = HM.HATModel(Net(), {"network_g": {"window_size": 16}, "scale": 2, "tile": {"tile_size": 32, "tile_pad": 16}})
+            m.img = torch.zeros(1, 3, 64, 64)
+            # stop at the device boundary: the planning above it is what is under test
+            try:
+                m.tile_process()
+                q.put("ran without a CUDA image")
+            except RuntimeError as e:
+                q.put("no CPU path" in str(e))
+        else:
+            q.put(True)                         # rank 1 never calls tile_process
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_tile_process_does_not_shard_without_group_or_flag():
+    import inspect
+    src = inspect.getsource(HM.HATModel.tile_process)
+    assert "self.group is not None or (self.opt['tile'].get('shard')" in src
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rank0_only_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(r is True for r in res), res
+
+
+# ---- world_size-2 gather over gloo (host logic of the N>1 path) ---------------------------------------
 def _worker(rank, world, port, geom, q):
     import torch.distributed as dist
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)

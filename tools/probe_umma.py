@@ -1,3 +1,4 @@
+# NOTE: needs a library built with the engineering probes: HATB200_ENGINEERING=1 python super_resolution_b200/build.py --force
 """Probe tcgen05 A-descriptor addressing with unaligned start rows / arbitrary SBO (see csrc/tc_probe.cu)."""
 import ctypes as C
 import os

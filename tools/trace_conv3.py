@@ -1,3 +1,4 @@
+# NOTE: needs a library built with the engineering probes: HATB200_ENGINEERING=1 python super_resolution_b200/build.py --force
 """Per-CTA timeline of one persistent 3x3 conv launch (engineering aid, HATB200_GEMM_TRACE=1).
     python tools/trace_conv3.py Cin N
 Slots (us since the first event): MMA thread, local tile i: 4i waiting for a free accumulator, 4i+1 waiting for the

@@ -1,3 +1,4 @@
+# NOTE: needs a library built with the engineering probes: HATB200_ENGINEERING=1 python super_resolution_b200/build.py --force
 """Per-CTA timeline of one persistent GEMM launch (engineering aid, HATB200_GEMM_TRACE=1).
     python tools/trace_gemm.py Cin N [plain|resid|aggr]
 Slots (us since the first event): 0/1 MMA warp start / weights resident; 8+2i / 9+2i MMA of local tile i issued /
