@@ -149,6 +149,15 @@ int hatb200_tensor2img(const void* x, int dtype, int B, int C, int H, int W, flo
 int hatb200_psnr_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C, int crop_border,
                     int test_y_channel, double* workspace, double* out, void* stream);
 
+/* basicsr.metrics.calculate_ssim (basicsr/metrics/psnr_ssim.py:85-129, _ssim :170-198) on two device uint8 HWC images
+ * (BGR when C == 3): crop_border, optional Y channel, float64 arithmetic; per channel the 11x11 Gaussian window
+ * (sigma 1.5) over the valid region, as cv2.filter2D(...)[5:-5, 5:-5].  workspace: HATB200_SSIM_MAX_BLOCKS doubles on
+ * device.  out (device, 2 doubles): {sum of the ssim map over all channels, window positions x channels};
+ * ssim = out[0] / out[1].  The cropped image must be at least 11x11. */
+#define HATB200_SSIM_MAX_BLOCKS 4096
+int hatb200_ssim_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C, int crop_border,
+                    int test_y_channel, double* workspace, double* out, void* stream);
+
 /* ---- single-kernel entry points (unit tests, ncu) ------------------------ */
 
 /* nn.LayerNorm(C), eps 1e-5 (hat_arch.py:222,:237,:331,:392,:844).
@@ -206,6 +215,36 @@ int hatb200_ocab_attention(const void* qkv, int dtype, int pitch, int B, int H, 
 int hatb200_dwconv_gate(const void* in, int dtype, int in_pitch, int B, int H, int W, int hid,
                         const float* dw_w /* (2hid,1,3,3) */, const float* dw_b,
                         void* out, int out_pitch, void* stream);
+
+/* ESC ConvAttn core on the tcgen05 banded-Toeplitz kernel (esc_arch.py:119-123; csrc/tc_plk.cu): x16 bf16 (M, 16) = the
+ * first 16 channels of norm1(x); out[:, :16] (bf16, (M, out_pitch)) = conv13x13(x16, plk_filter (16,16,13,13), pad 6)
+ * + depthwise3x3(x16, dyn[b] (16,1,3,3), pad 1); dyn (B, 16, 9) fp32 may be NULL.  Other columns of out are untouched. */
+int hatb200_esc_plk(const void* x16, int B, int H, int W, const float* plk_filter, const float* dyn, void* out,
+                    int out_pitch, void* stream);
+
+/* conv_first + input normalisation (hat_arch.py:849-853): x (B, in_chans, H, W) NCHW -> out fp32 (B*H*W, C) tokens of
+ * conv3x3((x - mean) * img_range, w (C, in_chans, 3, 3)) + bias. */
+int hatb200_conv_first(const void* x, int x_dtype, int B, int in_chans, int H, int W, const float* w, const float* bias,
+                       int C, const float* mean4, float img_range, float* out, void* stream);
+
+/* conv_last + de-normalisation (hat_arch.py:856-858): in (B*H*W, 64) tokens -> y (B, out_chans, H, W) NCHW of
+ * conv3x3(in, w (out_chans, 64, 3, 3)) + bias, then / img_range + mean.  use_tc=1 (bf16): the tensor-core route of
+ * the forward (N padded to 16 on conv3_tc, then the NCHW / affine pass); 0: the CUDA-core kernel. */
+int hatb200_conv_last(const void* in, int dtype, int B, int H, int W, const float* w, const float* bias, int out_chans,
+                      const float* mean4, float img_range, void* y, int y_dtype, int use_tc, void* stream);
+
+/* The two per-sample "finish" steps of a HAB in one launch: ECA gate (hat_arch.py:72-77) eca_scale (B, C) =
+ * sigmoid(conv1d_k5(mean over HW)) from the per-tile partial sums eca_partial (B, nchunk, C), and the ESC dynamic
+ * kernel (esc_arch.py:95-100) dyn (B, pdim, 9) = W2 gelu(W1 GAP + b1) + b2 from dyn_partial (B, nchunk, pdim). */
+int hatb200_hab_finish(const float* eca_partial, int nchunk, int B, int C, int HW, const float* eca_w5, float* eca_scale,
+                       const float* dyn_partial, int pdim, const float* w1, const float* b1, const float* w2,
+                       const float* b2, float* dyn, void* stream);
+
+/* Upsample stage (hat_arch.py:593-605): conv3x3 64 -> 64 r^2 with PixelShuffle(r) folded into the TMA store of the
+ * persistent conv3 kernel.  a bf16 (B*H*W, 64) tokens, w (64 r^2, 64, 3, 3), out bf16 (B, H r, W r, 64) channels-last:
+ * out[b, y r + i, x r + j, c] = conv[b, c r^2 + i r + j, y, x]  (integer address map, bit-exact). */
+int hatb200_conv_shuffle(const void* a, int B, int H, int W, const float* w, const float* bias, int r, void* out,
+                         void* stream);
 
 /* hatb200_dwconv_gate for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it).  No counterpart in the reference: added

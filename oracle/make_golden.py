@@ -285,7 +285,7 @@ def gen_postproc():
     """tensor2img / calculate_psnr of the unmodified reference (basicsr/utils/img_util.py, basicsr/metrics/psnr_ssim.py)."""
     load_ref.load_reference_hat()          # puts the reference's basicsr on sys.path
     from basicsr.utils.img_util import tensor2img
-    from basicsr.metrics.psnr_ssim import calculate_psnr
+    from basicsr.metrics.psnr_ssim import calculate_psnr, calculate_ssim
     a, b, gray, wide = postproc_inputs()
     # the reference clamps its argument IN PLACE (`.clamp_` on a view, img_util.py:67): feed it copies
     ia, ib = tensor2img([a.clone()]), tensor2img([b.clone()])
@@ -296,8 +296,14 @@ def gen_postproc():
         for ty in (False, True):
             psnr[f"cb{cb}_y{int(ty)}"] = float(calculate_psnr(ia, ib, crop_border=cb, test_y_channel=ty))
     psnr["gray_cb2_y1"] = float(calculate_psnr(out["gray"], tensor2img(gray * 0.97), crop_border=2, test_y_channel=True))
-    np.savez_compressed(os.path.join(GOLD, "postproc.npz"), psnr=json.dumps(psnr), **out)
-    print("postproc:", {k: v.shape for k, v in out.items()}, psnr)
+    ssim = {}
+    for cb in (0, 4):
+        for ty in (False, True):
+            ssim[f"cb{cb}_y{int(ty)}"] = float(calculate_ssim(ia, ib, crop_border=cb, test_y_channel=ty))
+    ssim["gray_cb2_y1"] = float(calculate_ssim(out["gray"], tensor2img(gray * 0.97), crop_border=2, test_y_channel=True))
+    ssim["gray_cb0_y0"] = float(calculate_ssim(out["gray"], tensor2img(gray * 0.97), crop_border=0, test_y_channel=False))
+    np.savez_compressed(os.path.join(GOLD, "postproc.npz"), psnr=json.dumps(psnr), ssim=json.dumps(ssim), **out)
+    print("postproc:", {k: v.shape for k, v in out.items()}, psnr, ssim)
 
 
 if __name__ == "__main__":
@@ -305,6 +311,9 @@ if __name__ == "__main__":
         sys.exit("reference not mounted; goldens can only be generated in the build container")
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "postproc":
+        gen_postproc()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "r2":       # only the round-2 image-range cases (minutes of CPU)
         gen_r2_cases(set(sys.argv[2:]))
         sys.exit(0)

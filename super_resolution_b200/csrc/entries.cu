@@ -70,6 +70,12 @@ int hatb200_psnr_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C
   return launch_psnr_u8(img, img2, H, W, C, crop_border, test_y_channel, workspace, out, (cudaStream_t)stream);
 }
 
+int hatb200_ssim_u8(const uint8_t* img, const uint8_t* img2, int H, int W, int C, int crop_border, int test_y_channel,
+                    double* workspace, double* out, void* stream) {
+  HB_REQUIRE(img && img2 && workspace && out && H >= 1 && W >= 1 && C >= 1, HATB200_EINVAL, "ssim_u8: bad arguments");
+  return launch_ssim_u8(img, img2, H, W, C, crop_border, test_y_channel, workspace, out, (cudaStream_t)stream);
+}
+
 int hatb200_layernorm(const float* x, int M, int C, const float* gamma, const float* beta, void* out, int out_dtype,
                       int out_pitch, void* out_head, int head_c, void* stream) {
   HB_REQUIRE(x && gamma && beta && out && out_pitch >= C, HATB200_EINVAL, "layernorm: bad arguments");

@@ -67,6 +67,9 @@ int launch_tensor2img(const void* x, int dt, int B, int C, int H, int W, float m
 int launch_psnr_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int crop_border, int test_y, double* ws,
                    double* out, cudaStream_t st);
 
+int launch_ssim_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int crop_border, int test_y, double* ws,
+                   double* out, cudaStream_t st);
+
 // ---- dense conv / GEMM over channels-last tokens ----
 struct ConvArgs {
   const void* A; int a_pitch; int a_coff; int Cin;   // input tokens (B*H*W, a_pitch), channels [a_coff, a_coff+Cin)

@@ -648,6 +648,97 @@ int launch_psnr_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int 
   return 0;
 }
 
+// calculate_ssim (basicsr/metrics/psnr_ssim.py:85-129, _ssim :170-198) on two uint8 HWC images: crop_border, optional
+// Y channel (as calculate_psnr), float64 arithmetic as the reference (cv2.filter2D on float64): per channel, the 11x11
+// Gaussian window (cv2.getGaussianKernel(11, 1.5), outer product) over the VALID region, ssim_map averaged.  A block
+// stages a (32+10) x (8+10) tile of both images in shared memory as doubles; one thread = one window position (121
+// taps, five running sums).  Blocks walk tiles grid-stride, per-block partial sums are added in index order
+// (deterministic).  out[0] = sum of ssim_map over all channels, out[1] = number of window positions x channels.
+constexpr int SS_TW = 32, SS_TH = 8, SS_K = 11, SS_HW = SS_TW + SS_K - 1, SS_HH = SS_TH + SS_K - 1;
+struct SsimWin { double k[SS_K]; };
+
+__global__ void __launch_bounds__(256) ssim_partial_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b,
+                                                           int W, int C, int cb, int h2, int w2, int test_y, int nch,
+                                                           int tiles_x, int tiles_y, const SsimWin win,
+                                                           double* __restrict__ partial) {
+  __shared__ double ta[SS_HH][SS_HW], tb[SS_HH][SS_HW];
+  __shared__ double red[256];
+  const int vh = h2 - (SS_K - 1), vw = w2 - (SS_K - 1);          // valid window positions
+  const double c1 = (0.01 * 255) * (0.01 * 255), c2 = (0.03 * 255) * (0.03 * 255);
+  const int lx = threadIdx.x % SS_TW, ly = threadIdx.x / SS_TW;
+  const long long ntiles = (long long)tiles_x * tiles_y * nch;
+  double acc = 0.0;
+  for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int ch = (int)(t / ((long long)tiles_x * tiles_y));
+    const int ty = (int)((t / tiles_x) % tiles_y), tx = (int)(t % tiles_x);
+    const int x0 = tx * SS_TW, y0 = ty * SS_TH;
+    __syncthreads();
+    for (int e = threadIdx.x; e < SS_HH * SS_HW; e += 256) {
+      const int hy = e / SS_HW, hx = e % SS_HW;
+      const int y = y0 + hy, x = x0 + hx;
+      double va = 0.0, vb = 0.0;
+      if (y < h2 && x < w2) {
+        const uint8_t* pa = a + ((size_t)(y + cb) * W + x + cb) * C;
+        const uint8_t* pb = b + ((size_t)(y + cb) * W + x + cb) * C;
+        if (test_y && C == 3) { va = y_of_bgr(pa); vb = y_of_bgr(pb); }
+        else if (test_y) {
+          va = (double)__fmul_rn(__fdiv_rn((float)pa[ch], 255.f), 255.f);
+          vb = (double)__fmul_rn(__fdiv_rn((float)pb[ch], 255.f), 255.f);
+        } else { va = (double)pa[ch]; vb = (double)pb[ch]; }
+      }
+      ta[hy][hx] = va; tb[hy][hx] = vb;
+    }
+    __syncthreads();
+    if (y0 + ly < vh && x0 + lx < vw) {
+      double m1 = 0, m2 = 0, s11 = 0, s22 = 0, s12 = 0;
+      for (int i = 0; i < SS_K; i++) {
+#pragma unroll
+        for (int j = 0; j < SS_K; j++) {
+          const double wgt = win.k[i] * win.k[j];
+          const double p = ta[ly + i][lx + j], q = tb[ly + i][lx + j];
+          m1 += wgt * p; m2 += wgt * q;
+          s11 += wgt * (p * p); s22 += wgt * (q * q); s12 += wgt * (p * q);
+        }
+      }
+      const double m11 = m1 * m1, m22 = m2 * m2, m12 = m1 * m2;
+      const double v1 = s11 - m11, v2 = s22 - m22, v12 = s12 - m12;
+      acc += ((2 * m12 + c1) * (2 * v12 + c2)) / ((m11 + m22 + c1) * (v1 + v2 + c2));
+    }
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = red[0];
+}
+
+int launch_ssim_u8(const uint8_t* a, const uint8_t* b, int H, int W, int C, int crop_border, int test_y, double* ws,
+                   double* out, cudaStream_t st) {
+  HB_REQUIRE(crop_border >= 0 && H - 2 * crop_border >= SS_K && W - 2 * crop_border >= SS_K, HATB200_EINVAL,
+             "ssim: crop_border %d leaves less than the 11x11 window of a %dx%d image", crop_border, H, W);
+  const int h2 = H - 2 * crop_border, w2 = W - 2 * crop_border;
+  const int vh = h2 - (SS_K - 1), vw = w2 - (SS_K - 1);
+  const int nch = (test_y && C == 3) ? 1 : C;
+  const int tiles_x = cdiv(vw, SS_TW), tiles_y = cdiv(vh, SS_TH);
+  const long long ntiles = (long long)tiles_x * tiles_y * nch;
+  int blocks = ntiles < HATB200_SSIM_MAX_BLOCKS ? (int)ntiles : HATB200_SSIM_MAX_BLOCKS;
+  SsimWin win;                        // cv2.getGaussianKernel(11, 1.5): exp(-x^2 / (2 sigma^2)), normalised, float64
+  double sum = 0.0;
+  for (int i = 0; i < SS_K; i++) {
+    const double x = i - (SS_K - 1) * 0.5;
+    win.k[i] = exp(-0.5 / (1.5 * 1.5) * x * x);
+    sum += win.k[i];
+  }
+  for (int i = 0; i < SS_K; i++) win.k[i] *= 1.0 / sum;
+  ssim_partial_kernel<<<blocks, 256, 0, st>>>(a, b, W, C, crop_border, h2, w2, test_y, nch, tiles_x, tiles_y, win, ws);
+  HB_CHECK_LAUNCH();
+  psnr_finish_kernel<<<1, 1, 0, st>>>(ws, blocks, (double)vh * vw * nch, out);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
 }  // namespace hb
 
 namespace hb {

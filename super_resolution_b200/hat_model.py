@@ -216,6 +216,29 @@ def calculate_psnr(img, img2, crop_border, input_order='HWC', test_y_channel=Fal
     return 10. * math.log10(255. * 255. / (sse / count))
 
 
+def calculate_ssim(img, img2, crop_border, input_order='HWC', test_y_channel=False):
+    """Device-side `basicsr.metrics.calculate_ssim` (basicsr/metrics/psnr_ssim.py:85-129, `_ssim` :170-198) for two uint8
+    CUDA images with range [0, 255] (HWC, BGR when 3 channels): float64, 11x11 Gaussian window over the valid region,
+    mean over channels.  One stencil kernel + a fixed-order finish; two doubles cross to the host."""
+    assert img.shape == img2.shape, (f'Image shapes are different: {img.shape}, {img2.shape}.')
+    if input_order not in ['HWC', 'CHW']:
+        raise ValueError(f'Wrong input_order {input_order}. Supported input_orders are "HWC" and "CHW"')
+    if not (img.is_cuda and img2.is_cuda and img.dtype == torch.uint8 and img2.dtype == torch.uint8):
+        raise RuntimeError("super_resolution_b200.calculate_ssim: uint8 CUDA tensors required")
+    if img.dim() == 2:
+        img, img2 = img[..., None], img2[..., None]
+    elif input_order == 'CHW':
+        img, img2 = img.permute(1, 2, 0), img2.permute(1, 2, 0)
+    img, img2 = img.contiguous(), img2.contiguous()
+    H, W, Cn = img.shape
+    ws = torch.empty(4096, dtype=torch.float64, device=img.device)
+    out = torch.empty(2, dtype=torch.float64, device=img.device)
+    _lib.check(_lib.lib().hatb200_ssim_u8(_ptr(img), _ptr(img2), H, W, Cn, int(crop_border), int(bool(test_y_channel)),
+                                          _ptr(ws), _ptr(out), _stream(img)))
+    total, count = out.cpu().tolist()
+    return total / count
+
+
 def save_network(net, save_path, param_key='params'):
     """Checkpoint file in the reference's on-disk format (`BaseModel.save_network`, basicsr/models/base_model.py:207-252):
     `{param_key: state_dict}` with CPU tensors, `module.` prefixes (DataParallel / DDP wrappers) stripped.  `net` and
@@ -251,11 +274,20 @@ def load_network(net, load_path, strict=True, param_key='params'):
 
 
 class HATModel:
-    """Inference half of the reference `HATModel` (hat_model.py:13-112) around a B200-native `HAT`.
+    """Inference half of the reference `HATModel` (hat_model.py:13-185) around a B200-native `HAT`.
+
+    Two ways to build it:
+      * `HATModel(opt)` -- the reference's signature, what `basicsr.models.build_model(opt)` calls
+        (`MODEL_REGISTRY.get(opt['model_type'])(opt)`, basicsr/models/__init__.py:17-28): builds the network from
+        `opt['network_g']` (type 'HAT'), moves it to the GPU and loads `opt['path']['pretrain_network_g']` with
+        `param_key_g` / `strict_load_g` (sr_model.py:18-32).  `hat/test.py` therefore runs unchanged once this
+        package is imported in place of `hat.models`.  Forward-only: `opt['is_train']` raises.
+      * `HATModel(net, opt)` -- around a network that already exists.
 
     opt: the reference's option dict; the keys read are the ones the reference reads:
     `opt['network_g']['window_size']`, `opt['scale']`, and optionally `opt['tile']['tile_size']`,
-    `opt['tile']['tile_pad']` (presence of `opt['tile']` selects tile mode, hat_model.py:139-141).
+    `opt['tile']['tile_pad']` (presence of `opt['tile']` selects tile mode, hat_model.py:139-141); for
+    `nondist_validation` also `opt['val']`, `opt['path']['visualization']`, `opt['name']`, `opt['is_train']`.
     group/dst: optional torch.distributed process group for tile sharding and the rank that receives the image.
 
     Sharding is opt-in, as the reference validates on one rank (sr_model.py:180-182 dist_validation ->
@@ -265,18 +297,53 @@ class HATModel:
     `opt['tile']['max_stack_tokens']` (default 2^20 LR pixels) caps how many same-shape tiles share one forward.
     """
 
-    def __init__(self, net, opt, group=None, dst=0):
+    def __init__(self, net_or_opt, opt=None, group=None, dst=0):
+        if opt is None and isinstance(net_or_opt, dict):
+            opt = net_or_opt
+            net = self._build_from_opt(opt)
+        else:
+            net = net_or_opt
         self.net_g = net
         self.opt = opt
         self.group = group
         self.dst = dst
+        self.is_train = bool(opt.get('is_train', False))
         self.scale = opt.get('scale', 1)
         self.mod_pad_h = self.mod_pad_w = 0
         self.lq = self.img = self.output = None
+        try:
+            self.device = next(net.parameters()).device
+        except (StopIteration, AttributeError):
+            self.device = torch.device('cuda')
+
+    @staticmethod
+    def _build_from_opt(opt):
+        """SRModel.__init__ (sr_model.py:18-32): build_network -> model_to_device -> load_network."""
+        import copy
+        if opt.get('is_train', False):
+            raise NotImplementedError("super_resolution_b200.HATModel is inference-only (is_train must be false)")
+        if opt.get('num_gpu', 1) == 0 or not torch.cuda.is_available():
+            raise RuntimeError("super_resolution_b200.HATModel has no CPU path: a CUDA device is required")
+        from .hat_arch import HAT
+        net_opt = copy.deepcopy(opt['network_g'])
+        typ = net_opt.pop('type', 'HAT')
+        if typ not in ('HAT', 'HAT_b200'):
+            raise NotImplementedError(f"network_g type '{typ}': this package implements the reference's 'HAT'")
+        net = HAT(**net_opt).eval().to(torch.device('cuda', torch.cuda.current_device()))
+        path = opt.get('path', {}) or {}
+        load_path = path.get('pretrain_network_g', None)
+        if load_path is not None:
+            load_network(net, load_path, path.get('strict_load_g', True), path.get('param_key_g', 'params'))
+        return net
 
     # -- reference API -------------------------------------------------------------------------
     def feed_data(self, data):                      # sr_model.py:87-90
-        self.lq = data['lq'] if isinstance(data, dict) else data
+        if isinstance(data, dict):
+            self.lq = data['lq'].to(self.device)
+            if 'gt' in data:
+                self.gt = data['gt'].to(self.device)
+        else:
+            self.lq = data
 
     def pre_process(self):                          # hat_model.py:16-26
         window_size = self.opt['network_g']['window_size']
@@ -342,6 +409,103 @@ class HATModel:
         crop_place(self.output, 0, 0, out, 0, 0, rh, rw)
         self.output = out
 
+    def get_current_visuals(self):                  # sr_model.py:266-272
+        out_dict = OrderedDict()
+        out_dict['lq'] = self.lq.detach().cpu()
+        out_dict['result'] = self.output.detach().cpu()
+        if hasattr(self, 'gt'):
+            out_dict['gt'] = self.gt.detach().cpu()
+        return out_dict
+
+    def dist_validation(self, dataloader, current_iter, tb_logger, save_img):      # sr_model.py:180-182
+        if self.opt.get('rank', 0) == 0:
+            self.nondist_validation(dataloader, current_iter, tb_logger, save_img)
+
+    def validation(self, dataloader, current_iter, tb_logger, save_img=False):     # base_model.py:41-53
+        if self.opt.get('dist', False):
+            self.dist_validation(dataloader, current_iter, tb_logger, save_img)
+        else:
+            self.nondist_validation(dataloader, current_iter, tb_logger, save_img)
+
+    def nondist_validation(self, dataloader, current_iter, tb_logger, save_img):
+        """hat_model.py:114-185, image by image: feed -> pre_process -> tile_process / process -> post_process ->
+        tensor2img -> metrics -> imwrite.  The HR image never leaves the GPU as floats: `tensor2img` and the PSNR /
+        SSIM metrics (`calculate_psnr`, `calculate_ssim`) run as kernels of libhatb200 on it; only the uint8 HWC image
+        (for imwrite) and two doubles per metric cross to the host.  Other metric types go to basicsr's registry."""
+        from os import path as osp
+        dataset_name = dataloader.dataset.opt['name']
+        with_metrics = self.opt['val'].get('metrics') is not None
+        if with_metrics:
+            if not hasattr(self, 'metric_results'):
+                self.metric_results = {metric: 0 for metric in self.opt['val']['metrics'].keys()}
+            self._initialize_best_metric_results(dataset_name)
+            self.metric_results = {metric: 0 for metric in self.metric_results}
+        idx = -1
+        for idx, val_data in enumerate(dataloader):
+            img_name = osp.splitext(osp.basename(val_data['lq_path'][0]))[0]
+            self.feed_data(val_data)
+            self.pre_process()
+            if 'tile' in self.opt:
+                self.tile_process()
+            else:
+                self.process()
+            self.post_process()
+            sr_dev = tensor2img([self.output], to_numpy=False)[0]
+            gt_dev = None
+            if hasattr(self, 'gt'):
+                gt_dev = tensor2img([self.gt], to_numpy=False)[0]
+                del self.gt
+            del self.lq
+            self.output = None
+            if save_img:
+                if self.opt.get('is_train', False):
+                    save_img_path = osp.join(self.opt['path']['visualization'], img_name, f'{img_name}_{current_iter}.png')
+                elif self.opt['val'].get('suffix'):
+                    save_img_path = osp.join(self.opt['path']['visualization'], dataset_name,
+                                             f'{img_name}_{self.opt["val"]["suffix"]}.png')
+                else:
+                    save_img_path = osp.join(self.opt['path']['visualization'], dataset_name,
+                                             f'{img_name}_{self.opt["name"]}.png')
+                _imwrite(sr_dev.cpu().numpy(), save_img_path)
+            if with_metrics:
+                for name, opt_ in self.opt['val']['metrics'].items():
+                    self.metric_results[name] += _device_metric(sr_dev, gt_dev, opt_)
+        if with_metrics and idx >= 0:
+            for metric in self.metric_results.keys():
+                self.metric_results[metric] /= (idx + 1)
+                self._update_best_metric_result(dataset_name, metric, self.metric_results[metric], current_iter)
+            self._log_validation_metric_values(current_iter, dataset_name, tb_logger)
+
+    def _initialize_best_metric_results(self, dataset_name):           # base_model.py:50-63
+        if hasattr(self, 'best_metric_results') and dataset_name in self.best_metric_results:
+            return
+        if not hasattr(self, 'best_metric_results'):
+            self.best_metric_results = dict()
+        record = dict()
+        for metric, content in self.opt['val']['metrics'].items():
+            better = content.get('better', 'higher')
+            record[metric] = dict(better=better, val=float('-inf') if better == 'higher' else float('inf'), iter=-1)
+        self.best_metric_results[dataset_name] = record
+
+    def _update_best_metric_result(self, dataset_name, metric, val, current_iter):      # base_model.py:65-73
+        rec = self.best_metric_results[dataset_name][metric]
+        if (rec['better'] == 'higher' and val >= rec['val']) or (rec['better'] != 'higher' and val <= rec['val']):
+            rec['val'], rec['iter'] = val, current_iter
+
+    def _log_validation_metric_values(self, current_iter, dataset_name, tb_logger):    # sr_model.py:251-264
+        import logging
+        log_str = f'Validation {dataset_name}\n'
+        for metric, value in self.metric_results.items():
+            log_str += f'\t # {metric}: {value:.4f}'
+            if hasattr(self, 'best_metric_results'):
+                log_str += (f'\tBest: {self.best_metric_results[dataset_name][metric]["val"]:.4f} @ '
+                            f'{self.best_metric_results[dataset_name][metric]["iter"]} iter')
+            log_str += '\n'
+        logging.getLogger('basicsr').info(log_str)
+        if tb_logger:
+            for metric, value in self.metric_results.items():
+                tb_logger.add_scalar(f'metrics/{dataset_name}/{metric}', value, current_iter)
+
     # -- convenience ---------------------------------------------------------------------------
     def test(self, lq):
         """pre_process -> (tile_)process -> post_process, as nondist_validation does per image
@@ -354,6 +518,49 @@ class HATModel:
             self.process()
         self.post_process()
         return self.output
+
+
+def _device_metric(sr_dev, gt_dev, opt_):
+    """calculate_metric (basicsr/metrics/__init__.py:10-20) with the PSNR / SSIM types served on the device."""
+    import copy
+    o = copy.deepcopy(opt_)
+    typ = o.pop('type')
+    o.pop('better', None)
+    if typ == 'calculate_psnr':
+        return calculate_psnr(sr_dev, gt_dev, **o)
+    if typ == 'calculate_ssim':
+        return calculate_ssim(sr_dev, gt_dev, **o)
+    try:
+        from basicsr.metrics import calculate_metric
+    except Exception as e:       # pragma: no cover
+        raise NotImplementedError(f"metric type '{typ}' needs basicsr's METRIC_REGISTRY") from e
+    data = dict(img=sr_dev.cpu().numpy())
+    if gt_dev is not None:
+        data['img2'] = gt_dev.cpu().numpy()
+    return calculate_metric(data, opt_)
+
+
+def _imwrite(img, file_path):
+    """basicsr.utils.imwrite (img_util.py:149-166): makedirs + cv2.imwrite."""
+    import os
+    os.makedirs(os.path.abspath(os.path.dirname(file_path)), exist_ok=True)
+    try:
+        import cv2
+    except Exception as e:       # pragma: no cover
+        raise RuntimeError("saving images needs OpenCV (cv2), as in the reference") from e
+    if not cv2.imwrite(file_path, img):
+        raise IOError('Failed in writing images.')
+
+
+try:  # the reference registers its class in basicsr's MODEL_REGISTRY (hat_model.py:13)
+    from basicsr.utils.registry import MODEL_REGISTRY as _MODEL_REGISTRY
+except Exception:
+    _MODEL_REGISTRY = None
+if _MODEL_REGISTRY is not None:
+    try:
+        _MODEL_REGISTRY.register(HATModel)
+    except AssertionError:       # the reference's own HATModel is registered in this process: keep ours under a suffix
+        _MODEL_REGISTRY.register(HATModel, suffix='b200')
 
 
 def _dist_ready():

@@ -1,0 +1,156 @@
+"""GPU: isolated parity of the kernels that round 1 only covered through whole-forward goldens:
+the tcgen05 Toeplitz 13x13 kernel (plk_tc), conv_first, the conv_last tensor-core route, hab_finish, and a BIT-EXACT
+integer test of the pixel-shuffle TMA store -- all through the C ABI, against torch-CPU fp32 restatements."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import hat_oracle as O
+from super_resolution_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+MEAN = (0.4488, 0.4371, 0.4040, 0.0)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _tok(x):      # (B,C,H,W) -> (B*H*W, C)
+    return x.permute(0, 2, 3, 1).reshape(-1, x.shape[1]).contiguous()
+
+
+def _img(t, B, H, W):
+    return t.view(B, H, W, -1).permute(0, 3, 1, 2)
+
+
+@pytest.mark.parametrize("B,H,W,with_dyn", [(1, 16, 32, True), (2, 32, 32, True), (3, 64, 64, True), (1, 48, 96, False),
+                                            (16, 64, 64, True)])
+def test_esc_plk_tcgen05(B, H, W, with_dyn):
+    """esc_arch.py:119-123: conv13x13 on the first 16 channels + per-sample dynamic depthwise 3x3."""
+    g = torch.Generator().manual_seed(31 + B)
+    x = torch.randn(B, 16, H, W, generator=g).bfloat16().float()
+    plk = (torch.randn(16, 16, 13, 13, generator=g) * 0.02)
+    dyn = torch.randn(B, 16, 9, generator=g) * 0.2 if with_dyn else None
+    ref = F.conv2d(x, plk.bfloat16().float(), padding=6)
+    if with_dyn:
+        ref = ref + torch.cat([F.conv2d(x[b:b + 1], dyn[b].view(16, 1, 3, 3), padding=1, groups=16) for b in range(B)])
+    x16 = _tok(x).to(DEV).bfloat16()
+    out = torch.full((B * H * W, 64), 3.0, dtype=torch.bfloat16, device=DEV)
+    plk_d, dyn_d = plk.to(DEV), (dyn.to(DEV) if with_dyn else None)        # keep the device copies alive over the call
+    _lib.check(_lib.lib().hatb200_esc_plk(_p(x16), B, H, W, _p(plk_d), _p(dyn_d), _p(out), 64, _stream()))
+    torch.cuda.synchronize()
+    got = _img(out[:, :16].float().cpu(), B, H, W)
+    err = (got - ref).abs().max().item()
+    assert err <= 2.0 ** -7 * max(1.0, ref.abs().max().item()), err
+    assert (out[:, 16:] == 3.0).all()                       # only channels [0, 16) are written
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,H,W,Cn,rng", [(2, 16, 32, 180, 1.0), (1, 32, 16, 144, 255.0)])
+def test_conv_first(dtype, B, H, W, Cn, rng):
+    g = torch.Generator().manual_seed(41)
+    x = torch.rand(B, 3, H, W, generator=g)
+    w = torch.randn(Cn, 3, 3, 3, generator=g) * 0.2
+    b = torch.randn(Cn, generator=g) * 0.1
+    xin = x.to(dtype).float()
+    mean = torch.tensor(MEAN[:3]).view(1, 3, 1, 1)
+    ref = _tok(F.conv2d((xin - mean) * rng, w, b, padding=1))
+    out = torch.zeros(B * H * W, Cn, device=DEV)
+    m4 = (C.c_float * 4)(*MEAN)
+    xd, wd, bd = x.to(DEV).to(dtype), w.to(DEV), b.to(DEV)
+    _lib.check(_lib.lib().hatb200_conv_first(_p(xd), _lib.dtype_code(dtype), B, 3, H, W, _p(wd), _p(bd), Cn, m4, rng,
+                                             _p(out), _stream()))
+    torch.cuda.synchronize()
+    err = (out.cpu() - ref).abs().max().item()
+    assert err <= 1e-5 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("use_tc,ydt", [(1, torch.bfloat16), (1, torch.float32), (0, torch.bfloat16), (0, torch.float32)])
+@pytest.mark.parametrize("B,H,W,rng", [(1, 32, 64, 1.0), (2, 128, 128, 255.0)])
+def test_conv_last_routes(use_tc, ydt, B, H, W, rng):
+    """hat_arch.py:856-858, both routes of the bf16 forward (tensor-core N=3->16 + NCHW/affine pass; CUDA-core kernel)."""
+    g = torch.Generator().manual_seed(43)
+    x = torch.randn(B, 64, H, W, generator=g).bfloat16().float()
+    w = torch.randn(3, 64, 3, 3, generator=g) * 0.05
+    b = torch.randn(3, generator=g) * 0.1
+    mean = torch.tensor(MEAN[:3]).view(1, 3, 1, 1)
+    wr = w.bfloat16().float() if use_tc else w
+    ref = F.conv2d(x, wr, b, padding=1) / rng + mean
+    y = torch.zeros(B, 3, H, W, dtype=ydt, device=DEV)
+    m4 = (C.c_float * 4)(*MEAN)
+    xd, wd, bd = _tok(x).to(DEV).bfloat16(), w.to(DEV), b.to(DEV)
+    _lib.check(_lib.lib().hatb200_conv_last(_p(xd), _lib.BF16, B, H, W, _p(wd), _p(bd), 3, m4, rng, _p(y),
+                                            _lib.dtype_code(ydt), use_tc, _stream()))
+    torch.cuda.synchronize()
+    err = (y.float().cpu() - ref).abs().max().item()
+    tol = 1e-5 if ydt == torch.float32 else 2.0 ** -8
+    assert err <= tol * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,Cn,hw", [(1, 180, 1024), (3, 144, 4096), (16, 180, 4096)])
+def test_hab_finish(B, Cn, hw):
+    """ECA gate (hat_arch.py:66-78) and ESC dynamic kernel (esc_arch.py:95-100) from per-tile partial sums."""
+    g = torch.Generator().manual_seed(47)
+    nchunk, pdim = hw // 128, 16
+    ep = torch.randn(B, nchunk, Cn, generator=g) * 10
+    dp = torch.randn(B, nchunk, pdim, generator=g) * 10
+    w5 = torch.randn(5, generator=g)
+    w1, b1 = torch.randn(8, 16, generator=g) * 0.3, torch.randn(8, generator=g) * 0.1
+    w2, b2 = torch.randn(144, 8, generator=g) * 0.3, torch.randn(144, generator=g) * 0.1
+    gap = ep.sum(1) / hw                                                # (B, C)
+    ref_s = torch.sigmoid(F.conv1d(gap.view(B, 1, Cn), w5.view(1, 1, 5), padding=2)).view(B, Cn)
+    ref_d = (F.gelu((dp.sum(1) / hw) @ w1.t() + b1) @ w2.t() + b2).view(B, pdim, 9)
+    s = torch.zeros(B, Cn, device=DEV)
+    d = torch.zeros(B, pdim, 9, device=DEV)
+    dev = [t.to(DEV) for t in (ep, w5, dp, w1, b1, w2, b2)]
+    _lib.check(_lib.lib().hatb200_hab_finish(_p(dev[0]), nchunk, B, Cn, hw, _p(dev[1]), _p(s), _p(dev[2]), pdim,
+                                             _p(dev[3]), _p(dev[4]), _p(dev[5]), _p(dev[6]), _p(d), _stream()))
+    torch.cuda.synchronize()
+    assert (s.cpu() - ref_s).abs().max().item() <= 1e-6
+    assert (d.cpu() - ref_d).abs().max().item() <= 1e-5 * max(1.0, ref_d.abs().max().item())
+
+
+@pytest.mark.parametrize("r,B,H,W", [(2, 1, 16, 16), (2, 3, 32, 48), (3, 2, 16, 32), (2, 1, 128, 128), (3, 1, 64, 64)])
+def test_pixel_shuffle_store_is_bit_exact(r, B, H, W):
+    """The PixelShuffle(r) permutation folded into the 5-D TMA store of conv3_tc (hat_arch.py:593-605) is integer
+    address arithmetic: out[b, y r + i, x r + j, c] must hold conv channel c r^2 + i r + j of pixel (b, y, x), exactly.
+    Every run makes the conv output a small integer that names one coordinate (exact in bf16)."""
+    N = 64 * r * r
+    src = O.pixel_shuffle_source(64, H, W, r)                 # (64, H r, W r): flat index into (64 r^2, H, W)
+    n_of, rem = src // (H * W), src % (H * W)
+    y_of, x_of = rem // W, rem % W
+    yy, xx, bb = torch.meshgrid(torch.arange(H), torch.arange(W), torch.arange(B), indexing="ij")
+
+    def run(pix_code, bias):
+        a = torch.zeros(B * H * W, 64)
+        if pix_code is not None:
+            a[:, 0] = pix_code.permute(2, 0, 1).reshape(-1).float()          # (b, y, x) token order
+        w = torch.zeros(N, 64, 3, 3)
+        if pix_code is not None:
+            w[:, 0, 1, 1] = 1.0
+        out = torch.full((B, H * r, W * r, 64), -1.0, dtype=torch.bfloat16, device=DEV)
+        ad, wd, bd = a.to(DEV).bfloat16(), w.to(DEV), bias.float().to(DEV)
+        _lib.check(_lib.lib().hatb200_conv_shuffle(_p(ad), B, H, W, _p(wd), _p(bd), r, _p(out), _stream()))
+        torch.cuda.synchronize()
+        return out.float().cpu().permute(0, 3, 1, 2).numpy()                # (B, 64, H r, W r)
+
+    zero_b = torch.zeros(N)
+    got_x = run(xx, zero_b)
+    got_y = run(yy, zero_b)
+    got_b = run(bb, zero_b)
+    got_nlo = run(None, torch.arange(N) % 256)
+    got_nhi = run(None, torch.arange(N) // 256)
+    for b in range(B):
+        assert np.array_equal(got_x[b], x_of.astype(np.float32)), "x coordinate of the source pixel"
+        assert np.array_equal(got_y[b], y_of.astype(np.float32)), "y coordinate of the source pixel"
+        assert np.array_equal(got_b[b], np.full_like(got_b[b], b)), "sample of the source pixel"
+        assert np.array_equal(got_nlo[b] + 256 * got_nhi[b], n_of.astype(np.float32)), "conv channel c r^2 + i r + j"

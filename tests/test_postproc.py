@@ -49,6 +49,20 @@ def test_oracle_psnr_matches_reference_golden():
     assert IO.calculate_psnr(z["a_bgr"], z["a_bgr"], 0) == float("inf")
 
 
+def test_oracle_ssim_matches_reference_golden():
+    z, _ = _gold()
+    ssim = json.loads(str(z["ssim"]))
+    for cb in (0, 4):
+        for ty in (False, True):
+            got = IO.calculate_ssim(z["a_bgr"], z["b_bgr"], cb, ty)
+            assert got == pytest.approx(ssim[f"cb{cb}_y{int(ty)}"], rel=1e-12), (cb, ty)
+    _, _, gray, _ = postproc_inputs()
+    g2 = IO.tensor2img((gray * 0.97).numpy())
+    assert IO.calculate_ssim(z["gray"], g2, 2, True) == pytest.approx(ssim["gray_cb2_y1"], rel=1e-12)
+    assert IO.calculate_ssim(z["gray"], g2, 0, False) == pytest.approx(ssim["gray_cb0_y0"], rel=1e-12)
+    assert IO.calculate_ssim(z["a_bgr"], z["a_bgr"], 0) == pytest.approx(1.0, abs=1e-15)
+
+
 @pytest.mark.skipif(not load_ref.reference_available(), reason="reference not mounted")
 def test_oracle_postproc_matches_live_reference():
     load_ref.load_reference_hat()
@@ -61,6 +75,9 @@ def test_oracle_postproc_matches_live_reference():
     assert np.array_equal(IO.tensor2img(x.numpy()), ix)
     for ty in (False, True):
         assert IO.calculate_psnr(ix, iy, 3, ty) == pytest.approx(calculate_psnr(ix, iy, 3, test_y_channel=ty), rel=1e-12)
+    from basicsr.metrics.psnr_ssim import calculate_ssim
+    for ty in (False, True):
+        assert IO.calculate_ssim(ix, iy, 3, ty) == pytest.approx(calculate_ssim(ix, iy, 3, test_y_channel=ty), rel=1e-12)
 
 
 def test_checkpoint_roundtrip_reference_layout(tmp_path):
@@ -149,3 +166,34 @@ def test_gpu_psnr_matches_reference():
     for ty in (False, True):
         ref = IO.calculate_psnr(x.numpy(), y.numpy(), 8, ty)
         assert math.isclose(calculate_psnr(x.to(dev), y.to(dev), 8, test_y_channel=ty), ref, rel_tol=1e-9)
+
+
+@pytest.mark.gpu
+def test_gpu_ssim_matches_reference():
+    """hatb200_ssim_u8 against the reference-generated values (basicsr/metrics/psnr_ssim.py:85-129) and, at HR size with
+    ragged tiles, against the oracle; 1e-9 relative (float64 sums in a different order than cv2.filter2D)."""
+    from super_resolution_b200 import calculate_ssim
+    z, _ = _gold()
+    ssim = json.loads(str(z["ssim"]))
+    dev = "cuda:0"
+    ia, ib = torch.from_numpy(z["a_bgr"]).to(dev), torch.from_numpy(z["b_bgr"]).to(dev)
+    for cb in (0, 4):
+        for ty in (False, True):
+            assert calculate_ssim(ia, ib, cb, test_y_channel=ty) == pytest.approx(ssim[f"cb{cb}_y{int(ty)}"], rel=1e-9)
+    assert calculate_ssim(ia, ia, 0) == pytest.approx(1.0, abs=1e-12)
+    assert calculate_ssim(ia.permute(2, 0, 1), ib.permute(2, 0, 1), 4, input_order="CHW") == \
+        pytest.approx(ssim["cb4_y0"], rel=1e-9)
+    _, _, gray, _ = postproc_inputs()
+    g2 = torch.from_numpy(IO.tensor2img((gray * 0.97).numpy())).to(dev)
+    gr = torch.from_numpy(z["gray"]).to(dev)
+    assert calculate_ssim(gr, g2, 2, test_y_channel=True) == pytest.approx(ssim["gray_cb2_y1"], rel=1e-9)
+    assert calculate_ssim(gr, g2, 0) == pytest.approx(ssim["gray_cb0_y0"], rel=1e-9)
+    # more tiles than blocks (grid-stride) and ragged edges, against the oracle
+    g = torch.Generator().manual_seed(13)
+    x = torch.randint(0, 256, (1083, 1531, 3), generator=g, dtype=torch.uint8)
+    y = (x.int() + torch.randint(-9, 10, x.shape, generator=g)).clamp(0, 255).to(torch.uint8)
+    for ty in (False, True):
+        ref = IO.calculate_ssim(x.numpy(), y.numpy(), 4, ty)
+        assert math.isclose(calculate_ssim(x.to(dev), y.to(dev), 4, test_y_channel=ty), ref, rel_tol=1e-9)
+    with pytest.raises(RuntimeError):
+        calculate_ssim(ia[:12, :12], ib[:12, :12], 2)          # 8x8 after the crop: smaller than the window
