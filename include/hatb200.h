@@ -246,6 +246,15 @@ int hatb200_hab_finish(const float* eca_partial, int nchunk, int B, int C, int H
 int hatb200_conv_shuffle(const void* a, int B, int H, int W, const float* w, const float* bias, int r, void* out,
                          void* stream);
 
+/* GatedDconvFFN back half in one persistent tcgen05 kernel (hat_arch.py:112-119, :237; csrc/tc_ffn.cu): h1 bf16
+ * (M, in_pitch) = fc1 output (proj channels [0, hid), gate [hid, 2 hid)); G = dw3x3(h1)[:, :hid] * SiLU(dw3x3(h1)[:, hid:])
+ * stays in shared memory; v = G . fc2_w^T + fc2_b + resid; out_f32 (M, N) = v; ln_out bf16 (M, ln_pitch) =
+ * LayerNorm(v; gamma, beta, eps 1e-5), pad columns zero.  resid / out_f32 fp32 (M, N) may alias. */
+int hatb200_ffn_tail_fused(const void* h1, int in_pitch, int B, int H, int W, int hid, const float* dw_w,
+                           const float* dw_b, const float* fc2_w, const float* fc2_b, int N, const float* resid,
+                           float* out_f32, const float* gamma, const float* beta, void* ln_out, int ln_pitch,
+                           void* stream);
+
 /* hatb200_dwconv_gate for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it).  No counterpart in the reference.
  * Same arguments, arithmetic and results as hatb200_dwconv_gate, but the
@@ -264,7 +273,7 @@ int hatb200_dwconv_gate_noalloc(const void* in, int dtype, int in_pitch, int B, 
 /* Engineering probes (csrc/tc_probe.cu), only in libraries built with HATB200_ENGINEERING=1; no reference counterpart.
  * One tcgen05.mma with caller-chosen descriptor fields, and the per-CTA %globaltimer trace of the last persistent
  * GEMM / conv3 launch made with HATB200_GEMM_TRACE set (tools/probe_umma.py, tools/trace_gemm.py, tools/trace_conv3.py). */
-int hatb200_probe_umma(const void* a, int R, const void* b, int r0, int sbo_bytes, int base_offset, void* out,
+int hatb200_probe_umma(const void* a, int R, const void* b, int r0, int sbo_bytes, int base_offset, float* out,
                        void* stream);
 int hatb200_debug_gemm_trace(unsigned long long* host, void* stream);
 #endif

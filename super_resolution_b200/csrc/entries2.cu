@@ -111,4 +111,28 @@ int hatb200_conv_shuffle(const void* a, int B, int H, int W, const float* w, con
   return finish(rc, st, "conv_shuffle");
 }
 
+int hatb200_ffn_tail_fused(const void* h1, int in_pitch, int B, int H, int W, int hid, const float* dw_w,
+                           const float* dw_b, const float* fc2_w, const float* fc2_b, int N, const float* resid,
+                           float* out_f32, const float* gamma, const float* beta, void* ln_out, int ln_pitch,
+                           void* stream) {
+  HB_REQUIRE(h1 && dw_w && dw_b && fc2_w && fc2_b && resid && out_f32 && gamma && beta && ln_out, HATB200_EINVAL,
+             "ffn_tail_fused: null tensor");
+  cudaStream_t st = (cudaStream_t)stream;
+  TmpPool2 pool;
+  const int Npad = tc_npad(N), Kpad = round_up(hid, 64);
+  bf16* w16;
+  float* dwt;
+  HB_TRY(pool.alloc((void**)&w16, (size_t)Npad * Kpad * sizeof(bf16), st));
+  HB_TRY(pool.alloc((void**)&dwt, (size_t)9 * 2 * hid * sizeof(float), st));
+  HB_TRY(launch_pack_w_bf16(fc2_w, HATB200_F32, N, hid, 1, w16, Npad, Kpad, 0, hid, st));
+  HB_TRY(launch_pack_w_f32(dw_w, HATB200_F32, 2 * hid, 1, 9, dwt, 2 * hid, 2 * hid, st));
+  FfnTailArgs fa{h1, in_pitch, B, H, W, hid, dwt, dw_b, w16, N, Npad, Kpad};
+  Epilogue ep;
+  ep.bias = fc2_b; ep.resid = resid; ep.resid_pitch = N; ep.out_f32 = out_f32; ep.out_f32_pitch = N;
+  ep.ln_gamma = gamma; ep.ln_beta = beta; ep.ln_out = ln_out; ep.ln_pitch = ln_pitch;
+  HB_REQUIRE(ffn2_tc_supported(fa, ep), HATB200_EUNSUPPORTED, "ffn_tail_fused: shape not supported by ffn2_tc");
+  int r = launch_ffn2_tc(fa, ep, st);
+  return finish(r, st, "ffn_tail_fused");
+}
+
 }  // extern "C"

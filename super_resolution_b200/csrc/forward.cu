@@ -290,12 +290,29 @@ struct Fwd {
     {  // GatedDconvFFN (hat_arch.py:107-119)
       Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.hp4;
       HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
+      set_ln(e2, next_ln, w.XN, next_head);
+      // depthwise 3x3 + gate + fc2 + residual + LayerNorm in one persistent tcgen05 kernel: the gated middle G never
+      // reaches HBM (tc_ffn.cu)
+      FfnTailArgs fa{w.H1, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, b.fc2.w16, b.fc2.O, b.fc2.Npad, b.fc2.Kpad};
+      Epilogue e3 = e2; e3.bias = b.fc2.bias;
+      // Measured on B200 (profiles/r02_ffn_fused_trace.txt): 88-94 us per launch against 39 + 43 us for dwgate + fc2 --
+      // the depthwise stage is FMA-pipe bound (17-20 us per 128-pixel tile whether 8 or 16 warps run it) and shares its
+      // issue slots with the epilogue warps, so the fused kernel is opt-in (HATB200_FFN_FUSED=1), not the default.
+      static const bool ffn_fused = getenv("HATB200_FFN_FUSED") && getenv("HATB200_FFN_FUSED")[0] == '1';
+      if (ffn_fused && tc() && !tc_disabled("ffn_dw_fc2") && ffn2_tc_supported(fa, e3)) {
+        const double Mt = (double)d.M;
+        int tid = t_begin("ffn_dw_fc2", 2.0 * Mt * (2.0 * d.hid * 9 + (double)d.hid * d.C),
+                          Mt * (2.0 * d.hid * d.es) + conv_bytes(b.fc2, Mt, e2) - Mt * d.hid * d.es, "ffn_tc");
+        int r = launch_ffn2_tc(fa, e3, st);
+        t_end(tid);
+        HB_TRY(r);
+        return dbg("ffn2_tc");
+      }
       int tid = t_begin("ffn_dwconv_gate", 2.0 * d.M * 2 * d.hid * 9, (double)d.M * 3 * d.hid * d.es, "dwgate");
       HB_TRY(launch_dwgate(w.H1, d.dt, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, w.G, d.hp2, d.hp2, st));
       t_end(tid);
       HB_TRY(dbg("dwgate"));
-      Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
-      set_ln(e2, next_ln, w.XN, next_head);
       HB_TRY(conv("ffn_fc2", b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
     }
     return 0;

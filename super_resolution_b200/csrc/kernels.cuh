@@ -102,6 +102,17 @@ inline int launch_conv_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, 
   return launch_tapconv_tc(a, w, Npad, Kpad, ep, st);
 }
 
+// ---- GatedDconvFFN back half fused (tc_ffn.cu): depthwise 3x3 + gate -> fc2 -> residual + LayerNorm epilogue ----
+struct FfnTailArgs {
+  const void* h1; int in_pitch;      // fc1 output, bf16 (B*H*W, in_pitch): proj channels [0, hid), gate [hid, 2 hid)
+  int B, H, W, hid;
+  const float* dw_w;                 // [9][2 hid] tap-major depthwise weights
+  const float* dw_b;                 // [2 hid]
+  const bf16* w2; int N, Npad, Kpad; // fc2 weights packed [Npad][Kpad] K-major (bias, residual, LN in the Epilogue)
+};
+bool ffn2_tc_supported(const FfnTailArgs& a, const Epilogue& ep);
+int launch_ffn2_tc(const FfnTailArgs& a, const Epilogue& ep, cudaStream_t st);
+
 // ---- ESC 13x13 conv + dynamic depthwise on tensor cores (tc_plk.cu) ----
 bool plk_tc_supported(int pdim, int ksize, int H, int W, int out_pitch);
 size_t plk_toeplitz_elems();

@@ -154,3 +154,45 @@ def test_pixel_shuffle_store_is_bit_exact(r, B, H, W):
         assert np.array_equal(got_y[b], y_of.astype(np.float32)), "y coordinate of the source pixel"
         assert np.array_equal(got_b[b], np.full_like(got_b[b], b)), "sample of the source pixel"
         assert np.array_equal(got_nlo[b] + 256 * got_nhi[b], n_of.astype(np.float32)), "conv channel c r^2 + i r + j"
+
+
+def _ffn_tail_case(B, H, W, hid, N, seed):
+    g = torch.Generator().manual_seed(seed)
+    in_pitch, ln_pitch = ((2 * hid + 63) // 64) * 64, ((N + 63) // 64) * 64
+    h1 = torch.randn(B, 2 * hid, H, W, generator=g).bfloat16().float()
+    dw_w = torch.randn(2 * hid, 1, 3, 3, generator=g) * 0.3
+    dw_b = torch.randn(2 * hid, generator=g) * 0.1
+    w2 = torch.randn(N, hid, generator=g) * (1.0 / hid ** 0.5)
+    b2 = torch.randn(N, generator=g) * 0.1
+    resid = torch.randn(B * H * W, N, generator=g)
+    gamma, beta = 1.0 + 0.1 * torch.randn(N, generator=g), 0.02 * torch.randn(N, generator=g)
+    t = F.conv2d(h1, dw_w, dw_b, padding=1, groups=2 * hid)
+    gated = (t[:, :hid] * F.silu(t[:, hid:])).bfloat16().float()               # G is a bf16 tensor-core operand
+    v = _tok(gated) @ w2.bfloat16().float().t() + b2 + resid
+    ln = F.layer_norm(v, (N,), gamma, beta, 1e-5)
+    h1t = torch.full((B * H * W, in_pitch), float("nan"), dtype=torch.bfloat16, device=DEV)   # pad columns: never read
+    h1t[:, :2 * hid] = _tok(h1).to(DEV).bfloat16()
+    out = torch.zeros(B * H * W, N, device=DEV)
+    ln_out = torch.full((B * H * W, ln_pitch), 5.0, dtype=torch.bfloat16, device=DEV)
+    dev = [x.to(DEV) for x in (dw_w, dw_b, w2, b2, resid, gamma, beta)]
+    _lib.check(_lib.lib().hatb200_ffn_tail_fused(_p(h1t), in_pitch, B, H, W, hid, _p(dev[0]), _p(dev[1]), _p(dev[2]),
+                                                 _p(dev[3]), N, _p(dev[4]), _p(out), _p(dev[5]), _p(dev[6]), _p(ln_out),
+                                                 ln_pitch, _stream()))
+    torch.cuda.synchronize()
+    return out.cpu(), v, ln_out.float().cpu(), ln, N
+
+
+@pytest.mark.parametrize("B,H,W,hid,N", [(1, 16, 8, 360, 180), (2, 32, 32, 360, 180), (1, 48, 24, 288, 144),
+                                         (3, 16, 16, 96, 48), (16, 64, 64, 360, 180), (1, 256, 256, 360, 180)])
+def test_ffn_tail_fused_tcgen05(B, H, W, hid, N):
+    """hat_arch.py:112-119 + :237: dw3x3 + gate -> fc2 -> + residual -> LayerNorm, one kernel; vs torch fp32 on the same
+    bf16-rounded operands (tolerance: the dwgate / linear_fused tests' bf16 bar on the gated operand, fp32 elsewhere)."""
+    out, v, ln_out, ln, N = _ffn_tail_case(B, H, W, hid, N, 50 + B)
+    err = (out - v).abs().max().item()
+    assert err <= 2.0 ** -7 * max(1.0, v.abs().max().item()), f"fp32 stream max-abs {err:.3e}"
+    err_ln = (ln_out[:, :N] - ln).abs().max().item()
+    assert err_ln <= 2.0 ** -6 * max(1.0, ln.abs().max().item()), f"LayerNorm output max-abs {err_ln:.3e}"
+    assert ln_out[:, N:].abs().max().item() == 0 if ln_out.shape[1] > N else True       # K padding of the consumer
+    # run to run identical (no race between the dw warps, the MMA thread and the epilogue)
+    out2, _, ln2, _, _ = _ffn_tail_case(B, H, W, hid, N, 50 + B)
+    assert torch.equal(out, out2) and torch.equal(ln_out, ln2)
