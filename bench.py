@@ -232,6 +232,72 @@ def summarize_profile(prof, peaks, tc_on):
     return roof, per_kernel, per_op, total_ms
 
 
+HATL_X4 = dict(HAT_X4, depths=[6] * 12, num_heads=[6] * 12)
+
+
+def run_tiled(world, rank, dev, runs=3):
+    """BASELINE configs[3] inside a timed region: HAT-L SRx4 (12 RHAG) bf16, ONE 1024x1024 LR image, tile 256 / pad 32
+    (16 tiles: 4 of 288x288, 8 of 288x320, 4 of 320x320), tiles sharded over the ranks longest-processing-time-first,
+    cropped HR cores gathered to rank 0 (NCCL send / recv over NVLink) INSIDE the timed region.  Strong scaling of one
+    image: CUDA events around HATModel.test on every rank, max over ranks; rank 0 also runs the same job alone so that
+    the efficiency against one GPU comes from the same process and box."""
+    import torch.distributed as dist
+    from super_resolution_b200 import HAT, HATModel
+    torch.manual_seed(0)
+    net = HAT(**HATL_X4).eval().to(dev)
+    x = torch.rand(1, 3, 1024, 1024, generator=torch.Generator().manual_seed(0)).bfloat16().to(dev)
+    opt = {"network_g": {"window_size": 16}, "scale": 4, "tile": {"tile_size": 256, "tile_pad": 32}}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(model):
+        model.record_events = True
+        for _ in range(2):                    # warm-up: one CUDA graph per stack shape
+            model.test(x)
+        tot, comp = [], []
+        for _ in range(runs):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            model.test(x)
+            e1.record()
+            torch.cuda.synchronize()
+            tot.append(e0.elapsed_time(e1))
+            comp.append(e0.elapsed_time(model.events['compute_end']))
+        return sum(tot) / runs, sum(comp) / runs
+
+    out_mp = 4096 * 4096 / 1e6
+    res = {"config": "BASELINE configs[3]: HAT-L SRx4 (12 RHAG) bf16, one 1024x1024 LR image, tile 256 / pad 32, "
+                     "16 tiles sharded over the ranks (LPT), HR cores gathered to rank 0 inside the timed region",
+           "n_gpus": world, "tiles": 16, "runs": runs, "scaling": "strong"}
+    t1 = None
+    if rank == 0:                             # the same job on one GPU (the other ranks wait at the barrier below)
+        world_, world = world, 1
+        t1, _ = timed(HATModel(net, opt))
+        world = world_
+    if world == 1:
+        res.update({"ms": t1, "out_mp_s": out_mp / (t1 * 1e-3)})
+        return res
+    dist.barrier()
+    model = HATModel(net, opt, group=dist.group.WORLD, dst=0)
+    t, c = timed(model)
+    v = torch.tensor([t, c, c], device=dev, dtype=torch.float64)
+    mx = v.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = v.clone()
+    dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    t_max, c_max, c_mean = mx[0].item(), mx[1].item(), sm[2].item() / world
+    if rank == 0:
+        res.update({"ms": t_max, "out_mp_s": out_mp / (t_max * 1e-3), "ms_1gpu": t1,
+                    "efficiency_vs_1gpu": t1 / (world * t_max), "compute_ms_max": c_max, "compute_ms_mean": c_mean,
+                    "imbalance": c_max / c_mean, "gather_ms": t_max - c_max,
+                    "gather_bytes": int(4096 * 4096 * 3 * 2 * (world - 1) / world)})
+    return res
+
+
 def run_ours(args):
     rank, world, local = dist_env()
     if not torch.cuda.is_available():
@@ -302,6 +368,11 @@ def run_ours(args):
     e2e_val = world * out_px / 1e6 / (t2.item() / K * 1e-3)
 
     launches = eng.last_launch_count
+    tiled = None
+    if not args.no_tiled:
+        del flush
+        torch.cuda.empty_cache()
+        tiled = run_tiled(world, rank, dev)
     if rank == 0:
         prof = eng.op_profile(x)
         torch.cuda.synchronize()
@@ -337,6 +408,8 @@ def run_ours(args):
             "per_kernel": per_kernel, "per_op": per_op, "profiled_eager_step_ms": prof_ms,
             "tcgen05_fallbacks": eng.last_fallback_count,
         }
+        if tiled is not None:
+            line["tiled"] = tiled
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
@@ -352,6 +425,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tiled", action="store_true", help="skip the configs[3] tiled HAT-L measurement")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -33,13 +33,60 @@ def mod_pad(h: int, w: int, window_size: int):
     return ph, pw
 
 
-def shard_tiles(rects, world_size: int):
-    """Assign tiles to ranks, longest-processing-time-first on the padded input area.
+# One stacked forward costs about as much as this many LR pixels of tile area on top of the area it processes
+# (B200, HAT-L tiles of 288-320 px, tools/time_tiles.py: T = 0.27 us/px * area + ~5.5 ms per forward -- launch ramps of
+# ~670 kernels and the last-wave quantisation of 650-800 work tiles on 148 SMs; profiles/r02_tiled_scaling.md)
+FORWARD_COST_PX = 20000
 
-    Deterministic (ties broken by the reference tile order hat_model.py:76), so every rank computes
-    the same assignment without communicating.  Returns a list of `world_size` lists of tile
-    indices, each in ascending (reference) order."""
+
+def shard_cost(rects, idxs, forward_cost_px=FORWARD_COST_PX):
+    """Cost model of one rank's share: padded input area + a fixed cost per stacked forward (= per distinct shape)."""
+    shapes = {(rects[i]["in_y1"] - rects[i]["in_y0"], rects[i]["in_x1"] - rects[i]["in_x0"]) for i in idxs}
+    return sum(h * w for h, w in ((rects[i]["in_y1"] - rects[i]["in_y0"], rects[i]["in_x1"] - rects[i]["in_x0"])
+                                  for i in idxs)) + forward_cost_px * len(shapes)
+
+
+_SHARD_CACHE = {}
+
+
+def shard_tiles(rects, world_size: int, forward_cost_px: int = FORWARD_COST_PX):
+    """Memoised `_shard_tiles` (the local search costs tens of milliseconds of host time for 16 tiles on 8 ranks;
+    an image stream of one size plans once)."""
+    key = (tuple((r["in_y1"] - r["in_y0"], r["in_x1"] - r["in_x0"]) for r in rects), world_size, forward_cost_px)
+    if key not in _SHARD_CACHE:
+        if len(_SHARD_CACHE) > 64:
+            _SHARD_CACHE.clear()
+        _SHARD_CACHE[key] = _shard_tiles(rects, world_size, forward_cost_px)
+    return [list(o) for o in _SHARD_CACHE[key]]
+
+
+def _shard_tiles(rects, world_size: int, forward_cost_px: int = FORWARD_COST_PX):
+    """Assign tiles to ranks: longest-processing-time-first on the padded input area, then a deterministic local
+    search (single-tile moves and pairwise swaps that lower the maximum, then the sum of squares, of `shard_cost`) --
+    same-shape tiles share one stacked forward, so a rank with two tiles of one shape beats one with two shapes.
+
+    Deterministic (ties broken by the reference tile order hat_model.py:76), so every rank computes the same
+    assignment without communicating.  Returns a list of `world_size` lists of tile indices, each in ascending
+    (reference) order."""
     area = lambda r: (r["in_y1"] - r["in_y0"]) * (r["in_x1"] - r["in_x0"])
+    shape = lambda r: (r["in_y1"] - r["in_y0"], r["in_x1"] - r["in_x0"])
+    if world_size > 1 and len(rects) > 32 and forward_cost_px > 0:
+        # Many units per rank (a batch of images): shape-major contiguous partition.  Units sorted by (shape, index) are
+        # cut into world_size runs of equal area, so a rank holds one or two shapes and its stacks are large (B200:
+        # 0.20 us per LR pixel in stacks of ten 320x320 tiles against 0.35 when every rank gets all nine shapes of a
+        # 540x960 image in forwards of one or two tiles; profiles/r02_tiled_scaling.md).
+        order = sorted(range(len(rects)), key=lambda i: (-area(rects[i]), shape(rects[i]), i))
+        total = sum(area(r) for r in rects)
+        owner = [[] for _ in range(world_size)]
+        acc, k = 0, 0
+        for i in order:
+            a = area(rects[i])
+            # move on when this unit's midpoint lies beyond the current rank's share of the total area
+            while k < world_size - 1 and acc + a / 2 > total * (k + 1) / world_size:
+                k += 1
+            owner[k].append(i)
+            acc += a
+        return [sorted(o) for o in owner]
     order = sorted(range(len(rects)), key=lambda i: (-area(rects[i]), i))
     load = [0] * world_size
     owner = [[] for _ in range(world_size)]
@@ -47,6 +94,33 @@ def shard_tiles(rects, world_size: int):
         r = min(range(world_size), key=lambda k: (load[k], k))
         owner[r].append(i)
         load[r] += area(rects[i])
+    if world_size == 1 or forward_cost_px <= 0:
+        return [sorted(o) for o in owner]
+    cost = lambda o: shard_cost(rects, o, forward_cost_px)
+    key = lambda ow: (max(cost(o) for o in ow), sum(cost(o) ** 2 for o in ow))
+    best = key(owner)
+    for _ in range(4 * len(rects)):                 # each accepted step strictly lowers `key`: terminates
+        cand, cand_key = None, best
+        for a in range(world_size):
+            for b in range(world_size):
+                if a == b:
+                    continue
+                for i in owner[a]:
+                    trial = [list(o) for o in owner]            # move i: a -> b
+                    trial[a].remove(i); trial[b].append(i)
+                    k = key(trial)
+                    if k < cand_key:
+                        cand, cand_key = trial, k
+                    if a < b:
+                        for j in owner[b]:                      # swap i <-> j
+                            trial = [list(o) for o in owner]
+                            trial[a].remove(i); trial[b].remove(j); trial[a].append(j); trial[b].append(i)
+                            k = key(trial)
+                            if k < cand_key:
+                                cand, cand_key = trial, k
+        if cand is None:
+            break
+        owner, best = cand, cand_key
     return [sorted(o) for o in owner]
 
 
@@ -60,7 +134,8 @@ def group_by_shape(rects, indices):
 
 
 # hatb200_forward indexes tokens with 32 bits (csrc/forward.cu check_geometry: B*H*W*16*64 < 2^31); a stacked forward
-# also needs ~1 KB of workspace per token, so stacks are capped well below that limit by default
+# also needs ~1 KB of workspace per token, so stacks are capped well below that limit by default (B200, HAT x4,
+# tools/time_scaling.py: 0.557 / 0.548 / 0.547 ms per 64x64 patch at 262k / 524k / 1M tokens -- no cliff up to the cap)
 MAX_FORWARD_TOKENS = (1 << 21) - 1
 DEFAULT_STACK_TOKENS = 1 << 20
 
@@ -88,31 +163,54 @@ def gather_cores(cores, rects, owners, batch, channels, dtype, device, dst=0, gr
     world = dist.get_world_size(group)
     if world == 1:
         return dict(cores)
+    flat = None
+    if rank != dst and owners[rank]:
+        flat = torch.cat([cores[i].reshape(-1) for i in owners[rank]])
+    bufs = exchange_flat(flat, rects, owners, batch, channels, dtype, device, dst, group)
+    if rank != dst:
+        return None
+    out = dict(cores)
+    for r, buf in bufs.items():
+        for i, view in flat_views(buf, rects, owners[r], batch, channels).items():
+            out[i] = view
+    return out
+
+
+def flat_numel(rects, idxs, batch, channels):
+    return sum(int(torch.Size(core_shape(rects[i], batch, channels)).numel()) for i in idxs)
+
+
+def flat_views(buf, rects, idxs, batch, channels):
+    """{tile index: (B, C, rh, rw) view} of one rank's flat message (tiles in ascending order, each contiguous)."""
+    out, off = {}, 0
+    for i in idxs:
+        shp = core_shape(rects[i], batch, channels)
+        n = int(torch.Size(shp).numel())
+        out[i] = buf[off:off + n].view(shp)
+        off += n
+    return out
+
+
+def exchange_flat(flat, rects, owners, batch, channels, dtype, device, dst=0, group=None):
+    """The one collective of tile mode: every rank other than `dst` sends its flat message of cropped HR cores,
+    `dst` receives one buffer per peer (returned as {rank: buffer}; {} elsewhere).  NCCL send / recv over NVLink."""
+    import torch.distributed as dist
+    rank = dist.get_rank(group)
+    world = dist.get_world_size(group)
     peer = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
-    numel = lambda i: int(torch.Size(core_shape(rects[i], batch, channels)).numel())
     ops, bufs = [], {}
     if rank == dst:
         for r in range(world):
             if r == dst or not owners[r]:
                 continue
-            bufs[r] = torch.empty(sum(numel(i) for i in owners[r]), dtype=dtype, device=device)
+            bufs[r] = torch.empty(flat_numel(rects, owners[r], batch, channels), dtype=dtype, device=device)
             ops.append(dist.P2POp(dist.irecv, bufs[r], peer(r), group))
-    elif owners[rank]:
-        flat = torch.cat([cores[i].reshape(-1) for i in owners[rank]])
+    elif flat is not None:
         ops.append(dist.P2POp(dist.isend, flat, peer(dst), group))
     if ops:
         for w in dist.batch_isend_irecv(ops):
             w.wait()
-    if rank != dst:
-        return None
-    out = dict(cores)
-    for r, buf in bufs.items():
-        off = 0
-        for i in owners[r]:
-            n = numel(i)
-            out[i] = buf[off:off + n].view(core_shape(rects[i], batch, channels))
-            off += n
-    return out
+    return bufs
 
 
 # --------------------------------------------------------------------------------------------------
@@ -311,6 +409,8 @@ class HATModel:
         self.scale = opt.get('scale', 1)
         self.mod_pad_h = self.mod_pad_w = 0
         self.lq = self.img = self.output = None
+        self.record_events = False      # bench: CUDA event after this rank's last forward / crop, before the gather
+        self.events = {}
         try:
             self.device = next(net.parameters()).device
         except (StopIteration, AttributeError):
@@ -367,36 +467,65 @@ class HATModel:
         if self.group is not None or (self.opt['tile'].get('shard') and _dist_ready()):
             import torch.distributed as dist
             world, rank = dist.get_world_size(self.group), dist.get_rank(self.group)
-        owners = shard_tiles(rects, world)
+        # The unit of work is one tile of ONE sample (every statistic of the network is per sample):
+        # unit u = tile * batch + sample, in the reference's loop order (tile outside, hat_model.py:56-76).  A batch of
+        # images therefore shards over the ranks together with its tiles, and stacks never exceed the token budget.
+        units = [dict(rects[i], tile=i, sample=b) for i in range(len(rects)) for b in range(batch)]
+        owners = shard_tiles(units, world)
         max_tokens = int(self.opt['tile'].get('max_stack_tokens', DEFAULT_STACK_TOKENS))
         self.net_g.eval()
-        cores = {}
-        with torch.no_grad():
-            stacks = [((th, tw), part) for (th, tw), idxs in group_by_shape(rects, owners[rank]).items()
-                      for part in split_stacks(idxs, th, tw, batch, max_tokens)]
-            for (th, tw), idxs in stacks:
-                stack = torch.empty((len(idxs) * batch, channel, th, tw), dtype=img.dtype, device=img.device)
-                for k, i in enumerate(idxs):        # extract (hat_model.py:77): one strided copy kernel per tile
-                    r = rects[i]
-                    crop_place(img, r["in_y0"], r["in_x0"], stack[k * batch:(k + 1) * batch], 0, 0, th, tw)
-                out = self.net_g(stack)
-                for k, i in enumerate(idxs):
-                    r = rects[i]
-                    core = torch.empty(core_shape(r, batch, channel), dtype=out.dtype, device=out.device)
-                    crop_place(out[k * batch:(k + 1) * batch], r["crop_y0"], r["crop_x0"], core, 0, 0,
-                               core.shape[2], core.shape[3])
-                    cores[i] = core
-        if world > 1:
-            cores = gather_cores(cores, rects, owners, batch, channel, img.dtype, img.device, self.dst, self.group)
-        if cores is None:                           # not the consumer rank
+        is_dst = world == 1 or rank == self.dst
+        # "start with black image" (hat_model.py:50): every output pixel is covered by exactly one core.  On the
+        # consumer rank the cores of its own units go straight from the network output into the image; the other
+        # ranks crop theirs straight into ONE flat send buffer (the message layout is implied by the shared plan).
+        if is_dst:
+            self.output = torch.empty((batch, channel, height * self.scale, width * self.scale), dtype=img.dtype,
+                                      device=img.device)
+            send, views = None, {}
+        else:
             self.output = None
-            return
-        # "start with black image" (hat_model.py:50): every output pixel is covered by exactly one core
-        self.output = torch.empty((batch, channel, height * self.scale, width * self.scale), dtype=img.dtype,
-                                  device=img.device)
-        for i, core in cores.items():
-            r = rects[i]
-            crop_place(core.contiguous(), 0, 0, self.output, r["out_y0"], r["out_x0"], core.shape[2], core.shape[3])
+            send = torch.empty(flat_numel(units, owners[rank], 1, channel), dtype=img.dtype, device=img.device)
+            views = flat_views(send, units, owners[rank], 1, channel)
+        # the stacked forward's result is cropped right away on the same stream: take the engine's own output buffer
+        # instead of a fresh copy of it
+        eng = self.net_g.engine() if hasattr(self.net_g, 'engine') else None
+        view0 = eng.output_view if eng is not None else False
+        if eng is not None:
+            eng.output_view = True
+        try:
+            self._run_stacks(img, units, owners[rank], channel, max_tokens, is_dst, views)
+        finally:
+            if eng is not None:
+                eng.output_view = view0
+        if self.record_events:
+            self.events['compute_end'] = torch.cuda.Event(enable_timing=True)
+            self.events['compute_end'].record()
+        if world > 1:
+            bufs = exchange_flat(send, units, owners, 1, channel, img.dtype, img.device, self.dst, self.group)
+            for r, buf in bufs.items():
+                for u, core in flat_views(buf, units, owners[r], 1, channel).items():
+                    q = units[u]
+                    crop_place(core, 0, 0, self.output[q["sample"]:q["sample"] + 1], q["out_y0"], q["out_x0"],
+                               core.shape[2], core.shape[3])
+
+    def _run_stacks(self, img, units, mine, channel, max_tokens, is_dst, views):
+        with torch.no_grad():
+            stacks = [((th, tw), part) for (th, tw), idxs in group_by_shape(units, mine).items()
+                      for part in split_stacks(idxs, th, tw, 1, max_tokens)]
+            for (th, tw), idxs in stacks:
+                stack = torch.empty((len(idxs), channel, th, tw), dtype=img.dtype, device=img.device)
+                for k, u in enumerate(idxs):        # extract (hat_model.py:77): one strided copy kernel per unit
+                    r = units[u]
+                    crop_place(img[r["sample"]:r["sample"] + 1], r["in_y0"], r["in_x0"], stack[k:k + 1], 0, 0, th, tw)
+                out = self.net_g(stack)
+                for k, u in enumerate(idxs):        # crop the padding off and place (hat_model.py:106-108)
+                    r = units[u]
+                    rh, rw = r["out_y1"] - r["out_y0"], r["out_x1"] - r["out_x0"]
+                    if is_dst:
+                        crop_place(out[k:k + 1], r["crop_y0"], r["crop_x0"], self.output[r["sample"]:r["sample"] + 1],
+                                   r["out_y0"], r["out_x0"], rh, rw)
+                    else:
+                        crop_place(out[k:k + 1], r["crop_y0"], r["crop_x0"], views[u], 0, 0, rh, rw)
 
     def post_process(self):                         # hat_model.py:110-112
         if self.output is None:

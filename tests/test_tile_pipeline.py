@@ -88,11 +88,12 @@ def test_split_stacks_caps_the_stacked_forward():
             assert len(p) * th * tw <= HM.DEFAULT_STACK_TOKENS < HM.MAX_FORWARD_TOKENS
         seen += idxs
     assert sorted(seen) == list(range(64))
-    assert [len(p) for p in HM.split_stacks(groups[(320, 320)], 320, 320, 1)] == [10, 10, 10, 6]
+    assert [len(p) for p in HM.split_stacks(groups[(320, 320)], 320, 320, 1, 1 << 20)] == [10, 10, 10, 6]
+    assert [len(p) for p in HM.split_stacks(groups[(320, 320)], 320, 320, 1, 1 << 18)] == [2] * 18
     # a single tile that is larger than the cap still gets its own forward (the C library then checks the hard limit)
     assert HM.split_stacks([0, 1], 1024, 1024, 2, max_tokens=1 << 20) == [[0], [1]]
     # 2560x2560 at 512/32 (576x576 interior tiles, the shipped HAT_tile_example geometry): 3 per stack
-    assert [len(p) for p in HM.split_stacks(list(range(9)), 576, 576, 1)] == [3, 3, 3]
+    assert [len(p) for p in HM.split_stacks(list(range(9)), 576, 576, 1, 1 << 20)] == [3, 3, 3]
 
 
 def _rank0_only_worker(rank, world, port, q):

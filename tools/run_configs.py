@@ -1,13 +1,16 @@
-"""Measure the BASELINE.json configurations other than the bench one (configs[2], [3], [4]) and print one JSON line
-each.  Under torchrun the tiled configurations shard their tiles over the ranks (HATModel.tile_process).
+"""Measure the BASELINE.json configurations other than the bench one (configs[2], [3], [4]) as SURVEY.md 8(d) restates
+them, and print one JSON line each.  Under torchrun the tiled configurations shard their (tile, image) units over the
+ranks (HATModel.tile_process) and gather the HR cores to rank 0 inside the timed region.
 
-    python tools/run_configs.py                       # 1 GPU
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/run_configs.py
+    python tools/run_configs.py [--cpu]              # 1 GPU (--cpu: add the CPU figure of configs[4], ~1 min)
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29533 tools/run_configs.py
 
-configs[2]  HAT SRx2 / SRx3 forward on a 256x256 LR image (bf16), PSNR of the bf16 path against our fp32 path
-configs[3]  HAT-L SRx4 (12 RHAG) bf16 tiled inference of a 1024x1024 LR image (tile 256, pad 32)
-configs[4]  HAT SRx4 tiled inference of 1024x1024 LR images (4096x4096 = "4K" output), batch sweep
-Random-init weights (randomised state_dict, seed 0), uniform synthetic input; timing with CUDA events, best of 3.
+configs[2]  HAT SRx2 / SRx3 forward on a 256x256 LR image (bf16); parity of these is in tests/test_parity_r2.py
+configs[3]  HAT-L SRx4 (12 RHAG) bf16 tiled inference of a 1024x1024 LR image (tile 256, pad 32; 16 tiles)
+configs[4]  HAT SRx4 bf16, 4K OUTPUT images: 3840x2160 -> LR 540x960, reflect-padded to 544 (hat_model.py:16-26),
+            tile 256 / pad 32 = 12 tiles per image with 224- and 64-wide remainders; batch sweep N = 1..32 images
+Randomised weights (seed 0), uniform synthetic input; CUDA events around HATModel.test on every rank, max over ranks,
+best of 3 after a warm-up (one CUDA graph per stack shape).
 """
 import json
 import math
@@ -70,9 +73,7 @@ def timed(fn, reps=3):
         out = fn()
         e1.record()
         torch.cuda.synchronize()
-        ms = max(e0.elapsed_time(e1), 0.0)
-        wall = (time.perf_counter() - t0) * 1e3
-        ms = max(ms, wall) if world > 1 else ms        # sharded: host-side gather included
+        ms = max(e0.elapsed_time(e1), 0.0)            # device time on this rank's stream (the gather is enqueued on it)
         if world > 1:
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -104,18 +105,49 @@ with torch.no_grad():
                  out_mp_s=round(256 * 256 * s * s / 1e6 / (ms * 1e-3), 2), psnr_bf16_vs_fp32_db=round(psnr(y16, y32, max(1.0, y32.abs().max().item())), 2),
                  n_gpus=1)
             del net
-    # ---- configs[3]: HAT-L x4, 1024x1024 tiled; configs[4]: HAT x4, 4K output tiled ----
-    for name, cfg, nimg in (("configs[3] HAT-L SRx4 (12 RHAG) 1024x1024 LR tiled (256/32), bf16", base(4, 12), 1),
-                            ("configs[4] HAT SRx4 1024x1024 LR -> 4096x4096 tiled (256/32), bf16", base(4), 1),
-                            ("configs[4] HAT SRx4 1024x1024 LR -> 4096x4096 tiled (256/32), bf16", base(4), 2)):
-        net = make_net(cfg)
-        opt = {"network_g": {"window_size": 16}, "scale": 4, "tile": {"tile_size": 256, "tile_pad": 32}}
-        model = HATModel(net, opt, group=dist.group.WORLD if world > 1 else None, dst=0)
-        x = torch.rand(nimg, 3, 1024, 1024, generator=torch.Generator().manual_seed(2)).bfloat16().to(dev)
-        model.test(x)            # warm-up: graphs per tile shape
-        ms, y = timed(lambda: model.test(x), reps=2)
-        emit(config=name, images=nimg, ms=round(ms, 2), out_mp_s=round(nimg * 4096 * 4096 / 1e6 / (ms * 1e-3), 2),
-             n_gpus=world, tiles_per_image=16, out_shape=list(y.shape) if y is not None else None)
-        del net, model
+    # ---- configs[3]: HAT-L x4, one 1024x1024 LR image, tiled ----
+    opt = {"network_g": {"window_size": 16}, "scale": 4, "tile": {"tile_size": 256, "tile_pad": 32}}
+    net = make_net(base(4, 12))
+    model = HATModel(net, opt, group=dist.group.WORLD if world > 1 else None, dst=0)
+    x = torch.rand(1, 3, 1024, 1024, generator=torch.Generator().manual_seed(2)).bfloat16().to(dev)
+    model.test(x)
+    ms, y = timed(lambda: model.test(x))
+    emit(config="configs[3] HAT-L SRx4 (12 RHAG) 1024x1024 LR tiled (256/32), bf16", images=1, ms=round(ms, 2),
+         out_mp_s=round(4096 * 4096 / 1e6 / (ms * 1e-3), 2), n_gpus=world, tiles_per_image=16,
+         out_shape=list(y.shape) if y is not None else None)
+    del net, model
+    # ---- configs[4]: HAT x4, 4K-output images (540x960 LR), batch sweep ----
+    net = make_net(base(4))
+    model = HATModel(net, opt, group=dist.group.WORLD if world > 1 else None, dst=0)
+    for nimg in (1, 2, 4, 8, 16, 32):
+        x = torch.rand(nimg, 3, 540, 960, generator=torch.Generator().manual_seed(3)).bfloat16().to(dev)
+        model.test(x)
+        ms, y = timed(lambda: model.test(x))
+        emit(config="configs[4] HAT SRx4 4K output (3840x2160; LR 540x960 reflect-padded to 544) tiled (256/32), bf16",
+             images=nimg, ms=round(ms, 2), ms_per_image=round(ms / nimg, 2),
+             out_mp_s=round(nimg * 3840 * 2160 / 1e6 / (ms * 1e-3), 2), n_gpus=world, tiles_per_image=12,
+             out_shape=list(y.shape) if y is not None else None)
+        del x, y
+    del net, model
+    # ---- CPU figure for configs[4]: the oracle port of the reference forward on the host cores ----
+    if rank == 0 and "--cpu" in sys.argv:
+        from oracle import hat_oracle as O
+        cfg = base(4)
+        torch.manual_seed(0)
+        sd = {k: v.clone() for k, v in HAT(**cfg).state_dict().items()}
+        threads = os.cpu_count() or 1
+        torch.set_num_threads(threads)
+        # one small tile class timed, the image scaled by processed LR pixels (the forward is local: cost ~ pixels)
+        th, tw = 64, 224
+        t = torch.rand(1, 3, th, tw)
+        O.hat_forward(t[:, :, :16, :16], sd, cfg)
+        t0 = time.perf_counter()
+        O.hat_forward(t, sd, cfg)
+        sec = time.perf_counter() - t0
+        px_image = 774144                       # processed LR pixels per image incl. tile padding
+        sec_image = sec * px_image / (th * tw)
+        emit(config="configs[4] CPU: oracle port of the reference forward, fp32", cores=threads,
+             sample=f"one {th}x{tw} tile timed ({sec:.1f} s), scaled by processed LR pixels to the 12 tiles of an image",
+             s_per_image_scaled=round(sec_image, 1), out_mp_s=round(3840 * 2160 / 1e6 / sec_image, 4))
 if world > 1:
     dist.destroy_process_group()
