@@ -84,6 +84,15 @@ const char* hatb200_param_key(hatb200_handle* h, int i);
 /* Build the packed device copies (allocates; call outside stream capture). */
 int hatb200_pack(hatb200_handle* h, void* stream);
 
+/* Pre-packed weight cache (no reference counterpart: the reference keeps only the fp32 state_dict,
+ * base_model.py:207-252).  The packed device copies are a pure function of (configuration, state_dict):
+ * hatb200_packed_bytes / hatb200_packed_export copy them into a host blob after hatb200_pack, hatb200_pack_import
+ * rebuilds them from such a blob WITHOUT any hatb200_set_param (the caller keys the blob, e.g. by a hash of the
+ * state_dict; a blob of another configuration or library version is rejected with HATB200_EPARAM). */
+int hatb200_packed_bytes(hatb200_handle* h, size_t* out);
+int hatb200_packed_export(hatb200_handle* h, void* host_dst, size_t cap, void* stream);
+int hatb200_pack_import(hatb200_handle* h, const void* host_src, size_t bytes, void* stream);
+
 /* Debug/engineering switches: "tensor_cores" (0/1), "sync_debug" (0/1), "op_timing" (0/1), "strict_tc" (0/1: in the
  * bf16 path a shape that no tcgen05 kernel takes fails with HATB200_EUNSUPPORTED instead of running the CUDA-core
  * kernel). */

@@ -45,6 +45,9 @@ _SIGNATURES = {
     "hatb200_num_params": (C.c_int, [C.c_void_p]),
     "hatb200_param_key": (C.c_char_p, [C.c_void_p, C.c_int]),
     "hatb200_pack": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "hatb200_packed_bytes": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
+    "hatb200_packed_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "hatb200_pack_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "hatb200_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "hatb200_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "hatb200_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,

@@ -102,6 +102,7 @@ struct hatb200_handle {
   int last_launches = 0;
   int last_fallbacks = 0;            // ops of the last bf16 forward that ran on a CUDA-core kernel instead of tcgen05
   std::vector<void*> allocs;
+  std::vector<size_t> alloc_bytes;   // sizes of `allocs` (packed-weight export / import)
   int* err_flag = nullptr;
   // packed weights
   float *conv_first_w = nullptr, *conv_first_b = nullptr;   // [9][IC][C]

@@ -4,14 +4,31 @@
 
 namespace hb {
 
+// The packed copies are a pure function of (configuration, state_dict): hatb200_packed_export / hatb200_pack_import
+// move them through a host blob (the pre-packed weight cache of SURVEY.md 8(f3), keyed by the caller).  Import runs
+// the SAME allocation sequence as a normal pack with every re-layout kernel skipped and every buffer filled from the
+// blob instead, so the handle's pointer structure is built by one code path.
+#define PK_TRY(call) do { if (!import_) HB_TRY(call); } while (0)
+
 struct Packer {
   hatb200_handle* h;
   cudaStream_t st;
+  const uint8_t* import_ = nullptr;   // host blob body (sizes checked against h->alloc_bytes of the export)
+  size_t import_bytes_ = 0, import_off_ = 0;
 
   int alloc(void** out, size_t bytes) {
     if (bytes == 0) bytes = 16;
     HB_CHECK_CUDA(cudaMalloc(out, bytes));
     h->allocs.push_back(*out);
+    h->alloc_bytes.push_back(bytes);
+    if (import_) {
+      HB_REQUIRE(import_off_ + bytes <= import_bytes_, HATB200_EPARAM,
+                 "pack_import: blob ends inside buffer %zu (offset %zu + %zu > %zu): written by another configuration "
+                 "or library version", h->allocs.size() - 1, import_off_, bytes, import_bytes_);
+      HB_CHECK_CUDA(cudaMemcpyAsync(*out, import_ + import_off_, bytes, cudaMemcpyHostToDevice, st));
+      import_off_ += bytes;
+      return 0;
+    }
     HB_CHECK_CUDA(cudaMemsetAsync(*out, 0, bytes, st));
     return 0;
   }
@@ -19,7 +36,7 @@ struct Packer {
     auto it = h->index.find(key);
     HB_REQUIRE(it != h->index.end(), HATB200_EPARAM, "pack: key '%s' is not part of this configuration", key.c_str());
     const ParamRef& p = h->params[it->second];
-    HB_REQUIRE(p.ptr != nullptr, HATB200_EPARAM, "pack: missing key '%s' (call hatb200_set_param first)", key.c_str());
+    HB_REQUIRE(import_ || p.ptr != nullptr, HATB200_EPARAM, "pack: missing key '%s' (call hatb200_set_param first)", key.c_str());
     *out = &p;
     return 0;
   }
@@ -29,7 +46,8 @@ struct Packer {
     const ParamRef* p;
     HB_TRY(get(key, &p));
     HB_TRY(alloc((void**)out, p->numel() * sizeof(float)));
-    return launch_to_f32(p->ptr, p->dtype, *out, p->numel(), st);
+    PK_TRY(launch_to_f32(p->ptr, p->dtype, *out, p->numel(), st));
+    return 0;
   }
   int ln(const std::string& prefix, LNW& w) {
     HB_TRY(vec(prefix + ".weight", &w.g));
@@ -47,16 +65,16 @@ struct Packer {
     int taps = KH * KW;
     w.Np = round_up(O, 64);
     HB_TRY(alloc((void**)&w.w32, (size_t)taps * I * w.Np * sizeof(float)));
-    HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, O, I, taps, w.w32, w.Np, w.Np, st));
+    PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, O, I, taps, w.w32, w.Np, w.Np, st));
     w.Npad = tc_npad(O);
     w.Kpad = kpad_of(I);
     HB_TRY(alloc((void**)&w.w16, (size_t)taps * w.Npad * w.Kpad * sizeof(bf16)));
-    HB_TRY(launch_pack_w_bf16(p->ptr, p->dtype, O, I, taps, w.w16, w.Npad, w.Kpad, 0, I, st));
+    PK_TRY(launch_pack_w_bf16(p->ptr, p->dtype, O, I, taps, w.w16, w.Npad, w.Kpad, 0, I, st));
     HB_TRY(alloc((void**)&w.bias, (size_t)O * sizeof(float)));
     if (!bkey.empty() && has(bkey)) {
       const ParamRef* b;
       HB_TRY(get(bkey, &b));
-      HB_TRY(launch_to_f32(b->ptr, b->dtype, w.bias, (size_t)O, st));
+      PK_TRY(launch_to_f32(b->ptr, b->dtype, w.bias, (size_t)O, st));
     }
     return 0;
   }
@@ -70,7 +88,8 @@ struct Packer {
     HB_TRY(alloc((void**)&w.w16s, (size_t)w.taps() * w.Npad * w.Kpad * sizeof(bf16)));
     HB_TRY(alloc((void**)&w.bias_s, (size_t)w.O * sizeof(float)));
     w.shuffle_r = r;
-    return launch_pack_w_bf16_shuffle(p->ptr, p->dtype, w.O, w.I, w.taps(), r, w.w16s, w.Npad, w.Kpad, w.bias, w.bias_s, st);
+    PK_TRY(launch_pack_w_bf16_shuffle(p->ptr, p->dtype, w.O, w.I, w.taps(), r, w.w16s, w.Npad, w.Kpad, w.bias, w.bias_s, st));
+    return 0;
   }
 
   int esc(const std::string& core, const std::string& plk_key, EscW& e, int C, int pdim, int k) {
@@ -80,7 +99,7 @@ struct Packer {
       const ParamRef* pw;
       HB_TRY(get(plk_key, &pw));
       HB_TRY(alloc((void**)&e.plk_wt, plk_toeplitz_elems() * sizeof(bf16)));
-      HB_TRY(launch_pack_plk_toeplitz(pw->ptr, pw->dtype, e.plk_wt, st));
+      PK_TRY(launch_pack_plk_toeplitz(pw->ptr, pw->dtype, e.plk_wt, st));
     }
     HB_TRY(vec(core + ".plk.dwc_proj.1.weight", &e.w1));
     HB_TRY(vec(core + ".plk.dwc_proj.1.bias", &e.b1));
@@ -97,20 +116,20 @@ struct Packer {
     w.O = 3 * C; w.I = C; w.KH = w.KW = 1;
     w.Np = round_up(3 * C, 64);
     HB_TRY(alloc((void**)&w.w32, (size_t)C * w.Np * sizeof(float)));
-    HB_TRY(launch_pack_w_f32(q->ptr, q->dtype, C, C, 1, w.w32, w.Np, C, st));
-    HB_TRY(launch_pack_w_f32(kv->ptr, kv->dtype, 2 * C, C, 1, w.w32 + C, w.Np, w.Np - C, st));
+    PK_TRY(launch_pack_w_f32(q->ptr, q->dtype, C, C, 1, w.w32, w.Np, C, st));
+    PK_TRY(launch_pack_w_f32(kv->ptr, kv->dtype, 2 * C, C, 1, w.w32 + C, w.Np, w.Np - C, st));
     w.Npad = tc_npad(3 * C);
     w.Kpad = kpad_of(C);
     HB_TRY(alloc((void**)&w.w16, (size_t)w.Npad * w.Kpad * sizeof(bf16)));
-    HB_TRY(launch_pack_w_bf16(q->ptr, q->dtype, C, C, 1, w.w16, C, w.Kpad, 0, C, st));
-    HB_TRY(launch_pack_w_bf16(kv->ptr, kv->dtype, 2 * C, C, 1, w.w16 + (size_t)C * w.Kpad, w.Npad - C, w.Kpad, 0, C, st));
+    PK_TRY(launch_pack_w_bf16(q->ptr, q->dtype, C, C, 1, w.w16, C, w.Kpad, 0, C, st));
+    PK_TRY(launch_pack_w_bf16(kv->ptr, kv->dtype, 2 * C, C, 1, w.w16 + (size_t)C * w.Kpad, w.Npad - C, w.Kpad, 0, C, st));
     HB_TRY(alloc((void**)&w.bias, (size_t)3 * C * sizeof(float)));
     if (has(op + ".q_proj.bias")) {
       const ParamRef *qb, *kvb;
       HB_TRY(get(op + ".q_proj.bias", &qb));
       HB_TRY(get(op + ".kv_proj.bias", &kvb));
-      HB_TRY(launch_to_f32(qb->ptr, qb->dtype, w.bias, (size_t)C, st));
-      HB_TRY(launch_to_f32(kvb->ptr, kvb->dtype, w.bias + C, (size_t)2 * C, st));
+      PK_TRY(launch_to_f32(qb->ptr, qb->dtype, w.bias, (size_t)C, st));
+      PK_TRY(launch_to_f32(kvb->ptr, kvb->dtype, w.bias + C, (size_t)2 * C, st));
     }
     return 0;
   }
@@ -127,15 +146,15 @@ struct Packer {
     w.O = 3 * HP; w.I = C; w.KH = w.KW = 1; w.algoO = 3 * C; w.algoI = C;
     w.Npad = tc_npad(w.O); w.Kpad = kpad_of(C);
     HB_TRY(alloc((void**)&w.w16, (size_t)w.Npad * w.Kpad * sizeof(bf16)));
-    HB_TRY(launch_pack_rows_headpad(q->ptr, q->dtype, C, heads, 1, w.w16, w.Kpad, 0, st));
-    HB_TRY(launch_pack_rows_headpad(kv->ptr, kv->dtype, C, heads, 2, w.w16, w.Kpad, HP, st));
+    PK_TRY(launch_pack_rows_headpad(q->ptr, q->dtype, C, heads, 1, w.w16, w.Kpad, 0, st));
+    PK_TRY(launch_pack_rows_headpad(kv->ptr, kv->dtype, C, heads, 2, w.w16, w.Kpad, HP, st));
     HB_TRY(alloc((void**)&w.bias, (size_t)w.O * sizeof(float)));
     if (has(op + ".q_proj.bias")) {
       const ParamRef *qb, *kvb;
       HB_TRY(get(op + ".q_proj.bias", &qb));
       HB_TRY(get(op + ".kv_proj.bias", &kvb));
-      HB_TRY(launch_pack_vec_headpad(qb->ptr, qb->dtype, C, heads, 1, w.bias, 0, st));
-      HB_TRY(launch_pack_vec_headpad(kvb->ptr, kvb->dtype, C, heads, 2, w.bias, HP, st));
+      PK_TRY(launch_pack_vec_headpad(qb->ptr, qb->dtype, C, heads, 1, w.bias, 0, st));
+      PK_TRY(launch_pack_vec_headpad(kvb->ptr, kvb->dtype, C, heads, 2, w.bias, HP, st));
     }
     if (h->cfg.ocab_esc_enable) {    // q and k/v come from different inputs (hat_arch.py:336-351): two head-padded GEMMs
       const ParamRef* srcs[2] = {q, kv};
@@ -147,12 +166,12 @@ struct Packer {
         t.O = nblk * HP; t.I = C; t.KH = t.KW = 1; t.algoO = nblk * C; t.algoI = C;
         t.Npad = tc_npad(t.O); t.Kpad = kpad_of(C);
         HB_TRY(alloc((void**)&t.w16, (size_t)t.Npad * t.Kpad * sizeof(bf16)));
-        HB_TRY(launch_pack_rows_headpad(srcs[i]->ptr, srcs[i]->dtype, C, heads, nblk, t.w16, t.Kpad, 0, st));
+        PK_TRY(launch_pack_rows_headpad(srcs[i]->ptr, srcs[i]->dtype, C, heads, nblk, t.w16, t.Kpad, 0, st));
         HB_TRY(alloc((void**)&t.bias, (size_t)t.O * sizeof(float)));
         if (has(op + bkeys[i])) {
           const ParamRef* b;
           HB_TRY(get(op + bkeys[i], &b));
-          HB_TRY(launch_pack_vec_headpad(b->ptr, b->dtype, C, heads, nblk, t.bias, 0, st));
+          PK_TRY(launch_pack_vec_headpad(b->ptr, b->dtype, C, heads, nblk, t.bias, 0, st));
         }
       }
     }
@@ -160,10 +179,11 @@ struct Packer {
     pj.O = C; pj.I = HP; pj.KH = pj.KW = 1; pj.algoO = C; pj.algoI = C;
     pj.Npad = tc_npad(C); pj.Kpad = kpad_of(HP);
     HB_TRY(alloc((void**)&pj.w16, (size_t)pj.Npad * pj.Kpad * sizeof(bf16)));
-    HB_TRY(launch_pack_cols_headpad(pr->ptr, pr->dtype, C, C, heads, pj.w16, pj.Npad, pj.Kpad, st));
+    PK_TRY(launch_pack_cols_headpad(pr->ptr, pr->dtype, C, C, heads, pj.w16, pj.Npad, pj.Kpad, st));
     pj.bias = o.proj.bias;
     HB_TRY(alloc((void**)&o.bias_l2, (size_t)heads * ATTN_TC_BIAS_FLOATS * sizeof(float)));
-    return launch_bias_l2(o.bias_compact, heads, ws, ows, o.bias_l2, st);
+    PK_TRY(launch_bias_l2(o.bias_compact, heads, ws, ows, o.bias_l2, st));
+    return 0;
   }
 
   int run() {
@@ -176,7 +196,7 @@ struct Packer {
     {  // conv_first: (C, IC, 3, 3) -> [9][IC][C]
       HB_TRY(get("conv_first.weight", &p));
       HB_TRY(alloc((void**)&h->conv_first_w, (size_t)9 * c.in_chans * C * sizeof(float)));
-      HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, C, c.in_chans, 9, h->conv_first_w, C, C, st));
+      PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, C, c.in_chans, 9, h->conv_first_w, C, C, st));
       HB_TRY(vec("conv_first.bias", &h->conv_first_b));
     }
     if (c.patch_norm) HB_TRY(ln("patch_embed.norm", h->pe_norm));
@@ -200,7 +220,7 @@ struct Packer {
         HB_TRY(conv(bp + ".mlp.fc2", b.fc2, C, hid, 1, 1));
         HB_TRY(get(bp + ".mlp.dw.weight", &p));
         HB_TRY(alloc((void**)&b.dw_w, (size_t)9 * 2 * hid * sizeof(float)));
-        HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, 2 * hid, 1, 9, b.dw_w, 2 * hid, 2 * hid, st));
+        PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, 2 * hid, 1, 9, b.dw_w, 2 * hid, 2 * hid, st));
         HB_TRY(vec(bp + ".mlp.dw.bias", &b.dw_b));
       }
       OcabW& o = lw.ocab;
@@ -220,7 +240,7 @@ struct Packer {
       int T = ws + ows - 1;
       HB_TRY(get(op + ".relative_position_bias_table", &p));
       HB_TRY(alloc((void**)&o.bias_compact, (size_t)o.heads * T * T * sizeof(float)));
-      HB_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
+      PK_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
                                    h->err_flag, st));
       if (ws == 16 && ows == 24) HB_TRY(ocab_tc(op, o, C, ws, ows));
       if (c.resi_conv) HB_TRY(conv(lp + ".conv", lw.conv, C, C, 3, 3));
@@ -239,11 +259,17 @@ struct Packer {
       }
       HB_TRY(get("conv_last.weight", &p));
       HB_TRY(alloc((void**)&h->conv_last_w, (size_t)9 * 64 * c.in_chans * sizeof(float)));
-      HB_TRY(launch_pack_w_f32(p->ptr, p->dtype, c.in_chans, 64, 9, h->conv_last_w, c.in_chans, c.in_chans, st));
+      PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, c.in_chans, 64, 9, h->conv_last_w, c.in_chans, c.in_chans, st));
       HB_TRY(vec("conv_last.bias", &h->conv_last_b));
       HB_TRY(conv("conv_last", h->conv_last_tc, c.in_chans, 64, 3, 3));
     }
     int flag = 0;
+    if (import_) {
+      HB_CHECK_CUDA(cudaStreamSynchronize(st));      // the blob may be freed by the caller after this returns
+      HB_REQUIRE(import_off_ == import_bytes_, HATB200_EPARAM, "pack_import: blob has %zu bytes, this configuration packs %zu",
+                 import_bytes_, import_off_);
+      return 0;
+    }
     HB_CHECK_CUDA(cudaMemcpyAsync(&flag, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
     HB_CHECK_CUDA(cudaStreamSynchronize(st));
     HB_REQUIRE(flag == 0, HATB200_EUNSUPPORTED,
@@ -256,16 +282,77 @@ struct Packer {
 
 }  // namespace hb
 
+static void pack_reset(hatb200_handle* h) {
+  for (void* p : h->allocs) cudaFree(p);
+  h->allocs.clear();
+  h->alloc_bytes.clear();
+  h->layers.clear();
+  h->packed = false;
+}
+
 extern "C" int hatb200_pack(hatb200_handle* h, void* stream) {
   HB_REQUIRE(h, HATB200_EINVAL, "pack: null handle");
   HB_CHECK_CUDA(cudaSetDevice(h->device));
-  for (void* p : h->allocs) cudaFree(p);
-  h->allocs.clear();
-  h->layers.clear();
-  h->packed = false;
+  pack_reset(h);
   hb::Packer pk{h, (cudaStream_t)stream};
   int r = pk.run();
   if (r != 0) return r;
+  h->packed = true;
+  return 0;
+}
+
+// ---- pre-packed weight cache: blob = header {magic, version, struct size, buffer count, body bytes}
+// + the packed buffers in allocation order ------------------------------------------------------------------------
+namespace {
+struct PackBlobHeader { uint32_t magic, version, cfg_size, count; uint64_t body; };
+constexpr uint32_t kPackMagic = 0x4b504248u;   // "HBPK"
+}
+
+extern "C" int hatb200_packed_bytes(hatb200_handle* h, size_t* out) {
+  HB_REQUIRE(h && out, HATB200_EINVAL, "packed_bytes: null argument");
+  HB_REQUIRE(h->packed, HATB200_EPARAM, "packed_bytes: weights are not packed");
+  size_t n = sizeof(PackBlobHeader);
+  for (size_t b : h->alloc_bytes) n += b;
+  *out = n;
+  return 0;
+}
+
+extern "C" int hatb200_packed_export(hatb200_handle* h, void* host_dst, size_t cap, void* stream) {
+  HB_REQUIRE(h && host_dst, HATB200_EINVAL, "packed_export: null argument");
+  HB_REQUIRE(h->packed, HATB200_EPARAM, "packed_export: weights are not packed");
+  size_t body = 0;
+  for (size_t b : h->alloc_bytes) body += b;
+  HB_REQUIRE(cap >= sizeof(PackBlobHeader) + body, HATB200_ENOMEM, "packed_export: buffer of %zu bytes, %zu needed", cap,
+             sizeof(PackBlobHeader) + body);
+  PackBlobHeader hd{kPackMagic, (uint32_t)HATB200_VERSION, (uint32_t)sizeof(hatb200_config), (uint32_t)h->allocs.size(), body};
+  memcpy(host_dst, &hd, sizeof(hd));
+  uint8_t* dst = (uint8_t*)host_dst + sizeof(hd);
+  cudaStream_t st = (cudaStream_t)stream;
+  for (size_t i = 0; i < h->allocs.size(); i++) {
+    HB_CHECK_CUDA(cudaMemcpyAsync(dst, h->allocs[i], h->alloc_bytes[i], cudaMemcpyDeviceToHost, st));
+    dst += h->alloc_bytes[i];
+  }
+  HB_CHECK_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int hatb200_pack_import(hatb200_handle* h, const void* host_src, size_t bytes, void* stream) {
+  HB_REQUIRE(h && host_src, HATB200_EINVAL, "pack_import: null argument");
+  HB_REQUIRE(bytes >= sizeof(PackBlobHeader), HATB200_EPARAM, "pack_import: blob of %zu bytes has no header", bytes);
+  PackBlobHeader hd;
+  memcpy(&hd, host_src, sizeof(hd));
+  HB_REQUIRE(hd.magic == kPackMagic && hd.version == (uint32_t)HATB200_VERSION && hd.cfg_size == sizeof(hatb200_config) &&
+                 hd.body == bytes - sizeof(hd),
+             HATB200_EPARAM, "pack_import: not a packed-weight blob of this library version");
+  HB_CHECK_CUDA(cudaSetDevice(h->device));
+  pack_reset(h);
+  hb::Packer pk{h, (cudaStream_t)stream};
+  pk.import_ = (const uint8_t*)host_src + sizeof(hd);
+  pk.import_bytes_ = (size_t)hd.body;
+  int r = pk.run();
+  if (r != 0) { pack_reset(h); return r; }
+  HB_REQUIRE(h->allocs.size() == hd.count, HATB200_EPARAM, "pack_import: blob holds %u buffers, this configuration packs %zu",
+             hd.count, h->allocs.size());
   h->packed = true;
   return 0;
 }

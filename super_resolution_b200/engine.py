@@ -53,6 +53,10 @@ class Engine:
         self._bound = None             # tensors borrowed by the handle (kept alive)
         self._sample = None            # staleness probe over every bound tensor
         self._probe_tensors = []
+        # pre-packed weight cache: directory of blobs keyed by a hash of (configuration, state_dict);
+        # None disables it.  A hit skips every hatb200_set_param and all re-layout kernels of hatb200_pack.
+        self.pack_cache_dir = os.environ.get("HATB200_PACK_CACHE") or None
+        self.pack_cache_hit = None     # True / False after a (re)bind with the cache enabled
         self.output_view = False       # True: graphed forwards return the graph's own output buffer (valid until the
                                        # next forward of the same shape) instead of a fresh copy of it
         self.last_fallback_count = 0
@@ -113,6 +117,22 @@ class Engine:
         if self._bound is not None and self._probe() == self._sample:
             return
         sd = m.state_dict(keep_vars=True)
+        stream = torch.cuda.current_stream(device)
+        cache_file = self._cache_file(sd) if self.pack_cache_dir else None
+        if cache_file is not None and os.path.exists(cache_file):
+            blob = open(cache_file, "rb").read()
+            rc = self.lib.hatb200_pack_import(self.handle, blob, len(blob), C.c_void_p(stream.cuda_stream))
+            if rc == 0:
+                for k, v in sd.items():
+                    if v.device != device:
+                        raise RuntimeError(f"parameter '{k}' is on {v.device} but the input is on {device}")
+                self.pack_cache_hit = True
+                self._bound = {}
+                self._probe_tensors = list(sd.values())
+                self._sample = self._probe()
+                self._graphs = {}
+                return
+            # a stale or foreign blob: fall through to a normal pack (and overwrite it)
         bound = {}
         for k, v in sd.items():
             t = v.detach()
@@ -125,12 +145,33 @@ class Engine:
             _lib.check(self.lib.hatb200_set_param(self.handle, k.encode(), C.c_void_p(t.data_ptr()),
                                                   _lib.dtype_code(t.dtype), shape, t.dim()))
             bound[k] = t
-        stream = torch.cuda.current_stream(device)
         _lib.check(self.lib.hatb200_pack(self.handle, C.c_void_p(stream.cuda_stream)))
+        if cache_file is not None:
+            self.pack_cache_hit = False
+            need = C.c_size_t()
+            _lib.check(self.lib.hatb200_packed_bytes(self.handle, C.byref(need)))
+            buf = C.create_string_buffer(need.value)
+            _lib.check(self.lib.hatb200_packed_export(self.handle, buf, need.value, C.c_void_p(stream.cuda_stream)))
+            os.makedirs(self.pack_cache_dir, exist_ok=True)
+            tmp = f"{cache_file}.{os.getpid()}.tmp"
+            with open(tmp, "wb") as f:
+                f.write(buf.raw)
+            os.replace(tmp, cache_file)           # atomic: concurrent ranks write identical content
         self._bound = bound
         self._probe_tensors = list(sd.values())
         self._sample = self._probe()
         self._graphs = {}
+
+    def _cache_file(self, sd):
+        """<pack_cache_dir>/<sha256 of configuration + every state_dict entry (key, dtype, shape, bytes)>.hbpk"""
+        import hashlib
+        hsh = hashlib.sha256()
+        hsh.update(bytes(_config_from_module(self.module)))
+        for k, v in sd.items():
+            t = v.detach()
+            hsh.update(f"{k}|{t.dtype}|{tuple(t.shape)}|".encode())
+            hsh.update(t.contiguous().cpu().view(torch.uint8).numpy().tobytes() if t.numel() else b"")
+        return os.path.join(self.pack_cache_dir, hsh.hexdigest() + ".hbpk")
 
     # -- forward ----------------------------------------------------------------
     def _workspace(self, B, H, W, code, device):

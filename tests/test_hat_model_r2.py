@@ -117,3 +117,37 @@ def test_nondist_validation_matches_the_reference_pipeline(tmp_path, tile):
     assert model.metric_results["psnr"] == pytest.approx(want["psnr"], rel=1e-4)
     assert model.metric_results["ssim"] == pytest.approx(want["ssim"], rel=1e-4)
     assert model.best_metric_results["Set2"]["psnr"]["iter"] == 7
+
+
+@pytest.mark.gpu
+def test_packed_weight_cache_keyed_by_state_dict_hash(tmp_path):
+    """f3: the packed (bf16 / tcgen05-layout) weight copies as a blob on disk keyed by the state_dict hash; a hit
+    rebuilds the handle without set_param / re-layout kernels and the forward is bit-identical; other weights miss."""
+    from super_resolution_b200 import HAT
+    cfg, sd, x, y_ref = load_case("mini_x4_32x32")
+    xd = x.to("cuda:0")
+
+    def net_with(sd_, cache):
+        net = HAT(**cfg).eval()
+        net.load_state_dict(sd_, strict=True)
+        net = net.to("cuda:0")
+        net.engine().pack_cache_dir = str(cache) if cache else None
+        return net
+
+    base = net_with(sd, None)
+    y0, y0b = base(xd), base(xd.bfloat16())
+    first = net_with(sd, tmp_path)
+    assert torch.equal(first(xd), y0) and first.engine().pack_cache_hit is False
+    files = list(tmp_path.glob("*.hbpk"))
+    assert len(files) == 1 and files[0].stat().st_size > 100000
+    second = net_with(sd, tmp_path)
+    assert torch.equal(second(xd), y0) and second.engine().pack_cache_hit is True
+    assert torch.equal(second(xd.bfloat16()), y0b)
+    sd2 = {k: (v * 1.01 if k == "conv_last.weight" else v) for k, v in sd.items()}
+    third = net_with(sd2, tmp_path)
+    assert not torch.equal(third(xd), y0) and third.engine().pack_cache_hit is False
+    assert len(list(tmp_path.glob("*.hbpk"))) == 2
+    # a truncated / foreign blob is rejected by the library and silently repacked
+    files[0].write_bytes(files[0].read_bytes()[:5000])
+    fourth = net_with(sd, tmp_path)
+    assert torch.equal(fourth(xd), y0) and fourth.engine().pack_cache_hit is False

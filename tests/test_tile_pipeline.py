@@ -173,6 +173,69 @@ def _worker(rank, world, port, geom, q):
         dist.destroy_process_group()
 
 
+def _unit_worker(rank, world, port, geom, batch, q):
+    """tile_process's own exchange (units = one tile of one sample, flat send buffer, exchange_flat, flat_views)."""
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        h, w, ts, tp, s = geom
+        rects = O.tile_rects(h, w, ts, tp, s)
+        units = [dict(rects[i], tile=i, sample=b) for i in range(len(rects)) for b in range(batch)]
+        owners = HM.shard_tiles(units, world)
+        assert sorted(sum(owners, [])) == list(range(len(units)))
+        val = lambda u: torch.arange(torch.Size(HM.core_shape(units[u], 1, 3)).numel(), dtype=torch.float32).view(
+            HM.core_shape(units[u], 1, 3)) * 1e-3 + u
+        send = None
+        if rank != 0:
+            send = torch.empty(HM.flat_numel(units, owners[rank], 1, 3))
+            for u, view in HM.flat_views(send, units, owners[rank], 1, 3).items():
+                view.copy_(val(u))
+        bufs = HM.exchange_flat(send, units, owners, 1, 3, torch.float32, torch.device("cpu"), dst=0)
+        if rank == 0:
+            ok = sorted(bufs) == [r for r in range(1, world) if owners[r]]
+            for r, buf in bufs.items():
+                for u, core in HM.flat_views(buf, units, owners[r], 1, 3).items():
+                    ok = ok and torch.equal(core, val(u))
+            q.put(bool(ok))
+        else:
+            q.put(bufs == {})
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("geom,batch", [((96, 128, 32, 16, 2), 1), ((64, 80, 32, 16, 4), 3), ((544, 960, 256, 32, 4), 4)])
+def test_unit_exchange_world2_gloo(geom, batch):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_unit_worker, args=(r, 2, port, geom, batch, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(res)
+
+
+def test_shape_aware_plans():
+    """configs[3] at 8 ranks: every rank gets a same-shape pair (one stacked forward); a batch of 4K-output images
+    (more than 32 units) is partitioned shape-major so that a rank holds few shapes."""
+    rects = O.tile_rects(1024, 1024, 256, 32, 4)
+    shape = lambda r: (r["in_y1"] - r["in_y0"], r["in_x1"] - r["in_x0"])
+    owners = HM.shard_tiles(rects, 8)
+    assert all(len(o) == 2 and shape(rects[o[0]]) == shape(rects[o[1]]) for o in owners)
+    rects = O.tile_rects(544, 960, 256, 32, 4)
+    units = [dict(rects[i], tile=i, sample=b) for i in range(len(rects)) for b in range(8)]
+    owners = HM.shard_tiles(units, 8)
+    assert sorted(sum(owners, [])) == list(range(96))
+    area = lambda o: sum(shape(units[i])[0] * shape(units[i])[1] for i in o)
+    assert max(area(o) for o in owners) <= 1.1 * sum(area(o) for o in owners) / 8
+    assert max(len({shape(units[i]) for i in o}) for o in owners) <= 4
+    assert owners == HM.shard_tiles(units, 8)
+
+
 @pytest.mark.parametrize("geom", [(96, 128, 32, 16, 2), (64, 64, 64, 16, 4)])
 def test_gather_cores_world2_gloo(geom):
     import torch.multiprocessing as mp
