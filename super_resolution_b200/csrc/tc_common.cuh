@@ -58,6 +58,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Relaxed wait for warps that expect to wait long (an epilogue warpgroup waiting for the next accumulator, a ring
+// producer waiting for a free stage): back off with nanosleep between polls so that the polling loop does not take
+// issue slots from the warps that are doing the work on the same scheduler.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, unsigned ns = 64) {
+  if (mbar_try_wait(bar, parity)) return;
+  long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    if (clock64() - t0 > 4000000000ll) {
+      printf("libhatb200: mbarrier wait timed out (block %d,%d thread %d parity %u)\n", blockIdx.x, blockIdx.y,
+             threadIdx.x, parity);
+      __trap();
+    }
+  }
+}
+
 // Raw shared-window addresses: the single MMA-issuing thread keeps its barrier addresses in registers and steps
 // them by 8 -- converting `&bar[s]` in the loop costs an S2UR (cluster CTA id) plus address arithmetic per use.
 __device__ __forceinline__ bool mbar_try_wait_a(uint32_t addr, uint32_t parity) {

@@ -187,13 +187,13 @@ ffn2_tc_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         for (int j = 0; j < p.nchunks; j++) {
           {
             const int s = wp.s;
-            mbar_wait(&w_empty[s], wp.ph ^ 1u);
+            if (p.dbg & 8) mbar_wait(&w_empty[s], wp.ph ^ 1u); else mbar_wait_relaxed(&w_empty[s], wp.ph ^ 1u);
             mbar_arrive_expect_tx(&w_full[s], w_bytes);
             tma_load_2d(smem + p.off_w + (size_t)s * p.w_stage_bytes, &tmW, &w_full[s], j * FF_CK, 0);
             wp.next(p.wst);
           }
           const int s = sp.s;
-          mbar_wait(&stg_empty[s], sp.ph ^ 1u);
+          if (p.dbg & 8) mbar_wait(&stg_empty[s], sp.ph ^ 1u); else mbar_wait_relaxed(&stg_empty[s], sp.ph ^ 1u);
           uint8_t* dst = smem + p.off_stg + (size_t)s * FF_STAGE;
           if (p.dbg & 4) { mbar_arrive(&stg_full[s]); sp.next(p.st); continue; }
           mbar_arrive_expect_tx(&stg_full[s], stg_bytes);
@@ -215,7 +215,7 @@ ffn2_tc_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         tc_fence_after();
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
         for (int j = 0; j < p.nchunks; j++) {
-          mbar_wait(&g_full[gp.s], gp.ph);
+          if (p.dbg & 8) mbar_wait(&g_full[gp.s], gp.ph); else mbar_wait_relaxed(&g_full[gp.s], gp.ph, 32);
           mbar_wait(&w_full[wp.s], wp.ph);
           tc_fence_after();
           const uint64_t ad = make_smem_desc(smem_u32(smem + p.off_g + (size_t)gp.s * FF_GT), 64);
@@ -282,7 +282,8 @@ ffn2_tc_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
       ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
       const bool tr = ws.wg_tid == 0 && i < 4;
       if (tr) FF_TRACE(16 + 4 * i);
-      mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
+      if (p.dbg & 8) mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
+      else mbar_wait_relaxed(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u, 128);
       tc_fence_after();
       if (tr) FF_TRACE(17 + 4 * i);
       if (!(p.dbg & 2)) run_tile<FeatResLn, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOF, &tmLN);
