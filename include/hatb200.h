@@ -62,6 +62,12 @@ typedef struct hatb200_config {
   float img_range;                /* hat_arch.py:850 */
   float qk_scale;                 /* <=0: head_dim^-0.5 (hat_arch.py:288) */
   float mean[4];                  /* hat_arch.py:658-662 */
+  /* sibling variant HATX (HAT/hat/archs/hatx_arch.py:708-975); all zero for HAT */
+  int32_t arch;                   /* 0 = HAT, 1 = HATX: HAB uses the spatial-gate FFN (hatx_arch.py:144-180) */
+  int32_t ocab_pad;               /* unfold padding of the OCAB key window: (ows-ws)/2 for HAT (hat_arch.py:296-297),
+                                     ceil((ows-ws)/2) for HATX (hatx_arch.py:316-322) */
+  int32_t kv_topk_keep;           /* HATX: keys kept per window, max(1, int(kv_topk_ratio * ows^2)); 0 = no pruning */
+  int32_t use_focus_bias;         /* HATX: focus head + tanh bias on the logits (hatx_arch.py:405-415) */
 } hatb200_config;
 
 typedef struct hatb200_handle hatb200_handle;

@@ -192,15 +192,28 @@ def gated_dconv_ffn(x, sd, prefix, h, w):
     return F.linear(t, sd[prefix + ".fc2.weight"], sd[prefix + ".fc2.bias"])
 
 
+def spatial_gate_ffn(x, sd, prefix, h, w):
+    """SpatialGateDConvFFN.forward of the sibling HATX, hatx_arch.py:160-180: fc1 -> split in halves (xa | xb) ->
+    depthwise 3x3 on xa only -> cat[xa * SiLU(xb), xb] -> fc2."""
+    t = F.linear(x, sd[prefix + ".fc1.weight"], sd[prefix + ".fc1.bias"])
+    c2 = t.shape[-1] // 2
+    xa = _to_img(t[..., :c2], h, w)
+    xb = t[..., c2:]
+    xa = _to_tok(F.conv2d(xa, sd[prefix + ".dw.weight"], sd[prefix + ".dw.bias"], padding=1, groups=c2))
+    t = torch.cat([xa * F.silu(xb), xb], dim=-1)
+    return F.linear(t, sd[prefix + ".fc2.weight"], sd[prefix + ".fc2.bias"])
+
+
 def hab(x, sd, prefix, h, w, cfg):
-    """HAB.forward, hat_arch.py:217-238 (drop_path is identity in eval)."""
+    """HAB.forward, hat_arch.py:217-238 (drop_path is identity in eval); HATX: hatx_arch.py:232-255 (SGFN)."""
     shortcut = x
     xn = _ln(x, sd, prefix + ".norm1")
     conv_x = _to_tok(cab(_to_img(xn, h, w), sd, prefix + ".conv_block"))
     attn_x = _to_tok(conv_attn(_to_img(xn, h, w), sd, prefix + ".esc_attn.core",
                                sd[prefix + ".esc_attn.plk_filter"], cfg["esc_pdim"]))
     x = shortcut + attn_x + conv_x * cfg["conv_scale"]
-    return x + gated_dconv_ffn(_ln(x, sd, prefix + ".norm2"), sd, prefix + ".mlp", h, w)
+    ffn = spatial_gate_ffn if cfg.get("arch") == "HATX" else gated_dconv_ffn
+    return x + ffn(_ln(x, sd, prefix + ".norm2"), sd, prefix + ".mlp", h, w)
 
 
 def ocab_bias(sd, prefix, rpi, nq, nk):
@@ -229,8 +242,10 @@ def ocab(x, sd, prefix, h, w, cfg, heads):
     nwy, nwx = h // ws, w // ws
     # window_partition (hat_arch.py:124-128)
     qw = q.view(b, nwy, ws, nwx, ws, c).permute(0, 1, 3, 2, 4, 5).reshape(b * nwy * nwx, ws * ws, c)
-    # nn.Unfold(ows, stride ws, pad (ows-ws)//2) over (B, 2C, H, W), hat_arch.py:359-364
-    kvu = F.unfold(_to_img(kv, h, w), kernel_size=ows, stride=ws, padding=(ows - ws) // 2)
+    # nn.Unfold(ows, stride ws, pad (ows-ws)//2) over (B, 2C, H, W), hat_arch.py:359-364; HATX pads by the CEILING
+    # (hatx_arch.py:316-322: overlap_ratio 0.6 gives a 25-wide window, 5 before and 4 after)
+    pad = (ows - ws + 1) // 2 if cfg.get("arch") == "HATX" else (ows - ws) // 2
+    kvu = F.unfold(_to_img(kv, h, w), kernel_size=ows, stride=ws, padding=pad)
     kvu = kvu.view(b, 2, c, ows * ows, nwy * nwx).permute(1, 0, 4, 3, 2).reshape(2, b * nwy * nwx, ows * ows, c)
     kw, vw = kvu[0], kvu[1]
     nb = qw.shape[0]
@@ -238,6 +253,8 @@ def ocab(x, sd, prefix, h, w, cfg, heads):
     kh = kw.view(nb, ows * ows, heads, d).permute(0, 2, 1, 3)
     vh = vw.view(nb, ows * ows, heads, d).permute(0, 2, 1, 3)
     attn = qh @ kh.transpose(-2, -1)
+    if cfg.get("arch") == "HATX":
+        attn = hatx_focus(attn, kw, y, sd, prefix, h, w, cfg, ows, pad)
     attn = attn + ocab_bias(sd, prefix, sd["relative_position_index_OCA"], ws * ws, ows * ows)[None]
     attn = torch.softmax(attn, dim=-1)
     o = (attn @ vh).transpose(1, 2).reshape(nb, ws * ws, c)
@@ -247,6 +264,36 @@ def ocab(x, sd, prefix, h, w, cfg, heads):
     m = F.linear(_ln(x, sd, prefix + ".norm2"), sd[prefix + ".mlp.0.weight"], sd[prefix + ".mlp.0.bias"])
     m = F.linear(F.gelu(m), sd[prefix + ".mlp.2.weight"], sd[prefix + ".mlp.2.bias"])
     return x + m
+
+
+def topk_keep_mask(score, k_keep):
+    """Keep the k_keep keys with the largest score; ties at the threshold are broken by the LOWER key index.  (The
+    reference calls torch.topk(sorted=False), hatx_arch.py:430, whose choice among equal scores is unspecified; equal
+    scores occur only among zero-padded keys, whose score is exactly 0 / tanh(0).)  score: (nb, nk) -> bool (nb, nk)."""
+    nk = score.shape[1]
+    order = torch.sort(score, dim=1, descending=True, stable=True).indices      # stable: equal scores keep index order
+    keep = torch.zeros_like(score, dtype=torch.bool)
+    keep.scatter_(1, order[:, :k_keep], True)
+    return keep
+
+
+def hatx_focus(attn, kw, y, sd, prefix, h, w, cfg, ows, pad):
+    """OCAB 'focus' options of HATX, hatx_arch.py:405-441: optional per-key focus bias tanh(focus_head(y)) added to the
+    logits, optional top-k key pruning (score = focus bias if present, else ||k||_2) with -1e4 on the pruned keys."""
+    ws = cfg["window_size"]
+    nb, nk = kw.shape[0], kw.shape[1]
+    focus = None
+    if cfg.get("use_focus_bias", False):
+        sal = _conv(F.gelu(_conv(_to_img(y, h, w), sd, prefix + ".focus_head.0", 0)), sd, prefix + ".focus_head.2", 0)
+        focus = torch.tanh(F.unfold(sal, kernel_size=ows, stride=ws, padding=pad).transpose(1, 2).reshape(nb, nk))
+        attn = attn + focus.view(nb, 1, 1, nk)
+    ratio = float(cfg.get("kv_topk_ratio", 1.0))
+    if ratio < 1.0:
+        k_keep = max(1, int(ratio * nk))
+        score = focus if focus is not None else torch.linalg.vector_norm(kw, ord=2, dim=-1)
+        keep = topk_keep_mask(score, k_keep)
+        attn = attn.masked_fill(~keep.view(nb, 1, 1, nk), -1e4)
+    return attn
 
 
 def rhag(x, sd, prefix, h, w, cfg, depth, heads):

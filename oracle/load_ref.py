@@ -49,6 +49,26 @@ def load_reference_hat():
     return mods["hat_arch"]
 
 
+def load_reference_hatx():
+    """Return the reference module `hat.archs.hatx_arch` (class `HATX`, the sibling variant of SURVEY.md 8(f4))."""
+    load_reference_hat()
+    full = "hat.archs.hatx_arch"
+    if full in sys.modules:
+        return sys.modules[full]
+    spec = importlib.util.spec_from_file_location(full, os.path.join(_ARCH_DIR, "hatx_arch.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[full] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def build_reference_hatx(cfg: dict):
+    mod = load_reference_hatx()
+    net = mod.HATX(**{k: v for k, v in cfg.items() if k != "arch"})
+    net.eval()
+    return net
+
+
 def build_reference(cfg: dict):
     """Instantiate the reference `HAT(**cfg)` in eval mode."""
     mod = load_reference_hat()

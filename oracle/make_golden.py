@@ -94,6 +94,44 @@ CASES_R2 = {
 }
 
 
+# ---- sibling variant HATX (reference HAT/hat/archs/hatx_arch.py) -----------------------------------
+def hatx_mini(**over):
+    v = dict(BASE, arch="HATX", embed_dim=48, depths=[2, 2], num_heads=[6, 6], compress_ratio=3, squeeze_factor=30,
+             upscale=2, conv_scale=0.03, hab_ffn_ratio=2.0)
+    v.update(over)
+    return v
+
+
+# name -> (cfg, state_dict seed, input seed, input shape).  The focus-bias + top-k COMBINATION is not in this list: its
+# threshold falls among zero-padded keys whose scores tie at tanh(0), and torch.topk leaves the choice among equal
+# scores unspecified (the oracle and the device break ties by key index; the reference differs by ~5e-4 there).
+CASES_HATX = {
+    "hatx_mini_x2_32x32":       (hatx_mini(), 31, 41, (2, 3, 32, 32)),
+    "hatx_mini_x2_topk":        (hatx_mini(kv_topk_ratio=0.6), 32, 42, (1, 3, 32, 48)),
+    "hatx_mini_x2_yaml_focus":  (hatx_mini(overlap_ratio=0.6, mlp_ratio=4.0, hab_ffn_ratio=3.0, esc_pdim=24, esc_kernel=15,
+                                           ocab_esc_enable=True, ocab_esc_pdim=32, ocab_esc_kernel=17,
+                                           use_focus_bias=True), 33, 43, (1, 3, 48, 32)),
+    "hatx_dims_x2_32x32":       (dict(BASE, arch="HATX", embed_dim=180, depths=[2], num_heads=[6], compress_ratio=3,
+                                      squeeze_factor=30, upscale=2, conv_scale=0.03, mlp_ratio=4.0, hab_ffn_ratio=3.0,
+                                      use_focus_bias=True), 34, 44, (1, 3, 32, 32)),
+}
+
+
+def gen_hatx_cases():
+    for name, (cfg, sd_seed, x_seed, shape) in CASES_HATX.items():
+        torch.manual_seed(0)
+        net = load_ref.build_reference_hatx(cfg)
+        sd = O.randomized_state_dict(net.state_dict(), sd_seed)
+        net.load_state_dict(sd, strict=True)
+        x = torch.rand(shape, generator=torch.Generator().manual_seed(x_seed), dtype=torch.float32)
+        y = load_ref.reference_forward(net, x)
+        err = (y - O.hat_forward(x, sd, cfg)).abs().max().item()
+        print(f"{name}: out {tuple(y.shape)} |y|max {y.abs().max():.3f} keys {len(sd)} oracle-vs-reference max-abs {err:.2e}")
+        assert err <= 1e-4 * max(1.0, y.abs().max().item())
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), cfg=json.dumps(cfg), sd_seed=sd_seed, x_seed=x_seed,
+                            x_shape=np.array(shape), y=y.numpy(), torch_version=torch.__version__)
+
+
 def _load_ref_hat_model():
     load_ref.load_reference_hat()
     import importlib.util
@@ -311,6 +349,9 @@ if __name__ == "__main__":
         sys.exit("reference not mounted; goldens can only be generated in the build container")
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
+    if len(sys.argv) > 1 and sys.argv[1] == "hatx":
+        gen_hatx_cases()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "postproc":
         gen_postproc()
         sys.exit(0)
@@ -323,3 +364,4 @@ if __name__ == "__main__":
     gen_manifest()
     gen_forward_cases()
     gen_r2_cases()
+    gen_hatx_cases()

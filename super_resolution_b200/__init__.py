@@ -9,8 +9,8 @@ Public surface (mirrors the reference's own for this path):
   * `load_network`, `save_network` -- the reference's checkpoint file format (basicsr/models/base_model.py:207-315)
 The arithmetic lives in `libhatb200.so` (csrc/, include/hatb200.h).
 """
-from .hat_arch import HAT  # noqa: F401
+from .hat_arch import HAT, HATX  # noqa: F401
 from .hat_model import HATModel, calculate_psnr, calculate_ssim, load_network, save_network, tensor2img  # noqa: F401
 
-__all__ = ["HAT", "HATModel", "tensor2img", "calculate_psnr", "calculate_ssim", "load_network", "save_network"]
+__all__ = ["HAT", "HATX", "HATModel", "tensor2img", "calculate_psnr", "calculate_ssim", "load_network", "save_network"]
 __version__ = "0.1.0"

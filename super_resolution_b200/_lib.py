@@ -25,6 +25,7 @@ class Config(C.Structure):
         ("upscale", C.c_int32), ("upsampler", C.c_int32), ("resi_conv", C.c_int32), ("patch_norm", C.c_int32),
         ("qkv_bias", C.c_int32), ("conv_scale", C.c_float), ("img_range", C.c_float), ("qk_scale", C.c_float),
         ("mean", C.c_float * 4),
+        ("arch", C.c_int32), ("ocab_pad", C.c_int32), ("kv_topk_keep", C.c_int32), ("use_focus_bias", C.c_int32),
     ]
 
 

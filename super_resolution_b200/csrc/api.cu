@@ -65,9 +65,15 @@ static void build_registry(hatb200_handle* h) {
       add_wb(h, bp + ".conv_block.cab.2", {C, c.cab_mid, 3, 3});
       add_param(h, bp + ".conv_block.cab.3.conv.weight", {1, 1, 5});
       add_wb(h, bp + ".norm2", {C});
-      add_wb(h, bp + ".mlp.fc1", {2 * c.ffn_hidden, C});
-      add_wb(h, bp + ".mlp.dw", {2 * c.ffn_hidden, 1, 3, 3});
-      add_wb(h, bp + ".mlp.fc2", {C, c.ffn_hidden});
+      if (c.arch == 1) {      // HATX spatial-gate FFN (hatx_arch.py:144-158): fc1 C -> hid, dw on hid / 2, fc2 hid -> C
+        add_wb(h, bp + ".mlp.fc1", {c.ffn_hidden, C});
+        add_wb(h, bp + ".mlp.dw", {c.ffn_hidden / 2, 1, 3, 3});
+        add_wb(h, bp + ".mlp.fc2", {C, c.ffn_hidden});
+      } else {
+        add_wb(h, bp + ".mlp.fc1", {2 * c.ffn_hidden, C});
+        add_wb(h, bp + ".mlp.dw", {2 * c.ffn_hidden, 1, 3, 3});
+        add_wb(h, bp + ".mlp.fc2", {C, c.ffn_hidden});
+      }
     }
     std::string op = lp + ".residual_group.overlap_attn";
     int T = ws + ows - 1;
@@ -82,6 +88,10 @@ static void build_registry(hatb200_handle* h) {
     add_wb(h, op + ".mlp.0", {c.ffn_hidden, C});
     add_wb(h, op + ".mlp.2", {C, c.ffn_hidden});
     if (c.ocab_esc_enable) add_esc(h, op + ".esc_core", C, c.ocab_esc_pdim);
+    if (c.arch == 1 && c.use_focus_bias) {      // hatx_arch.py:355-361
+      add_wb(h, op + ".focus_head.0", {C / 4, C, 1, 1});
+      add_wb(h, op + ".focus_head.2", {1, C / 4, 1, 1});
+    }
     if (c.resi_conv) add_wb(h, lp + ".conv", {C, C, 3, 3});
   }
   add_wb(h, "norm", {C});
@@ -118,9 +128,21 @@ int hatb200_create(const hatb200_config* cfg, hatb200_handle** out) {
   HB_REQUIRE(c.embed_dim >= 8 && c.embed_dim <= 256, HATB200_EUNSUPPORTED, "embed_dim=%d not in 8..256", c.embed_dim);
   HB_REQUIRE(c.window_size >= 2 && c.window_size <= 16, HATB200_EUNSUPPORTED, "window_size=%d not in 2..16",
              c.window_size);
-  HB_REQUIRE(c.overlap_win_size >= c.window_size && ((c.overlap_win_size - c.window_size) & 1) == 0,
-             HATB200_EUNSUPPORTED, "overlap window %d must exceed window %d by an even amount", c.overlap_win_size,
-             c.window_size);
+  HB_REQUIRE(c.arch == 0 || c.arch == 1, HATB200_EINVAL, "arch=%d (0 = HAT, 1 = HATX)", c.arch);
+  HB_REQUIRE(c.overlap_win_size >= c.window_size && c.overlap_win_size <= 32, HATB200_EUNSUPPORTED,
+             "overlap window %d must be in [window %d, 32]", c.overlap_win_size, c.window_size);
+  if (c.arch == 0)
+    HB_REQUIRE(((c.overlap_win_size - c.window_size) & 1) == 0 && c.ocab_pad == (c.overlap_win_size - c.window_size) / 2 &&
+                   c.kv_topk_keep == 0 && c.use_focus_bias == 0, HATB200_EUNSUPPORTED,
+               "HAT: overlap window %d must exceed window %d by an even amount (pad %d) and the HATX options must be off",
+               c.overlap_win_size, c.window_size, c.ocab_pad);
+  // nn.Unfold(ows, stride ws, pad) must yield exactly one key window per query window (hat_arch.py:296-297)
+  HB_REQUIRE(2 * c.ocab_pad >= c.overlap_win_size - c.window_size && 2 * c.ocab_pad < c.overlap_win_size, HATB200_EUNSUPPORTED,
+             "ocab_pad=%d does not tile windows of %d with overlap windows of %d", c.ocab_pad, c.window_size,
+             c.overlap_win_size);
+  HB_REQUIRE(c.kv_topk_keep >= 0 && c.kv_topk_keep <= c.overlap_win_size * c.overlap_win_size, HATB200_EINVAL,
+             "kv_topk_keep=%d", c.kv_topk_keep);
+  if (c.arch == 1) HB_REQUIRE(c.ffn_hidden % 2 == 0, HATB200_EINVAL, "Hidden(%d) must be even for spatial gate split.", c.ffn_hidden);
   HB_REQUIRE(c.cab_mid >= 1 && c.ffn_hidden >= 1, HATB200_EINVAL, "cab_mid=%d ffn_hidden=%d", c.cab_mid, c.ffn_hidden);
   HB_REQUIRE(c.esc_pdim >= 2 && c.esc_pdim <= 64 && c.esc_pdim <= c.embed_dim && (c.esc_kernel & 1),
              HATB200_EUNSUPPORTED, "esc_pdim=%d esc_kernel=%d", c.esc_pdim, c.esc_kernel);

@@ -14,7 +14,8 @@ constexpr int KCHUNK_ROWS = 8;   // key rows staged per pass
 template <typename T, int DMAX>
 __global__ void __launch_bounds__(256) attn_simt_kernel(const T* __restrict__ qkv, int pitch, int H, int W, int C,
                                                         int heads, int ws, int ows, const float* __restrict__ bias,
-                                                        T* __restrict__ out, int out_pitch, int out_zero_to) {
+                                                        T* __restrict__ out, int out_pitch, int out_zero_to, int pad,
+                                                        const float* __restrict__ kadd) {
   extern __shared__ float smem[];
   const int d = C / heads;
   const int dp = (d + 3) & ~3;
@@ -28,7 +29,7 @@ __global__ void __launch_bounds__(256) attn_simt_kernel(const T* __restrict__ qk
   const int b = win / (nwx * nwy);
   const int wrem = win % (nwx * nwy);
   const int wy = wrem / nwx, wx = wrem % nwx;
-  const int pad = (ows - ws) / 2;
+  const float* ka = kadd ? kadd + (size_t)win * ows * ows : nullptr;    // HATX focus bias / top-k pruning
   const int tid = threadIdx.x;
   const int nq = ws * ws;
   const bool active = tid < nq;
@@ -68,8 +69,10 @@ __global__ void __launch_bounds__(256) attn_simt_kernel(const T* __restrict__ qk
       const int ky = ky0 + kr;
       const float* brow = sbias + (ky - qy + ws - 1) * Tn + (ws - 1 - qx);
       for (int kx = 0; kx < ows; kx++) {
+        const float extra = ka ? ka[ky * ows + kx] : 0.f;
+        if (extra == -INFINITY) continue;       // pruned key: exp(-1e4 + bias - max) is exactly 0 (hatx_arch.py:437-441)
         const float* kp = sk + (kr * ows + kx) * dp;
-        float s = 0.f;
+        float s = extra;
 #pragma unroll
         for (int i = 0; i < DMAX; i += 4) {
           if (i < dp) {
@@ -125,14 +128,15 @@ static int launch_t(const AttnArgs& a, cudaStream_t st) {
   size_t smem = ((size_t)((Tn * Tn + 3) & ~3) + 2 * (size_t)KCHUNK_ROWS * a.ows * dp) * sizeof(float);
   dim3 grid(a.B * (a.H / a.ws) * (a.W / a.ws), a.heads);
   int threads = round_up(a.ws * a.ws, 32);
+  const int pad = a.pad >= 0 ? a.pad : (a.ows - a.ws) / 2;
   if (d <= 32) {
     HB_CHECK_CUDA(cudaFuncSetAttribute(attn_simt_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attn_simt_kernel<T, 32><<<grid, threads, smem, st>>>((const T*)a.qkv, a.pitch, a.H, a.W, a.C, a.heads, a.ws, a.ows,
-                                                         a.bias, (T*)a.out, a.out_pitch, a.out_zero_to);
+                                                         a.bias, (T*)a.out, a.out_pitch, a.out_zero_to, pad, a.kadd);
   } else {
     HB_CHECK_CUDA(cudaFuncSetAttribute(attn_simt_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attn_simt_kernel<T, 64><<<grid, threads, smem, st>>>((const T*)a.qkv, a.pitch, a.H, a.W, a.C, a.heads, a.ws, a.ows,
-                                                         a.bias, (T*)a.out, a.out_pitch, a.out_zero_to);
+                                                         a.bias, (T*)a.out, a.out_pitch, a.out_zero_to, pad, a.kadd);
   }
   HB_CHECK_LAUNCH();
   return 0;
@@ -142,7 +146,7 @@ int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st) {
   int d = a.C / a.heads;
   HB_REQUIRE(a.C % a.heads == 0 && d <= 64, HATB200_EUNSUPPORTED, "attention: head_dim=%d unsupported (<=64)", d);
   HB_REQUIRE(a.ws * a.ws <= 256, HATB200_EUNSUPPORTED, "attention: window_size=%d unsupported (<=16)", a.ws);
-  HB_REQUIRE(a.H % a.ws == 0 && a.W % a.ws == 0 && ((a.ows - a.ws) & 1) == 0, HATB200_EINVAL,
+  HB_REQUIRE(a.H % a.ws == 0 && a.W % a.ws == 0 && (a.pad >= 0 || ((a.ows - a.ws) & 1) == 0), HATB200_EINVAL,
              "attention: bad window geometry");
   if (dt == HATB200_F32) return launch_t<float>(a, st);
   if (dt == HATB200_BF16) return launch_t<bf16>(a, st);

@@ -15,6 +15,7 @@ namespace hb {
 
 struct Dims {
   int B, H, W, M, C, Cp, mid, midp, hid, hp2, hp4, qkvp, h1p, pdim, opdim, hpad;
+  int f1, f1p;   // fc1 output channels of a HAB and their pitch: 2 hid (HAT gated FFN) or hid (HATX spatial-gate FFN)
   int dt;      // storage dtype of activations
   size_t es;   // element size of T
 };
@@ -25,6 +26,8 @@ static Dims make_dims(const hatb200_config& c, int B, int H, int W, int dt) {
   d.C = c.embed_dim; d.Cp = round_up(d.C, 64);
   d.mid = c.cab_mid; d.midp = round_up(d.mid, 64);
   d.hid = c.ffn_hidden; d.hp2 = round_up(d.hid, 64); d.hp4 = round_up(2 * d.hid, 64);
+  d.f1 = c.arch == 1 ? d.hid : 2 * d.hid; d.f1p = round_up(d.f1, 64);
+  if (c.arch == 1 && c.use_focus_bias && round_up(c.embed_dim / 4, 64) > d.midp) d.midp = round_up(c.embed_dim / 4, 64);
   d.qkvp = round_up(3 * d.C, 64);
   d.hpad = 0;                                   // tcgen05 attention: heads * 32 channels per q / k / v
   for (int L = 0; L < c.num_layers; L++)
@@ -71,6 +74,12 @@ static void plan(const hatb200_config& c, const Dims& d, char* base, Workspace& 
   w.part16 = (float*)take((size_t)d.B * nchunk * 64 * 4);
   w.eca_s = (float*)take((size_t)d.B * d.C * 4);
   w.dyn = (float*)take((size_t)d.B * 64 * 9 * 4);
+  if (c.arch == 1 && (c.use_focus_bias || c.kv_topk_keep > 0)) {
+    const int ows = c.overlap_win_size, ws = c.window_size;
+    w.SAL = take(M * 16 * d.es);
+    w.KN = (float*)take(M * 4);
+    w.KADD = (float*)take((size_t)d.B * (d.H / ws) * (d.W / ws) * ows * ows * 4);
+  }
   w.bytes = off;
 }
 
@@ -238,10 +247,19 @@ struct Fwd {
   void set_ln(Epilogue& ep, const LNW* n, void* out, int head_c) {
     if (!n) return;
     ep.ln_gamma = n->g; ep.ln_beta = n->b; ep.ln_out = out; ep.ln_pitch = d.Cp;
-    if (head_c) {
+    if (head_c && !(tc() && head_c > 16)) {      // wider heads (HATX configs: esc_pdim 24 / 32) are extracted by head_after()
       ep.ln_head = w.X16; ep.ln_head_c = head_c; ep.ln_head_colsum = w.part16;
       if (plk_tc(head_c)) ep.ln_head_pad = w.X16P;
     }
+  }
+
+  // The fused epilogues carry a compact head of at most 16 channels; for a wider ESC head the LayerNorm output is
+  // copied out and pooled by two small kernels right after the fused layer.
+  int head_after(int head_c) {
+    if (!(tc() && head_c > 16)) return 0;
+    HB_TRY(launch_head_copy(w.XN, d.dt, d.Cp, (size_t)d.M, head_c, w.X16, st));
+    HB_TRY(launch_colsum(w.X16, d.dt, head_c, d.B, d.H * d.W, head_c, w.part16, st));
+    return dbg("head_after");
   }
 
   // ESC ConvAttn core on xn (esc_arch.py:119-123): writes the mixed first-pdim channels into
@@ -287,7 +305,18 @@ struct Fwd {
       set_ln(ep, &b.n2, w.XN2, 0);
       HB_TRY(conv("esc_aggr", b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
-    {  // GatedDconvFFN (hat_arch.py:107-119)
+    if (c.arch == 1) {  // HATX SpatialGateDConvFFN (hatx_arch.py:160-180): fc1 -> [dw3x3(xa) * SiLU(xb) | xb] -> fc2
+      Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.f1p;
+      HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
+      int tid = t_begin("ffn_spatial_gate", 2.0 * d.M * (d.hid / 2) * 9, (double)d.M * 2 * d.hid * d.es, "sgate");
+      HB_TRY(launch_sgate(w.H1, d.dt, d.f1p, d.B, d.H, d.W, d.hid / 2, b.dw_w, b.dw_b, w.G, d.hp2, d.hp2, st));
+      t_end(tid);
+      HB_TRY(dbg("sgate"));
+      Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
+      set_ln(e2, next_ln, w.XN, next_head);
+      HB_TRY(conv("ffn_fc2", b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
+      HB_TRY(head_after(next_ln ? next_head : 0));
+    } else {  // GatedDconvFFN (hat_arch.py:107-119)
       Epilogue ep; ep.out_t = w.H1; ep.out_t_pitch = d.hp4;
       HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
       Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
@@ -307,6 +336,7 @@ struct Fwd {
         int r = launch_ffn2_tc(fa, e3, st);
         t_end(tid);
         HB_TRY(r);
+        HB_TRY(head_after(next_ln ? next_head : 0));
         return dbg("ffn2_tc");
       }
       int tid = t_begin("ffn_dwconv_gate", 2.0 * d.M * 2 * d.hid * 9, (double)d.M * 3 * d.hid * d.es, "dwgate");
@@ -314,6 +344,7 @@ struct Fwd {
       t_end(tid);
       HB_TRY(dbg("dwgate"));
       HB_TRY(conv("ffn_fc2", b.fc2, w.G, d.hp2, 0, d.H, d.W, e2));
+      HB_TRY(head_after(next_ln ? next_head : 0));
     }
     return 0;
   }
@@ -327,7 +358,10 @@ struct Fwd {
     // tcgen05 attention (bf16 path, default geometry): head-padded qkv / proj weights
     const int hp = o.heads * ATTN_TC_DP;
     AttnTcArgs ta{w.H1, 3 * hp, d.B, d.H, d.W, o.heads, dh, c.window_size, c.overlap_win_size, o.bias_l2, w.G, hp};
-    const bool use_attn_tc = tc() && o.bias_l2 != nullptr && !tc_disabled("ocab_attention") && attn_tc_supported(ta);
+    // HATX focus bias / top-k pruning (hatx_arch.py:405-441) live in the CUDA-core attention kernel
+    const bool hatx_opts = c.arch == 1 && (c.use_focus_bias || c.kv_topk_keep > 0);
+    const bool use_attn_tc = tc() && !hatx_opts && o.bias_l2 != nullptr && !tc_disabled("ocab_attention") &&
+                             attn_tc_supported(ta);
     if (c.ocab_esc_enable) {   // K/V from y = ConvAttnWrapper(xn) (hat_arch.py:336-344)
       HB_CHECK_CUDA(cudaMemcpyAsync(w.XN2, w.XN, (size_t)d.M * d.Cp * d.es, cudaMemcpyDeviceToDevice, st));
       HB_TRY(esc_mix(o.esc, w.XN2));
@@ -361,6 +395,23 @@ struct Fwd {
       } else {
         AttnArgs a{w.H1, d.qkvp, d.B, d.H, d.W, d.C, o.heads, c.window_size, c.overlap_win_size, o.bias_compact,
                    w.G, d.Cp, d.Cp};
+        a.pad = c.ocab_pad;
+        if (hatx_opts) {
+          const void* ysrc = c.ocab_esc_enable ? w.U : w.XN;          // y: the tensor K / V were projected from
+          const void* sal = nullptr;
+          if (c.use_focus_bias) {      // focus_head(y): 1x1 C -> C/4, GELU, 1x1 -> 1 (hatx_arch.py:355-361, :408)
+            Epilogue e0; e0.act = ACT_GELU; e0.out_t = w.T1; e0.out_t_pitch = d.midp; e0.out_t_zero_to = d.midp;
+            HB_TRY(conv_impl("ocab_focus", o.focus0, ysrc, d.Cp, 0, d.H, d.W, e0));
+            Epilogue e1; e1.out_t = w.SAL; e1.out_t_pitch = 16;
+            HB_TRY(conv_impl("ocab_focus", o.focus1, w.T1, d.midp, 0, d.H, d.W, e1));
+            sal = w.SAL;
+          } else {                     // score = ||k||_2 over all C key channels (hatx_arch.py:426)
+            HB_TRY(launch_knorm(w.H1, d.dt, d.qkvp, d.C, d.C, (size_t)d.M, w.KN, st));
+          }
+          HB_TRY(launch_ocab_focus_prep(sal, d.dt, 16, sal ? nullptr : w.KN, d.B, d.H, d.W, c.window_size,
+                                        c.overlap_win_size, c.ocab_pad, c.kv_topk_keep, w.KADD, st));
+          a.kadd = w.KADD;
+        }
         HB_TRY(launch_attn_simt(d.dt, a, st));
       }
       t_end(tid);
@@ -432,6 +483,7 @@ struct Fwd {
         Epilogue ep; ep.resid = w.XA; ep.resid_pitch = d.C; ep.out_f32 = w.XA; ep.out_f32_pitch = d.C;
         set_ln(ep, nl, w.XN, nh);
         HB_TRY(conv("rhag_conv", lw.conv, w.XN2, d.Cp, 0, d.H, d.W, ep));
+        HB_TRY(head_after(nl ? nh : 0));
       } else {
         HB_TRY(launch_add_convert(w.XA, w.XB, d.M, d.C, w.XA, nullptr, d.dt, 0, 0, st));
         HB_TRY(ln(w.XA, *nl, w.XN, nh));

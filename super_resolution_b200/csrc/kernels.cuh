@@ -45,6 +45,13 @@ int launch_hab_finish(const float* eca_partial, int nchunk, int B, int C, int HW
 // GatedDconvFFN middle (hat_arch.py:112-116)
 int launch_dwgate(const void* in, int dt, int in_pitch, int B, int H, int W, int hid, const float* w /*(2hid,9)*/,
                   const float* b, void* out, int out_pitch, int zero_to, cudaStream_t st);
+// sibling variant HATX (hatx_arch.py): spatial-gate FFN middle, key norms, focus / top-k term per (window, key)
+int launch_sgate(const void* in, int dt, int in_pitch, int B, int H, int W, int c2, const float* w /*[9][c2]*/,
+                 const float* b, void* out, int out_pitch, int zero_to, cudaStream_t st);
+int launch_head_copy(const void* in, int dt, int pitch, size_t M, int hc, void* out, cudaStream_t st);
+int launch_knorm(const void* qkv, int dt, int pitch, int k_off, int C, size_t M, float* out, cudaStream_t st);
+int launch_ocab_focus_prep(const void* sal, int dt, int sal_pitch, const float* knorm, int B, int H, int W, int ws, int ows,
+                           int pad, int k_keep, float* kadd, cudaStream_t st);
 // out_t[m, c] = a[m, c] + b[m, c] (b optional), fp32 in (M, C); optional fp32 copy to out_f32 (may alias a)
 int launch_add_convert(const float* a, const float* b, int M, int C, float* out_f32, void* out_t, int dt, int out_pitch,
                        int zero_to, cudaStream_t st);
@@ -127,6 +134,8 @@ struct AttnArgs {
   int B, H, W, C, heads, ws, ows;
   const float* bias;                 // (heads, (ws+ows-1)^2) compact table, see pack_ocab_bias
   void* out; int out_pitch; int out_zero_to;
+  int pad = -1;                      // unfold padding of the key window; -1: (ows - ws) / 2 (HAT)
+  const float* kadd = nullptr;       // HATX: (windows, ows^2) additive term per key, -inf = pruned (launch_ocab_focus_prep)
 };
 int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st);
 // tcgen05 kernel (tc_attn.cu): head-padded bf16 layout, head_dim padded to 32 channels (pad channels zero):

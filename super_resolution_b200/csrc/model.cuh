@@ -53,6 +53,7 @@ struct OcabW {
   float* bias_compact = nullptr;   // (heads, (ws+ows-1)^2)
   // tcgen05 attention path: head-padded (head_dim -> 32) qkv / proj weights and the log2e-scaled bias table
   ConvW qkv_tc, proj_tc;
+  ConvW focus0, focus1;            // HATX focus head: 1x1 C -> C/4 (GELU) -> 1 (hatx_arch.py:355-361)
   ConvW q_tc, kv_tc;               // ocab_esc_enable: separate head-padded q / kv GEMMs (different inputs)
   float* bias_l2 = nullptr;        // (heads, 1536)
   ConvW proj, mlp0, mlp2;
@@ -77,6 +78,8 @@ struct Workspace {           // carved from the caller's scratch buffer
   void *F64 = nullptr, *UP1 = nullptr, *UP2 = nullptr;   // tail
   float* CL32 = nullptr;                                 // conv_last output, pixels-last fp32 (B*Hr*Wr, 4), bf16 path
   float *part = nullptr, *part16 = nullptr, *eca_s = nullptr, *dyn = nullptr;
+  void* SAL = nullptr;                                   // HATX: T (M, 16) focus-head output (column 0)
+  float *KN = nullptr, *KADD = nullptr;                  // HATX: per-token ||k||_2; per (window, key) additive term / -inf
   size_t bytes = 0;
 };
 

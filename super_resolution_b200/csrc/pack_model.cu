@@ -216,11 +216,12 @@ struct Packer {
         HB_TRY(conv(bp + ".conv_block.cab.0", b.cab0, c.cab_mid, C, 3, 3));
         HB_TRY(conv(bp + ".conv_block.cab.2", b.cab2, C, c.cab_mid, 3, 3));
         HB_TRY(vec(bp + ".conv_block.cab.3.conv.weight", &b.eca_w5));
-        HB_TRY(conv(bp + ".mlp.fc1", b.fc1, 2 * hid, C, 1, 1));
+        const int f1 = c.arch == 1 ? hid : 2 * hid, dwc = c.arch == 1 ? hid / 2 : 2 * hid;   // HATX: hatx_arch.py:152-157
+        HB_TRY(conv(bp + ".mlp.fc1", b.fc1, f1, C, 1, 1));
         HB_TRY(conv(bp + ".mlp.fc2", b.fc2, C, hid, 1, 1));
         HB_TRY(get(bp + ".mlp.dw.weight", &p));
-        HB_TRY(alloc((void**)&b.dw_w, (size_t)9 * 2 * hid * sizeof(float)));
-        PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, 2 * hid, 1, 9, b.dw_w, 2 * hid, 2 * hid, st));
+        HB_TRY(alloc((void**)&b.dw_w, (size_t)9 * dwc * sizeof(float)));
+        PK_TRY(launch_pack_w_f32(p->ptr, p->dtype, dwc, 1, 9, b.dw_w, dwc, dwc, st));
         HB_TRY(vec(bp + ".mlp.dw.bias", &b.dw_b));
       }
       OcabW& o = lw.ocab;
@@ -234,6 +235,14 @@ struct Packer {
         HB_TRY(conv(op + ".kv_proj", o.kv, 2 * C, C, 1, 1));
         HB_TRY(esc(op + ".esc_core", op + ".esc_plk", o.esc, C, c.ocab_esc_pdim, c.ocab_esc_kernel));
       }
+      if (c.arch == 1 && c.use_focus_bias) {
+        HB_TRY(conv(op + ".focus_head.0", o.focus0, C / 4, C, 1, 1));
+        HB_TRY(conv(op + ".focus_head.2", o.focus1, 1, C / 4, 1, 1));
+      }
+      if (c.arch == 1 && !c.ocab_esc_enable) {      // the CUDA-core HATX attention path takes q and k / v from separate GEMMs
+        HB_TRY(conv(op + ".q_proj", o.q, C, C, 1, 1));
+        HB_TRY(conv(op + ".kv_proj", o.kv, 2 * C, C, 1, 1));
+      }
       HB_TRY(conv(op + ".proj", o.proj, C, C, 1, 1));
       HB_TRY(conv(op + ".mlp.0", o.mlp0, hid, C, 1, 1));
       HB_TRY(conv(op + ".mlp.2", o.mlp2, C, hid, 1, 1));
@@ -242,7 +251,7 @@ struct Packer {
       HB_TRY(alloc((void**)&o.bias_compact, (size_t)o.heads * T * T * sizeof(float)));
       PK_TRY(launch_pack_ocab_bias(p->ptr, p->dtype, (const int64_t*)rpi->ptr, o.heads, ws, ows, o.bias_compact,
                                    h->err_flag, st));
-      if (ws == 16 && ows == 24) HB_TRY(ocab_tc(op, o, C, ws, ows));
+      if (ws == 16 && ows == 24 && c.ocab_pad == 4) HB_TRY(ocab_tc(op, o, C, ws, ows));
       if (c.resi_conv) HB_TRY(conv(lp + ".conv", lw.conv, C, C, 3, 3));
     }
     HB_TRY(ln("norm", h->final_norm));

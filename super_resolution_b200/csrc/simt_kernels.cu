@@ -825,3 +825,147 @@ int launch_tokens_to_nchw(const void* in, int dt, int pitch, int B, int C, int h
   return 0;
 }
 }  // namespace hb
+
+// ---------------------------------------------------------------------------
+// Sibling variant HATX (HAT/hat/archs/hatx_arch.py).
+// ---------------------------------------------------------------------------
+namespace hb {
+
+// SpatialGateDConvFFN middle (hatx_arch.py:166-178): in (M, in_pitch) holds fc1's output (xa = channels [0, c2),
+// xb = [c2, 2 c2));  out[:, :c2] = (dw3x3(xa) + bias) * SiLU(xb),  out[:, c2:2 c2] = xb,  columns up to zero_to = 0.
+template <typename T>
+__global__ void sgate_kernel(const T* __restrict__ in, int in_pitch, int B, int H, int W, int c2,
+                             const float* __restrict__ w /*[9][c2]*/, const float* __restrict__ bias,
+                             T* __restrict__ out, int out_pitch, int cols) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t total = (size_t)B * H * W * cols;
+  if (idx >= total) return;
+  const int c = (int)(idx % cols);
+  const size_t m = idx / cols;
+  float v = 0.f;
+  if (c < c2) {
+    const int px = (int)(m % W), py = (int)((m / W) % H);
+    float a = bias[c];
+#pragma unroll
+    for (int ky = 0; ky < 3; ky++) {
+      const int yy = py + ky - 1;
+      if (yy < 0 || yy >= H) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; kx++) {
+        const int xx = px + kx - 1;
+        if (xx < 0 || xx >= W) continue;
+        a = fmaf(to_f(in[(m + (size_t)(ky - 1) * W + (kx - 1)) * in_pitch + c]), w[(ky * 3 + kx) * c2 + c], a);
+      }
+    }
+    v = a * silu_f(to_f(in[m * in_pitch + c2 + c]));
+  } else if (c < 2 * c2) {
+    v = to_f(in[m * in_pitch + c]);
+  }
+  out[m * out_pitch + c] = from_f<T>(v);
+}
+
+template <typename T>
+__global__ void head_copy_kernel(const T* __restrict__ in, int pitch, size_t M, int hc, T* __restrict__ out) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * hc) return;
+  const size_t m = idx / hc;
+  const int c = (int)(idx % hc);
+  out[idx] = in[m * pitch + c];
+}
+
+int launch_head_copy(const void* in, int dt, int pitch, size_t M, int hc, void* out, cudaStream_t st) {
+  HB_DISPATCH_T(dt, T, {
+    head_copy_kernel<T><<<(unsigned)((M * hc + 255) / 256), 256, 0, st>>>((const T*)in, pitch, M, hc, (T*)out);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_sgate(const void* in, int dt, int in_pitch, int B, int H, int W, int c2, const float* w, const float* b,
+                 void* out, int out_pitch, int zero_to, cudaStream_t st) {
+  const int cols = zero_to > 2 * c2 ? zero_to : 2 * c2;
+  HB_REQUIRE(in_pitch >= 2 * c2 && out_pitch >= cols, HATB200_EINVAL, "sgate: pitches %d / %d for %d channels", in_pitch,
+             out_pitch, 2 * c2);
+  const size_t total = (size_t)B * H * W * cols;
+  HB_DISPATCH_T(dt, T, {
+    sgate_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)in, in_pitch, B, H, W, c2, w, b, (T*)out,
+                                                                    out_pitch, cols);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ||k||_2 over the C key channels of every token (hatx_arch.py:426): one warp per token, fp32.
+template <typename T>
+__global__ void knorm_kernel(const T* __restrict__ qkv, int pitch, int k_off, int C, size_t M, float* __restrict__ out) {
+  const size_t m = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) {
+    const float v = to_f(qkv[m * pitch + k_off + c]);
+    s = fmaf(v, v, s);
+  }
+  s = warp_sum(s);
+  if (lane == 0) out[m] = sqrtf(s);
+}
+
+int launch_knorm(const void* qkv, int dt, int pitch, int k_off, int C, size_t M, float* out, cudaStream_t st) {
+  HB_DISPATCH_T(dt, T, {
+    knorm_kernel<T><<<(unsigned)((M * 32 + 255) / 256), 256, 0, st>>>((const T*)qkv, pitch, k_off, C, M, out);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Per (window, key) term of the HATX OCAB (hatx_arch.py:405-441): kadd = tanh(saliency) of the key's token when the
+// focus bias is on (0 for keys in the unfold padding), else 0; -inf for keys pruned by the top-k (score = the focus
+// term when present, else ||k||_2; zero-padded keys score exactly 0).  The reference masks with -1e4 BEFORE the
+// relative-position bias; exp(-1e4 + bias - max) is exactly 0 in fp32, so a pruned key is simply skipped.  Ties at the
+// threshold are broken by the lower key index (torch.topk leaves them unspecified).  One block per window.
+template <typename T>
+__global__ void __launch_bounds__(256) ocab_focus_prep_kernel(const T* __restrict__ sal, int sal_pitch,
+                                                              const float* __restrict__ knorm, int H, int W, int ws,
+                                                              int ows, int pad, int k_keep, float* __restrict__ kadd) {
+  __shared__ float score[1024];
+  const int nwx = W / ws, nwy = H / ws, nk = ows * ows;
+  const int win = blockIdx.x;
+  const int b = win / (nwx * nwy), wr = win % (nwx * nwy), wy = wr / nwx, wx = wr % nwx;
+  for (int k = threadIdx.x; k < nk; k += blockDim.x) {
+    const int yy = wy * ws - pad + k / ows, xx = wx * ws - pad + k % ows;
+    float v = 0.f;
+    if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+      const size_t tok = ((size_t)b * H + yy) * W + xx;
+      v = sal ? tanhf(to_f(sal[tok * sal_pitch])) : knorm[tok];
+    }
+    score[k] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < nk; k += blockDim.x) {
+    const float sk = score[k];
+    bool keep = true;
+    if (k_keep > 0 && k_keep < nk) {
+      int rank = 0;
+      for (int j = 0; j < nk; j++) {
+        const float sj = score[j];
+        rank += (sj > sk || (sj == sk && j < k)) ? 1 : 0;
+      }
+      keep = rank < k_keep;
+    }
+    kadd[(size_t)win * nk + k] = keep ? (sal ? sk : 0.f) : -INFINITY;
+  }
+}
+
+int launch_ocab_focus_prep(const void* sal, int dt, int sal_pitch, const float* knorm, int B, int H, int W, int ws, int ows,
+                           int pad, int k_keep, float* kadd, cudaStream_t st) {
+  HB_REQUIRE(ows * ows <= 1024, HATB200_EUNSUPPORTED, "focus_prep: overlap window %d too large", ows);
+  HB_REQUIRE(sal || knorm, HATB200_EINVAL, "focus_prep: neither a saliency map nor key norms");
+  const int wins = B * (H / ws) * (W / ws);
+  HB_DISPATCH_T(dt, T, {
+    ocab_focus_prep_kernel<T><<<wins, 256, 0, st>>>((const T*)sal, sal_pitch, knorm, H, W, ws, ows, pad, k_keep, kadd);
+  });
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace hb

@@ -38,6 +38,13 @@ def _config_from_module(m) -> _lib.Config:
     c.conv_scale = float(m.conv_scale)
     c.img_range = float(m.img_range)
     c.qk_scale = float(m.qk_scale) if m.qk_scale else 0.0
+    ows = c.overlap_win_size
+    hatx = getattr(m, "arch", "HAT") == "HATX"
+    c.arch = 1 if hatx else 0
+    c.ocab_pad = (ows - m.window_size + 1) // 2 if hatx else (ows - m.window_size) // 2       # hatx_arch.py:316-318
+    ratio = float(getattr(m, "kv_topk_ratio", 1.0))
+    c.kv_topk_keep = max(1, int(ratio * ows * ows)) if (hatx and ratio < 1.0) else 0         # hatx_arch.py:421
+    c.use_focus_bias = int(hatx and bool(getattr(m, "use_focus_bias", False)))
     mean = [float(v) for v in m.mean.flatten().tolist()]
     for i in range(4):
         c.mean[i] = mean[i] if i < len(mean) else (mean[0] if len(mean) == 1 else 0.0)

@@ -81,19 +81,29 @@ class _GatedDconvFFN(_Holder):             # hat_arch.py:95-105
         self.fc2 = nn.Linear(hidden, dim)
 
 
-class _HAB(_Holder):                       # hat_arch.py:172-215
-    def __init__(self, dim, compress_ratio, mlp_ratio, norm_layer, esc_pdim, esc_kernel):
+class _SpatialGateDConvFFN(_Holder):       # HATX, hatx_arch.py:144-158
+    def __init__(self, dim, mlp_ratio):
+        super().__init__()
+        hidden = int(dim * mlp_ratio)
+        assert hidden % 2 == 0, f"Hidden({hidden}) must be even for spatial gate split."
+        self.fc1 = nn.Linear(dim, hidden)
+        self.dw = nn.Conv2d(hidden // 2, hidden // 2, 3, 1, 1, groups=hidden // 2)
+        self.fc2 = nn.Linear(hidden, dim)
+
+
+class _HAB(_Holder):                       # hat_arch.py:172-215; HATX: hatx_arch.py:185-230 (sgfn=True)
+    def __init__(self, dim, compress_ratio, mlp_ratio, norm_layer, esc_pdim, esc_kernel, sgfn=False):
         super().__init__()
         self.norm1 = norm_layer(dim)
         self.esc_attn = _ESCConvAttn(dim, esc_pdim, esc_kernel)
         self.conv_block = _CAB(dim, compress_ratio)
         self.norm2 = norm_layer(dim)
-        self.mlp = _GatedDconvFFN(dim, mlp_ratio)
+        self.mlp = (_SpatialGateDConvFFN if sgfn else _GatedDconvFFN)(dim, mlp_ratio)
 
 
-class _OCAB(_Holder):                      # hat_arch.py:267-324
+class _OCAB(_Holder):                      # hat_arch.py:267-324; HATX: hatx_arch.py:289-365 (focus head)
     def __init__(self, dim, window_size, overlap_ratio, num_heads, qkv_bias, mlp_ratio, norm_layer,
-                 esc_enable, esc_pdim, esc_kernel):
+                 esc_enable, esc_pdim, esc_kernel, use_focus_bias=False):
         super().__init__()
         ows = int(window_size * overlap_ratio) + window_size
         self.norm1 = norm_layer(dim)
@@ -110,16 +120,23 @@ class _OCAB(_Holder):                      # hat_arch.py:267-324
             self.esc_core = _ConvAttnWrapper(dim, esc_pdim)
             self.esc_plk = nn.Parameter(torch.randn(esc_pdim, esc_pdim, esc_kernel, esc_kernel))
             nn.init.orthogonal_(self.esc_plk)
+        if use_focus_bias:
+            self.focus_head = nn.Sequential(nn.Conv2d(dim, dim // 4, 1, 1, 0), nn.GELU(), nn.Conv2d(dim // 4, 1, 1, 1, 0))
 
 
 class _AttenBlocks(_Holder):               # hat_arch.py:395-464
     def __init__(self, dim, depth, num_heads, window_size, compress_ratio, overlap_ratio, mlp_ratio, qkv_bias,
-                 norm_layer, esc_pdim, esc_kernel, ocab_esc_enable, ocab_esc_pdim, ocab_esc_kernel):
+                 norm_layer, esc_pdim, esc_kernel, ocab_esc_enable, ocab_esc_pdim, ocab_esc_kernel,
+                 hab_ffn_ratio=None, use_focus_bias=False):
         super().__init__()
+        # HATX: HAB uses the spatial-gate FFN.  The reference stores `hab_ffn_ratio` (hatx_arch.py:790) but never passes
+        # it on: RHAG / AttenBlocks / HAB all receive `mlp_ratio` (hatx_arch.py:824, :514), so the SGFN hidden width is
+        # int(dim * mlp_ratio) -- the reference's behaviour is what the state_dict layout follows.
+        sgfn = hab_ffn_ratio is not None
         self.blocks = nn.ModuleList([
-            _HAB(dim, compress_ratio, mlp_ratio, norm_layer, esc_pdim, esc_kernel) for _ in range(depth)])
+            _HAB(dim, compress_ratio, mlp_ratio, norm_layer, esc_pdim, esc_kernel, sgfn) for _ in range(depth)])
         self.overlap_attn = _OCAB(dim, window_size, overlap_ratio, num_heads, qkv_bias, mlp_ratio, norm_layer,
-                                  ocab_esc_enable, ocab_esc_pdim, ocab_esc_kernel)
+                                  ocab_esc_enable, ocab_esc_pdim, ocab_esc_kernel, use_focus_bias)
 
 
 class _RHAG(_Holder):                      # hat_arch.py:484-553
@@ -173,6 +190,12 @@ class HAT(nn.Module):
                  esc_kernel: int = 13, esc_use_dynamic: bool = True, ocab_esc_enable: bool = False,
                  ocab_esc_pdim: int = 16, ocab_esc_kernel: int = 13, **kwargs):
         super().__init__()
+        # HATX (subclass below) passes its three extra arguments through these private keywords
+        hab_ffn_ratio = kwargs.pop('_hab_ffn_ratio', None)
+        self.kv_topk_ratio = float(kwargs.pop('_kv_topk_ratio', 1.0))
+        self.use_focus_bias = bool(kwargs.pop('_use_focus_bias', False))
+        self.hab_ffn_ratio = hab_ffn_ratio
+        self.arch = 'HATX' if hab_ffn_ratio is not None else 'HAT'
         if ape:
             raise NotImplementedError("ape=True (absolute position embedding, hat_arch.py:699-702) is not "
                                       "implemented; no shipped configuration uses it")
@@ -221,7 +244,8 @@ class HAT(nn.Module):
             _RHAG(embed_dim, resi_connection, depth=depths[i], num_heads=num_heads[i], window_size=window_size,
                   compress_ratio=compress_ratio, overlap_ratio=overlap_ratio, mlp_ratio=mlp_ratio, qkv_bias=qkv_bias,
                   norm_layer=norm_layer, esc_pdim=esc_pdim, esc_kernel=esc_kernel, ocab_esc_enable=ocab_esc_enable,
-                  ocab_esc_pdim=ocab_esc_pdim, ocab_esc_kernel=ocab_esc_kernel)
+                  ocab_esc_pdim=ocab_esc_pdim, ocab_esc_kernel=ocab_esc_kernel, hab_ffn_ratio=hab_ffn_ratio,
+                  use_focus_bias=self.use_focus_bias)
             for i in range(self.num_layers)])
         self.norm = norm_layer(self.num_features)
 
@@ -336,7 +360,28 @@ class HAT(nn.Module):
         return out
 
 
+class HATX(HAT):
+    r"""B200-native `HATX`, the sibling variant of the reference (HAT/hat/archs/hatx_arch.py:708-975): HAT whose HAB
+    uses the Spatial-Gate DConv FFN (hidden width int(dim * mlp_ratio): `hab_ffn_ratio` is accepted and, as in the
+    reference, unused; fc1 -> split -> depthwise 3x3 on the first half -> cat[xa *
+    SiLU(xb), xb] -> fc2, hatx_arch.py:144-180) and whose OCAB pads its overlap window by the ceiling
+    (hatx_arch.py:316-322) and optionally adds a per-key focus bias and prunes keys to the top `kv_topk_ratio`
+    (hatx_arch.py:405-441).  Same state_dict layout as the reference class.  With the options at their defaults the
+    OCAB runs on the tcgen05 attention kernel; with focus bias / top-k / an odd overlap it runs on the CUDA-core
+    attention (counted by `engine().last_fallback_count`).  Ties of the top-k at the threshold (only possible among
+    zero-padded keys) are broken by the lower key index; the reference's torch.topk leaves them unspecified."""
+
+    def __init__(self, *args, hab_ffn_ratio: float = 2.0, kv_topk_ratio: float = 1.0, use_focus_bias: bool = False,
+                 **kwargs):
+        super().__init__(*args, _hab_ffn_ratio=float(hab_ffn_ratio), _kv_topk_ratio=kv_topk_ratio,
+                         _use_focus_bias=use_focus_bias, **kwargs)
+
+
 if _ARCH_REGISTRY is not None:
+    try:
+        _ARCH_REGISTRY.register(HATX)
+    except AssertionError:
+        _ARCH_REGISTRY.register(HATX, suffix='b200')
     try:
         _ARCH_REGISTRY.register(HAT)
     except AssertionError:

@@ -16,6 +16,9 @@ FORWARD_CASES = [
 ]
 
 
+HATX_CASES = ["hatx_mini_x2_32x32", "hatx_mini_x2_topk", "hatx_mini_x2_yaml_focus", "hatx_dims_x2_32x32"]
+
+
 def load_manifest():
     with open(os.path.join(GOLDEN, "state_dict_manifest.json")) as f:
         return json.load(f)
@@ -42,12 +45,20 @@ def load_case(name):
     box); key order equality with the reference is asserted by the manifest test."""
     z = np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False)
     cfg = json.loads(str(z["cfg"]))
-    from super_resolution_b200.hat_arch import HAT
-    net = HAT(**cfg)
+    net = build_module(cfg)
     sd = O.randomized_state_dict(net.state_dict(), int(z["sd_seed"]))
     shape = tuple(int(v) for v in z["x_shape"])
     x = torch.rand(shape, generator=torch.Generator().manual_seed(int(z["x_seed"])), dtype=torch.float32)
     return cfg, sd, x, torch.from_numpy(z["y"])
+
+
+def build_module(cfg):
+    """Our drop-in module for a golden's cfg: `HATX` when the cfg carries arch == 'HATX' (the key is the oracle's
+    switch, not a constructor argument), else `HAT`."""
+    from super_resolution_b200.hat_arch import HAT, HATX
+    if cfg.get("arch") == "HATX":
+        return HATX(**{k: v for k, v in cfg.items() if k != "arch"})
+    return HAT(**cfg)
 
 
 # round 2: full-depth variants at BASELINE sizes with image-range outputs -- the north_star's bars asserted literally

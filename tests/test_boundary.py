@@ -84,7 +84,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     # the engineering probes are declared under HATB200_ENGINEERING and are not part of the product library
     exported = set(re.findall(r"\bT (hatb200_[a-z0-9_]+)\b", nm))
     assert exported == set(declared), exported ^ set(declared)
-    assert __import__("ctypes").sizeof(_lib.Config) == 356   # sizeof(hatb200_config); create() re-checks it
+    assert __import__("ctypes").sizeof(_lib.Config) == 372   # sizeof(hatb200_config); create() re-checks it
 
 
 def test_tile_plan_c_abi_bit_exact():
