@@ -22,7 +22,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
-from super_resolution_b200 import HAT, HATModel  # noqa: E402
+from super_resolution_b200 import HAT, HATX, HATModel  # noqa: E402
 
 rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
 torch.cuda.set_device(local)
@@ -39,9 +39,9 @@ def base(scale, depths=6, **over):
     return cfg
 
 
-def make_net(cfg):
+def make_net(cfg, cls=HAT):
     torch.manual_seed(0)
-    net = HAT(**cfg).eval()
+    net = cls(**cfg).eval()
     sd = net.state_dict()
     g = torch.Generator().manual_seed(0)
     for k, v in sd.items():      # a fresh init leaves the dynamic-kernel branch at zero and every LayerNorm at identity:
@@ -104,6 +104,23 @@ with torch.no_grad():
             emit(config=f"configs[2] HAT SRx{s} 256x256 LR, batch 1, bf16", ms=round(ms, 3),
                  out_mp_s=round(256 * 256 * s * s / 1e6 / (ms * 1e-3), 2), psnr_bf16_vs_fp32_db=round(psnr(y16, y32, max(1.0, y32.abs().max().item())), 2),
                  n_gpus=1)
+            del net
+    # ---- the sibling variants at benchmark scale (batch 16 of 64x64 LR, bf16) ----
+    if world == 1:
+        yaml_hatx = dict(conv_scale=0.03, overlap_ratio=0.6, mlp_ratio=4.0, hab_ffn_ratio=3.0, esc_pdim=24, esc_kernel=15,
+                         ocab_esc_enable=True, ocab_esc_pdim=32, ocab_esc_kernel=17, kv_topk_ratio=0.6, use_focus_bias=True)
+        for name, cls, cfg in (("f4 HAT SRx4 with ocab_esc_enable=True (tcgen05 attention)", HAT, base(4, ocab_esc_enable=True)),
+                               ("f4 HATX SRx2, options at their defaults (spatial-gate FFN, tcgen05 attention)", HATX, base(2)),
+                               ("f4 HATX SRx2, options of train_HAT_SRx2_ESC_OCAB_from_scratch.yml (ESC 24/15, OCAB ESC "
+                                "32/17, overlap 0.6, focus bias, top-k 0.6: CUDA-core attention / ESC kernels)", HATX,
+                                base(2, **yaml_hatx))):
+            net = make_net(cfg, cls)
+            x = torch.rand(16, 3, 64, 64, generator=torch.Generator().manual_seed(4)).bfloat16().to(dev)
+            net(x)
+            ms, y = timed(lambda: net(x))
+            s_ = cfg["upscale"]
+            emit(config=name, ms=round(ms, 3), out_mp_s=round(16 * 64 * 64 * s_ * s_ / 1e6 / (ms * 1e-3), 2), n_gpus=1,
+                 launches=net.engine().last_launch_count, cuda_core_fallbacks=net.engine().last_fallback_count)
             del net
     # ---- configs[3]: HAT-L x4, one 1024x1024 LR image, tiled ----
     opt = {"network_g": {"window_size": 16}, "scale": 4, "tile": {"tile_size": 256, "tile_pad": 32}}
