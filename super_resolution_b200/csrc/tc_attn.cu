@@ -15,9 +15,10 @@
 //   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (8-stage ring, prefetches across units)
 //   warp 1   MMA issuer:   S[g] = Q[g] K_c^T  (M128 N96 K32)  and  O[g] = P[g] V_c  (M128 N32 K96)
 //   warps 2-5 / 6-9  softmax warpgroups g = 0/1, one query row per thread (rows 0-127 / 128-255):
-//            pass 1: S*log2e + bias -> running max (row parked back in TMEM); pass 2: exp2, row sum, P as bf16
-//            into shared memory in the UMMA K-major layout; the per-chunk O (fp32, TMEM) is folded into
-//            registers with the usual online-softmax rescale, so nothing is ever renormalised in TMEM.
+//            one pass per 96-key chunk: S*log2e + bias, exp2 against the chunk's reference exponent (running
+//            reference or the maximum of the chunk's first 32 logits), row sum, P as bf16 into shared memory in the
+//            UMMA K-major layout; the per-chunk O (fp32, TMEM) is folded into registers with the usual online-softmax
+//            rescale, so nothing is ever renormalised in TMEM.
 // TMEM: S double-buffered per warpgroup (4 x 96 columns) + O double-buffered per warpgroup (4 x 32) = 512.
 #include "kernels.cuh"
 #include "tc_common.cuh"
@@ -203,9 +204,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
       for (int i = 0; i < DP; i++) o_reg[i] = 0.f;
 
-      auto fold_o = [&](int kc) {      // o_reg = o_reg * alpha(kc) + O(kc)
+      auto wait_o = [&](int kc) {      // PV of chunk kc finished: O(kc) is in TMEM and the P buffer is free again
         mbar_wait(&o_full[g][kc & 1], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
         tc_fence_after();
+      };
+      auto fold_o = [&](int kc) {      // o_reg = o_reg * alpha(kc) + O(kc)
         uint32_t r[32];
         tmem_ld32(tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP, r);
         tmem_ld_wait();
@@ -213,45 +216,53 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int i = 0; i < DP; i++) o_reg[i] = fmaf(o_reg[i], alpha_prev, __uint_as_float(r[i]));
       };
 
+      // ONE pass per 96-key chunk (round 2; round 1 ran two passes with the logits parked back in TMEM): the reference
+      // exponent of a chunk is m_c = max(running reference, max of the chunk's FIRST 32 logits) -- not its true maximum,
+      // which would need all 96 logits before the first exp2.  Softmax is shift invariant, so any reference gives the
+      // same result as long as nothing overflows: p = 2^(v - m_c) can exceed 1 by however much the last 64 logits of the
+      // chunk exceed the first 32, bf16 has the exponent range of fp32, and the exponent is clamped at 126 (a row whose
+      // logits spread by more than 2^126 inside one chunk is a hard max anyway).  TMEM loads are software pipelined
+      // (sub-block s + 1 is in flight while s is processed); the bias row comes through ld.shared with immediate offsets.
+      const uint32_t bias_a = smem_u32(bias_s);
+      auto lds_f = [](uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
       for (int kc = 0; kc < NCH; kc++) {
         const int sb = kc & 1;
         const uint32_t s_addr = tmem_base + lane_sel + (uint32_t)(g * 2 + sb) * S_COLS;
         mbar_wait(&s_full[g][sb], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
         tc_fence_after();
-        const float* bchunk = bias_s + kc * KROWS * TN;
-        // ---- pass 1: logits in the log2 domain, running max; the row is parked back in TMEM ----
-        float cmax = -INFINITY;
+        const uint32_t bchunk = bias_a + (uint32_t)(kc * KROWS * TN) * 4u;
+        uint32_t ra[32], rb[32];
+        tmem_ld32(s_addr, ra);
+        tmem_ld_wait();
+        tmem_ld32(s_addr + 32, rb);                              // in flight while sub-block 0 is processed
+        // logits of sub-block 0 in the log2 domain, their maximum -> this chunk's reference
+        float smax = -INFINITY;
 #pragma unroll
-        for (int sub = 0; sub < 3; sub++) {
-          uint32_t r[32];
-          tmem_ld32(s_addr + sub * 32, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const int local = sub * 32 + j;                     // key inside the chunk: 4 rows of 24
-            const float v = fmaf(__uint_as_float(r[j]), LOG2E, bchunk[(local / OWS) * TN + (local % OWS)]);
-            cmax = fmaxf(cmax, v);
-            r[j] = __float_as_uint(v);
-          }
-          tmem_st32(s_addr + sub * 32, r);
+        for (int j = 0; j < 32; j++) {
+          const float v = fmaf(__uint_as_float(ra[j]), LOG2E, lds_f(bchunk + (uint32_t)((j / OWS) * TN + (j % OWS)) * 4u));
+          smax = fmaxf(smax, v);
+          ra[j] = __float_as_uint(v);
         }
-        tmem_st_wait();
-        const float m_new = fmaxf(m_run, cmax);
-        const float alpha = ex2_approx(m_run - m_new);          // 0 for the first chunk (m_run = -inf)
-        // PV of the previous chunk must have finished reading P before it is overwritten; fold its O
-        if (kc > 0) fold_o(kc - 1);
-        // ---- pass 2: p = 2^(s - m), row sum, P (bf16) into the K-major SWIZZLE_64B operand layout ----
+        const float m_c = fmaxf(m_run, smax);
+        const float alpha = ex2_approx(m_run - m_c);             // 0 for the first chunk (m_run = -inf)
+        // PV of the previous chunk must have finished reading P before it is overwritten; its O is folded at the end
+        // of this iteration (O is double buffered), after P of this chunk has been handed to the tensor core
+        if (kc > 0) wait_o(kc - 1);
         float csum = 0.f;
-#pragma unroll
-        for (int sub = 0; sub < 3; sub++) {
-          uint32_t r[32];
-          tmem_ld32(s_addr + sub * 32, r);
-          tmem_ld_wait();
+        auto emit = [&](const int sub, uint32_t (&r)[32], const bool logits_ready) __attribute__((always_inline)) {
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 16; j++) {
-            const float p0 = ex2_approx(__uint_as_float(r[2 * j]) - m_new);
-            const float p1 = ex2_approx(__uint_as_float(r[2 * j + 1]) - m_new);
+            float v0, v1;
+            if (logits_ready) {
+              v0 = __uint_as_float(r[2 * j]); v1 = __uint_as_float(r[2 * j + 1]);
+            } else {
+              const int l0 = sub * 32 + 2 * j, l1 = l0 + 1;
+              v0 = fmaf(__uint_as_float(r[2 * j]), LOG2E, lds_f(bchunk + (uint32_t)((l0 / OWS) * TN + (l0 % OWS)) * 4u));
+              v1 = fmaf(__uint_as_float(r[2 * j + 1]), LOG2E, lds_f(bchunk + (uint32_t)((l1 / OWS) * TN + (l1 % OWS)) * 4u));
+            }
+            const float p0 = ex2_approx(fminf(v0 - m_c, 126.f));
+            const float p1 = ex2_approx(fminf(v1 - m_c, 126.f));
             csum += p0 + p1;
             __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
             pk[j] = *reinterpret_cast<uint32_t*>(&h2);
@@ -260,15 +271,23 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
           for (int c = 0; c < 4; c++)
             *reinterpret_cast<uint4*>(blk + ((c ^ psw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-        }
+        };
+        emit(0, ra, true);
+        tmem_ld_wait();
+        tmem_ld32(s_addr + 64, ra);                              // sub-block 2 in flight while sub-block 1 is processed
+        emit(1, rb, false);
+        tmem_ld_wait();
+        emit(2, ra, false);
         l_run = fmaf(l_run, alpha, csum);
-        m_run = m_new;
-        alpha_prev = alpha;
+        m_run = m_c;
         fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
         tc_fence_before();
         mbar_arrive(&p_full[g]);
         mbar_arrive(&s_empty[g][sb]);
+        if (kc > 0) fold_o(kc - 1);
+        alpha_prev = alpha;
       }
+      wait_o(NCH - 1);
       fold_o(NCH - 1);
       // ---- normalise and store: 32 (padded) head channels of one token ----
       const float inv = 1.f / l_run;
