@@ -144,12 +144,15 @@ int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st);
 struct AttnTcArgs {
   const void* qkv; int pitch;
   int B, H, W, heads, head_dim, ws, ows;
-  const float* bias_l2;              // (heads, 1536): compact table * log2(e), zero padded (launch_bias_l2)
+  const float* bias_l2;              // (heads, 39 x 48): compact table * log2(e), rows zero padded (launch_bias_l2)
   void* out; int out_pitch;
 };
 int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st);
 bool attn_tc_supported(const AttnTcArgs& a);
-constexpr int ATTN_TC_DP = 32, ATTN_TC_BIAS_FLOATS = 1536;
+// bias table in shared memory: 39 rows (dy) at a pitch of 48 floats -- pitch = 16 (mod 32) puts the two query rows a
+// warp covers (lanes 0-15 / 16-31, addresses 48 floats apart) on disjoint bank halves, so the per-key bias read is
+// conflict free (pitch 39 was 2-way conflicted on 9 of the 32 banks)
+constexpr int ATTN_TC_DP = 32, ATTN_TC_BIAS_PITCH = 48, ATTN_TC_BIAS_FLOATS = 39 * ATTN_TC_BIAS_PITCH;
 // pack-time helpers for the head-padded layout (tc_attn.cu)
 int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
                              cudaStream_t st);

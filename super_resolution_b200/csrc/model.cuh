@@ -55,7 +55,7 @@ struct OcabW {
   ConvW qkv_tc, proj_tc;
   ConvW focus0, focus1;            // HATX focus head: 1x1 C -> C/4 (GELU) -> 1 (hatx_arch.py:355-361)
   ConvW q_tc, kv_tc;               // ocab_esc_enable: separate head-padded q / kv GEMMs (different inputs)
-  float* bias_l2 = nullptr;        // (heads, 1536)
+  float* bias_l2 = nullptr;        // (heads, ATTN_TC_BIAS_FLOATS)
   ConvW proj, mlp0, mlp2;
   EscW esc;
   int heads = 0;

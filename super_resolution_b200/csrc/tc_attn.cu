@@ -12,13 +12,13 @@
 // with TMA out-of-bounds zero fill standing in for the unfold padding -- no unfold tensor, no S matrix in HBM
 // (reference: 906 MB of fp32 logits at the bench config).
 // A persistent CTA walks (window, head) units.  Warp roles (320 threads):
-//   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (8-stage ring, prefetches across units)
+//   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (6-stage ring, prefetches across units)
 //   warp 1   MMA issuer:   S[g] = Q[g] K_c^T  (M128 N96 K32)  and  O[g] = P[g] V_c  (M128 N32 K96)
 //   warps 2-5 / 6-9  softmax warpgroups g = 0/1, one query row per thread (rows 0-127 / 128-255):
 //            one pass per 96-key chunk: S*log2e + bias, exp2 against the chunk's reference exponent (running
 //            reference or the maximum of the chunk's first 32 logits), row sum, P as bf16 into shared memory in the
-//            UMMA K-major layout; the per-chunk O (fp32, TMEM) is folded into registers with the usual online-softmax
-//            rescale, so nothing is ever renormalised in TMEM.
+//            UMMA K-major layout (double buffered); the per-chunk O (fp32, TMEM) is folded into registers with the usual
+//            online-softmax rescale, so nothing is ever renormalised in TMEM.
 // TMEM: S double-buffered per warpgroup (4 x 96 columns) + O double-buffered per warpgroup (4 x 32) = 512.
 #include "kernels.cuh"
 #include "tc_common.cuh"
@@ -30,20 +30,22 @@ using namespace tc;
 namespace {
 constexpr int AT_THREADS = 320;
 constexpr int WS = 16, OWS = 24, PADW = 4, DP = 32, TN = 39;     // window, overlap window, ring, padded head dim, 16+24-1
+constexpr int BP = ATTN_TC_BIAS_PITCH;                           // bias table row pitch in shared memory (see kernels.cuh)
 constexpr int KC = 96, NCH = 6, KROWS = 4;                       // keys per chunk (4 key rows), chunks per unit
-constexpr int KV_STAGES = 8;
-constexpr int Q_BYTES = 256 * 64, BIAS_FLOATS = 1536, BIAS_BYTES = BIAS_FLOATS * 4;
-constexpr int QST_BYTES = Q_BYTES + BIAS_BYTES;                  // 22528
+constexpr int KV_STAGES = 6;                                     // one unit of K/V chunks in flight
+constexpr int Q_BYTES = 256 * 64, BIAS_FLOATS = ATTN_TC_BIAS_FLOATS, BIAS_BYTES = BIAS_FLOATS * 4;
+constexpr int QST_BYTES = (Q_BYTES + BIAS_BYTES + 1023) / 1024 * 1024;   // 24576: Q tiles stay swizzle aligned
 constexpr int K_BYTES = KC * 64, KVST_BYTES = 2 * K_BYTES;       // 6144, 12288
-constexpr int P_BYTES = 3 * 128 * 64;                            // 24576 per warpgroup
-constexpr int SMEM_BYTES = 2 * QST_BYTES + KV_STAGES * KVST_BYTES + 2 * P_BYTES + 1024;
+constexpr int P_BYTES = 3 * 128 * 64;                            // 24576 per warpgroup and buffer
+constexpr int SMEM_BYTES = 2 * QST_BYTES + KV_STAGES * KVST_BYTES + 4 * P_BYTES + 1024;      // 222208
+static_assert(BIAS_BYTES % 16 == 0 && QST_BYTES % 128 == 0, "bulk copy / TMA destination alignment");
 constexpr uint32_t S_COLS = 96, O_COL0 = 384;
 constexpr float LOG2E = 1.4426950408889634f;
 
 struct AttnParams {
   int B, H, W, heads, nwx, nwy, units;
   int k_off, v_off;          // first k / v channel
-  const float* bias_l2;      // (heads, 1536): compact rel-pos bias * log2(e)
+  const float* bias_l2;      // (heads, 39 x 48): compact rel-pos bias * log2(e), rows padded to BP
   bf16* out;
   int out_pitch;
 };
@@ -58,6 +60,26 @@ __device__ __forceinline__ uint64_t make_desc_mn64(uint32_t addr) {
   d |= 4ull << 61;                      // SWIZZLE_64B
   return d;
 }
+// packed fp32 pairs: one issue slot for two lanes of work (the softmax warps are issue bound, not pipe bound)
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long*>(&a)),
+      "l"(*reinterpret_cast<unsigned long long*>(&b)), "l"(*reinterpret_cast<unsigned long long*>(&c)));
+  return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long*>(&a)),
+      "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+// byte offset of key l (0..95) of a chunk inside the bias table: 4 key rows of 24
+__device__ __forceinline__ constexpr uint32_t bias_off(int l) { return (uint32_t)((l / OWS) * BP + (l % OWS)) * 4u; }
 }  // namespace
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
@@ -66,13 +88,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __shared__ __align__(8) uint64_t q_full[2], q_empty[2];
   __shared__ __align__(8) uint64_t kv_full[KV_STAGES], kv_empty[KV_STAGES];
   __shared__ __align__(8) uint64_t s_full[2][2], s_empty[2][2];
-  __shared__ __align__(8) uint64_t p_full[2], o_full[2][2];
+  __shared__ __align__(8) uint64_t p_full[2][2], o_full[2][2];
   __shared__ uint32_t tmem_slot;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sm_q = smem;                                  // [2][Q 16 KB | bias 6 KB]
   uint8_t* sm_kv = sm_q + 2 * QST_BYTES;                 // [KV_STAGES][K 6 KB | V 6 KB]
-  uint8_t* sm_p = sm_kv + KV_STAGES * KVST_BYTES;        // [2][3 blocks of 128 rows x 64 B]
+  uint8_t* sm_p = sm_kv + KV_STAGES * KVST_BYTES;        // [2 warpgroups][2 buffers][3 blocks of 128 rows x 64 B]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -81,8 +103,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int i = 0; i < 2; i++) {
       mbar_init(&q_full[i], 1);
       mbar_init(&q_empty[i], 1 + 256);
-      mbar_init(&p_full[i], 128);
       for (int j = 0; j < 2; j++) {
+        mbar_init(&p_full[i][j], 128);
         mbar_init(&s_full[i][j], 1);
         mbar_init(&s_empty[i][j], 128);
         mbar_init(&o_full[i][j], 1);
@@ -104,21 +126,21 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   const int wins = p.nwx * p.nwy;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer =====  (runs a whole unit ahead: relaxed waits keep its polling off the issue port)
     if (elect_one()) {
       int ui = 0, kvit = 0;
       for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
         const int head = u % p.heads, win = u / p.heads;
         const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
         const int qb = ui & 1;
-        mbar_wait(&q_empty[qb], (((uint32_t)ui >> 1) & 1u) ^ 1u);
+        mbar_wait_relaxed(&q_empty[qb], (((uint32_t)ui >> 1) & 1u) ^ 1u);
         uint8_t* qs = sm_q + qb * QST_BYTES;
-        mbar_arrive_expect_tx(&q_full[qb], QST_BYTES);
+        mbar_arrive_expect_tx(&q_full[qb], Q_BYTES + BIAS_BYTES);
         tma_load_4d(qs, &tmQ, &q_full[qb], head * DP, wx * WS, wy * WS, b);
         bulk_load_1d(qs + Q_BYTES, p.bias_l2 + (size_t)head * BIAS_FLOATS, BIAS_BYTES, &q_full[qb]);
         for (int kc = 0; kc < NCH; kc++, kvit++) {
           const int st = kvit % KV_STAGES;
-          mbar_wait(&kv_empty[st], (((uint32_t)(kvit / KV_STAGES)) & 1u) ^ 1u);
+          mbar_wait_relaxed(&kv_empty[st], (((uint32_t)(kvit / KV_STAGES)) & 1u) ^ 1u);
           uint8_t* ks = sm_kv + st * KVST_BYTES;
           mbar_arrive_expect_tx(&kv_full[st], KVST_BYTES);
           const int x0 = wx * WS - PADW, y0 = wy * WS - PADW + kc * KROWS;
@@ -129,33 +151,37 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) =====
+    // One flat software pipeline over all chunks of all units of this CTA:  S(c) is issued before PV(c - 1), also
+    // across a unit boundary, so the first logits of the next unit are in TMEM while the softmax warpgroups still
+    // finish the previous one.
     if (elect_one()) {
       const uint32_t idesc_s = make_idesc_bf16(128, KC);
       const uint32_t idesc_o = make_idesc_bf16(128, DP) | (1u << 16);     // B operand MN-major
       int ui = 0, kvit = 0;
+      int pv_slot = -1, pv_kc = 0, pv_ui = 0;                             // the PV still to be issued
+      auto issue_pv = [&]() {
+        const uint32_t v_addr = smem_u32(sm_kv + pv_slot * KVST_BYTES + K_BYTES);
+        const int pb = pv_kc & 1;
+        for (int g = 0; g < 2; g++) {
+          mbar_wait(&p_full[g][pb], (uint32_t)(pv_ui * 3 + (pv_kc >> 1)) & 1u);
+          tc_fence_after();
+          const uint32_t p_addr = smem_u32(sm_p + (g * 2 + pb) * P_BYTES);
+          const uint32_t d_o = tmem_base + O_COL0 + (uint32_t)(g * 2 + pb) * DP;
+#pragma unroll
+          for (int j = 0; j < KC / 16; j++) {
+            const uint64_t ad = make_smem_desc(p_addr + (j >> 1) * 8192 + (j & 1) * 32, 64);
+            const uint64_t bd = make_desc_mn64(v_addr + j * 1024);
+            umma_bf16(d_o, ad, bd, idesc_o, j != 0 ? 1u : 0u);
+          }
+          umma_commit(&o_full[g][pb]);
+        }
+        umma_commit(&kv_empty[pv_slot]);
+      };
       for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
         const int qb = ui & 1;
         const uint32_t q_addr = smem_u32(sm_q + qb * QST_BYTES);
         mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
         tc_fence_after();
-        auto issue_pv = [&](int kc, int kvslot) {
-          const uint32_t v_addr = smem_u32(sm_kv + kvslot * KVST_BYTES + K_BYTES);
-          for (int g = 0; g < 2; g++) {
-            mbar_wait(&p_full[g], (uint32_t)(ui * NCH + kc) & 1u);
-            tc_fence_after();
-            const uint32_t p_addr = smem_u32(sm_p + g * P_BYTES);
-            const uint32_t d_o = tmem_base + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP;
-#pragma unroll
-            for (int j = 0; j < KC / 16; j++) {
-              const uint64_t ad = make_smem_desc(p_addr + (j >> 1) * 8192 + (j & 1) * 32, 64);
-              const uint64_t bd = make_desc_mn64(v_addr + j * 1024);
-              umma_bf16(d_o, ad, bd, idesc_o, j != 0 ? 1u : 0u);
-            }
-            umma_commit(&o_full[g][kc & 1]);
-          }
-          umma_commit(&kv_empty[kvslot]);
-        };
-        int prev_slot = 0;
         for (int kc = 0; kc < NCH; kc++, kvit++) {
           const int st = kvit % KV_STAGES;
           mbar_wait(&kv_full[st], ((uint32_t)(kvit / KV_STAGES)) & 1u);
@@ -175,11 +201,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             umma_commit(&s_full[g][sb]);
           }
           if (kc == NCH - 1) umma_commit(&q_empty[qb]);      // Q tile consumed once these MMAs complete
-          if (kc >= 1) issue_pv(kc - 1, prev_slot);
-          prev_slot = st;
+          if (pv_slot >= 0) issue_pv();
+          pv_slot = st; pv_kc = kc; pv_ui = ui;
         }
-        issue_pv(NCH - 1, prev_slot);
       }
+      if (pv_slot >= 0) issue_pv();
     }
   } else {
     // ===== softmax warpgroups =====
@@ -189,48 +215,51 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int qi = g * 128 + row;
     const int qy = qi / WS, qx = qi % WS;
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
-    uint8_t* prow = sm_p + g * P_BYTES + row * 64;
     const int psw = (row >> 1) & 3;                 // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
+    const float2 L2 = make_float2(LOG2E, LOG2E);
     int ui = 0;
     for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
       const int head = u % p.heads, win = u / p.heads;
       const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
       const int qb = ui & 1;
       mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
-      const float* bias_s = reinterpret_cast<const float*>(sm_q + qb * QST_BYTES + Q_BYTES) + (WS - 1 - qy) * TN +
-                            (WS - 1 - qx);
-      float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
-      float o_reg[DP];
+      // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address
+      const uint32_t bias_a = smem_u32(sm_q + qb * QST_BYTES + Q_BYTES) + (uint32_t)((WS - 1 - qy) * BP + (WS - 1 - qx)) * 4u;
+      float m_run = -INFINITY, alpha_prev = 0.f;
+      float2 l2 = make_float2(0.f, 0.f);            // row sum, even / odd keys
+      float2 o_reg[DP / 2];
 #pragma unroll
-      for (int i = 0; i < DP; i++) o_reg[i] = 0.f;
+      for (int i = 0; i < DP / 2; i++) o_reg[i] = make_float2(0.f, 0.f);
 
-      auto wait_o = [&](int kc) {      // PV of chunk kc finished: O(kc) is in TMEM and the P buffer is free again
+      auto fold_o = [&](int kc) {      // wait for PV(kc);  o_reg = o_reg * alpha(kc) + O(kc)
         mbar_wait(&o_full[g][kc & 1], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
         tc_fence_after();
-      };
-      auto fold_o = [&](int kc) {      // o_reg = o_reg * alpha(kc) + O(kc)
         uint32_t r[32];
         tmem_ld32(tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP, r);
         tmem_ld_wait();
+        const float2 a2 = make_float2(alpha_prev, alpha_prev);
 #pragma unroll
-        for (int i = 0; i < DP; i++) o_reg[i] = fmaf(o_reg[i], alpha_prev, __uint_as_float(r[i]));
+        for (int i = 0; i < DP / 2; i++)
+          o_reg[i] = ffma2(o_reg[i], a2, make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])));
       };
 
-      // ONE pass per 96-key chunk (round 2; round 1 ran two passes with the logits parked back in TMEM): the reference
-      // exponent of a chunk is m_c = max(running reference, max of the chunk's FIRST 32 logits) -- not its true maximum,
-      // which would need all 96 logits before the first exp2.  Softmax is shift invariant, so any reference gives the
-      // same result as long as nothing overflows: p = 2^(v - m_c) can exceed 1 by however much the last 64 logits of the
-      // chunk exceed the first 32, bf16 has the exponent range of fp32, and the exponent is clamped at 126 (a row whose
-      // logits spread by more than 2^126 inside one chunk is a hard max anyway).  TMEM loads are software pipelined
-      // (sub-block s + 1 is in flight while s is processed); the bias row comes through ld.shared with immediate offsets.
-      const uint32_t bias_a = smem_u32(bias_s);
-      auto lds_f = [](uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; };
+      // ONE pass per 96-key chunk (round 1 ran two passes with the logits parked back in TMEM): the reference exponent
+      // of a chunk is m_c = max(running reference, max of the chunk's FIRST 32 logits) -- not its true maximum, which
+      // would need all 96 logits before the first exp2.  Softmax is shift invariant, so any reference gives the same
+      // result as long as nothing overflows: p = 2^(v - m_c) exceeds 1 by however much the last 64 logits of the chunk
+      // exceed the first 32, P is bf16 (the exponent range of fp32) and the sums are fp32; a spread of ~100 octaves or
+      // more inside one chunk shows up as a huge row sum and sends the warp through the exact two-pass path below.
+      // TMEM loads are software pipelined (sub-block s + 1 in flight while s is processed), the bias comes through
+      // ld.shared at immediate offsets, the arithmetic is packed f32x2 (FFMA2 / FADD2: half the issue slots), P is
+      // double buffered so PV(kc) only has to finish before chunk kc + 2 is written, and O(kc - 1) is folded after
+      // P(kc) has been handed over.
       for (int kc = 0; kc < NCH; kc++) {
         const int sb = kc & 1;
         const uint32_t s_addr = tmem_base + lane_sel + (uint32_t)(g * 2 + sb) * S_COLS;
         mbar_wait(&s_full[g][sb], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
         tc_fence_after();
-        const uint32_t bchunk = bias_a + (uint32_t)(kc * KROWS * TN) * 4u;
+        const uint32_t bchunk = bias_a + (uint32_t)(kc * KROWS * BP) * 4u;
+        const uint32_t prow = smem_u32(sm_p) + (uint32_t)((g * 2 + sb) * P_BYTES + row * 64);
         uint32_t ra[32], rb[32];
         tmem_ld32(s_addr, ra);
         tmem_ld_wait();
@@ -238,39 +267,33 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // logits of sub-block 0 in the log2 domain, their maximum -> this chunk's reference
         float smax = -INFINITY;
 #pragma unroll
-        for (int j = 0; j < 32; j++) {
-          const float v = fmaf(__uint_as_float(ra[j]), LOG2E, lds_f(bchunk + (uint32_t)((j / OWS) * TN + (j % OWS)) * 4u));
-          smax = fmaxf(smax, v);
-          ra[j] = __float_as_uint(v);
+        for (int j = 0; j < 16; j++) {
+          const float2 v = ffma2(make_float2(__uint_as_float(ra[2 * j]), __uint_as_float(ra[2 * j + 1])), L2,
+                                 make_float2(lds_f32(bchunk + bias_off(2 * j)), lds_f32(bchunk + bias_off(2 * j + 1))));
+          smax = fmaxf(smax, fmaxf(v.x, v.y));
+          ra[2 * j] = __float_as_uint(v.x); ra[2 * j + 1] = __float_as_uint(v.y);
         }
-        const float m_c = fmaxf(m_run, smax);
-        const float alpha = ex2_approx(m_run - m_c);             // 0 for the first chunk (m_run = -inf)
-        // PV of the previous chunk must have finished reading P before it is overwritten; its O is folded at the end
-        // of this iteration (O is double buffered), after P of this chunk has been handed to the tensor core
-        if (kc > 0) wait_o(kc - 1);
-        float csum = 0.f;
+        float m_c = fmaxf(m_run, smax);
+        float alpha = ex2_approx(m_run - m_c);                   // 0 for the first chunk (m_run = -inf)
+        float2 nm = make_float2(-m_c, -m_c);
+        float2 cs = make_float2(0.f, 0.f);
         auto emit = [&](const int sub, uint32_t (&r)[32], const bool logits_ready) __attribute__((always_inline)) {
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 16; j++) {
-            float v0, v1;
-            if (logits_ready) {
-              v0 = __uint_as_float(r[2 * j]); v1 = __uint_as_float(r[2 * j + 1]);
-            } else {
-              const int l0 = sub * 32 + 2 * j, l1 = l0 + 1;
-              v0 = fmaf(__uint_as_float(r[2 * j]), LOG2E, lds_f(bchunk + (uint32_t)((l0 / OWS) * TN + (l0 % OWS)) * 4u));
-              v1 = fmaf(__uint_as_float(r[2 * j + 1]), LOG2E, lds_f(bchunk + (uint32_t)((l1 / OWS) * TN + (l1 % OWS)) * 4u));
-            }
-            const float p0 = ex2_approx(fminf(v0 - m_c, 126.f));
-            const float p1 = ex2_approx(fminf(v1 - m_c, 126.f));
-            csum += p0 + p1;
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+            float2 v = make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            if (!logits_ready)
+              v = ffma2(v, L2, make_float2(lds_f32(bchunk + bias_off(sub * 32 + 2 * j)), lds_f32(bchunk + bias_off(sub * 32 + 2 * j + 1))));
+            v = fadd2(v, nm);
+            const float2 pp = make_float2(ex2_approx(v.x), ex2_approx(v.y));
+            cs = fadd2(cs, pp);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(pp.x, pp.y);
             pk[j] = *reinterpret_cast<uint32_t*>(&h2);
           }
-          uint8_t* blk = prow + sub * 8192;
 #pragma unroll
           for (int c = 0; c < 4; c++)
-            *reinterpret_cast<uint4*>(blk + ((c ^ psw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (uint32_t)(sub * 8192) + (uint32_t)((c ^ psw) << 4)),
+                         "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3]) : "memory");
         };
         emit(0, ra, true);
         tmem_ld_wait();
@@ -278,19 +301,53 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         emit(1, rb, false);
         tmem_ld_wait();
         emit(2, ra, false);
-        l_run = fmaf(l_run, alpha, csum);
+        // Overflow guard (never taken on image-like data): a logit of the last 64 keys exceeded the reference by ~100
+        // octaves, so the chunk's row sum is 2^100 or more (or inf / NaN) -- too close to where P (bf16), the PV
+        // accumulator or the running sums overflow.  Redo the chunk for the whole warp (tcgen05.ld is warp collective)
+        // with the exact maximum of all 96 logits; the logits are still in TMEM and P has not been handed over.
+        if (__any_sync(0xffffffffu, !(cs.x + cs.y < 1.2676506e30f))) {
+          float mx = m_run;
+#pragma unroll 1
+          for (int sub = 0; sub < 3; sub++) {
+            tmem_ld32(s_addr + sub * 32, ra);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(ra[j]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + j))));
+          }
+          m_c = mx;
+          alpha = ex2_approx(m_run - m_c);
+          cs = make_float2(0.f, 0.f);
+#pragma unroll 1
+          for (int sub = 0; sub < 3; sub++) {
+            tmem_ld32(s_addr + sub * 32, ra);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              const float p0 = ex2_approx(fmaf(__uint_as_float(ra[2 * j]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j))) - m_c);
+              const float p1 = ex2_approx(fmaf(__uint_as_float(ra[2 * j + 1]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j + 1))) - m_c);
+              cs.x += p0; cs.y += p1;
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+              pk[j] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (uint32_t)(sub * 8192) + (uint32_t)((c ^ psw) << 4)),
+                           "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3]) : "memory");
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&s_empty[g][sb]);                            // the logits are consumed: S(kc + 2) may overwrite them
+        l2 = ffma2(l2, make_float2(alpha, alpha), cs);
         m_run = m_c;
         fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
-        tc_fence_before();
-        mbar_arrive(&p_full[g]);
-        mbar_arrive(&s_empty[g][sb]);
-        if (kc > 0) fold_o(kc - 1);
+        mbar_arrive(&p_full[g][sb]);
+        if (kc > 0) fold_o(kc - 1);     // also: PV(kc - 1) done -> its P buffer is free for chunk kc + 1
         alpha_prev = alpha;
       }
-      wait_o(NCH - 1);
       fold_o(NCH - 1);
       // ---- normalise and store: 32 (padded) head channels of one token ----
-      const float inv = 1.f / l_run;
+      const float inv = 1.f / (l2.x + l2.y);
       const size_t tok = ((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx;
       bf16* orow = p.out + tok * p.out_pitch + head * DP;
 #pragma unroll
@@ -298,7 +355,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         uint4 t;
         __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
 #pragma unroll
-        for (int j = 0; j < 4; j++) h2[j] = __floats2bfloat162_rn(o_reg[8 * c + 2 * j] * inv, o_reg[8 * c + 2 * j + 1] * inv);
+        for (int j = 0; j < 4; j++) h2[j] = __floats2bfloat162_rn(o_reg[4 * c + j].x * inv, o_reg[4 * c + j].y * inv);
         reinterpret_cast<uint4*>(orow)[c] = t;
       }
       mbar_arrive(&q_empty[qb]);        // bias table of this stage consumed
@@ -403,7 +460,8 @@ __global__ void bias_l2_kernel(const float* __restrict__ compact, int heads, int
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= heads * BIAS_FLOATS) return;
   int h = idx / BIAS_FLOATS, i = idx % BIAS_FLOATS;
-  dst[idx] = i < rows ? compact[(size_t)h * rows + i] * LOG2E : 0.f;
+  int r = i / BP, c = i % BP;
+  dst[idx] = c < TN ? compact[(size_t)h * rows + r * TN + c] * LOG2E : 0.f;
 }
 
 int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
@@ -429,7 +487,7 @@ int launch_pack_cols_headpad(const void* src, int dt, int O, int C, int heads, b
 }
 int launch_bias_l2(const float* compact, int heads, int ws, int ows, float* dst, cudaStream_t st) {
   int rows = (ws + ows - 1) * (ws + ows - 1);
-  HB_REQUIRE(rows <= BIAS_FLOATS, HATB200_EUNSUPPORTED, "bias_l2: table too large");
+  HB_REQUIRE(rows == TN * TN, HATB200_EUNSUPPORTED, "bias_l2: window 16 / overlap window 24 only");
   bias_l2_kernel<<<(heads * BIAS_FLOATS + 255) / 256, 256, 0, st>>>(compact, heads, rows, dst);
   HB_CHECK_LAUNCH();
   return 0;

@@ -168,12 +168,18 @@ def test_ocab_attention_tcgen05(geom):
     _attention_case(torch.bfloat16, geom, 1)
 
 
-def _attention_case(dtype, geom, use_tc):
+def test_ocab_attention_tcgen05_wide_logit_spread():
+    """Logits spread over hundreds of octaves inside one 96-key chunk: the one-pass softmax (reference exponent from
+    the chunk's first 32 keys) overflows and must take its exact two-pass path; the result is a near-hard max."""
+    _attention_case(torch.bfloat16, (2, 32, 48, 180, 6), 1, qscale=40.0)
+
+
+def _attention_case(dtype, geom, use_tc, qscale=1.0):
     B, H, W, Cn, heads = geom
     ws, ows = 16, 24
     g = torch.Generator().manual_seed(3)
     qkv = torch.randn(B, H, W, 3 * Cn, generator=g)
-    qkv[..., :Cn] *= (Cn // heads) ** -0.5
+    qkv[..., :Cn] *= (Cn // heads) ** -0.5 * qscale
     table = torch.randn(heads, 39 * 39, generator=g) * 0.5
     src = qkv.bfloat16().float() if dtype == torch.bfloat16 else qkv
     ref = _attention_reference(src, B, H, W, Cn, heads, ws, ows, table)
