@@ -15,11 +15,11 @@
 //   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (6-stage ring, prefetches across units)
 //   warp 1   MMA issuer:   S[g] = Q[g] K_c^T  (M128 N96 K32)  and  O[g] = P[g] V_c  (M128 N32 K96)
 //   warps 2-5 / 6-9  softmax warpgroups g = 0/1, one query row per thread (rows 0-127 / 128-255):
-//            one pass per 96-key chunk: S*log2e + bias, exp2 against the chunk's reference exponent (running
-//            reference or the maximum of the chunk's first 32 logits), row sum, P as bf16 into shared memory in the
-//            UMMA K-major layout (double buffered); the per-chunk O (fp32, TMEM) is folded into registers with the usual
-//            online-softmax rescale, so nothing is ever renormalised in TMEM.
-// TMEM: S double-buffered per warpgroup (4 x 96 columns) + O double-buffered per warpgroup (4 x 32) = 512.
+//            one pass per 96-key chunk: S*log2e + bias, exp2 against a fixed per-row reference exponent (the maximum
+//            of the row's first 32 logits), row sum, P as bf16 into shared memory in the UMMA K-major layout (double
+//            buffered).  O accumulates over the six chunks in TMEM (no per-chunk rescale: a fixed reference needs none);
+//            a chunk that would overflow takes the exact `rescale_chunk` path (see the kernel).
+// TMEM: S double-buffered per warpgroup (4 x 96 columns) + O per warpgroup, alternating per unit (4 x 32) = 512.
 #include "kernels.cuh"
 #include "tc_common.cuh"
 
@@ -88,7 +88,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __shared__ __align__(8) uint64_t q_full[2], q_empty[2];
   __shared__ __align__(8) uint64_t kv_full[KV_STAGES], kv_empty[KV_STAGES];
   __shared__ __align__(8) uint64_t s_full[2][2], s_empty[2][2];
-  __shared__ __align__(8) uint64_t p_full[2][2], o_full[2][2];
+  __shared__ __align__(8) uint64_t p_full[2][2], pv_done[2][2];
   __shared__ uint32_t tmem_slot;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -107,7 +107,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_init(&p_full[i][j], 128);
         mbar_init(&s_full[i][j], 1);
         mbar_init(&s_empty[i][j], 128);
-        mbar_init(&o_full[i][j], 1);
+        mbar_init(&pv_done[i][j], 1);
       }
     }
     for (int i = 0; i < KV_STAGES; i++) {
@@ -159,21 +159,21 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       const uint32_t idesc_o = make_idesc_bf16(128, DP) | (1u << 16);     // B operand MN-major
       int ui = 0, kvit = 0;
       int pv_slot = -1, pv_kc = 0, pv_ui = 0;                             // the PV still to be issued
-      auto issue_pv = [&]() {
+      auto issue_pv = [&]() {             // O(unit) += P(kc) V(kc): accumulates over the six chunks of a unit in TMEM
         const uint32_t v_addr = smem_u32(sm_kv + pv_slot * KVST_BYTES + K_BYTES);
         const int pb = pv_kc & 1;
         for (int g = 0; g < 2; g++) {
           mbar_wait(&p_full[g][pb], (uint32_t)(pv_ui * 3 + (pv_kc >> 1)) & 1u);
           tc_fence_after();
           const uint32_t p_addr = smem_u32(sm_p + (g * 2 + pb) * P_BYTES);
-          const uint32_t d_o = tmem_base + O_COL0 + (uint32_t)(g * 2 + pb) * DP;
+          const uint32_t d_o = tmem_base + O_COL0 + (uint32_t)(g * 2 + (pv_ui & 1)) * DP;
 #pragma unroll
           for (int j = 0; j < KC / 16; j++) {
             const uint64_t ad = make_smem_desc(p_addr + (j >> 1) * 8192 + (j & 1) * 32, 64);
             const uint64_t bd = make_desc_mn64(v_addr + j * 1024);
-            umma_bf16(d_o, ad, bd, idesc_o, j != 0 ? 1u : 0u);
+            umma_bf16(d_o, ad, bd, idesc_o, (j != 0 || pv_kc != 0) ? 1u : 0u);
           }
-          umma_commit(&o_full[g][pb]);
+          umma_commit(&pv_done[g][pb]);
         }
         umma_commit(&kv_empty[pv_slot]);
       };
@@ -225,34 +225,21 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
       // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address
       const uint32_t bias_a = smem_u32(sm_q + qb * QST_BYTES + Q_BYTES) + (uint32_t)((WS - 1 - qy) * BP + (WS - 1 - qx)) * 4u;
-      float m_run = -INFINITY, alpha_prev = 0.f;
+      const uint32_t o_addr = tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (ui & 1)) * DP;
+      float m_ref = 0.f;
       float2 l2 = make_float2(0.f, 0.f);            // row sum, even / odd keys
-      float2 o_reg[DP / 2];
-#pragma unroll
-      for (int i = 0; i < DP / 2; i++) o_reg[i] = make_float2(0.f, 0.f);
 
-      auto fold_o = [&](int kc) {      // wait for PV(kc);  o_reg = o_reg * alpha(kc) + O(kc)
-        mbar_wait(&o_full[g][kc & 1], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
-        tc_fence_after();
-        uint32_t r[32];
-        tmem_ld32(tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (kc & 1)) * DP, r);
-        tmem_ld_wait();
-        const float2 a2 = make_float2(alpha_prev, alpha_prev);
-#pragma unroll
-        for (int i = 0; i < DP / 2; i++)
-          o_reg[i] = ffma2(o_reg[i], a2, make_float2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1])));
-      };
-
-      // ONE pass per 96-key chunk (round 1 ran two passes with the logits parked back in TMEM): the reference exponent
-      // of a chunk is m_c = max(running reference, max of the chunk's FIRST 32 logits) -- not its true maximum, which
-      // would need all 96 logits before the first exp2.  Softmax is shift invariant, so any reference gives the same
-      // result as long as nothing overflows: p = 2^(v - m_c) exceeds 1 by however much the last 64 logits of the chunk
-      // exceed the first 32, P is bf16 (the exponent range of fp32) and the sums are fp32; a spread of ~100 octaves or
-      // more inside one chunk shows up as a huge row sum and sends the warp through the exact two-pass path below.
+      // ONE pass per 96-key chunk against a FIXED reference exponent per row (round 1: two passes per chunk with the
+      // logits parked back in TMEM, and an online-softmax rescale of O per chunk).  Softmax is shift invariant, so
+      // the reference does not have to be the row maximum: m_ref = max of the row's first 32 logits, p = 2^(v - m_ref)
+      // for all 576 keys, P in bf16 (the exponent range of fp32), row sum and O in fp32 -- any logit up to ~60
+      // octaves above the reference is exact.  With a fixed reference there is no rescale, so the tensor core
+      // accumulates O over the six chunks in TMEM and the softmax warps never touch it until the unit is done.
+      // Guard: a chunk whose row sum reaches 2^60 (or is inf / NaN) sends the warp through `rescale_chunk` -- exact
+      // maximum of the chunk, P recomputed, O and the row sum rescaled in place.  Not taken on image-like data.
       // TMEM loads are software pipelined (sub-block s + 1 in flight while s is processed), the bias comes through
-      // ld.shared at immediate offsets, the arithmetic is packed f32x2 (FFMA2 / FADD2: half the issue slots), P is
-      // double buffered so PV(kc) only has to finish before chunk kc + 2 is written, and O(kc - 1) is folded after
-      // P(kc) has been handed over.
+      // ld.shared at immediate offsets, the arithmetic is packed f32x2 (FFMA2 / FADD2: half the issue slots), and P is
+      // double buffered so PV(kc) only has to finish before chunk kc + 2 is written.
       for (int kc = 0; kc < NCH; kc++) {
         const int sb = kc & 1;
         const uint32_t s_addr = tmem_base + lane_sel + (uint32_t)(g * 2 + sb) * S_COLS;
@@ -264,19 +251,23 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         tmem_ld32(s_addr, ra);
         tmem_ld_wait();
         tmem_ld32(s_addr + 32, rb);                              // in flight while sub-block 0 is processed
-        // logits of sub-block 0 in the log2 domain, their maximum -> this chunk's reference
-        float smax = -INFINITY;
+        if (kc == 0) {
+          // logits of sub-block 0 in the log2 domain; their maximum is this row's reference
+          float smax = -INFINITY;
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-          const float2 v = ffma2(make_float2(__uint_as_float(ra[2 * j]), __uint_as_float(ra[2 * j + 1])), L2,
-                                 make_float2(lds_f32(bchunk + bias_off(2 * j)), lds_f32(bchunk + bias_off(2 * j + 1))));
-          smax = fmaxf(smax, fmaxf(v.x, v.y));
-          ra[2 * j] = __float_as_uint(v.x); ra[2 * j + 1] = __float_as_uint(v.y);
+          for (int j = 0; j < 16; j++) {
+            const float2 v = ffma2(make_float2(__uint_as_float(ra[2 * j]), __uint_as_float(ra[2 * j + 1])), L2,
+                                   make_float2(lds_f32(bchunk + bias_off(2 * j)), lds_f32(bchunk + bias_off(2 * j + 1))));
+            smax = fmaxf(smax, fmaxf(v.x, v.y));
+            ra[2 * j] = __float_as_uint(v.x); ra[2 * j + 1] = __float_as_uint(v.y);
+          }
+          m_ref = smax;
         }
-        float m_c = fmaxf(m_run, smax);
-        float alpha = ex2_approx(m_run - m_c);                   // 0 for the first chunk (m_run = -inf)
-        float2 nm = make_float2(-m_c, -m_c);
+        const float2 nm = make_float2(-m_ref, -m_ref);
         float2 cs = make_float2(0.f, 0.f);
+        // P buffer `sb` was last read by PV(kc - 2) (of the previous unit for kc < 2)
+        const int pvn = ui * 3 + (kc >> 1);                      // completions of pv_done[g][sb] needed so far
+        if (pvn > 0) mbar_wait(&pv_done[g][sb], (uint32_t)(pvn - 1) & 1u);
         auto emit = [&](const int sub, uint32_t (&r)[32], const bool logits_ready) __attribute__((always_inline)) {
           uint32_t pk[16];
 #pragma unroll
@@ -295,18 +286,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (uint32_t)(sub * 8192) + (uint32_t)((c ^ psw) << 4)),
                          "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3]) : "memory");
         };
-        emit(0, ra, true);
+        if (kc == 0) emit(0, ra, true); else emit(0, ra, false);
         tmem_ld_wait();
         tmem_ld32(s_addr + 64, ra);                              // sub-block 2 in flight while sub-block 1 is processed
         emit(1, rb, false);
         tmem_ld_wait();
         emit(2, ra, false);
-        // Overflow guard (never taken on image-like data): a logit of the last 64 keys exceeded the reference by ~100
-        // octaves, so the chunk's row sum is 2^100 or more (or inf / NaN) -- too close to where P (bf16), the PV
-        // accumulator or the running sums overflow.  Redo the chunk for the whole warp (tcgen05.ld is warp collective)
-        // with the exact maximum of all 96 logits; the logits are still in TMEM and P has not been handed over.
-        if (__any_sync(0xffffffffu, !(cs.x + cs.y < 1.2676506e30f))) {
-          float mx = m_run;
+        if (__any_sync(0xffffffffu, !(cs.x + cs.y < 1.1529215e18f))) {
+          // ---- rescale_chunk (rare): exact maximum, P again, O and the row sum moved to the new reference ----
+          float mx = m_ref;
 #pragma unroll 1
           for (int sub = 0; sub < 3; sub++) {
             tmem_ld32(s_addr + sub * 32, ra);
@@ -314,8 +302,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
             for (int j = 0; j < 32; j++) mx = fmaxf(mx, fmaf(__uint_as_float(ra[j]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + j))));
           }
-          m_c = mx;
-          alpha = ex2_approx(m_run - m_c);
+          const float alpha = ex2_approx(m_ref - mx);            // 1 for the rows of the warp that did not overflow
+          m_ref = mx;
           cs = make_float2(0.f, 0.f);
 #pragma unroll 1
           for (int sub = 0; sub < 3; sub++) {
@@ -324,8 +312,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             uint32_t pk[16];
 #pragma unroll
             for (int j = 0; j < 16; j++) {
-              const float p0 = ex2_approx(fmaf(__uint_as_float(ra[2 * j]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j))) - m_c);
-              const float p1 = ex2_approx(fmaf(__uint_as_float(ra[2 * j + 1]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j + 1))) - m_c);
+              const float p0 = ex2_approx(fmaf(__uint_as_float(ra[2 * j]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j))) - mx);
+              const float p1 = ex2_approx(fmaf(__uint_as_float(ra[2 * j + 1]), LOG2E, lds_f32(bchunk + bias_off(sub * 32 + 2 * j + 1))) - mx);
               cs.x += p0; cs.y += p1;
               __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
               pk[j] = *reinterpret_cast<uint32_t*>(&h2);
@@ -335,18 +323,30 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (uint32_t)(sub * 8192) + (uint32_t)((c ^ psw) << 4)),
                            "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3]) : "memory");
           }
+          l2.x *= alpha; l2.y *= alpha;
+          if (kc > 0) {                  // O holds chunks 0 .. kc - 1 at the old reference; PV(kc - 1) must have landed
+            mbar_wait(&pv_done[g][sb ^ 1], (uint32_t)(ui * 3 + ((kc - 1) >> 1)) & 1u);
+            tc_fence_after();
+            tmem_ld32(o_addr, ra);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j++) ra[j] = __float_as_uint(__uint_as_float(ra[j]) * alpha);
+            tmem_st32(o_addr, ra);
+            tmem_st_wait();
+          }
         }
+        l2 = fadd2(l2, cs);
         tc_fence_before();
         mbar_arrive(&s_empty[g][sb]);                            // the logits are consumed: S(kc + 2) may overwrite them
-        l2 = ffma2(l2, make_float2(alpha, alpha), cs);
-        m_run = m_c;
         fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
         mbar_arrive(&p_full[g][sb]);
-        if (kc > 0) fold_o(kc - 1);     // also: PV(kc - 1) done -> its P buffer is free for chunk kc + 1
-        alpha_prev = alpha;
       }
-      fold_o(NCH - 1);
-      // ---- normalise and store: 32 (padded) head channels of one token ----
+      // ---- O of the unit is complete once PV(5) has landed: normalise and store 32 (padded) head channels ----
+      mbar_wait(&pv_done[g][1], (uint32_t)(ui * 3 + 2) & 1u);
+      tc_fence_after();
+      uint32_t ro[32];
+      tmem_ld32(o_addr, ro);
+      tmem_ld_wait();
       const float inv = 1.f / (l2.x + l2.y);
       const size_t tok = ((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx;
       bf16* orow = p.out + tok * p.out_pitch + head * DP;
@@ -355,7 +355,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         uint4 t;
         __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
 #pragma unroll
-        for (int j = 0; j < 4; j++) h2[j] = __floats2bfloat162_rn(o_reg[4 * c + j].x * inv, o_reg[4 * c + j].y * inv);
+        for (int j = 0; j < 4; j++)
+          h2[j] = __floats2bfloat162_rn(__uint_as_float(ro[8 * c + 2 * j]) * inv, __uint_as_float(ro[8 * c + 2 * j + 1]) * inv);
         reinterpret_cast<uint4*>(orow)[c] = t;
       }
       mbar_arrive(&q_empty[qb]);        // bias table of this stage consumed
