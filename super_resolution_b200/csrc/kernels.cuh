@@ -144,7 +144,7 @@ int launch_attn_simt(int dt, const AttnArgs& a, cudaStream_t st);
 struct AttnTcArgs {
   const void* qkv; int pitch;
   int B, H, W, heads, head_dim, ws, ows;
-  const float* bias_l2;              // (heads, 39 x 48): compact table * log2(e), rows zero padded (launch_bias_l2)
+  const float* bias_l2;              // (heads, 2, 39 x 48): compact table * log2(e), rows zero padded, + shifted copy (launch_bias_l2)
   void* out; int out_pitch;
 };
 int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st);
@@ -152,7 +152,10 @@ bool attn_tc_supported(const AttnTcArgs& a);
 // bias table in shared memory: 39 rows (dy) at a pitch of 48 floats -- pitch = 16 (mod 32) puts the two query rows a
 // warp covers (lanes 0-15 / 16-31, addresses 48 floats apart) on disjoint bank halves, so the per-key bias read is
 // conflict free (pitch 39 was 2-way conflicted on 9 of the 32 banks)
-constexpr int ATTN_TC_DP = 32, ATTN_TC_BIAS_PITCH = 48, ATTN_TC_BIAS_FLOATS = 39 * ATTN_TC_BIAS_PITCH;
+// Two copies per head, the second shifted by one float (B[j] = A[j + 1]): queries with odd x read pairs of A, queries
+// with even x pairs of B, so every thread's (kx, kx + 1) bias pair is one aligned 8-byte load.
+constexpr int ATTN_TC_DP = 32, ATTN_TC_BIAS_PITCH = 48, ATTN_TC_BIAS_TABLE = 39 * ATTN_TC_BIAS_PITCH;
+constexpr int ATTN_TC_BIAS_FLOATS = 2 * ATTN_TC_BIAS_TABLE;
 // pack-time helpers for the head-padded layout (tc_attn.cu)
 int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
                              cudaStream_t st);

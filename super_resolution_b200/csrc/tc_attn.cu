@@ -7,12 +7,13 @@
 //
 // B200 mapping.  The qkv GEMM writes a head-padded layout (head_dim 30 -> 32: q | k | v, each heads x 32
 // channels, pad channels exactly zero), so every operand tile is a TMA box of the token tensor:
-//   Q   {32 ch, 16 x, 16 y}              -> 256 rows x 64 B  (K-major A operand, SWIZZLE_64B)
+//   Q   {32 ch, 8 x of one parity, 16 y} -> 128 rows x 64 B  (K-major A operand, SWIZZLE_64B), twice: warpgroup 0
+//                                            takes the even query columns of the window, warpgroup 1 the odd ones
 //   K,V {32 ch, 24 x, 4 y} per key chunk ->  96 rows x 64 B  (K: K-major B operand; V: MN-major B operand)
 // with TMA out-of-bounds zero fill standing in for the unfold padding -- no unfold tensor, no S matrix in HBM
 // (reference: 906 MB of fp32 logits at the bench config).
 // A persistent CTA walks (window, head) units.  Warp roles (320 threads):
-//   warp 0   TMA producer: Q + bias table (2 stages), K/V chunks (6-stage ring, prefetches across units)
+//   warp 0   TMA producer: Q + bias tables (2 stages), K/V chunks (5-stage ring, prefetches across units)
 //   warp 1   MMA issuer:   S[g] = Q[g] K_c^T  (M128 N96 K32)  and  O[g] = P[g] V_c  (M128 N32 K96)
 //   warps 2-5 / 6-9  softmax warpgroups g = 0/1, one query row per thread (rows 0-127 / 128-255):
 //            one pass per 96-key chunk: S*log2e + bias, exp2 against a fixed per-row reference exponent (the maximum
@@ -32,12 +33,12 @@ constexpr int AT_THREADS = 320;
 constexpr int WS = 16, OWS = 24, PADW = 4, DP = 32, TN = 39;     // window, overlap window, ring, padded head dim, 16+24-1
 constexpr int BP = ATTN_TC_BIAS_PITCH;                           // bias table row pitch in shared memory (see kernels.cuh)
 constexpr int KC = 96, NCH = 6, KROWS = 4;                       // keys per chunk (4 key rows), chunks per unit
-constexpr int KV_STAGES = 6;                                     // one unit of K/V chunks in flight
+constexpr int KV_STAGES = 5;
 constexpr int Q_BYTES = 256 * 64, BIAS_FLOATS = ATTN_TC_BIAS_FLOATS, BIAS_BYTES = BIAS_FLOATS * 4;
-constexpr int QST_BYTES = (Q_BYTES + BIAS_BYTES + 1023) / 1024 * 1024;   // 24576: Q tiles stay swizzle aligned
+constexpr int QST_BYTES = (Q_BYTES + BIAS_BYTES + 1023) / 1024 * 1024;   // 31744: Q tiles stay swizzle aligned
 constexpr int K_BYTES = KC * 64, KVST_BYTES = 2 * K_BYTES;       // 6144, 12288
 constexpr int P_BYTES = 3 * 128 * 64;                            // 24576 per warpgroup and buffer
-constexpr int SMEM_BYTES = 2 * QST_BYTES + KV_STAGES * KVST_BYTES + 4 * P_BYTES + 1024;      // 222208
+constexpr int SMEM_BYTES = 2 * QST_BYTES + KV_STAGES * KVST_BYTES + 4 * P_BYTES + 1024;      // 224256
 static_assert(BIAS_BYTES % 16 == 0 && QST_BYTES % 128 == 0, "bulk copy / TMA destination alignment");
 constexpr uint32_t S_COLS = 96, O_COL0 = 384;
 constexpr float LOG2E = 1.4426950408889634f;
@@ -45,7 +46,7 @@ constexpr float LOG2E = 1.4426950408889634f;
 struct AttnParams {
   int B, H, W, heads, nwx, nwy, units;
   int k_off, v_off;          // first k / v channel
-  const float* bias_l2;      // (heads, 39 x 48): compact rel-pos bias * log2(e), rows padded to BP
+  const float* bias_l2;      // (heads, 2, 39 x 48): compact rel-pos bias * log2(e), rows padded to BP, + copy shifted by one
   bf16* out;
   int out_pitch;
 };
@@ -72,6 +73,11 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long*>(&a)),
       "l"(*reinterpret_cast<unsigned long long*>(&b)));
   return *reinterpret_cast<float2*>(&r);
+}
+__device__ __forceinline__ float2 lds_f32x2(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
 }
 __device__ __forceinline__ float lds_f32(uint32_t a) {
   float v;
@@ -136,7 +142,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_wait_relaxed(&q_empty[qb], (((uint32_t)ui >> 1) & 1u) ^ 1u);
         uint8_t* qs = sm_q + qb * QST_BYTES;
         mbar_arrive_expect_tx(&q_full[qb], Q_BYTES + BIAS_BYTES);
-        tma_load_4d(qs, &tmQ, &q_full[qb], head * DP, wx * WS, wy * WS, b);
+        tma_load_4d(qs, &tmQ, &q_full[qb], head * DP, 0, wx * (WS / 2), b * p.H + wy * WS);          // even columns
+        tma_load_4d(qs + Q_BYTES / 2, &tmQ, &q_full[qb], head * DP, 1, wx * (WS / 2), b * p.H + wy * WS);   // odd columns
         bulk_load_1d(qs + Q_BYTES, p.bias_l2 + (size_t)head * BIAS_FLOATS, BIAS_BYTES, &q_full[qb]);
         for (int kc = 0; kc < NCH; kc++, kvit++) {
           const int st = kvit % KV_STAGES;
@@ -212,19 +219,45 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int g = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;            // query row inside this warpgroup's half
-    const int qi = g * 128 + row;
-    const int qy = qi / WS, qx = qi % WS;
+    const int qy = row >> 3, qx = 2 * (row & 7) + g;  // warpgroup g holds the window's columns of parity g (see tmQ)
     const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
     const int psw = (row >> 1) & 3;                 // SWIZZLE_64B: 16-byte chunk index ^= (row / 2) % 4
     const float2 L2 = make_float2(LOG2E, LOG2E);
+    // Deferred unit epilogue: the last PV of a unit is still in flight when its softmax is done, so the normalise +
+    // store of unit i runs after chunk 0 of unit i + 1 has been handed to the tensor core (O alternates per unit).
+    bool pend = false;
+    int pend_ui = 0;
+    float pend_l = 1.f;
+    bf16* pend_row = nullptr;
+    auto flush = [&]() {
+      mbar_wait(&pv_done[g][1], (uint32_t)(pend_ui * 3 + 2) & 1u);
+      tc_fence_after();
+      uint32_t ro[32];
+      tmem_ld32(tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (pend_ui & 1)) * DP, ro);
+      tmem_ld_wait();
+      const float inv = 1.f / pend_l;
+#pragma unroll
+      for (int c = 0; c < 4; c++) {       // 32 (padded) head channels of one token
+        uint4 t;
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          h2[j] = __floats2bfloat162_rn(__uint_as_float(ro[8 * c + 2 * j]) * inv, __uint_as_float(ro[8 * c + 2 * j + 1]) * inv);
+        reinterpret_cast<uint4*>(pend_row)[c] = t;
+      }
+      pend = false;
+    };
     int ui = 0;
     for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
       const int head = u % p.heads, win = u / p.heads;
       const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
       const int qb = ui & 1;
       mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
-      // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address
-      const uint32_t bias_a = smem_u32(sm_q + qb * QST_BYTES + Q_BYTES) + (uint32_t)((WS - 1 - qy) * BP + (WS - 1 - qx)) * 4u;
+      // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address.
+      // 15 - qx is even for warpgroup 1 (aligned pairs of table A) and odd for warpgroup 0, which reads the copy
+      // shifted by one float at index - 1.
+      const uint32_t bias_a = smem_u32(sm_q + qb * QST_BYTES + Q_BYTES) +
+                              (uint32_t)((1 - g) * ATTN_TC_BIAS_TABLE + (WS - 1 - qy) * BP + (WS - 1 - qx) - (1 - g)) * 4u;
       const uint32_t o_addr = tmem_base + lane_sel + O_COL0 + (uint32_t)(g * 2 + (ui & 1)) * DP;
       float m_ref = 0.f;
       float2 l2 = make_float2(0.f, 0.f);            // row sum, even / odd keys
@@ -257,7 +290,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < 16; j++) {
             const float2 v = ffma2(make_float2(__uint_as_float(ra[2 * j]), __uint_as_float(ra[2 * j + 1])), L2,
-                                   make_float2(lds_f32(bchunk + bias_off(2 * j)), lds_f32(bchunk + bias_off(2 * j + 1))));
+                                   lds_f32x2(bchunk + bias_off(2 * j)));
             smax = fmaxf(smax, fmaxf(v.x, v.y));
             ra[2 * j] = __float_as_uint(v.x); ra[2 * j + 1] = __float_as_uint(v.y);
           }
@@ -274,7 +307,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           for (int j = 0; j < 16; j++) {
             float2 v = make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
             if (!logits_ready)
-              v = ffma2(v, L2, make_float2(lds_f32(bchunk + bias_off(sub * 32 + 2 * j)), lds_f32(bchunk + bias_off(sub * 32 + 2 * j + 1))));
+              v = ffma2(v, L2, lds_f32x2(bchunk + bias_off(sub * 32 + 2 * j)));
             v = fadd2(v, nm);
             const float2 pp = make_float2(ex2_approx(v.x), ex2_approx(v.y));
             cs = fadd2(cs, pp);
@@ -340,27 +373,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_arrive(&s_empty[g][sb]);                            // the logits are consumed: S(kc + 2) may overwrite them
         fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
         mbar_arrive(&p_full[g][sb]);
+        if (kc == 0 && pend) flush();
       }
-      // ---- O of the unit is complete once PV(5) has landed: normalise and store 32 (padded) head channels ----
-      mbar_wait(&pv_done[g][1], (uint32_t)(ui * 3 + 2) & 1u);
-      tc_fence_after();
-      uint32_t ro[32];
-      tmem_ld32(o_addr, ro);
-      tmem_ld_wait();
-      const float inv = 1.f / (l2.x + l2.y);
-      const size_t tok = ((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx;
-      bf16* orow = p.out + tok * p.out_pitch + head * DP;
-#pragma unroll
-      for (int c = 0; c < 4; c++) {
-        uint4 t;
-        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&t);
-#pragma unroll
-        for (int j = 0; j < 4; j++)
-          h2[j] = __floats2bfloat162_rn(__uint_as_float(ro[8 * c + 2 * j]) * inv, __uint_as_float(ro[8 * c + 2 * j + 1]) * inv);
-        reinterpret_cast<uint4*>(orow)[c] = t;
-      }
-      mbar_arrive(&q_empty[qb]);        // bias table of this stage consumed
+      mbar_arrive(&q_empty[qb]);        // bias tables of this stage consumed
+      // O of this unit is complete once PV(5) has landed; it is picked up after chunk 0 of the next unit (`flush`)
+      pend = true; pend_ui = ui; pend_l = l2.x + l2.y;
+      pend_row = p.out + (((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx) * p.out_pitch + head * DP;
     }
+    if (pend) flush();
   }
   tc_fence_before();
   __syncthreads();
@@ -385,9 +405,11 @@ int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st) {
   CUtensorMap tmQ, tmKV;
   uint64_t dims[4] = {(uint64_t)a.pitch, (uint64_t)a.W, (uint64_t)a.H, (uint64_t)a.B};
   uint64_t str[3] = {(uint64_t)a.pitch * 2, (uint64_t)a.W * a.pitch * 2, (uint64_t)a.H * a.W * a.pitch * 2};
-  {
-    uint32_t box[4] = {DP, WS, WS, 1};
-    HB_TRY(tc::make_tmap_bf16(&tmQ, a.qkv, 4, dims, str, box, DP * 2));
+  {   // Q: the x axis split into (x / 2, parity) so that one box is the 8 columns of one parity of a window
+    uint64_t qdims[4] = {(uint64_t)a.pitch, 2, (uint64_t)a.W / 2, (uint64_t)a.H * a.B};
+    uint64_t qstr[3] = {(uint64_t)a.pitch * 2, (uint64_t)a.pitch * 4, (uint64_t)a.W * a.pitch * 2};
+    uint32_t box[4] = {DP, 1, WS / 2, WS};
+    HB_TRY(tc::make_tmap_bf16(&tmQ, a.qkv, 4, qdims, qstr, box, DP * 2));
   }
   {
     uint32_t box[4] = {DP, OWS, KROWS, 1};
@@ -461,8 +483,9 @@ __global__ void bias_l2_kernel(const float* __restrict__ compact, int heads, int
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= heads * BIAS_FLOATS) return;
   int h = idx / BIAS_FLOATS, i = idx % BIAS_FLOATS;
-  int r = i / BP, c = i % BP;
-  dst[idx] = c < TN ? compact[(size_t)h * rows + r * TN + c] * LOG2E : 0.f;
+  int copy = i / ATTN_TC_BIAS_TABLE, j = i % ATTN_TC_BIAS_TABLE + copy;      // copy 1 is shifted by one float
+  int r = j / BP, c = j % BP;
+  dst[idx] = (r < TN && c < TN) ? compact[(size_t)h * rows + r * TN + c] * LOG2E : 0.f;
 }
 
 int launch_pack_rows_headpad(const void* src, int dt, int C, int heads, int nblk, bf16* dst, int Kpad, int dst_row0,
