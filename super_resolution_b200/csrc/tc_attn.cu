@@ -27,6 +27,7 @@
 namespace hb {
 
 using namespace tc;
+unsigned long long* gemm_trace_arm(cudaStream_t st);
 
 namespace {
 constexpr int AT_THREADS = 320;
@@ -49,6 +50,7 @@ struct AttnParams {
   const float* bias_l2;      // (heads, 2, 39 x 48): compact rel-pos bias * log2(e), rows padded to BP, + copy shifted by one
   bf16* out;
   int out_pitch;
+  unsigned long long* trace;   // engineering (HATB200_GEMM_TRACE): per-CTA cycle counters of warp 2, else null
 };
 
 // MN-major (B = V[key][d]) shared-memory descriptor: 64-byte rows, SWIZZLE_64B, 8-key groups 512 B apart
@@ -88,6 +90,7 @@ __device__ __forceinline__ float lds_f32(uint32_t a) {
 __device__ __forceinline__ constexpr uint32_t bias_off(int l) { return (uint32_t)((l / OWS) * BP + (l % OWS)) * 4u; }
 }  // namespace
 
+template <int DBG>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -247,12 +250,17 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       }
       pend = false;
     };
+    long long tc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, c0 = 0;
+    const bool tr = DBG == 5 && p.trace != nullptr;
+#define AT_T(i) do { if (tr) { const long long c1 = clock64(); tc[i] += c1 - c0; c0 = c1; } } while (0)
+    if (tr) c0 = clock64();
     int ui = 0;
     for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
       const int head = u % p.heads, win = u / p.heads;
       const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
       const int qb = ui & 1;
       mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
+      AT_T(0);
       // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address.
       // 15 - qx is even for warpgroup 1 (aligned pairs of table A) and odd for warpgroup 0, which reads the copy
       // shifted by one float at index - 1.
@@ -278,11 +286,13 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         const uint32_t s_addr = tmem_base + lane_sel + (uint32_t)(g * 2 + sb) * S_COLS;
         mbar_wait(&s_full[g][sb], (uint32_t)(ui * 3 + (kc >> 1)) & 1u);
         tc_fence_after();
+        AT_T(1);
         const uint32_t bchunk = bias_a + (uint32_t)(kc * KROWS * BP) * 4u;
         const uint32_t prow = smem_u32(sm_p) + (uint32_t)((g * 2 + sb) * P_BYTES + row * 64);
         uint32_t ra[32], rb[32];
         tmem_ld32(s_addr, ra);
         tmem_ld_wait();
+        AT_T(2);
         tmem_ld32(s_addr + 32, rb);                              // in flight while sub-block 0 is processed
         if (kc == 0) {
           // logits of sub-block 0 in the log2 domain; their maximum is this row's reference
@@ -301,6 +311,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // P buffer `sb` was last read by PV(kc - 2) (of the previous unit for kc < 2)
         const int pvn = ui * 3 + (kc >> 1);                      // completions of pv_done[g][sb] needed so far
         if (pvn > 0) mbar_wait(&pv_done[g][sb], (uint32_t)(pvn - 1) & 1u);
+        AT_T(3);
         auto emit = [&](const int sub, uint32_t (&r)[32], const bool logits_ready) __attribute__((always_inline)) {
           uint32_t pk[16];
 #pragma unroll
@@ -320,11 +331,16 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                          "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3]) : "memory");
         };
         if (kc == 0) emit(0, ra, true); else emit(0, ra, false);
+        AT_T(4);
         tmem_ld_wait();
+        AT_T(5);
         tmem_ld32(s_addr + 64, ra);                              // sub-block 2 in flight while sub-block 1 is processed
         emit(1, rb, false);
+        AT_T(4);
         tmem_ld_wait();
+        AT_T(5);
         emit(2, ra, false);
+        AT_T(4);
         if (__any_sync(0xffffffffu, !(cs.x + cs.y < 1.1529215e18f))) {
           // ---- rescale_chunk (rare): exact maximum, P again, O and the row sum moved to the new reference ----
           float mx = m_ref;
@@ -373,7 +389,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_arrive(&s_empty[g][sb]);                            // the logits are consumed: S(kc + 2) may overwrite them
         fence_proxy_async();            // P (generic-proxy stores) -> visible to the tensor core (async proxy)
         mbar_arrive(&p_full[g][sb]);
+        AT_T(6);
         if (kc == 0 && pend) flush();
+        AT_T(7);
       }
       mbar_arrive(&q_empty[qb]);        // bias tables of this stage consumed
       // O of this unit is complete once PV(5) has landed; it is picked up after chunk 0 of the next unit (`flush`)
@@ -381,6 +399,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       pend_row = p.out + (((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx) * p.out_pitch + head * DP;
     }
     if (pend) flush();
+    AT_T(7);
+    if (tr && lane == 0 && (warp == 2 || warp == 6))
+      for (int i = 0; i < 10; i++) p.trace[(size_t)blockIdx.x * 64 + (warp == 6 ? 16 : 0) + i] = (unsigned long long)tc[i];
+#undef AT_T
   }
   tc_fence_before();
   __syncthreads();
@@ -422,15 +444,25 @@ int launch_attn_tc(const AttnTcArgs& a, cudaStream_t st) {
   p.k_off = a.heads * DP; p.v_off = 2 * a.heads * DP;
   p.bias_l2 = a.bias_l2;
   p.out = (bf16*)a.out; p.out_pitch = a.out_pitch;
+  p.trace = nullptr;
+#ifdef HATB200_ENGINEERING
+  if (getenv("HATB200_ATTN_TRACE")) {       // cycle budget of the softmax warps (tools/trace_attn.py)
+    p.trace = gemm_trace_arm(st);
+    cudaFuncSetAttribute(attn_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    launch_pdl(attn_tc_kernel<5>, dim3(p.units < 148 ? p.units : 148), dim3(AT_THREADS), SMEM_BYTES, st, tmQ, tmKV, p);
+    HB_CHECK_LAUNCH();
+    return 0;
+  }
+#endif
   static bool attr_set = false;
   if (!attr_set) {
-    HB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr_set = true;
   }
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   int grid = p.units < sms ? p.units : sms;
-  launch_pdl(attn_tc_kernel, dim3(grid), dim3(AT_THREADS), SMEM_BYTES, st, tmQ, tmKV, p);
+  launch_pdl(attn_tc_kernel<0>, dim3(grid), dim3(AT_THREADS), SMEM_BYTES, st, tmQ, tmKV, p);
   HB_CHECK_LAUNCH();
   return 0;
 }
