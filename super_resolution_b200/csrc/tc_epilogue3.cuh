@@ -305,14 +305,15 @@ inline int feat_select(const Epilogue& ep) {
 }
 
 // The whole epilogue of one tile for the calling warp.  F: feature set; TS: Tile2D / Tile4D.
-template <class F, bool GROUPED, class TS>
+// PRE: the accumulator already contains the fp32 residual (tc_gemm.cu preloads it with tcgen05.cp), the epilogue skips it.
+template <class F, bool GROUPED, class TS, bool PRE = false>
 __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>& ws, const RowInfo& ri, const TS& ts,
                                          const CUtensorMap* tmOF, const CUtensorMap* tmOT, const CUtensorMap* tmLN) {
   constexpr int GW32 = WarpState<GROUPED>::GW32, GW16 = WarpState<GROUPED>::GW16;
   constexpr bool RING = feat_ring<F>();
   const int lane = ws.lane, quarter = ws.quarter, row = ws.row, g = ws.g, n0 = ws.n0, nch = ws.nch;
   // feature present?  compile-time for an EXACT set, a uniform run-time test otherwise
-  const bool has_u = F::U && (F::EXACT || ws.has_u), has_resid = F::RESID && (F::EXACT || ws.has_resid);
+  const bool has_u = F::U && (F::EXACT || ws.has_u), has_resid = !PRE && F::RESID && (F::EXACT || ws.has_resid);
   const bool do_ln = F::LN && (F::EXACT || ep.ln_out != nullptr);
   const bool out32 = F::OUT32 && (F::EXACT || ep.out_f32 != nullptr), out16 = F::OUT16 && (F::EXACT || ep.out_t != nullptr);
   const bool do_cs = F::COLSUM && (F::EXACT || ep.colsum != nullptr);

@@ -50,6 +50,8 @@ constexpr int G3_MAX_OPS = MAX_OPS;    // operand ring stages per warpgroup
 constexpr int G3_TILE_M = 128;
 constexpr int G3_BK = 64;
 constexpr int G3_SMEM_LIMIT = 227 * 1024 - 2048;   // static shared memory (barriers) stays below 2 KB
+constexpr int G3_PRE_MAX = 6;          // preload ring stages (one stage = 128 rows x 32 fp32 columns, SWIZZLE_128B)
+constexpr int G3_PRE_BYTES = G3_TILE_M * 32 * 4;
 
 struct G3Params {
   int M, H, W, hw;
@@ -60,6 +62,7 @@ struct G3Params {
   int stages, stage_bytes;  // activation ring (stage = A tile [+ W k-block])
   int ops, op_stage_bytes, op_u_off;   // operand ring per warpgroup
   int has_resid, has_u;
+  int pre, pre_stages, off_pre;        // fp32 residual preloaded into the accumulator (tcgen05.cp), its TMA ring
   uint32_t acc_stride, tmem_cols;
   // shared memory offsets (bytes from the 1024-aligned base)
   int off_b, off_a, off_op, off_stg32, off_stg16, off_tab, smem_bytes;
@@ -78,8 +81,14 @@ struct G3Params {
 // can only read its own 32 TMEM lanes, so the extra parallelism comes from the columns: two warpgroups per accumulator
 // stage, each running the unchanged per-tile epilogue on one half of the n-tile (plain bf16 layers only: no row
 // statistics, no operand ring; 576 threads, no ring-producer warps).
-template <class F, bool GROUPED, int NWG = 2>
-__global__ void __launch_bounds__(NWG == 4 ? 64 + 128 * 4 : G3_THREADS, 1)
+//
+// PRE (round 2): the fp32 residual never passes through the epilogue threads.  A dedicated producer warp TMA-loads it
+// in 128-row x 32-column boxes (SWIZZLE_128B), the MMA-issuing thread copies each box into the accumulator with four
+// tcgen05.cp.128x256b (shared memory -> TMEM; tools/probe_tmem_cp.py: row r -> lane r, column c -> column c), and
+// the tile's MMAs then ACCUMULATE on top of it (the tensor pipe runs cp and mma in issue order).  `acc` arrives in the
+// epilogue as resid + A W^T: no ring stage, no shared-memory read and no add for the largest operand of the layer.
+template <class F, bool GROUPED, int NWG = 2, bool PRE = false>
+__global__ void __launch_bounds__(NWG == 4 ? 64 + 128 * 4 : (PRE ? G3_THREADS + 32 : G3_THREADS), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU,
                const __grid_constant__ CUtensorMap tmOF, const __grid_constant__ CUtensorMap tmOT,
@@ -92,6 +101,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ __align__(8) uint64_t op_full[2][G3_MAX_OPS];
   __shared__ __align__(8) uint64_t op_empty[2][G3_MAX_OPS];
+  __shared__ __align__(8) uint64_t pre_full[G3_PRE_MAX], pre_empty[G3_PRE_MAX];
   __shared__ uint32_t tmem_slot;
   __shared__ float hsum[8][16];                       // per epilogue warp: column sums of the LN head
 
@@ -112,6 +122,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(&b_bar, 1);
+    for (int s = 0; s < G3_PRE_MAX; s++) {
+      mbar_init(&pre_full[s], 1);
+      mbar_init(&pre_empty[s], 1);
+    }
     for (int g = 0; g < 2; g++) {
       mbar_init(&tmem_full_bar[g], 1);
       mbar_init(&tmem_empty_bar[g], 64 * NWG);
@@ -169,7 +183,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       G3_TRACE(0);
       if (p.b_resident) mbar_wait(&b_bar, 0);
       G3_TRACE(1);
-      RingPos rp;
+      RingPos rp, pp;
       int i = 0;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
         const int g = i & 1;
@@ -177,6 +191,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         if (i < 6) G3_TRACE(8 + 2 * i);
         const uint32_t acc = tmem_base + (uint32_t)g * p.acc_stride;
+        if (PRE) {
+          for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
+            mbar_wait(&pre_full[pp.s], pp.ph);
+            tc_fence_after();
+            const uint64_t rd = make_smem_desc(smem_u32(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES), 128);
+#pragma unroll
+            for (int q = 0; q < 4; q++)       // 8 fp32 columns (256 bits) per copy; +32 bytes inside the swizzle atom
+              asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(acc + (uint32_t)(32 * c + 8 * q)), "l"(rd + 2 * q) : "memory");
+            umma_commit(&pre_empty[pp.s]);    // frees the stage once the copies have read it
+          }
+        }
         for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
           const int s = rp.s;
           mbar_wait(&full_bar[s], rp.ph);
@@ -185,18 +210,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t sb = p.b_resident ? smem_u32(smem + p.off_b + (size_t)kb * p.BN * 128) : sa + A_BYTES;
           const uint64_t ad = make_smem_desc(sa, 128), bd = make_smem_desc(sb, 128);
 #pragma unroll
-          for (int k = 0; k < G3_BK / 16; k++) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)(kb | k));
+          for (int k = 0; k < G3_BK / 16; k++) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, PRE ? 1u : (uint32_t)(kb | k));
           umma_commit(&empty_bar[s]);       // frees the ring slot once these MMAs have read it
         }
         umma_commit(&tmem_full_bar[g]);     // accumulator of tile i complete
         if (i < 6) G3_TRACE(9 + 2 * i);
       }
     }
+  } else if (PRE && warp == 12) {
+    // ===== residual preload producer: 128 x 32 fp32 boxes of every tile of this CTA, as far ahead as the ring allows =====
+    if (elect_one()) {
+      prefetch_tmap(&tmR);
+      pdl_wait();
+      RingPos pp;
+      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
+        for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
+          mbar_wait(&pre_empty[pp.s], pp.ph ^ 1u);
+          mbar_arrive_expect_tx(&pre_full[pp.s], (uint32_t)G3_PRE_BYTES);
+          tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, t * G3_TILE_M);
+        }
+      }
+    }
   } else if (warp >= 2 + 4 * NWG) {
     // ===== operand-ring producer of warpgroup g: residual / CAB-branch chunks, as far ahead as the ring allows =====
     const int g = warp - 10;
-    if (feat_ring<F>() && (p.has_resid || p.has_u) && elect_one()) {
-      if (p.has_resid) prefetch_tmap(&tmR);
+    const int ring_resid = PRE ? 0 : p.has_resid;
+    if (feat_ring<F>() && (ring_resid || p.has_u) && elect_one()) {
+      if (ring_resid) prefetch_tmap(&tmR);
       if (p.has_u) prefetch_tmap(&tmU);
       pdl_wait();
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
@@ -207,7 +247,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const Tile2D ts{t * G3_TILE_M};
         const int tn = t + 2 * (int)gridDim.x;          // this warpgroup's next tile
         const Tile2D nx{tn * G3_TILE_M};
-        produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, p.has_resid,
+        produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, ring_resid,
                      p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr);
       }
     }
@@ -226,7 +266,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ws.ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
     ws.op_full = op_full[g]; ws.op_empty = op_empty[g];
     ws.ops = p.ops; ws.op_stage_bytes = p.op_stage_bytes; ws.op_u_off = p.op_u_off;
-    ws.has_resid = p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
+    ws.has_resid = PRE ? 0 : p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
     ws.prof = p.trace != nullptr && p.prof;
     ws.hsum = hsum; ws.sred = nullptr;                   // no tile column sums in the 1x1 layers
     ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
@@ -255,7 +295,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       if (tr) G3_TRACE(25 + g * 16 + 4 * (i >> 1));
       const Tile2D ts{m0};
-      run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+      run_tile<F, GROUPED, Tile2D, PRE>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
@@ -327,20 +367,27 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   if (cols > 512) return false;
   p.tmem_cols = cols;
   p.has_resid = ep.resid != nullptr; p.has_u = ep.eca_u != nullptr;
-  const bool ring = p.has_resid || p.has_u;
+  static const bool no_pre = getenv("HATB200_G3_PRE") && getenv("HATB200_G3_PRE")[0] == '0';       // engineering: A/B
+  // not with the CAB branch in the same epilogue (esc_aggr): its operand ring keeps the epilogue the long pole, and the
+  // preload then only lengthens the issuer's serial chain (B200: 46.5 us without, 47.8 us with)
+  p.pre = (!no_pre && p.has_resid && !p.has_u && p.BN % 32 == 0 && feat_select(ep) != FEAT_PLAIN) ? 1 : 0;
+  p.pre_stages = 0; p.off_pre = 0;
+  const bool ring = (p.has_resid && !p.pre) || p.has_u;
   grouped = p.BN % 64 == 0;                 // stores leave as 128-byte rows (2 fp32 / 4 bf16 chunks per TMA store)
   const bool f32o = ep.out_f32 != nullptr, bf16o = ep.out_t != nullptr || ep.ln_out != nullptr;
   // fp32 staging is idle during the LayerNorm pass and vice versa: share it unless pass 1 also writes bf16
   p.share_stg = f32o && bf16o && ep.out_t == nullptr;
   const int b_bytes = p.BN * Kpad * 2;
   const int tab = round_up(5 * p.BN * 4, 1024);
-  p.stg_bufs = (f32o && ep.out_t != nullptr) ? 1 : 2;
+  // preload kernels: the serial chain is the issuer's (residual boxes, then the k-blocks), so shared memory goes to
+  // activation / preload stages before a second staging buffer (B200 sweep: fc2 43.0 -> 41.6 us, OCAB mlp2 59.7 -> 50.9)
+  p.stg_bufs = ((f32o && ep.out_t != nullptr) || p.pre) ? 1 : 2;
   static const bool nwg2 = getenv("HATB200_G3_NWG") && getenv("HATB200_G3_NWG")[0] == '2';
   p.nwg = (!nwg2 && grouped && p.BN % 128 == 0 && feat_select(ep) == FEAT_PLAIN) ? 4 : 2;
   const int ewarps = 4 * p.nwg;
   const int stg32 = f32o ? ewarps * p.stg_bufs * 32 * (grouped ? 128 : 64) : 0;
   const int stg16 = bf16o && !p.share_stg ? ewarps * p.stg_bufs * 32 * (grouped ? 128 : 32) : 0;
-  const int rb = p.has_resid ? G3_TILE_M * CW * 4 : 0, ub = p.has_u ? G3_TILE_M * CW * 2 : 0;
+  const int rb = (p.has_resid && !p.pre) ? G3_TILE_M * CW * 4 : 0, ub = p.has_u ? G3_TILE_M * CW * 2 : 0;
   p.op_u_off = rb;
   p.op_stage_bytes = round_up(rb + ub, 1024);
   // Shared-memory plan.  Candidates: weights resident or streamed, staging double or single buffered, operand
@@ -350,6 +397,7 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   static const int force_ops = getenv("HATB200_G3_OPS") ? atoi(getenv("HATB200_G3_OPS")) : 0;          // engineering
   static const int force_bufs = getenv("HATB200_G3_STGBUFS") ? atoi(getenv("HATB200_G3_STGBUFS")) : 0;
   static const int force_res = getenv("HATB200_G3_RESIDENT") ? atoi(getenv("HATB200_G3_RESIDENT")) : -1;
+  static const int force_pre = getenv("HATB200_G3_PRESTAGES") ? atoi(getenv("HATB200_G3_PRESTAGES")) : 0;
   int best_score = -1;
   G3Params best = p;
   for (int resident = 1; resident >= 0; resident--) {
@@ -359,20 +407,24 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
       const int s32 = stg32 / p.stg_bufs * bufs, s16 = stg16 / p.stg_bufs * bufs;
       const int stage = G3_TILE_M * G3_BK * 2 + (resident ? 0 : p.BN * 128);
       const int fixed = tab + s32 + s16 + (resident ? round_up(b_bytes, 1024) : 0);
-      for (int ops = ring ? G3_MAX_OPS : 0; ops >= (ring ? 2 : 0); ops--) {
+      for (int ops = ring ? G3_MAX_OPS : 0; ops >= (ring ? 2 : 0); ops--)
+      for (int pre = p.pre ? 4 : 0; pre >= (p.pre ? 2 : 0); pre--) {
         if (force_ops && ring && ops != force_ops) continue;
-        const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes;
+        if (force_pre && p.pre && pre != force_pre) continue;
+        const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes - pre * G3_PRE_BYTES;
         int st = avail > 0 ? avail / stage : 0;
         if (st > G3_MAX_STAGES) st = G3_MAX_STAGES;
         if (st > p.kblocks * 2 && st > 4) st = p.kblocks * 2 > 4 ? p.kblocks * 2 : 4;
         if (st < 2) continue;
         // score: ring depth first (x4), then activation stages (capped at 4), resident weights (+3 when K is
         // short enough that the panel load is not a long prologue), double-buffered staging (+2)
-        const int score = (ring ? 4 * ops : 0) + (st > 4 ? 4 : st) + (resident ? (p.kblocks <= 3 ? 3 : 1) : 0) + 2 * (bufs - 1);
+        const int score = (ring ? 4 * ops : 0) + (st > 4 ? 4 : st) + (resident ? (p.kblocks <= 3 ? 3 : 1) : 0) + 2 * (bufs - 1) +
+                          3 * (pre > 4 ? 4 : pre);
         if (score > best_score) {
           best_score = score;
           best = p;
           best.b_resident = resident; best.stage_bytes = stage; best.stages = st; best.ops = ops; best.stg_bufs = bufs;
+          best.pre_stages = pre;
         }
       }
     }
@@ -384,12 +436,14 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
     const int s32 = stg32 / bufs0 * p.stg_bufs, s16 = stg16 / bufs0 * p.stg_bufs;
     const int resident = p.b_resident, stage = p.stage_bytes;
     if (getenv("HATB200_TRACE"))
-      fprintf(stderr, "[gemm_tc] N=%d K=%d BN=%d resident=%d stages=%d ops=%d stg_bufs=%d share=%d nwg=%d\n", p.N, Kpad, p.BN,
-              resident, p.stages, p.ops, p.stg_bufs, p.share_stg, p.nwg);
+      fprintf(stderr, "[gemm_tc] N=%d K=%d BN=%d resident=%d stages=%d ops=%d stg_bufs=%d share=%d nwg=%d pre=%d x %d\n", p.N, Kpad,
+              p.BN, resident, p.stages, p.ops, p.stg_bufs, p.share_stg, p.nwg, p.pre, p.pre_stages);
     int off = 0;
     p.off_b = off; off += resident ? round_up(b_bytes, 1024) : 0;
     p.off_a = off; off += p.stages * stage;
     p.off_op = off; off += 2 * p.ops * p.op_stage_bytes;
+    off = round_up(off, 1024);
+    p.off_pre = off; off += p.pre_stages * G3_PRE_BYTES;
     p.off_stg32 = off; off += s32;
     p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += s16;
     p.off_tab = off; off += tab;
@@ -430,8 +484,8 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
   if (p.has_resid) {     // columns >= N read as zero
     uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)ep.resid_pitch * 4};
-    uint32_t box[2] = {(uint32_t)CW, G3_TILE_M};
-    HB_TRY(tc::make_tmap_f32(&tmR, ep.resid, 2, dims, str, box, CW * 4));
+    uint32_t box[2] = {p.pre ? 32u : (uint32_t)CW, G3_TILE_M};
+    HB_TRY(tc::make_tmap_f32(&tmR, ep.resid, 2, dims, str, box, p.pre ? 128 : CW * 4));
   }
   if (p.has_u) {         // columns >= N read as zero (U's own pad columns are never touched)
     uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
@@ -476,6 +530,11 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     G3_ATTR(FeatAll); G3_ATTR(FeatPlain); G3_ATTR(FeatResLn); G3_ATTR(FeatResULn);
 #undef G3_ATTR
     HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<FeatPlain, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+#define G3_ATTR_PRE(F_) \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim)); \
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
+    G3_ATTR_PRE(FeatAll); G3_ATTR_PRE(FeatResLn); G3_ATTR_PRE(FeatResULn);
+#undef G3_ATTR_PRE
     attr_set = true;
   }
   const int n_tiles = Npad / p.BN;
@@ -490,6 +549,12 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     if (grouped) launch_pdl(gemm_tc_kernel<F_, true>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
     else launch_pdl(gemm_tc_kernel<F_, false>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);       \
   } while (0)
+#define G3_LAUNCH_R(F_)                                                                                              \
+  do {                                                                                                               \
+    if (!p.pre) G3_LAUNCH(F_);                                                                                       \
+    else if (grouped) launch_pdl(gemm_tc_kernel<F_, true, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
+    else launch_pdl(gemm_tc_kernel<F_, false, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);            \
+  } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;     // engineering: A/B the specialisation
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {
     case FEAT_PLAIN:
@@ -497,10 +562,11 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
         launch_pdl(gemm_tc_kernel<FeatPlain, true, 4>, grid, dim3(64 + 128 * 4), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);
       else G3_LAUNCH(FeatPlain);
       break;
-    case FEAT_RESLN: G3_LAUNCH(FeatResLn); break;
-    case FEAT_RESULN: G3_LAUNCH(FeatResULn); break;
-    default: G3_LAUNCH(FeatAll); break;
+    case FEAT_RESLN: G3_LAUNCH_R(FeatResLn); break;
+    case FEAT_RESULN: G3_LAUNCH_R(FeatResULn); break;
+    default: G3_LAUNCH_R(FeatAll); break;
   }
+#undef G3_LAUNCH_R
 #undef G3_LAUNCH
   HB_CHECK_LAUNCH();
   return 0;

@@ -91,6 +91,105 @@ extern "C" int hatb200_probe_umma(const void* a, int R, const void* b, int r0, i
   return 0;
 }
 
+// ---- probe 2: tcgen05.cp.128x256b (shared memory -> TMEM, issued by one thread).  Does a 128-row x 32-fp32 tile that
+// TMA wrote with SWIZZLE_128B (mode 0) / as four 8-column SWIZZLE_32B boxes (mode 1) land as "row r -> lane r,
+// column c -> TMEM column c" when copied 8 columns (256 bits) at a time with the matching K-major descriptor?
+// If yes, the fp32 residual can be PRELOADED into the accumulator and the MMA accumulates on top of it.
+namespace hb {
+__global__ void __launch_bounds__(128, 1)
+tmem_cp_probe_kernel(const __grid_constant__ CUtensorMap tm, int mode, float* __restrict__ out) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar, done;
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    mbar_init(&done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc(&tmem_slot, 32);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bar, 128 * 128);
+    if (mode == 0) tma_load_2d(smem, &tm, &bar, 0, 0);
+    else for (int i = 0; i < 4; i++) tma_load_2d(smem + i * 4096, &tm, &bar, 8 * i, 0);
+    mbar_wait(&bar, 0);
+    tc_fence_after();
+    for (int i = 0; i < 4; i++) {
+      const uint64_t d = mode == 0 ? make_smem_desc(smem_u32(smem) + 32 * i, 128) : make_smem_desc(smem_u32(smem) + 4096 * i, 32);
+      asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(tmem_base + 8 * i), "l"(d) : "memory");
+    }
+    umma_commit(&done);
+  }
+  mbar_wait(&done, 0);
+  tc_fence_after();
+  const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
+  uint32_t r[32];
+  tmem_ld32(trow, r);
+  tmem_ld_wait();
+  for (int j = 0; j < 32; j++) out[(size_t)(warp * 32 + lane) * 32 + j] = __uint_as_float(r[j]);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 32);
+  }
+}
+}  // namespace hb
+
+// src, out: (128, 32) fp32 device
+extern "C" int hatb200_probe_tmem_cp(const float* src, int mode, float* out, void* stream) {
+  CUtensorMap tm;
+  uint64_t dims[2] = {32, 128};
+  uint64_t str[1] = {128};
+  uint32_t box[2] = {mode == 0 ? 32u : 8u, 128};
+  HB_TRY(tc::make_tmap_f32(&tm, src, 2, dims, str, box, mode == 0 ? 128 : 32));
+  const size_t smem = 16384 + 1024;
+  HB_CHECK_CUDA(cudaFuncSetAttribute(tmem_cp_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tmem_cp_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(tm, mode, out);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---- probe 3: what does the memory system give a kernel with the esc_aggr traffic pattern and no arithmetic?
+// o32 = r + a + u (fp32), o16 = bf16(o32): reads two bf16 streams + one fp32 stream, writes one fp32 + one bf16 stream,
+// 16-byte accesses, grid-stride, `ctas` CTAs of 1024 threads.  n8 = number of 8-element groups.
+namespace hb {
+__global__ void __launch_bounds__(1024) stream_probe_kernel(const uint4* __restrict__ a, const uint4* __restrict__ u,
+                                                            const float4* __restrict__ r, float4* __restrict__ o32,
+                                                            uint4* __restrict__ o16, size_t n8, int rev) {
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += (size_t)gridDim.x * blockDim.x) {
+    const size_t i = rev ? n8 - 1 - i0 : i0;
+    const uint4 av = a[i], uv = u[i];
+    const float4 r0 = r[2 * i], r1 = r[2 * i + 1];
+    const uint32_t aw[4] = {av.x, av.y, av.z, av.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w};
+    float v[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      v[2 * j] += __uint_as_float(aw[j] << 16) + __uint_as_float(uw[j] << 16);
+      v[2 * j + 1] += __uint_as_float(aw[j] & 0xffff0000u) + __uint_as_float(uw[j] & 0xffff0000u);
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+      o[j] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    o32[2 * i] = make_float4(v[0], v[1], v[2], v[3]);
+    o32[2 * i + 1] = make_float4(v[4], v[5], v[6], v[7]);
+    o16[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+}  // namespace hb
+extern "C" int hatb200_probe_stream(const void* a, const void* u, const void* r, void* o32, void* o16, size_t n8, int ctas,
+                                    int rev, void* stream) {
+  stream_probe_kernel<<<ctas, 1024, 0, (cudaStream_t)stream>>>((const uint4*)a, (const uint4*)u, (const float4*)r,
+                                                               (float4*)o32, (uint4*)o16, n8, rev);
+  HB_CHECK_LAUNCH();
+  return 0;
+}
+
 // engineering: copy the last traced GEMM launch's per-CTA event timestamps (ns) to the host: (1024, 64) uint64
 namespace hb { unsigned long long* gemm_trace_buffer(); }
 extern "C" int hatb200_debug_gemm_trace(unsigned long long* host, void* stream) {
