@@ -112,6 +112,19 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 enum { ACT_NONE = 0, ACT_GELU = 1, ACT_LRELU = 2 };
 
+// A job for EXTRA CTAs of a launch (side_jobs.cuh): kind 0 = none.  Extra CTA j handles sample j (j < B).
+struct SideJob {
+  int kind = 0;                 // 1: eca_finish, 2: dyn_finish
+  int B = 0, nchunk = 0, C = 0; // C: channels (eca) / pdim (dyn)
+  float inv_hw = 0.f;
+  const float* partial = nullptr;
+  const float* w1 = nullptr;    // eca: w5;  dyn: w1
+  const float* b1 = nullptr;
+  const float* w2 = nullptr;
+  const float* b2 = nullptr;
+  float* out = nullptr;         // eca: scale (B, C);  dyn: (B, pdim, 9)
+};
+
 // Epilogue shared by the CUDA-core and tcgen05 conv/GEMM kernels.
 // value order:  v = acc + bias[n]; v += dyn-depthwise term; v *= scale (n < scale_ncols);
 //               v = act(v); v += eca_coef * eca_scale[b,n] * U[m,n]; v += resid[m,n]
@@ -148,6 +161,7 @@ struct Epilogue {
   void* ln_head_pad = nullptr;       // optional second copy of the head, x-padded (B, H, W+12, ln_head_c) for tc_plk.cu
   float* ln_head_colsum = nullptr;   // fp32 (num_m_tiles, ln_head_c) per-tile column sums of the LN head
   float* colsum = nullptr;           // fp32 (num_m_tiles, N) per-tile column sums of v (GAP partials)
+  SideJob side;                      // honoured by tc_conv3.cu only (the caller checks conv3_tc_supported first)
 };
 
 }  // namespace hb

@@ -186,6 +186,15 @@ struct Fwd {
     return conv(tag, cw, A, 64, 0, H, W, ep);
   }
 
+  // will conv(tag, ...) run on the persistent 3x3 kernel in a way that can carry a side job (side_jobs.cuh)?
+  bool side_ok(const char* tag, const ConvW& cw, const void* A, int a_pitch, int H, int W, Epilogue ep) const {
+    static const bool off = getenv("HATB200_SIDE_JOBS") && getenv("HATB200_SIDE_JOBS")[0] == '0';     // engineering: A/B
+    if (off || !tc() || tc_disabled(tag)) return false;
+    ConvArgs a{A, a_pitch, 0, cw.I, d.B, H, W, cw.KH, cw.KW, cw.O};
+    if (!ep.bias) ep.bias = cw.bias;
+    return !gemm_tc_supported(a, cw.Npad, cw.Kpad, ep) && conv3_tc_side_ok(a, cw.Npad, cw.Kpad, ep);
+  }
+
   // engineering switch: HATB200_TC_DISABLE=tag1,tag2 keeps the named ops on the CUDA-core kernel (bisecting)
   static bool tc_disabled(const char* tag) {
     const char* v = getenv("HATB200_TC_DISABLE");
@@ -264,13 +273,14 @@ struct Fwd {
 
   // ESC ConvAttn core on xn (esc_arch.py:119-123): writes the mixed first-pdim channels into
   // dst[:, :pdim] (dst already holds xn elsewhere).  Needs X16 + part16 from the preceding LN.
-  int esc_mix(const EscW& e, void* dst, bool dyn_done = false) {
+  // `side`: a per-sample job for extra CTAs of the 13x13 kernel (only passed when that kernel runs, see hab())
+  int esc_mix(const EscW& e, void* dst, bool dyn_done = false, const SideJob* side = nullptr) {
     int nchunk = colsum_chunks(d.H * d.W);
     if (!dyn_done) HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, e.pdim, d.H * d.W, e.w1, e.b1, e.w2, e.b2, w.dyn, st));
     if (e.plk_wt && plk_tc(e.pdim)) {
       double Mt = (double)d.M;
       int tid = t_begin("esc_plk13", 2.0 * Mt * e.pdim * e.pdim * (e.plk.taps() + 9.0 / e.pdim), Mt * 2 * e.pdim * d.es, "plk_tc");
-      int r = launch_plk_tc((const bf16*)w.X16P, d.B, d.H, d.W, e.plk_wt, w.dyn, (bf16*)dst, d.Cp, st);
+      int r = launch_plk_tc((const bf16*)w.X16P, d.B, d.H, d.W, e.plk_wt, w.dyn, (bf16*)dst, d.Cp, st, side);
       t_end(tid);
       HB_TRY(r);
       return dbg("plk_tc");
@@ -286,18 +296,36 @@ struct Fwd {
   int hab(const HabW& b, const float* src, float* dst, const LNW* next_ln, int next_head) {
     const hatb200_config& c = h->cfg;
     int nchunk = colsum_chunks(d.H * d.W);
+    // The two per-sample "finish" steps (ESC dynamic kernel from the LN head's pool partials, ECA gate from conv2's)
+    // ride as extra CTAs of kernels that run anyway: dyn_finish in cab_conv1's tail (its inputs exist since the previous
+    // block), eca_finish on the SMs the 13x13 kernel leaves idle (the gate is only needed by esc_aggr after it).
+    // Whatever cannot ride (CUDA-core routes, other shapes) keeps its own launch.
+    const float inv_hw = 1.0f / (float)(d.H * d.W);
+    SideJob dynj; dynj.kind = 2; dynj.B = d.B; dynj.nchunk = nchunk; dynj.C = b.esc.pdim; dynj.inv_hw = inv_hw;
+    dynj.partial = w.part16; dynj.w1 = b.esc.w1; dynj.b1 = b.esc.b1; dynj.w2 = b.esc.w2; dynj.b2 = b.esc.b2; dynj.out = w.dyn;
+    SideJob ecaj; ecaj.kind = 1; ecaj.B = d.B; ecaj.nchunk = nchunk; ecaj.C = d.C; ecaj.inv_hw = inv_hw;
+    ecaj.partial = w.part; ecaj.w1 = b.eca_w5; ecaj.out = w.eca_s;
+    bool dyn_rides = false;
     {  // CAB conv1 + GELU
       Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.T1; ep.out_t_pitch = d.midp; ep.out_t_zero_to = d.midp;
+      dyn_rides = b.esc.pdim <= 64 && b.esc.pdim % 2 == 0 && side_ok("cab_conv1", b.cab0, w.XN, d.Cp, d.H, d.W, ep);
+      if (dyn_rides) ep.side = dynj;
       HB_TRY(conv("cab_conv1", b.cab0, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
+    static const bool side_off = getenv("HATB200_SIDE_JOBS") && getenv("HATB200_SIDE_JOBS")[0] == '0';
+    const bool eca_rides = !side_off && tc() && b.esc.plk_wt && plk_tc(b.esc.pdim);
     {  // CAB conv2 -> U, with GAP partials for ECA
       Epilogue ep; ep.out_t = w.U; ep.out_t_pitch = d.Cp; ep.colsum = w.part;
       HB_TRY(conv("cab_conv2", b.cab2, w.T1, d.midp, 0, d.H, d.W, ep));
-      // ECA gate of this branch and the ESC branch's per-sample dynamic kernel in one launch
-      HB_TRY(launch_hab_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, w.part16, b.esc.pdim, b.esc.w1,
-                               b.esc.b1, b.esc.w2, b.esc.b2, w.dyn, st));
+      if (!dyn_rides && !eca_rides)      // both in one launch of their own
+        HB_TRY(launch_hab_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, w.part16, b.esc.pdim, b.esc.w1,
+                                 b.esc.b1, b.esc.w2, b.esc.b2, w.dyn, st));
+      else if (!dyn_rides)
+        HB_TRY(launch_dyn_finish(w.part16, nchunk, d.B, b.esc.pdim, d.H * d.W, b.esc.w1, b.esc.b1, b.esc.w2, b.esc.b2, w.dyn, st));
+      else if (!eca_rides)
+        HB_TRY(launch_eca_finish(w.part, nchunk, d.B, d.C, d.H * d.W, b.eca_w5, w.eca_s, st));
     }
-    HB_TRY(esc_mix(b.esc, w.XN, true));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
+    HB_TRY(esc_mix(b.esc, w.XN, true, eca_rides ? &ecaj : nullptr));   // XN[:, :pdim] <- plk conv + dynamic dw (CAB has consumed XN)
     {  // aggr 1x1 + HAB combine (hat_arch.py:236) [+ norm2]
       Epilogue ep;
       ep.eca_u = w.U; ep.eca_pitch = d.Cp; ep.eca_scale = w.eca_s; ep.eca_coef = c.conv_scale;

@@ -97,6 +97,7 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
 bool gemm_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
 // persistent halo-resident tcgen05 3x3 conv (tc_conv3.cu); same packed weights and epilogue semantics
 int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st);
+bool conv3_tc_side_ok(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
 bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep);
 // picks the tcgen05 kernel for the shape (1x1 -> tc_gemm, 3x3 -> tc_conv3, else / fallback tc_tapconv)
 inline bool conv_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
@@ -126,7 +127,7 @@ size_t plk_toeplitz_elems();
 int launch_pack_plk_toeplitz(const void* src, int dt, bf16* dst, cudaStream_t st);
 int launch_plk_pad_copy(const bf16* src, int B, int H, int W, bf16* dst, cudaStream_t st);
 int launch_plk_tc(const bf16* xpad, int B, int H, int W, const bf16* wt, const float* dyn, bf16* out, int out_pitch,
-                  cudaStream_t st);
+                  cudaStream_t st, const SideJob* side = nullptr);
 
 // ---- OCAB attention core (hat_arch.py:354-388) ----
 struct AttnArgs {

@@ -1,6 +1,7 @@
 // simt_kernels.cu -- CUDA-core kernels of the HAT forward: the HBM-bound ops of the
 // bf16 path and every small op of both paths.  fp32 arithmetic, storage type T.
 #include "kernels.cuh"
+#include "side_jobs.cuh"
 
 namespace hb {
 
@@ -299,37 +300,6 @@ int launch_colsum(const void* in, int dt, int pitch, int B, int HW, int nc, floa
   return 0;
 }
 
-// Sum of `n` per-tile partials `stride` floats apart, in index order (deterministic), with 16 loads in flight:
-// these finish kernels are one small block per sample and nothing but the latency of this dependent chain.
-__device__ __forceinline__ float chunk_sum(const float* __restrict__ p, int n, int stride) {
-  float s = 0.f;
-  for (int k0 = 0; k0 < n; k0 += 16) {
-    float t[16];
-#pragma unroll
-    for (int j = 0; j < 16; j++) t[j] = k0 + j < n ? __ldg(p + (size_t)(k0 + j) * stride) : 0.f;
-#pragma unroll
-    for (int j = 0; j < 16; j++) s += t[j];
-  }
-  return s;
-}
-
-// ECA gate: sigmoid(conv1d_k5(mean over HW)) across the channel axis, zero padded
-// ends, no bias (hat_arch.py:66-77).  One block per sample.
-__device__ __forceinline__ void eca_finish_body(int b, const float* __restrict__ partial, int nchunk, int C, float inv_hw,
-                                                const float* __restrict__ w5, float* __restrict__ scale, float* mean) {
-  for (int c = threadIdx.x; c < C; c += blockDim.x) mean[c] = chunk_sum(partial + (size_t)b * nchunk * C + c, nchunk, C) * inv_hw;
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float a = 0.f;
-#pragma unroll
-    for (int j = 0; j < 5; j++) {
-      int cc = c + j - 2;
-      if (cc >= 0 && cc < C) a = fmaf(w5[j], mean[cc], a);
-    }
-    scale[(size_t)b * C + c] = sigmoid_f(a);
-  }
-}
-
 __global__ void eca_finish_kernel(const float* __restrict__ partial, int nchunk, int C, float inv_hw,
                                   const float* __restrict__ w5, float* __restrict__ scale) {
   extern __shared__ float mean[];  // C
@@ -343,29 +313,6 @@ int launch_eca_finish(const float* partial, int nchunk, int B, int C, int HW, co
   launch_pdl(eca_finish_kernel, dim3(B), dim3(256), C * sizeof(float), st, partial, nchunk, C, 1.0f / (float)HW, w5, scale);
   HB_CHECK_LAUNCH();
   return 0;
-}
-
-// ESC dynamic depthwise kernel per sample (esc_arch.py:95-100, :121):
-// dyn = W2 . gelu(W1 . GAP(x[:, :pdim]) + b1) + b2, reshaped (pdim, 3, 3).
-__device__ __forceinline__ void dyn_finish_body(int b, const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,
-                                                const float* __restrict__ w1, const float* __restrict__ b1,
-                                                const float* __restrict__ w2, const float* __restrict__ b2,
-                                                float* __restrict__ dyn, float* mean, float* hid) {
-  const int half = pdim / 2;
-  for (int c = threadIdx.x; c < pdim; c += blockDim.x)
-    mean[c] = chunk_sum(partial + (size_t)b * nchunk * pdim + c, nchunk, pdim) * inv_hw;
-  __syncthreads();
-  for (int o = threadIdx.x; o < half; o += blockDim.x) {
-    float a = b1[o];
-    for (int i = 0; i < pdim; i++) a = fmaf(w1[o * pdim + i], mean[i], a);
-    hid[o] = gelu_f(a);
-  }
-  __syncthreads();
-  for (int j = threadIdx.x; j < pdim * 9; j += blockDim.x) {
-    float a = b2[j];
-    for (int i = 0; i < half; i++) a = fmaf(w2[j * half + i], hid[i], a);
-    dyn[(size_t)b * pdim * 9 + j] = a;
-  }
 }
 
 __global__ void dyn_finish_kernel(const float* __restrict__ partial, int nchunk, int pdim, float inv_hw,

@@ -31,6 +31,7 @@
 // Replaces F.conv2d at hat_arch.py:84-86 (CAB), :544 (RHAG conv), :854 (conv_after_body), :855 (conv_before_upsample).
 #include <stdlib.h>
 
+#include "side_jobs.cuh"
 #include "tc_epilogue3.cuh"
 
 namespace hb {
@@ -71,6 +72,7 @@ struct C3Params {
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
   int shuf_r;                    // > 1: pixel-shuffle store (columns pre-permuted to (i, j, c))
   int lean;                      // MMA issue through the unrolled c3_issue_tiles (grp == 3, kblocks 1 or 3, no tap rotation)
+  int main_ctas;                 // CTAs that walk tiles; blockIdx.x >= main_ctas runs ep.side (side_jobs.cuh) and exits
   int probe;                     // engineering (HATB200_C3_PROBE=1, with tracing): time 64 back-to-back MMAs before the tile loop
 };
 
@@ -168,12 +170,20 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __shared__ float hsum[8][16];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  if ((int)blockIdx.x >= p.main_ctas) {
+    // extra CTAs (whole clusters): a small per-sample job that only needs results of EARLIER kernels.  They are
+    // dispatched when the first tile-walking CTAs retire, i.e. inside this launch's tail, and cost no launch.
+    pdl_wait();
+    pdl_trigger();
+    run_side_job(ep.side, (int)blockIdx.x - p.main_ctas, reinterpret_cast<float*>(smem));
+    return;
+  }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.y * p.BN;
   // CTA pair: rank r of cluster q takes tile 2 * pair + r of every pair the cluster walks
   const uint32_t rank = TWO ? cluster_ctarank() : 0u;
   const int t_first = TWO ? (int)(blockIdx.x & ~1u) + (int)rank : (int)blockIdx.x;
-  const int t_step = (int)gridDim.x;
+  const int t_step = p.main_ctas;
   float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);
   float* tab_gamma = tab_bias + p.BN;
   float* tab_beta = tab_gamma + p.BN;
@@ -632,6 +642,11 @@ bool conv3_tc_supported(const ConvArgs& a, int Npad, int Kpad, const Epilogue& e
   return true;
 }
 
+// can this launch carry ep.side as extra CTAs?  (the tcgen05 kernel takes the shape and it is one n-tile)
+bool conv3_tc_side_ok(const ConvArgs& a, int Npad, int Kpad, const Epilogue& ep) {
+  return conv3_tc_supported(a, Npad, Kpad, ep) && Npad == tc_bn(a.N);
+}
+
 int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const Epilogue& ep, cudaStream_t st) {
   C3Params p;
   bool grouped, two;
@@ -699,6 +714,11 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
   if (per_n > p.tiles) per_n = p.tiles;
   if (two) per_n &= ~1;
   dim3 grid(per_n, n_tiles);
+  p.main_ctas = per_n;
+  if (ep.side.kind) {        // extra CTAs (whole clusters) for the side job: one per sample
+    HB_REQUIRE(n_tiles == 1, HATB200_EUNSUPPORTED, "conv3_tc: a side job needs a single n-tile");
+    grid.x = (unsigned)(per_n + round_up(ep.side.B, 2));
+  }
 #define C3_LAUNCH(F_)                                                                                              \
   do {                                                                                                             \
     if (two) {                                                                                                     \

@@ -77,6 +77,31 @@ __device__ __forceinline__ void mul2(float& d0, float& d1, float a0, float a1, f
 }
 
 
+// Exact (erf) GELU of two values, nn.GELU() of the reference (hat_arch.py:85, :114), for the bf16 tensor-core path:
+//   gelu(v) = 0.5 v (1 + erf(v / sqrt 2)) = max(v, 0) - 0.5 |v| P(t) exp(-v^2 / 2),   t = 1 / (1 + p |v| / sqrt 2)
+// with Abramowitz-Stegun 7.1.26 for erfc (|error of erf| <= 1.5e-7; of this gelu <= 2.2e-7 over [-12, 12] in float64, and the
+// result is rounded to bf16 next).  19 issue slots per PAIR (packed FFMA2 / FMUL2, 4 MUFU) against ~80 for two erff calls
+// whose two argument ranges diverge inside a warp: CAB conv1 and the OCAB MLP were bound by this one line
+// (6.46 M warp instructions per conv1 launch, 80 % of them erff).
+__device__ __forceinline__ void gelu2(float& v0, float& v1) {
+  const float a0 = fabsf(v0), a1 = fabsf(v1);
+  float d0, d1, q0, q1, s0, s1, w0, w1;
+  fma2(d0, d1, a0, a1, 0.23164189f, 0.23164189f, 1.f, 1.f);
+  float t0, t1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  fma2(q0, q1, t0, t1, 1.061405429f, 1.061405429f, -1.453152027f, -1.453152027f);
+  fma2(q0, q1, q0, q1, t0, t1, 1.421413741f, 1.421413741f);
+  fma2(q0, q1, q0, q1, t0, t1, -0.284496736f, -0.284496736f);
+  fma2(q0, q1, q0, q1, t0, t1, 0.254829592f, 0.254829592f);
+  mul2(q0, q1, q0, q1, t0, t1);
+  mul2(s0, s1, v0, v1, v0, v1);
+  mul2(s0, s1, s0, s1, -0.72134752f, -0.72134752f);            // -0.5 log2(e)
+  mul2(w0, w1, a0, a1, ex2_approx(s0), ex2_approx(s1));
+  mul2(w0, w1, w0, w1, q0, q1);
+  fma2(v0, v1, w0, w1, -0.5f, -0.5f, fmaxf(v0, 0.f), fmaxf(v1, 0.f));
+}
+
 // swizzle of 16-byte granule index for a tile whose rows are RB bytes wide (TMA SWIZZLE_{32,64,128}B, tile base
 // aligned to the swizzle period)
 template <int RB>
@@ -366,7 +391,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     }
     if (F::ACT && act == ACT_GELU) {
 #pragma unroll
-      for (int j = 0; j < CW; j++) v[j] = gelu_f(v[j]);
+      for (int j = 0; j < CW; j += 2) gelu2(v[j], v[j + 1]);
     } else if (F::ACT && act == ACT_LRELU) {
 #pragma unroll
       for (int j = 0; j < CW; j++) v[j] = lrelu_f(v[j]);

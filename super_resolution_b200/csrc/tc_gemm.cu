@@ -165,8 +165,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
       RingPos rp;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
+        const int tn = t + (int)gridDim.x;
         for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
           const int s = rp.s;
+          if (PRE && p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmA, p.a_coff + kb * G3_BK, tn * G3_TILE_M);
           mbar_wait(&empty_bar[s], rp.ph ^ 1u);
           uint8_t* sa = smem + p.off_a + (size_t)s * p.stage_bytes;
           mbar_arrive_expect_tx(&full_bar[s], tx);
@@ -224,7 +226,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       pdl_wait();
       RingPos pp;
       for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
+        const int tn = t + (int)gridDim.x;             // this CTA's next tile: start it towards L2 now (p.l2_ahead)
         for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
+          if (p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmR, n0 + 32 * c, tn * G3_TILE_M);
           mbar_wait(&pre_empty[pp.s], pp.ph ^ 1u);
           mbar_arrive_expect_tx(&pre_full[pp.s], (uint32_t)G3_PRE_BYTES);
           tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, t * G3_TILE_M);

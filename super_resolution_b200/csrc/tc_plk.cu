@@ -16,6 +16,7 @@
 
 #include "kernels.cuh"
 #include "tc_common.cuh"
+#include "side_jobs.cuh"
 
 namespace hb {
 
@@ -38,6 +39,8 @@ struct PlkParams {
   const float* dyn;          // (B, 16, 9) per-sample depthwise kernels (may be null)
   bf16* out;                 // token tensor, channels [0,16) of each token are overwritten
   int out_pitch;
+  int main_ctas;             // blockIdx.x >= main_ctas: extra CTA running `side` (side_jobs.cuh) for sample blockIdx.x - main_ctas
+  SideJob side;
 };
 }  // namespace
 
@@ -48,6 +51,14 @@ plk_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
   __shared__ uint32_t tmem_slot;
   __shared__ __align__(16) float sdk[9 * PD];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  if ((int)blockIdx.x >= p.main_ctas) {
+    // extra CTAs: a per-sample job of earlier kernels' results (the ECA gate the NEXT kernel needs), on SMs this
+    // launch leaves idle (128 tiles on 148 SMs at the bench shape)
+    pdl_wait();
+    pdl_trigger();
+    run_side_job(p.side, (int)blockIdx.x - p.main_ctas, reinterpret_cast<float*>(smem));
+    return;
+  }
   uint8_t* sm_b = smem;
   uint8_t* sm_h = smem + B_STAGES * BST_BYTES;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -237,7 +248,7 @@ bool plk_tc_supported(int pdim, int ksize, int H, int W, int out_pitch) {
 }
 
 int launch_plk_tc(const bf16* xpad, int B, int H, int W, const bf16* wt, const float* dyn, bf16* out, int out_pitch,
-                  cudaStream_t st) {
+                  cudaStream_t st, const SideJob* side) {
   CUtensorMap tmX, tmW;
   const int G = (W + 2 * PH) / 4;
   {
@@ -261,7 +272,9 @@ int launch_plk_tc(const bf16* xpad, int B, int H, int W, const bf16* wt, const f
     HB_CHECK_CUDA(cudaFuncSetAttribute(plk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PLK_SMEM));
     attr_set = true;
   }
-  launch_pdl(plk_tc_kernel, dim3(B * p.tiles_x * p.tiles_y), dim3(PLK_THREADS), PLK_SMEM, st, tmX, tmW, p);
+  p.main_ctas = B * p.tiles_x * p.tiles_y;
+  if (side) p.side = *side;
+  launch_pdl(plk_tc_kernel, dim3(p.main_ctas + (side ? side->B : 0)), dim3(PLK_THREADS), PLK_SMEM, st, tmX, tmW, p);
   HB_CHECK_LAUNCH();
   return 0;
 }
