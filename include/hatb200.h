@@ -291,6 +291,13 @@ int hatb200_dwconv_gate_noalloc(const void* in, int dtype, int in_pitch, int B, 
 int hatb200_probe_umma(const void* a, int R, const void* b, int r0, int sbo_bytes, int base_offset, float* out,
                        void* stream);
 int hatb200_debug_gemm_trace(unsigned long long* host, void* stream);
+/* tcgen05.cp.128x256b probe (tools/probe_tmem_cp.py): copies a TMA-written 128 x 32 fp32 tile (mode 0: one SWIZZLE_128B
+ * box, mode 1: four SWIZZLE_32B boxes) into TMEM and reads it back; the residual preload of csrc/tc_gemm.cu rests on it. */
+int hatb200_probe_tmem_cp(const float* src, int mode, float* out, void* stream);
+/* Memory-system ceiling of the esc_aggr traffic pattern with no arithmetic (tools/probe_stream.py): o32 = r + a + u,
+ * o16 = bf16(o32) over n8 groups of 8 elements, `ctas` CTAs of 1024 threads, optionally walking backwards (rev). */
+int hatb200_probe_stream(const void* a, const void* u, const void* r, void* o32, void* o16, size_t n8, int ctas, int rev,
+                         void* stream);
 #endif
 
 #ifdef __cplusplus
