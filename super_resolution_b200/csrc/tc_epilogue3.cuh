@@ -283,6 +283,13 @@ struct WarpState {
   RingPos k;                                      // operand-ring cursor of this warpgroup (consumer side)
   int g, ew, quarter, lane, wg_tid, row;
   int BN, N, n0, nch, H, W, hw;
+  // N-split CTA pair (tc_gemm.cu, SPLIT): this CTA owns columns [n0, n0 + BN) of a LayerNorm row, its cluster peer the
+  // rest; the fp32 store map is based at column n0 (so_f32 = 0 then), row statistics are exchanged through xch
+  int so_f32 = 0;                                 // column origin of fp32 stores in tmOF coordinates (n0 unless split)
+  float2* xch = nullptr;                          // [2 parities][2 stages][128 rows]: (mean, M2) written by the PEER
+  uint64_t* xch_bar = nullptr;                    // [2 stages]: 128 remote arrivals per tile
+  uint32_t peer = 0;                              // cluster rank of the peer
+  uint32_t xch_n = 0;                             // exchanges done by this warp (parity / buffer)
   bool last_ntile;
   bool prof = false;                              // engineering: accumulate wait cycles (HATB200_GEMM_TRACE)
   long long t_ring = 0, t_stg = 0, t_p1 = 0, t_p2 = 0;
@@ -331,7 +338,8 @@ inline int feat_select(const Epilogue& ep) {
 
 // The whole epilogue of one tile for the calling warp.  F: feature set; TS: Tile2D / Tile4D.
 // PRE: the accumulator already contains the fp32 residual (tc_gemm.cu preloads it with tcgen05.cp), the epilogue skips it.
-template <class F, bool GROUPED, class TS, bool PRE = false>
+// SPLIT: the row is shared with the cluster peer (see WarpState); LayerNorm statistics are merged across the pair.
+template <class F, bool GROUPED, class TS, bool PRE = false, bool SPLIT = false>
 __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>& ws, const RowInfo& ri, const TS& ts,
                                          const CUtensorMap* tmOF, const CUtensorMap* tmOT, const CUtensorMap* tmLN) {
   constexpr int GW32 = WarpState<GROUPED>::GW32, GW16 = WarpState<GROUPED>::GW16;
@@ -438,7 +446,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
       if (slot == 0) ws.st32.begin(lane);
       if (ws.prof) ws.t_stg += clock64() - tw;
       ws.st32.put_f32(lane, slot, v);
-      if (slot == GW32 - 1 || ci == nch - 1) ws.st32.flush(tmOF, lane, n0 + (ci - slot) * CW, ts, quarter);
+      if (slot == GW32 - 1 || ci == nch - 1) ws.st32.flush(tmOF, lane, (SPLIT ? ws.so_f32 : n0) + (ci - slot) * CW, ts, quarter);
     }
     if (out16) {
       const int slot = ci % GW16;
@@ -475,15 +483,37 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
     if (ws.share_stg) { if (elect_one()) bulk_wait_read<0>(); __syncwarp(); }   // fp32 stores have left the shared staging
     tmem_st_wait();
     // pad columns hold exact zeros: remove their contribution to the shifted sums
-    const float npad = (float)(ws.BN - ws.N);
+    const int nmine = SPLIT ? max(0, min(ws.BN, ws.N - n0)) : ws.N;       // valid columns of this CTA
+    const float npad = (float)(ws.BN - nmine);
     const float s1 = s1a + s1b + npad * ln_k;
     const float s2 = s2a + s2b - npad * ln_k * ln_k;
-    const float inv_n = 1.f / (float)ws.N;
-    const float mean_d = s1 * inv_n;
-    const float var = fmaxf(s2 * inv_n - mean_d * mean_d, 0.f);
-    const float rstd = rsqrtf(var + 1e-5f);
-    const float nmr = -(ln_k + mean_d) * rstd;    // (x - mean) * rstd = x * rstd + nmr
-    const bool head = F::HEAD && ep.ln_head != nullptr;
+    float rstd, nmr;
+    if (SPLIT) {
+      // (mean, M2) of my columns -> the peer's shared memory, its barrier; mine arrive the same way; merge (Chan et al.)
+      const float fm = (float)nmine, fp = (float)(ws.N - nmine);
+      const float mean_m = ln_k + s1 / fm;
+      const float m2_m = fmaxf(s2 - s1 * s1 / fm, 0.f);
+      const uint32_t slot = ((ws.xch_n & 1u) * 2u + (uint32_t)g) * 128u + (uint32_t)row;
+      const uint32_t remote = mapa_u32(ws.xch + slot, ws.peer);
+      asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(mean_m), "f"(m2_m) : "memory");
+      mbar_arrive_cluster(mapa_u32(&ws.xch_bar[g], ws.peer));
+      mbar_wait_cluster(&ws.xch_bar[g], ws.xch_n & 1u);
+      const float2 pr = ws.xch[slot];
+      ws.xch_n++;
+      const float inv_n = 1.f / (float)ws.N;
+      const float delta = pr.x - mean_m;
+      const float mean = (fm * mean_m + fp * pr.x) * inv_n;
+      const float m2 = m2_m + pr.y + delta * delta * fm * fp * inv_n;
+      rstd = rsqrtf(m2 * inv_n + 1e-5f);
+      nmr = -mean * rstd;
+    } else {
+      const float inv_n = 1.f / (float)ws.N;
+      const float mean_d = s1 * inv_n;
+      const float var = fmaxf(s2 * inv_n - mean_d * mean_d, 0.f);
+      rstd = rsqrtf(var + 1e-5f);
+      nmr = -(ln_k + mean_d) * rstd;    // (x - mean) * rstd = x * rstd + nmr
+    }
+    const bool head = F::HEAD && ep.ln_head != nullptr && (!SPLIT || n0 == 0);
     auto pass2 = [&](const int ci, uint32_t (&rc)[CW], uint32_t (&rn)[CW]) __attribute__((always_inline)) {
       const int nb = ci * CW;
       float ga[CW], be[CW], v[CW];
@@ -535,7 +565,7 @@ __device__ __forceinline__ void run_tile(const Epilogue& ep, WarpState<GROUPED>&
       pass2(ci, rb, ra);
       if (ci + 1 < nch) pass2(ci + 1, ra, rb);
     }
-    for (int nb = ws.BN; nb < ep.ln_pitch; nb += CW * GW16) {   // pad columns beyond the (single) n-tile
+    for (int nb = ws.BN; !SPLIT && nb < ep.ln_pitch; nb += CW * GW16) {   // pad columns beyond the (single) n-tile
       ws.st16.begin(lane);
       ws.st16.put_zero(lane);
       ws.st16.flush(tmLN, lane, nb, ts, quarter);

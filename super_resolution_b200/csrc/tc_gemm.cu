@@ -63,6 +63,7 @@ struct G3Params {
   int ops, op_stage_bytes, op_u_off;   // operand ring per warpgroup
   int has_resid, has_u;
   int pre, pre_stages, off_pre;        // fp32 residual preloaded into the accumulator (tcgen05.cp), its TMA ring
+  int split;                           // N-split CTA pairs: BN is HALF of the LayerNorm row, the cluster peer owns the rest
   uint32_t acc_stride, tmem_cols;
   // shared memory offsets (bytes from the 1024-aligned base)
   int off_b, off_a, off_op, off_stg32, off_stg16, off_tab, smem_bytes;
@@ -87,12 +88,20 @@ struct G3Params {
 // tcgen05.cp.128x256b (shared memory -> TMEM; tools/probe_tmem_cp.py: row r -> lane r, column c -> column c), and
 // the tile's MMAs then ACCUMULATE on top of it (the tensor pipe runs cp and mma in issue order).  `acc` arrives in the
 // epilogue as resid + A W^T: no ring stage, no shared-memory read and no add for the largest operand of the layer.
-template <class F, bool GROUPED, int NWG = 2, bool PRE = false>
+//
+// SPLIT (round 2): the two CTAs of a cluster share every 128-token tile -- rank r owns columns [r * BN, (r + 1) * BN) of
+// the row (BN = 96 of N = 180): half of the weight panel (resident again for K = 384), half of the residual boxes, half
+// of the epilogue per tile, 512 tiles on 74 pairs = 6.92 -> 7 rounds instead of 3.46 -> 4 on 148 CTAs.  Plain
+// cta_group::1 MMAs (M128 x N96); only the LayerNorm statistics cross the pair: (mean, M2) of each half row go to the
+// peer's shared memory (st.shared::cluster + remote mbarrier arrive) and are merged (tc_epilogue3.cuh).  fp32 / LN stores
+// use per-rank tensor maps (tmOF / tmOF1, tmLN / tmLN1) based at the rank's first column so that boxes clip at its edge.
+template <class F, bool GROUPED, int NWG = 2, bool PRE = false, bool SPLIT = false>
 __global__ void __launch_bounds__(NWG == 4 ? 64 + 128 * 4 : (PRE ? G3_THREADS + 32 : G3_THREADS), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmU,
                const __grid_constant__ CUtensorMap tmOF, const __grid_constant__ CUtensorMap tmOT,
-               const __grid_constant__ CUtensorMap tmLN, const G3Params p, const Epilogue ep) {
+               const __grid_constant__ CUtensorMap tmLN, const __grid_constant__ CUtensorMap tmOF1,
+               const __grid_constant__ CUtensorMap tmLN1, const G3Params p, const Epilogue ep) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[G3_MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[G3_MAX_STAGES];
@@ -104,10 +113,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __shared__ __align__(8) uint64_t pre_full[G3_PRE_MAX], pre_empty[G3_PRE_MAX];
   __shared__ uint32_t tmem_slot;
   __shared__ float hsum[8][16];                       // per epilogue warp: column sums of the LN head
+  __shared__ __align__(8) float2 xch[SPLIT ? 2 * 2 * 128 : 1];   // SPLIT: (mean, M2) of the peer's half rows
+  __shared__ __align__(8) uint64_t xch_bar[2];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.y * p.BN;
+  const int crank = SPLIT ? (int)cluster_ctarank() : 0;                     // rank in the N-split pair
+  const int walker = SPLIT ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;      // which tiles this CTA walks ...
+  const int wstep = SPLIT ? (int)(gridDim.x >> 1) : (int)gridDim.x;         // ... and in what stride
+  const int n0 = SPLIT ? crank * p.BN : blockIdx.y * p.BN;
   constexpr int A_BYTES = G3_TILE_M * G3_BK * 2;
   float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);   // [BN]
   float* tab_gamma = tab_bias + p.BN;                             // [BN]
@@ -127,6 +141,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(&pre_empty[s], 1);
     }
     for (int g = 0; g < 2; g++) {
+      mbar_init(&xch_bar[g], 128);
       mbar_init(&tmem_full_bar[g], 1);
       mbar_init(&tmem_empty_bar[g], 64 * NWG);
       for (int s = 0; s < G3_MAX_OPS; s++) {
@@ -146,7 +161,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == 1) tmem_alloc(&tmem_slot, p.tmem_cols);
   tc_fence_before();
-  __syncthreads();
+  if (SPLIT) cluster_sync_all();      // the peer's exchange barriers are initialised before anything remote arrives on them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
@@ -164,8 +180,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       pdl_trigger();
       const uint32_t tx = (uint32_t)(A_BYTES + (p.b_resident ? 0 : p.BN * 128));
       RingPos rp;
-      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
-        const int tn = t + (int)gridDim.x;
+      for (int t = walker; t < p.m_tiles; t += wstep) {
+        const int tn = t + wstep;
         for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
           const int s = rp.s;
           if (PRE && p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmA, p.a_coff + kb * G3_BK, tn * G3_TILE_M);
@@ -187,7 +203,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       G3_TRACE(1);
       RingPos rp, pp;
       int i = 0;
-      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
+      for (int t = walker; t < p.m_tiles; t += wstep, i++) {
         const int g = i & 1;
         mbar_wait(&tmem_empty_bar[g], (((uint32_t)i >> 1) & 1u) ^ 1u);     // epilogue has drained this stage
         tc_fence_after();
@@ -225,8 +241,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       prefetch_tmap(&tmR);
       pdl_wait();
       RingPos pp;
-      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x) {
-        const int tn = t + (int)gridDim.x;             // this CTA's next tile: start it towards L2 now (p.l2_ahead)
+      for (int t = walker; t < p.m_tiles; t += wstep) {
+        const int tn = t + wstep;                      // this CTA's next tile: start it towards L2 now (p.l2_ahead)
         for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
           if (p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmR, n0 + 32 * c, tn * G3_TILE_M);
           mbar_wait(&pre_empty[pp.s], pp.ph ^ 1u);
@@ -246,10 +262,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint8_t* ring = smem + p.off_op + (size_t)g * p.ops * p.op_stage_bytes;
       RingPos k;
       int i = 0;
-      for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
+      for (int t = walker; t < p.m_tiles; t += wstep, i++) {
         if ((i & 1) != g) continue;
         const Tile2D ts{t * G3_TILE_M};
-        const int tn = t + 2 * (int)gridDim.x;          // this warpgroup's next tile
+        const int tn = t + 2 * wstep;                   // this warpgroup's next tile
         const Tile2D nx{tn * G3_TILE_M};
         produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, ring_resid,
                      p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr);
@@ -273,17 +289,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ws.has_resid = PRE ? 0 : p.has_resid; ws.has_u = p.has_u; ws.share_stg = p.share_stg;
     ws.prof = p.trace != nullptr && p.prof;
     ws.hsum = hsum; ws.sred = nullptr;                   // no tile column sums in the 1x1 layers
+    ws.so_f32 = 0; ws.xch = xch; ws.xch_bar = xch_bar; ws.peer = (uint32_t)(crank ^ 1);
+    const CUtensorMap* pOF = (SPLIT && crank) ? &tmOF1 : &tmOF;
+    const CUtensorMap* pLN = (SPLIT && crank) ? &tmLN1 : &tmLN;
     ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
     ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
     ws.st16.base = smem + p.off_stg16 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st16)::BUF);
     if (lane == 0) {
-      if (ep.out_f32) prefetch_tmap(&tmOF);
+      if (ep.out_f32) prefetch_tmap(pOF);
       if (ep.out_t) prefetch_tmap(&tmOT);
-      if (ep.ln_out) prefetch_tmap(&tmLN);
+      if (ep.ln_out) prefetch_tmap(pLN);
     }
     pdl_wait();          // the epilogue reads the ECA gate / ring operands and writes the outputs
     int i = 0;
-    for (int t = blockIdx.x; t < p.m_tiles; t += gridDim.x, i++) {
+    for (int t = walker; t < p.m_tiles; t += wstep, i++) {
       if ((i & 1) != g) continue;
       const int m0 = t * G3_TILE_M;
       RowInfo ri;
@@ -299,7 +318,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       if (tr) G3_TRACE(25 + g * 16 + 4 * (i >> 1));
       const Tile2D ts{m0};
-      run_tile<F, GROUPED, Tile2D, PRE>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+      run_tile<F, GROUPED, Tile2D, PRE, SPLIT>(ep, ws, ri, ts, pOF, &tmOT, pLN);
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[g]);
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
@@ -312,7 +331,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if (SPLIT) cluster_sync_all();      // no CTA leaves while its peer may still write into its shared memory
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -349,6 +369,18 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   if ((a.a_pitch * 2) % 16 || (a.a_coff * 2) % 16) return false;
   p.BN = tc_bn(a.N);
   if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
+  // N-split CTA pairs for the residual + LayerNorm layers whose row is one n-tile (see the kernel)
+  // MEASURED SLOWER on B200 and therefore opt-in (HATB200_G3_SPLIT=1; parity-green, tests/test_gpu_kernels.py): esc_aggr
+  // 46.4 -> 51.8 us, fc2 42.2 -> 48.3 us.  Pass 1 of a half row halves (5.5 -> 2.8 us per tile) but every tile is a
+  // rendezvous of the two CTAs -- the statistics exchange waits 2-4 us per tile for the slower peer (trace_gemm.py:
+  // pass 2 2.3 -> 4.4 us), which costs more than 7 half tiles instead of 4 whole ones saves.
+  const char* split_env = getenv("HATB200_G3_SPLIT");
+  const bool no_split = !(split_env && split_env[0] == '1');
+  static const bool no_pre0 = getenv("HATB200_G3_PRE") && getenv("HATB200_G3_PRE")[0] == '0';
+  const int feat0 = feat_select(ep);
+  p.split = (!no_split && ep.ln_out && Npad == p.BN && p.BN % 64 == 0 && M / G3_TILE_M >= 2 &&
+             ((feat0 == FEAT_RESLN && !no_pre0) || feat0 == FEAT_RESULN)) ? 1 : 0;
+  if (p.split) p.BN /= 2;
   // features this kernel does not implement (tc_tapconv.cu handles those layers)
   if (ep.colsum || ep.dyn_k || ep.shuffle_r != 1) return false;
   if (ep.scale_ncols % CW) return false;
@@ -359,7 +391,7 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   if (ep.ln_out && ((ep.ln_pitch * 2) % 16 || ((uintptr_t)ep.ln_out & 15) || ep.ln_pitch < a.N)) return false;
   if (ep.resid && ((ep.resid_pitch * 4) % 16 || ((uintptr_t)ep.resid & 15))) return false;
   if (ep.eca_u && ((ep.eca_pitch * 2) % 16 || ((uintptr_t)ep.eca_u & 15) || ep.eca_pitch < a.N)) return false;
-  if (ep.ln_out && Npad != p.BN) return false;                    // LayerNorm needs the whole row in one CTA
+  if (ep.ln_out && Npad != p.BN * (p.split ? 2 : 1)) return false;     // LayerNorm needs the whole row in one CTA (pair)
   if (ep.ln_head && (ep.ln_head_c > 16 || !ep.ln_out)) return false;
   p.M = (int)M; p.H = a.H; p.W = a.W; p.hw = a.H * a.W;
   p.a_coff = a.a_coff; p.kblocks = Kpad / G3_BK;
@@ -377,7 +409,9 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   p.pre = (!no_pre && p.has_resid && !p.has_u && p.BN % 32 == 0 && feat_select(ep) != FEAT_PLAIN) ? 1 : 0;
   p.pre_stages = 0; p.off_pre = 0;
   const bool ring = (p.has_resid && !p.pre) || p.has_u;
-  grouped = p.BN % 64 == 0;                 // stores leave as 128-byte rows (2 fp32 / 4 bf16 chunks per TMA store)
+  // stores leave as 128-byte rows (2 fp32 / 4 bf16 chunks per TMA store); a split row ends its last bf16 group early and
+  // the per-rank tensor map clips the box there
+  grouped = p.BN % 64 == 0 || (p.split && p.BN % 32 == 0);
   const bool f32o = ep.out_f32 != nullptr, bf16o = ep.out_t != nullptr || ep.ln_out != nullptr;
   // fp32 staging is idle during the LayerNorm pass and vice versa: share it unless pass 1 also writes bf16
   p.share_stg = f32o && bf16o && ep.out_t == nullptr;
@@ -402,6 +436,7 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
   static const int force_bufs = getenv("HATB200_G3_STGBUFS") ? atoi(getenv("HATB200_G3_STGBUFS")) : 0;
   static const int force_res = getenv("HATB200_G3_RESIDENT") ? atoi(getenv("HATB200_G3_RESIDENT")) : -1;
   static const int force_pre = getenv("HATB200_G3_PRESTAGES") ? atoi(getenv("HATB200_G3_PRESTAGES")) : 0;
+  const int smem_limit = G3_SMEM_LIMIT - (p.split ? 4096 : 0);     // the pair's exchange buffer is static shared memory
   int best_score = -1;
   G3Params best = p;
   for (int resident = 1; resident >= 0; resident--) {
@@ -415,7 +450,7 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
       for (int pre = p.pre ? 4 : 0; pre >= (p.pre ? 2 : 0); pre--) {
         if (force_ops && ring && ops != force_ops) continue;
         if (force_pre && p.pre && pre != force_pre) continue;
-        const int avail = G3_SMEM_LIMIT - fixed - 2 * ops * p.op_stage_bytes - pre * G3_PRE_BYTES;
+        const int avail = smem_limit - fixed - 2 * ops * p.op_stage_bytes - pre * G3_PRE_BYTES;
         int st = avail > 0 ? avail / stage : 0;
         if (st > G3_MAX_STAGES) st = G3_MAX_STAGES;
         if (st > p.kblocks * 2 && st > 4) st = p.kblocks * 2 > 4 ? p.kblocks * 2 : 4;
@@ -452,7 +487,7 @@ static bool gemm_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue&
     p.off_stg16 = p.share_stg ? p.off_stg32 : off; off += s16;
     p.off_tab = off; off += tab;
     p.smem_bytes = off;
-    return off <= G3_SMEM_LIMIT;
+    return off <= smem_limit;
   }
 }
 
@@ -497,11 +532,17 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     uint32_t box[2] = {(uint32_t)CW, G3_TILE_M};
     HB_TRY(tc::make_tmap_bf16(&tmU, ep.eca_u, 2, dims, str, box, CW * 2));
   }
+  CUtensorMap tmOF1, tmLN1;
+  tmOF1 = tmA; tmLN1 = tmA;
   if (ep.out_f32) {      // stores clip at N
-    uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
+    uint64_t dims[2] = {(uint64_t)(p.split ? p.BN : p.N), (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)ep.out_f32_pitch * 4};
     uint32_t box[2] = {w32, 32};
     HB_TRY(tc::make_tmap_f32(&tmOF, ep.out_f32, 2, dims, str, box, w32 * 4));
+    if (p.split) {       // rank 1: columns [BN, N), map based at column BN
+      dims[0] = (uint64_t)(p.N - p.BN);
+      HB_TRY(tc::make_tmap_f32(&tmOF1, ep.out_f32 + p.BN, 2, dims, str, box, w32 * 4));
+    }
   }
   if (ep.out_t) {        // stores clip at max(N, zero_to): the pad columns in between receive computed zeros
     const int width = ep.out_t_zero_to > p.N ? ep.out_t_zero_to : p.N;
@@ -511,10 +552,15 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     HB_TRY(tc::make_tmap_bf16(&tmOT, (const bf16*)ep.out_t + ep.out_t_coff, 2, dims, str, box, w16 * 2));
   }
   if (ep.ln_out) {       // LayerNorm output: pad columns up to ln_pitch are written as zero
-    uint64_t dims[2] = {(uint64_t)ep.ln_pitch, (uint64_t)p.M};
+    uint64_t dims[2] = {(uint64_t)(p.split ? p.BN : ep.ln_pitch), (uint64_t)p.M};
     uint64_t str[1] = {(uint64_t)ep.ln_pitch * 2};
     uint32_t box[2] = {w16, 32};
     HB_TRY(tc::make_tmap_bf16(&tmLN, ep.ln_out, 2, dims, str, box, w16 * 2));
+    if (p.split) {       // rank 1: columns [BN, ln_pitch) (its pad columns come out as computed zeros)
+      HB_REQUIRE(ep.ln_pitch <= 2 * p.BN && ep.ln_pitch > p.BN, HATB200_EUNSUPPORTED, "gemm_tc: split row wider than the pair");
+      dims[0] = (uint64_t)(ep.ln_pitch - p.BN);
+      HB_TRY(tc::make_tmap_bf16(&tmLN1, (const bf16*)ep.ln_out + p.BN, 2, dims, str, box, w16 * 2));
+    }
   }
   p.trace = nullptr; p.prof = 0;
   p.l2_ahead = getenv("HATB200_G3_L2AHEAD") ? atoi(getenv("HATB200_G3_L2AHEAD")) : 0;
@@ -539,31 +585,51 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<F_, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
     G3_ATTR_PRE(FeatAll); G3_ATTR_PRE(FeatResLn); G3_ATTR_PRE(FeatResULn);
 #undef G3_ATTR_PRE
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<FeatResLn, true, 2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim - 4096));
+    HB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<FeatResULn, true, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim - 4096));
     attr_set = true;
   }
-  const int n_tiles = Npad / p.BN;
+  const int n_tiles = p.split ? 1 : Npad / p.BN;
   int per_n = sm_count() / n_tiles;
   if (per_n < 1) per_n = 1;
   if (per_n > p.m_tiles) per_n = p.m_tiles;
   dim3 grid(per_n, n_tiles);
+  if (p.split) {         // clusters of two along x: 74 pairs walk the tiles, rank = column half
+    HB_REQUIRE(grouped, HATB200_EUNSUPPORTED, "gemm_tc: split needs grouped stores");
+    int pairs = sm_count() / 2;
+    if (pairs > p.m_tiles) pairs = p.m_tiles;
+    grid = dim3(2 * pairs, 1);
+    if (feat_select(ep) == FEAT_RESLN && p.pre)
+      launch_pdl_cluster(gemm_tc_kernel<FeatResLn, true, 2, true, true>, 2, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU,
+                         tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep);
+    else if (feat_select(ep) == FEAT_RESULN && !p.pre)
+      launch_pdl_cluster(gemm_tc_kernel<FeatResULn, true, 2, false, true>, 2, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU,
+                         tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep);
+    else {
+      set_error("gemm_tc: split planned for an epilogue without a split kernel");
+      return HATB200_EUNSUPPORTED;
+    }
+    HB_CHECK_LAUNCH();
+    return 0;
+  }
   const bool ring = p.has_resid || p.has_u;
   // epilogue specialisation: the first compile-time feature set that covers this layer exactly, else the generic one
 #define G3_LAUNCH(F_)                                                                                                \
   do {                                                                                                               \
-    if (grouped) launch_pdl(gemm_tc_kernel<F_, true>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
-    else launch_pdl(gemm_tc_kernel<F_, false>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);       \
+    if (grouped) launch_pdl(gemm_tc_kernel<F_, true>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep); \
+    else launch_pdl(gemm_tc_kernel<F_, false>, grid, dim3(G3_THREADS), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep);       \
   } while (0)
 #define G3_LAUNCH_R(F_)                                                                                              \
   do {                                                                                                               \
     if (!p.pre) G3_LAUNCH(F_);                                                                                       \
-    else if (grouped) launch_pdl(gemm_tc_kernel<F_, true, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep); \
-    else launch_pdl(gemm_tc_kernel<F_, false, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);            \
+    else if (grouped) launch_pdl(gemm_tc_kernel<F_, true, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep); \
+    else launch_pdl(gemm_tc_kernel<F_, false, 2, true>, grid, dim3(G3_THREADS + 32), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep);            \
   } while (0)
   static const bool generic_only = getenv("HATB200_EPI_GENERIC") != nullptr;     // engineering: A/B the specialisation
   switch (generic_only ? FEAT_ALL : feat_select(ep)) {
     case FEAT_PLAIN:
       if (p.nwg == 4)
-        launch_pdl(gemm_tc_kernel<FeatPlain, true, 4>, grid, dim3(64 + 128 * 4), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, p, ep);
+        launch_pdl(gemm_tc_kernel<FeatPlain, true, 4>, grid, dim3(64 + 128 * 4), smem, st, tmA, tmB, tmR, tmU, tmOF, tmOT, tmLN, tmOF1, tmLN1, p, ep);
       else G3_LAUNCH(FeatPlain);
       break;
     case FEAT_RESLN: G3_LAUNCH_R(FeatResLn); break;

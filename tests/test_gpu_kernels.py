@@ -399,3 +399,14 @@ def test_conv3_fused_tcgen05(shape):
 ])
 def test_conv3_fused_tcgen05_full_size(shape):
     _conv3_fused_case(*shape, seed=5)
+
+
+@pytest.mark.gpu
+def test_linear_fused_n_split_pair_opt_in(monkeypatch):
+    """HATB200_G3_SPLIT=1: the residual + LayerNorm layers on N-split CTA pairs (each CTA half of the row, LayerNorm
+    statistics merged across the cluster through distributed shared memory).  Opt-in because it measured slower; the
+    numerics are the same epilogue, so the full-size cases must still pass."""
+    monkeypatch.setenv("HATB200_G3_SPLIT", "1")
+    _linear_fused_case(16, 64, 64, 360, 180, True, False, True, True, False, 0, seed=3)     # ffn fc2 at bench size
+    _linear_fused_case(16, 64, 64, 180, 180, True, True, True, False, False, 0, seed=3)     # ESC aggr at bench size
+    _linear_fused_case(2, 16, 32, 360, 180, True, False, True, True, False, 0)              # fewer tiles than pairs

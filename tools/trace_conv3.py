@@ -14,6 +14,7 @@ L = _lib.lib()
 p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
 B, H, W = 16, 64, 64
 Cin, N = int(sys.argv[1]) if len(sys.argv) > 1 else 180, int(sys.argv[2]) if len(sys.argv) > 2 else 60
+ACT = int(sys.argv[3]) if len(sys.argv) > 3 else 0          # 1: GELU (CAB conv1)
 M = B * H * W
 pitch = ((Cin + 63) // 64) * 64
 x = torch.zeros(M, pitch, dtype=torch.bfloat16, device="cuda"); x[:, :Cin] = torch.randn(M, Cin, device="cuda").bfloat16()
@@ -25,7 +26,7 @@ st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 for _ in range(3):
     flush.zero_()
-    _lib.check(L.hatb200_conv_fused(p(x), pitch, Cin, B, H, W, p(w), p(b), N, 3, 0, None, None, p(out), opitch, 0, None, None,
+    _lib.check(L.hatb200_conv_fused(p(x), pitch, Cin, B, H, W, p(w), p(b), N, 3, ACT, None, None, p(out), opitch, 0, None, None,
                                     None, 0, None, None, None, st))
 torch.cuda.synchronize()
 buf = np.zeros((1024, 64), dtype=np.uint64)
@@ -39,7 +40,7 @@ if int(os.environ.get("HATB200_C3_PROBE", "0")) & 1:
     print("in-kernel probe: cycles per MMA over 64 back-to-back issues: median %.1f min %.1f max %.1f" % (np.median(pr) / 64, pr.min() / 64, pr.max() / 64))
 t[:, 31] = 0
 t0 = t[live][t[live] > 0].min()
-print(Cin, N, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
+print(Cin, N, "act", ACT, "ctas", live.sum(), "span us", (t[live].max() - t0) / 1000)
 for cta in list(np.nonzero(live)[0][:2]) + [int(np.nonzero(live)[0][-1])]:
     r_ = t[cta]
     ev = {k: int(r_[k] - t0) for k in range(32) if r_[k] > 0}
