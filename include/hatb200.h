@@ -27,7 +27,8 @@ extern "C" {
 #define HATB200_VERSION 100
 #define HATB200_MAX_LAYERS 32
 
-enum { HATB200_F32 = 0, HATB200_BF16 = 1, HATB200_F16 = 2, HATB200_I64 = 3 };
+enum { HATB200_F32 = 0, HATB200_BF16 = 1, HATB200_F16 = 2, HATB200_I64 = 3,
+       HATB200_U8 = 4   /* only as y_dtype of hatb200_forward: the image as tensor2img bytes, see there */ };
 
 enum {
   HATB200_OK = 0,
@@ -112,7 +113,10 @@ int hatb200_workspace_bytes(hatb200_handle* h, int B, int H, int W, int compute_
  * y: (B,in_chans,H*s,W*s) NCHW; x_dtype selects the arithmetic: F32 -> fp32
  * CUDA-core path (parity mode), BF16 -> bf16 tensor-core path (fp32
  * accumulate).  H and W must be multiples of window_size (the reference raises
- * from calculate_mask -> window_partition, hat_arch.py:124-128, :831). */
+ * from calculate_mask -> window_partition, hat_arch.py:124-128, :831).
+ * y_dtype HATB200_U8 (bf16 path only): y is (B, H*s, W*s, in_chans) bytes = tensor2img(rgb2bgr=True, min_max=(0,1)) of
+ * the bf16 image (basicsr/utils/img_util.py:38-95: clamp, * 255, numpy round, channel order reversed), written by the
+ * conv_last epilogue itself -- bit-identical to hatb200_tensor2img of the bf16 forward, a quarter of its D2H bytes. */
 int hatb200_forward(hatb200_handle* h, const void* x, int x_dtype, int B, int H, int W,
                     void* y, int y_dtype, void* workspace, size_t ws_bytes, void* stream);
 /* HAT.forward_features (hat_arch.py:828-846): x is the (B, embed_dim, H, W) output of conv_first, y the
@@ -244,7 +248,9 @@ int hatb200_conv_first(const void* x, int x_dtype, int B, int in_chans, int H, i
 
 /* conv_last + de-normalisation (hat_arch.py:856-858): in (B*H*W, 64) tokens -> y (B, out_chans, H, W) NCHW of
  * conv3x3(in, w (out_chans, 64, 3, 3)) + bias, then / img_range + mean.  use_tc=1 (bf16): the tensor-core route of
- * the forward (N padded to 16 on conv3_tc, then the NCHW / affine pass); 0: the CUDA-core kernel. */
+ * the forward (N padded to 16 on conv3_tc, whose epilogue applies the affine and writes the NCHW planes -- or, y_dtype
+ * HATB200_U8, the (B, H, W, out_chans) tensor2img bytes); 2: the round-1 two-pass form of it (fp32 pixels-last, then a
+ * transpose kernel); 0: the CUDA-core kernel. */
 int hatb200_conv_last(const void* in, int dtype, int B, int H, int W, const float* w, const float* bias, int out_chans,
                       const float* mean4, float img_range, void* y, int y_dtype, int use_tc, void* stream);
 

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libhatb200.so")
 MAX_LAYERS = 32
 NOALLOC_MAX_HID = 1024      # HATB200_NOALLOC_MAX_HID
 
-F32, BF16, F16, I64 = 0, 1, 2, 3
+F32, BF16, F16, I64, U8 = 0, 1, 2, 3, 4
 
 
 class Config(C.Structure):
@@ -134,7 +134,7 @@ def check(code):
 def dtype_code(torch_dtype):
     import torch
     try:
-        return {torch.float32: F32, torch.bfloat16: BF16, torch.float16: F16, torch.int64: I64}[torch_dtype]
+        return {torch.float32: F32, torch.bfloat16: BF16, torch.float16: F16, torch.int64: I64, torch.uint8: U8}[torch_dtype]
     except KeyError:
         raise TypeError(f"unsupported dtype {torch_dtype}") from None
 

@@ -162,6 +162,14 @@ struct Epilogue {
   float* ln_head_colsum = nullptr;   // fp32 (num_m_tiles, ln_head_c) per-tile column sums of the LN head
   float* colsum = nullptr;           // fp32 (num_m_tiles, N) per-tile column sums of v (GAP partials)
   SideJob side;                      // honoured by tc_conv3.cu only (the caller checks conv3_tc_supported first)
+  // conv_last in one pass (tc_conv3.cu, FeatLast; hat_arch.py:858): y = (acc + bias) / img_range + mean written straight
+  // to the NCHW image (nchw_dt F32 / BF16), or, nchw_dt = HATB200_U8, tensor2img of it (img_util.py:38-95: the value as
+  // the compute dtype holds it, clamp to [0, 1], * 255, round half to even) as (B, H, W, oc) bytes with the channel
+  // order reversed (RGB -> BGR).  No other output.
+  void* nchw_y = nullptr;
+  int nchw_dt = 0, nchw_oc = 0, nchw_via_bf16 = 0;
+  float nchw_range = 1.f;
+  float nchw_mean[4] = {0.f, 0.f, 0.f, 0.f};
 };
 
 }  // namespace hb

@@ -69,10 +69,17 @@ int hatb200_conv_last(const void* in, int dtype, int B, int H, int W, const floa
     HB_TRY(launch_pack_w_bf16(w, HATB200_F32, out_chans, 64, 9, w16, Npad, Kpad, 0, 64, st));
     ConvArgs a{in, 64, 0, 64, B, H, W, 3, 3, out_chans};
     Epilogue ep;
-    ep.bias = bias; ep.out_f32 = cl32; ep.out_f32_pitch = 4;
+    ep.bias = bias;
+    if (use_tc == 2) {       // round-1 route: fp32 pixels-last, then the affine transpose kernel
+      ep.out_f32 = cl32; ep.out_f32_pitch = 4;
+      HB_REQUIRE(y_dtype != HATB200_U8, HATB200_EUNSUPPORTED, "conv_last: U8 output needs the one-pass route");
+    } else {                 // one pass: the conv3 epilogue writes the image (or its tensor2img bytes) itself
+      ep.nchw_y = y; ep.nchw_dt = y_dtype; ep.nchw_oc = out_chans; ep.nchw_range = img_range; ep.nchw_via_bf16 = 1;
+      for (int o = 0; o < 4; o++) ep.nchw_mean[o] = mean4[o];
+    }
     HB_REQUIRE(conv3_tc_supported(a, Npad, Kpad, ep), HATB200_EUNSUPPORTED, "conv_last: shape not supported by conv3_tc");
     r = launch_conv3_tc(a, w16, Npad, Kpad, ep, st);
-    if (r == 0) r = launch_nhwc_to_nchw_affine(cl32, 4, B, out_chans, H, W, mean4, img_range, y, y_dtype, st);
+    if (r == 0 && use_tc == 2) r = launch_nhwc_to_nchw_affine(cl32, 4, B, out_chans, H, W, mean4, img_range, y, y_dtype, st);
   } else {
     float* wp;
     HB_TRY(pool.alloc((void**)&wp, (size_t)9 * 64 * out_chans * sizeof(float), st));

@@ -560,6 +560,24 @@ struct Fwd {
     // tensor-core route: N = 3 padded to a 16-column MMA tile on the persistent conv3 kernel (fp32 pixels-last out),
     // then one pass that applies "/ img_range + mean" and writes the NCHW planes.  (The CUDA-core kernel below spends
     // one shared-memory weight load per FMA: 172 us for 16 x 256 x 256 pixels.)
+    if (tc() && h->conv_last_tc.w16 && c.in_chans <= 4 && !tc_disabled("conv_last")) {
+      // one pass (round 2): the conv3 epilogue itself applies "/ img_range + mean" and writes the NCHW planes -- or,
+      // y_dtype U8, the tensor2img bytes (clamp, * 255, round half to even, HWC, BGR) of the bf16 image
+      const ConvW& cw = h->conv_last_tc;
+      ConvArgs a{hr, 64, 0, 64, d.B, hh, hw, 3, 3, cw.O};
+      Epilogue ep; ep.bias = cw.bias;
+      ep.nchw_y = y; ep.nchw_dt = y_dt; ep.nchw_oc = c.in_chans; ep.nchw_range = c.img_range; ep.nchw_via_bf16 = 1;
+      for (int o = 0; o < 4; o++) ep.nchw_mean[o] = o < c.in_chans ? c.mean[o] : 0.f;
+      static const bool two_pass = getenv("HATB200_CONV_LAST_2PASS") != nullptr;       // engineering: A/B
+      if (!two_pass && conv3_tc_supported(a, cw.Npad, cw.Kpad, ep)) {
+        if (tid >= 0) h->recs[tid].kernel = "conv3_tc";
+        HB_TRY(launch_conv3_tc(a, cw.w16, cw.Npad, cw.Kpad, ep, st));
+        t_end(tid);
+        return dbg("conv_last one pass");
+      }
+    }
+    HB_REQUIRE(y_dt != HATB200_U8, HATB200_EUNSUPPORTED,
+               "y_dtype U8 needs the one-pass tcgen05 conv_last (bf16 compute, tensor cores on, <= 4 image channels)");
     if (tc() && w.CL32 && h->conv_last_tc.w16 && c.in_chans <= 4 && !tc_disabled("conv_last")) {
       const ConvW& cw = h->conv_last_tc;
       ConvArgs a{hr, 64, 0, 64, d.B, hh, hw, 3, 3, cw.O};
@@ -623,8 +641,8 @@ static int forward_common(hatb200_handle* h, const void* x, int x_dtype, int B, 
   HB_REQUIRE(x && y, HATB200_EINVAL, "forward: null tensor");
   HB_REQUIRE(x_dtype == HATB200_F32 || x_dtype == HATB200_BF16, HATB200_EUNSUPPORTED,
              "forward: input dtype %d (only F32 and BF16 are implemented)", x_dtype);
-  HB_REQUIRE(y_dtype == HATB200_F32 || y_dtype == HATB200_BF16, HATB200_EUNSUPPORTED, "forward: output dtype %d",
-             y_dtype);
+  HB_REQUIRE(y_dtype == HATB200_F32 || y_dtype == HATB200_BF16 || (y_dtype == HATB200_U8 && !features_only),
+             HATB200_EUNSUPPORTED, "forward: output dtype %d", y_dtype);
   HB_REQUIRE(h->packed, HATB200_EPARAM, "forward: weights are not packed (hatb200_set_param + hatb200_pack first)");
   Fwd f;
   f.h = h;

@@ -55,7 +55,7 @@ constexpr int C3_TW = 8, C3_TH = 16;                   // tile: 128 pixels = UMM
 constexpr int C3_HW = C3_TW + 2, C3_HH = C3_TH + 2;    // halo
 constexpr int C3_HROW = C3_HW * 128;                   // bytes between two halo image rows of one 64-channel block
 constexpr int C3_HALO_KB = ((C3_HH * C3_HW * 128 + 1023) / 1024) * 1024;   // 23552: one 64-channel block of a halo
-constexpr int C3_MAX_HST = 2, C3_MAX_WST = 16;
+constexpr int C3_MAX_HST = 4, C3_MAX_WST = 16;
 constexpr int C3_SMEM_LIMIT = 227 * 1024 - 2048;
 
 struct C3Params {
@@ -502,10 +502,38 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait(&tmem_full_bar[g], ((uint32_t)i >> 1) & 1u);
       tc_fence_after();
       if (tr) C3_TRACE(17 + 4 * i);
-      run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
-      tc_fence_before();
-      if (TWO) mbar_arrive_cluster(empty0[g]);      // rank 0 issues the next MMAs into both CTAs' stage g
-      else mbar_arrive(&tmem_empty_bar[g]);
+      if (F::LAST) {
+        // conv_last in one pass (hat_arch.py:858): the accumulator's first columns are the image channels.  Four
+        // columns per row out of TMEM, the stage handed back at once, then (acc + bias) / img_range + mean straight
+        // into the NCHW planes (8-pixel runs per image row), or the tensor2img bytes of it (Epilogue::nchw_*).
+        uint32_t a4[4];
+        tmem_ld4(ri.trow, a4);
+        tmem_ld_wait();
+        tc_fence_before();
+        if (TWO) mbar_arrive_relaxed_cluster(empty0[g]);       // relaxed: see tc_common.cuh (image stores are in flight)
+        else mbar_arrive_relaxed(&tmem_empty_bar[g]);
+        const size_t hw = (size_t)p.H * p.W, pix = (size_t)ri.py * p.W + ri.px;
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+          if (o >= ep.nchw_oc || (p.probe & 2)) break;
+          float v = __fadd_rn(__fdiv_rn(__uint_as_float(a4[o]) + tab_bias[o], ep.nchw_range), ep.nchw_mean[o]);
+          if (ep.nchw_dt == HATB200_F32) {
+            reinterpret_cast<float*>(ep.nchw_y)[((size_t)ts.b * ep.nchw_oc + o) * hw + pix] = v;
+          } else if (ep.nchw_dt == HATB200_BF16) {
+            reinterpret_cast<bf16*>(ep.nchw_y)[((size_t)ts.b * ep.nchw_oc + o) * hw + pix] = __float2bfloat16_rn(v);
+          } else {                        // HATB200_U8: tensor2img of the value as the compute dtype holds it
+            if (ep.nchw_via_bf16) v = __bfloat162float(__float2bfloat16_rn(v));
+            v = fminf(fmaxf(v, 0.f), 1.f);
+            reinterpret_cast<uint8_t*>(ep.nchw_y)[((size_t)ts.b * hw + pix) * ep.nchw_oc + (ep.nchw_oc - 1 - o)] =
+                (uint8_t)rintf(__fmul_rn(v, 255.0f));
+          }
+        }
+      } else {
+        run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
+        tc_fence_before();
+        if (TWO) mbar_arrive_cluster(empty0[g]);      // rank 0 issues the next MMAs into both CTAs' stage g
+        else mbar_arrive(&tmem_empty_bar[g]);
+      }
       if (tr) C3_TRACE(18 + 4 * i);
     }
     if (elect_one()) bulk_wait_all();
@@ -544,6 +572,9 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
   p.BN = tc_bn(a.N);
   if (Npad != tc_npad(a.N) || p.BN < 16 || p.BN > 256 || p.BN % 16) return false;
   if (ep.dyn_k || ep.eca_u || ep.scale_ncols) return false;      // tc_tapconv.cu keeps those layers
+  if (ep.nchw_y && (ep.nchw_oc < 1 || ep.nchw_oc > 4 || a.N != ep.nchw_oc || Npad != p.BN || ep.out_f32 || ep.out_t || ep.ln_out ||
+                    ep.colsum || ep.resid || ep.act != ACT_NONE || ep.shuffle_r != 1))
+    return false;
   if (ep.shuffle_r != 1) {      // conv + PixelShuffle: only with (i, j, c)-ordered rows, plain bf16 output of 64 channels
     const int r = ep.shuffle_r;
     if (!ep.shuffle_perm || (r != 2 && r != 3) || a.N != 64 * r * r || p.BN % 64) return false;
@@ -597,6 +628,9 @@ static bool conv3_geometry(const ConvArgs& a, int Npad, int Kpad, const Epilogue
     int hst = (pass & 4) ? 1 : 2, bufs = (pass & 1) || (f32o && ep.out_t) ? 1 : 2;
     if (force_grp) grp = force_grp;
     const int want = (grp == 3 ? 2 : 3) - (pass >= 8 ? 1 : 0);
+    // conv_last (64 -> 3 at HR size): 0.5 us of MMAs per tile and an epilogue of a few instructions, so the halo of tile
+    // t + 2 (issued when tile t's MMAs retire) is late with two stages; a third one took 78.3 -> 65.9 us
+    if (ep.nchw_y && !(pass & 4)) hst = 3;
     if (force_hst) hst = force_hst;
     if (force_bufs) bufs = force_bufs;
     p.grp = grp;
@@ -703,7 +737,7 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     HB_CHECK_CUDA(cudaFuncSetAttribute(conv3_tc_kernel<F_, G_, T_>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim))
 #define C3_ATTR(F_) \
     C3_ATTR1(F_, false, false); C3_ATTR1(F_, true, false); C3_ATTR1(F_, false, true); C3_ATTR1(F_, true, true)
-    C3_ATTR(FeatAll); C3_ATTR(FeatPlain); C3_ATTR(FeatColsum); C3_ATTR(FeatResLn);
+    C3_ATTR(FeatAll); C3_ATTR(FeatPlain); C3_ATTR(FeatColsum); C3_ATTR(FeatResLn); C3_ATTR(FeatLast);
 #undef C3_ATTR
 #undef C3_ATTR1
     attr_set = true;
@@ -734,6 +768,7 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     case FEAT_PLAIN: C3_LAUNCH(FeatPlain); break;
     case FEAT_COLSUM: C3_LAUNCH(FeatColsum); break;
     case FEAT_RESLN: C3_LAUNCH(FeatResLn); break;
+    case FEAT_LAST: C3_LAUNCH(FeatLast); break;
     default: C3_LAUNCH(FeatAll); break;
   }
 #undef C3_LAUNCH

@@ -309,11 +309,13 @@ struct RowInfo {
 // no feature branches at all (the generic body costs 266 instructions per 16-column chunk, 40 of them arithmetic,
 // and the epilogue warps -- two per scheduler -- are issue/latency bound: profiles/r01_ncu_fc2_*).  ACT, SCALE and
 // HEAD stay run-time inside a set that enables them.  The host picks the first matching set (feat_match).
-struct FeatAll    { static constexpr bool EXACT = 0, ACT = 1, SCALE = 1, U = 1, RESID = 1, OUT32 = 1, OUT16 = 1, LN = 1, HEAD = 1, COLSUM = 1; };
-struct FeatPlain  { static constexpr bool EXACT = 1, ACT = 1, SCALE = 1, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 0; };
-struct FeatColsum { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 1; };
-struct FeatResLn  { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 1, COLSUM = 0; };
-struct FeatResULn { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 1, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 0, COLSUM = 0; };
+struct FeatAll    { static constexpr bool EXACT = 0, ACT = 1, SCALE = 1, U = 1, RESID = 1, OUT32 = 1, OUT16 = 1, LN = 1, HEAD = 1, COLSUM = 1, LAST = 0; };
+struct FeatPlain  { static constexpr bool EXACT = 1, ACT = 1, SCALE = 1, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 0, LAST = 0; };
+struct FeatColsum { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 0, OUT32 = 0, OUT16 = 1, LN = 0, HEAD = 0, COLSUM = 1, LAST = 0; };
+struct FeatResLn  { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 1, COLSUM = 0, LAST = 0; };
+struct FeatResULn { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 1, RESID = 1, OUT32 = 1, OUT16 = 0, LN = 1, HEAD = 0, COLSUM = 0, LAST = 0; };
+// conv_last: no generic output at all, the kernel's own few lines write the image (Epilogue::nchw_y)
+struct FeatLast   { static constexpr bool EXACT = 1, ACT = 0, SCALE = 0, U = 0, RESID = 0, OUT32 = 0, OUT16 = 0, LN = 0, HEAD = 0, COLSUM = 0, LAST = 1; };
 template <class F> constexpr bool feat_ring() { return F::U || F::RESID; }
 
 // does the feature set F cover this epilogue exactly (EXACT) / at least (generic)?
@@ -327,8 +329,9 @@ inline bool feat_match(const Epilogue& ep) {
   if (F::EXACT) return u == F::U && r == F::RESID && o32 == F::OUT32 && o16 == F::OUT16 && ln == F::LN && cs == F::COLSUM;
   return (!u || F::U) && (!r || F::RESID) && (!o32 || F::OUT32) && (!o16 || F::OUT16) && (!ln || F::LN) && (!cs || F::COLSUM);
 }
-enum { FEAT_ALL = 0, FEAT_PLAIN, FEAT_COLSUM, FEAT_RESLN, FEAT_RESULN };
+enum { FEAT_ALL = 0, FEAT_PLAIN, FEAT_COLSUM, FEAT_RESLN, FEAT_RESULN, FEAT_LAST };
 inline int feat_select(const Epilogue& ep) {
+  if (ep.nchw_y) return FEAT_LAST;
   if (feat_match<FeatPlain>(ep)) return FEAT_PLAIN;
   if (feat_match<FeatColsum>(ep)) return FEAT_COLSUM;
   if (feat_match<FeatResLn>(ep)) return FEAT_RESLN;

@@ -66,6 +66,8 @@ class Engine:
         self.pack_cache_hit = None     # True / False after a (re)bind with the cache enabled
         self.output_view = False       # True: graphed forwards return the graph's own output buffer (valid until the
                                        # next forward of the same shape) instead of a fresh copy of it
+        self.output_u8 = False         # True (bf16 inputs): forward returns the image as tensor2img bytes, (B, H*s, W*s, C)
+                                       # uint8 BGR written by the conv_last epilogue (hatb200.h, y_dtype HATB200_U8)
         self.last_fallback_count = 0
         self._ws = None
         self._graphs = {}
@@ -224,10 +226,18 @@ class Engine:
             s = m.upscale if m.upsampler == 'pixelshuffle' else 1
             ws = self._workspace(B, H, W, _lib.dtype_code(x.dtype), x.device)
             if not self.use_cuda_graph or torch.cuda.is_current_stream_capturing():
-                y = torch.empty((B, m.in_chans, H * s, W * s), dtype=x.dtype, device=x.device)
+                y = self._alloc_y(x, s)
                 self._launch(x, y, ws)
                 return y
             return self._forward_graphed(x, ws, s)
+
+    def _alloc_y(self, x, s):
+        B, _, H, W = x.shape
+        if self.output_u8:
+            if x.dtype != torch.bfloat16:
+                raise NotImplementedError("output_u8 is implemented for bfloat16 inputs (the tensor-core path)")
+            return torch.empty((B, H * s, W * s, self.module.in_chans), dtype=torch.uint8, device=x.device)
+        return torch.empty((B, self.module.in_chans, H * s, W * s), dtype=x.dtype, device=x.device)
 
     def forward_features(self, x: torch.Tensor) -> torch.Tensor:
         """HAT.forward_features (hat_arch.py:828-846): (B, embed_dim, H, W) -> (B, embed_dim, H, W), eager launches."""
@@ -252,12 +262,11 @@ class Engine:
             return y
 
     def _forward_graphed(self, x, ws, s):
-        key = (tuple(x.shape), x.dtype)
+        key = (tuple(x.shape), x.dtype, bool(self.output_u8))
         entry = self._graphs.get(key)
         if entry is None:
-            B, _, H, W = x.shape
             xs = torch.empty_like(x)
-            ys = torch.empty((B, self.module.in_chans, H * s, W * s), dtype=x.dtype, device=x.device)
+            ys = self._alloc_y(x, s)
             xs.copy_(x)
             self._launch(xs, ys, ws)             # eager warm-up (also surfaces errors outside capture)
             torch.cuda.current_stream().synchronize()

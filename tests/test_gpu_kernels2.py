@@ -74,10 +74,12 @@ def test_conv_first(dtype, B, H, W, Cn, rng):
     assert err <= 1e-5 * max(1.0, ref.abs().max().item()), err
 
 
-@pytest.mark.parametrize("use_tc,ydt", [(1, torch.bfloat16), (1, torch.float32), (0, torch.bfloat16), (0, torch.float32)])
+@pytest.mark.parametrize("use_tc,ydt", [(1, torch.bfloat16), (1, torch.float32), (2, torch.bfloat16), (2, torch.float32),
+                                        (0, torch.bfloat16), (0, torch.float32)])
 @pytest.mark.parametrize("B,H,W,rng", [(1, 32, 64, 1.0), (2, 128, 128, 255.0)])
 def test_conv_last_routes(use_tc, ydt, B, H, W, rng):
-    """hat_arch.py:856-858, both routes of the bf16 forward (tensor-core N=3->16 + NCHW/affine pass; CUDA-core kernel)."""
+    """hat_arch.py:856-858, the routes of the bf16 forward: 1 = tensor-core N=3->16 with the affine + NCHW store in the
+    conv3 epilogue (one pass), 2 = the same conv followed by the NCHW/affine pass (round 1), 0 = CUDA-core kernel."""
     g = torch.Generator().manual_seed(43)
     x = torch.randn(B, 64, H, W, generator=g).bfloat16().float()
     w = torch.randn(3, 64, 3, 3, generator=g) * 0.05
@@ -94,6 +96,27 @@ def test_conv_last_routes(use_tc, ydt, B, H, W, rng):
     err = (y.float().cpu() - ref).abs().max().item()
     tol = 1e-5 if ydt == torch.float32 else 2.0 ** -8
     assert err <= tol * max(1.0, ref.abs().max().item()), err
+
+
+def test_conv_last_u8_mode_is_tensor2img_of_the_bf16_image():
+    """y_dtype U8: (B, H, W, 3) bytes, BGR = tensor2img (img_util.py:38-95) of the bf16 NCHW image of the same entry."""
+    from super_resolution_b200 import tensor2img
+    g = torch.Generator().manual_seed(44)
+    B, H, W = 2, 64, 96
+    x = torch.randn(B, 64, H, W, generator=g).bfloat16().float()
+    w = torch.randn(3, 64, 3, 3, generator=g) * 0.02
+    b = torch.rand(3, generator=g)                     # values spread over and beyond [0, 1]: the clamp matters
+    m4 = (C.c_float * 4)(*MEAN)
+    xd, wd, bd = _tok(x).to(DEV).bfloat16(), w.to(DEV), b.to(DEV)
+    y16 = torch.zeros(B, 3, H, W, dtype=torch.bfloat16, device=DEV)
+    y8 = torch.zeros(B, H, W, 3, dtype=torch.uint8, device=DEV)
+    for y in (y16, y8):
+        _lib.check(_lib.lib().hatb200_conv_last(_p(xd), _lib.BF16, B, H, W, _p(wd), _p(bd), 3, m4, 1.0, _p(y),
+                                                _lib.dtype_code(y.dtype), 1, _stream()))
+    torch.cuda.synchronize()
+    assert y16.float().min() < 0 and y16.float().max() > 1
+    want = torch.stack([torch.from_numpy(tensor2img(y16[i:i + 1])) for i in range(B)])
+    assert torch.equal(y8.cpu(), want)
 
 
 @pytest.mark.parametrize("B,Cn,hw", [(1, 180, 1024), (3, 144, 4096), (16, 180, 4096)])

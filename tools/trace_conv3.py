@@ -12,7 +12,7 @@ from super_resolution_b200 import _lib
 lib = C.CDLL(_lib.LIB_PATH)
 L = _lib.lib()
 p = lambda t: None if t is None else C.c_void_p(t.data_ptr())
-B, H, W = 16, 64, 64
+B, H, W = int(os.environ.get("TRACE_B", "16")), 64, 64
 Cin, N = int(sys.argv[1]) if len(sys.argv) > 1 else 180, int(sys.argv[2]) if len(sys.argv) > 2 else 60
 ACT = int(sys.argv[3]) if len(sys.argv) > 3 else 0          # 1: GELU (CAB conv1)
 M = B * H * W
