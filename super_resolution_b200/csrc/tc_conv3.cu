@@ -531,8 +531,11 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       } else {
         run_tile<F, GROUPED>(ep, ws, ri, ts, &tmOF, &tmOT, &tmLN);
         tc_fence_before();
-        if (TWO) mbar_arrive_cluster(empty0[g]);      // rank 0 issues the next MMAs into both CTAs' stage g
-        else mbar_arrive(&tmem_empty_bar[g]);
+        // rank 0 issues the next MMAs into both CTAs' stage g.  Relaxed (tc_common.cuh): the barrier only guards the TMEM
+        // stage, whose loads / stores have completed (wait::ld / wait::st); a release would also wait for the generic
+        // stores of the tile (pool partials, LayerNorm head) at GPU scope
+        if (TWO) mbar_arrive_relaxed_cluster(empty0[g]);
+        else mbar_arrive_relaxed(&tmem_empty_bar[g]);
       }
       if (tr) C3_TRACE(18 + 4 * i);
     }

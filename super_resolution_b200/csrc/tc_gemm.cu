@@ -320,7 +320,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const Tile2D ts{m0};
       run_tile<F, GROUPED, Tile2D, PRE, SPLIT>(ep, ws, ri, ts, pOF, &tmOT, pLN);
       tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[g]);
+      mbar_arrive_relaxed(&tmem_empty_bar[g]);      // guards the TMEM stage only (tc_common.cuh)
       if (tr) G3_TRACE(26 + g * 16 + 4 * (i >> 1));
     }
     if (elect_one()) bulk_wait_all();       // staging buffers must outlive the last stores
