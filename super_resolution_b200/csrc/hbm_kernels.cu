@@ -68,11 +68,15 @@ dwgate_bf16_kernel(const __grid_constant__ CUtensorMap tmIn, int H, int W, int h
   uint8_t* sp = dw_smem;
   uint8_t* sg = sp + DW_HALF_BYTES;
   __shared__ __align__(8) uint64_t bar;
+  // Blocks are dispatched in blockIdx order, z slowest; fc1 (the producer of `in`) wrote sample 0 first and sample B - 1
+  // last, and 94 MB of H1 do not all stay in L2.  Walking the samples (and tiles) BACKWARDS starts with what fc1 wrote
+  // last -- still resident -- instead of evicting it while re-fetching the oldest part from HBM.
   const int tiles_x = W / DW_TW;
-  const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+  const int bxr = (int)(gridDim.x - 1 - blockIdx.x);
+  const int tx = bxr % tiles_x, ty = bxr / tiles_x;
   const int x0 = tx * DW_TW, y0 = ty * DW_TH;
   const int c0 = blockIdx.y * DW_CC;
-  const int b = blockIdx.z;
+  const int b = (int)(gridDim.z - 1 - blockIdx.z);
   if (threadIdx.x == 0) {
     tc::mbar_init(&bar, 1);
     tc::fence_barrier_init();
