@@ -331,6 +331,10 @@ struct Fwd {
       ep.eca_u = w.U; ep.eca_pitch = d.Cp; ep.eca_scale = w.eca_s; ep.eca_coef = c.conv_scale;
       ep.resid = src; ep.resid_pitch = d.C; ep.out_f32 = dst; ep.out_f32_pitch = d.C;
       set_ln(ep, &b.n2, w.XN2, 0);
+      // backwards: the fp32 stream `src` was written front to back by the previous block three launches ago, so its
+      // tail is what L2 still holds; starting there saves HBM reads that a front-to-back walk would evict first
+      static const bool fwd_only = getenv("HATB200_WALK_BACK") && getenv("HATB200_WALK_BACK")[0] == '0';
+      ep.walk_back = fwd_only ? 0 : 1;
       HB_TRY(conv("esc_aggr", b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
     if (c.arch == 1) {  // HATX SpatialGateDConvFFN (hatx_arch.py:160-180): fc1 -> [dw3x3(xa) * SiLU(xb) | xb] -> fc2

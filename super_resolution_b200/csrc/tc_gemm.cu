@@ -63,6 +63,7 @@ struct G3Params {
   int ops, op_stage_bytes, op_u_off;   // operand ring per warpgroup
   int has_resid, has_u;
   int pre, pre_stages, off_pre;        // fp32 residual preloaded into the accumulator (tcgen05.cp), its TMA ring
+  int rev;                             // walk the token tiles from the last to the first (Epilogue::walk_back)
   int split;                           // N-split CTA pairs: BN is HALF of the LayerNorm row, the cluster peer owns the rest
   uint32_t acc_stride, tmem_cols;
   // shared memory offsets (bytes from the 1024-aligned base)
@@ -122,6 +123,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int walker = SPLIT ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;      // which tiles this CTA walks ...
   const int wstep = SPLIT ? (int)(gridDim.x >> 1) : (int)gridDim.x;         // ... and in what stride
   const int n0 = SPLIT ? crank * p.BN : blockIdx.y * p.BN;
+  // first token of the t-th tile this launch walks: backwards when p.rev (the launch then STARTS with the rows its
+  // producer wrote last, which L2 still holds -- see launch_gemm_tc)
+  auto row0 = [&](int t) { return (p.rev ? p.m_tiles - 1 - t : t) * G3_TILE_M; };
   constexpr int A_BYTES = G3_TILE_M * G3_BK * 2;
   float* tab_bias = reinterpret_cast<float*>(smem + p.off_tab);   // [BN]
   float* tab_gamma = tab_bias + p.BN;                             // [BN]
@@ -184,11 +188,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int tn = t + wstep;
         for (int kb = 0; kb < p.kblocks; kb++, rp.next(p.stages)) {
           const int s = rp.s;
-          if (PRE && p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmA, p.a_coff + kb * G3_BK, tn * G3_TILE_M);
+          if (PRE && p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmA, p.a_coff + kb * G3_BK, row0(tn));
           mbar_wait(&empty_bar[s], rp.ph ^ 1u);
           uint8_t* sa = smem + p.off_a + (size_t)s * p.stage_bytes;
           mbar_arrive_expect_tx(&full_bar[s], tx);
-          tma_load_2d(sa, &tmA, &full_bar[s], p.a_coff + kb * G3_BK, t * G3_TILE_M);
+          tma_load_2d(sa, &tmA, &full_bar[s], p.a_coff + kb * G3_BK, row0(t));
           if (!p.b_resident) tma_load_2d(sa + A_BYTES, &tmB, &full_bar[s], kb * G3_BK, n0);
         }
       }
@@ -244,10 +248,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int t = walker; t < p.m_tiles; t += wstep) {
         const int tn = t + wstep;                      // this CTA's next tile: start it towards L2 now (p.l2_ahead)
         for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
-          if (p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmR, n0 + 32 * c, tn * G3_TILE_M);
+          if (p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmR, n0 + 32 * c, row0(tn));
           mbar_wait(&pre_empty[pp.s], pp.ph ^ 1u);
           mbar_arrive_expect_tx(&pre_full[pp.s], (uint32_t)G3_PRE_BYTES);
-          tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, t * G3_TILE_M);
+          tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, row0(t));
         }
       }
     }
@@ -264,9 +268,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int i = 0;
       for (int t = walker; t < p.m_tiles; t += wstep, i++) {
         if ((i & 1) != g) continue;
-        const Tile2D ts{t * G3_TILE_M};
+        const Tile2D ts{row0(t)};
         const int tn = t + 2 * wstep;                   // this warpgroup's next tile
-        const Tile2D nx{tn * G3_TILE_M};
+        const Tile2D nx{row0(tn)};
         produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, ring_resid,
                      p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr);
       }
@@ -304,7 +308,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int i = 0;
     for (int t = walker; t < p.m_tiles; t += wstep, i++) {
       if ((i & 1) != g) continue;
-      const int m0 = t * G3_TILE_M;
+      const int m0 = row0(t);
       RowInfo ri;
       ri.m = m0 + ws.row;
       ri.b = m0 / p.hw;                                  // a tile never straddles two samples (hw % 128 == 0)
@@ -562,6 +566,7 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
       HB_TRY(tc::make_tmap_bf16(&tmLN1, (const bf16*)ep.ln_out + p.BN, 2, dims, str, box, w16 * 2));
     }
   }
+  p.rev = ep.walk_back ? 1 : 0;
   p.trace = nullptr; p.prof = 0;
   p.l2_ahead = getenv("HATB200_G3_L2AHEAD") ? atoi(getenv("HATB200_G3_L2AHEAD")) : 0;
   if (getenv("HATB200_GEMM_TRACE")) {
