@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define HATB200_VERSION 100
+#define HATB200_VERSION 101
 #define HATB200_MAX_LAYERS 32
 
 enum { HATB200_F32 = 0, HATB200_BF16 = 1, HATB200_F16 = 2, HATB200_I64 = 3,

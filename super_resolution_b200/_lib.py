@@ -120,8 +120,8 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
-        if l.hatb200_version() != 100:
-            raise ImportError(f"libhatb200 version {l.hatb200_version()} does not match this binding (100)")
+        if l.hatb200_version() != 101:
+            raise ImportError(f"libhatb200 version {l.hatb200_version()} does not match this binding (101)")
         _lib = l
     return _lib
 

@@ -72,7 +72,7 @@ def test_no_cpu_path():
 
 def test_library_loads_and_exports_every_declared_symbol():
     l = _lib.lib()
-    assert l.hatb200_version() == 100
+    assert l.hatb200_version() == 101
     header = open(os.path.join(ROOT, "include", "hatb200.h")).read()
     product, eng = re.subn(r"#ifdef HATB200_ENGINEERING.*?#endif", "", header, flags=re.S)
     assert eng == 1
