@@ -186,6 +186,14 @@ struct Fwd {
     return conv(tag, cw, A, 64, 0, H, W, ep);
   }
 
+  // The fp32 residual stream of the blocks (XB: M x C x 4 bytes, read and rewritten in place by esc_aggr and fc2 of every
+  // block) is kept in L2 with the evict_last policy when it is comfortably smaller than L2 (47 MB of 126 MB at the
+  // bench shape); larger streams would only thrash among themselves.
+  int pin_stream() const {
+    static const int mode = getenv("HATB200_L2_PIN") ? atoi(getenv("HATB200_L2_PIN")) : 1;
+    return mode && (size_t)d.M * d.C * 4 <= ((size_t)56 << 20);
+  }
+
   // will conv(tag, ...) run on the persistent 3x3 kernel in a way that can carry a side job (side_jobs.cuh)?
   bool side_ok(const char* tag, const ConvW& cw, const void* A, int a_pitch, int H, int W, Epilogue ep) const {
     static const bool off = getenv("HATB200_SIDE_JOBS") && getenv("HATB200_SIDE_JOBS")[0] == '0';     // engineering: A/B
@@ -335,6 +343,7 @@ struct Fwd {
       // tail is what L2 still holds; starting there saves HBM reads that a front-to-back walk would evict first
       static const bool fwd_only = getenv("HATB200_WALK_BACK") && getenv("HATB200_WALK_BACK")[0] == '0';
       ep.walk_back = fwd_only ? 0 : 1;
+      ep.pin_stream = pin_stream();
       HB_TRY(conv("esc_aggr", b.esc.aggr, w.XN, d.Cp, 0, d.H, d.W, ep));
     }
     if (c.arch == 1) {  // HATX SpatialGateDConvFFN (hatx_arch.py:160-180): fc1 -> [dw3x3(xa) * SiLU(xb) | xb] -> fc2
@@ -353,6 +362,7 @@ struct Fwd {
       HB_TRY(conv("ffn_fc1", b.fc1, w.XN2, d.Cp, 0, d.H, d.W, ep));
       Epilogue e2; e2.resid = dst; e2.resid_pitch = d.C; e2.out_f32 = dst; e2.out_f32_pitch = d.C;
       set_ln(e2, next_ln, w.XN, next_head);
+      e2.pin_stream = pin_stream();
       // depthwise 3x3 + gate + fc2 + residual + LayerNorm in one persistent tcgen05 kernel: the gated middle G never
       // reaches HBM (tc_ffn.cu)
       FfnTailArgs fa{w.H1, d.hp4, d.B, d.H, d.W, d.hid, b.dw_w, b.dw_b, b.fc2.w16, b.fc2.O, b.fc2.Npad, b.fc2.Kpad};

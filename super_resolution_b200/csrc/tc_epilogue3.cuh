@@ -41,6 +41,25 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* s
                "r"(smem_u32(src)), "r"(c0), "r"(c1)
                : "memory");
 }
+// L2 eviction-priority policy for the fp32 residual stream (47 MB at the bench shape, read and rewritten in place by two
+// launches of every block): evict_last keeps it resident across the ~600 MB of other traffic per block.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void tma_store_2d_hint(const CUtensorMap* m, const void* src, int c0, int c1, uint64_t pol) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], "
+      "[%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(pol)
+      : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
@@ -154,6 +173,7 @@ struct Stager {
   static constexpr int BUF = 32 * RB;
   uint8_t* base;
   uint32_t n = 0;                    // stores issued by this warp
+  uint64_t policy = 0;               // != 0: L2 cache-hint policy of the stores (Tile2D only)
   int nbuf = 2;                      // 2: double buffered; 1: single buffer (shared memory is short)
   __device__ __forceinline__ uint8_t* buf() const { return base + (nbuf == 2 ? (n & 1) : 0) * BUF; }
   // before the first write of a group: the store that last read this buffer must be done reading it
@@ -192,7 +212,7 @@ struct Stager {
     fence_proxy_async();
     __syncwarp();
     if (elect_one()) {               // same leader every time (full mask): bulk groups are per-thread state
-      ts.store(tm, buf(), c0, quarter);
+      ts.store(tm, buf(), c0, quarter, policy);
       bulk_commit();
     }
     n++;
@@ -204,11 +224,13 @@ struct Stager {
 // Tile2D: rows are 128 consecutive tokens m0 .. m0+127; store maps are 2-D (col, token), box {w, 32}.
 struct Tile2D {
   int m0;
-  __device__ __forceinline__ void store(const CUtensorMap* tm, const void* src, int col, int quarter) const {
-    tma_store_2d(tm, src, col, m0 + quarter * 32);
+  __device__ __forceinline__ void store(const CUtensorMap* tm, const void* src, int col, int quarter, uint64_t pol = 0) const {
+    if (pol) tma_store_2d_hint(tm, src, col, m0 + quarter * 32, pol);
+    else tma_store_2d(tm, src, col, m0 + quarter * 32);
   }
-  __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col) const {
-    tma_load_2d(dst, tm, bar, col, m0);
+  __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col, uint64_t pol = 0) const {
+    if (pol) tma_load_2d_hint(dst, tm, bar, col, m0, pol);
+    else tma_load_2d(dst, tm, bar, col, m0);
   }
   __device__ __forceinline__ void prefetch(const CUtensorMap* tm, int col) const { tma_prefetch_2d(tm, col, m0); }
 };
@@ -219,7 +241,7 @@ struct Tile4D {
   int r = 1, H = 0;      // r > 1: conv + PixelShuffle(r) with (i, j, c)-ordered columns: the 64-column block starting at
                          // `col` is sub-pixel (i, j) = (col/64 / r, col/64 % r) of every pixel of the tile; the store map
                          // is 5-D {c, j, x, i, b*H + y} over the (B, H*r, W*r, 64) output
-  __device__ __forceinline__ void store(const CUtensorMap* tm, const void* src, int col, int quarter) const {
+  __device__ __forceinline__ void store(const CUtensorMap* tm, const void* src, int col, int quarter, uint64_t = 0) const {
     if (r > 1) {
       const int blk = col >> 6, i = blk / r, j = blk - i * r;
       tma_store_5d(tm, src, 0, j, x0, i, b * H + y0 + quarter * 4);
@@ -227,7 +249,7 @@ struct Tile4D {
       tma_store_4d(tm, src, col, x0, y0 + quarter * 4, b);
     }
   }
-  __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col) const {
+  __device__ __forceinline__ void load(void* dst, const CUtensorMap* tm, uint64_t* bar, int col, uint64_t = 0) const {
     tma_load_4d(dst, tm, bar, col, x0, y0, b);
   }
   __device__ __forceinline__ void prefetch(const CUtensorMap* tm, int col) const { tma_prefetch_4d(tm, col, x0, y0, b); }
@@ -596,7 +618,7 @@ __device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tm
                                              const CUtensorMap* tmU, uint8_t* ring,
                                              uint64_t* op_full, uint64_t* op_empty, int ops, int op_stage_bytes,
                                              int op_u_off, int has_resid, int has_u, int n0, int nch, RingPos& k,
-                                             const TS* next = nullptr) {
+                                             const TS* next = nullptr, uint64_t resid_policy = 0) {
   const uint32_t bytes = (uint32_t)((has_resid ? 128 * CW * 4 : 0) + (has_u ? 128 * CW * 2 : 0));
   for (int ci = 0; ci < nch; ci++, k.next(ops)) {
     const int s = k.s;
@@ -609,7 +631,7 @@ __device__ __forceinline__ void produce_tile(const TS& ts, const CUtensorMap* tm
     mbar_wait(&op_empty[s], k.ph ^ 1u);
     uint8_t* st = ring + (size_t)s * op_stage_bytes;
     mbar_arrive_expect_tx(&op_full[s], bytes);
-    if (has_resid) ts.load(st, tmR, &op_full[s], n0 + ci * CW);
+    if (has_resid) ts.load(st, tmR, &op_full[s], n0 + ci * CW, resid_policy);
     if (has_u) ts.load(st + op_u_off, tmU, &op_full[s], n0 + ci * CW);
   }
 }

@@ -64,6 +64,7 @@ struct G3Params {
   int has_resid, has_u;
   int pre, pre_stages, off_pre;        // fp32 residual preloaded into the accumulator (tcgen05.cp), its TMA ring
   int rev;                             // walk the token tiles from the last to the first (Epilogue::walk_back)
+  int pin;                             // fp32 residual stream in / out with the L2 evict_last policy (Epilogue::pin_stream)
   int split;                           // N-split CTA pairs: BN is HALF of the LayerNorm row, the cluster peer owns the rest
   uint32_t acc_stride, tmem_cols;
   // shared memory offsets (bytes from the 1024-aligned base)
@@ -245,13 +246,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       prefetch_tmap(&tmR);
       pdl_wait();
       RingPos pp;
+      const uint64_t pol = p.pin ? l2_policy_evict_last() : 0;
       for (int t = walker; t < p.m_tiles; t += wstep) {
         const int tn = t + wstep;                      // this CTA's next tile: start it towards L2 now (p.l2_ahead)
         for (int c = 0; c < p.BN / 32; c++, pp.next(p.pre_stages)) {
           if (p.l2_ahead && tn < p.m_tiles) tma_prefetch_2d(&tmR, n0 + 32 * c, row0(tn));
           mbar_wait(&pre_empty[pp.s], pp.ph ^ 1u);
           mbar_arrive_expect_tx(&pre_full[pp.s], (uint32_t)G3_PRE_BYTES);
-          tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, row0(t));
+          if (p.pin) tma_load_2d_hint(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, row0(t), pol);
+          else tma_load_2d(smem + p.off_pre + (size_t)pp.s * G3_PRE_BYTES, &tmR, &pre_full[pp.s], n0 + 32 * c, row0(t));
         }
       }
     }
@@ -272,7 +275,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int tn = t + 2 * wstep;                   // this warpgroup's next tile
         const Tile2D nx{row0(tn)};
         produce_tile(ts, &tmR, &tmU, ring, op_full[g], op_empty[g], p.ops, p.op_stage_bytes, p.op_u_off, ring_resid,
-                     p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr);
+                     p.has_u, n0, p.BN / CW, k, (p.l2_ahead && tn < p.m_tiles) ? &nx : nullptr,
+                     p.pin ? l2_policy_evict_last() : 0);
       }
     }
   } else {
@@ -297,6 +301,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const CUtensorMap* pOF = (SPLIT && crank) ? &tmOF1 : &tmOF;
     const CUtensorMap* pLN = (SPLIT && crank) ? &tmLN1 : &tmLN;
     ws.st32.nbuf = ws.st16.nbuf = p.stg_bufs;
+    if (p.pin) ws.st32.policy = l2_policy_evict_last();
     ws.st32.base = smem + p.off_stg32 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st32)::BUF);
     ws.st16.base = smem + p.off_stg16 + (size_t)ws.ew * (p.stg_bufs * decltype(ws.st16)::BUF);
     if (lane == 0) {
@@ -567,6 +572,7 @@ int launch_gemm_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const E
     }
   }
   p.rev = ep.walk_back ? 1 : 0;
+  p.pin = ep.pin_stream ? 1 : 0;
   p.trace = nullptr; p.prof = 0;
   p.l2_ahead = getenv("HATB200_G3_L2AHEAD") ? atoi(getenv("HATB200_G3_L2AHEAD")) : 0;
   if (getenv("HATB200_GEMM_TRACE")) {
