@@ -162,7 +162,7 @@ struct Epilogue {
   float* ln_head_colsum = nullptr;   // fp32 (num_m_tiles, ln_head_c) per-tile column sums of the LN head
   float* colsum = nullptr;           // fp32 (num_m_tiles, N) per-tile column sums of v (GAP partials)
   int pin_stream = 0;                // tc_gemm.cu: fp32 residual in / out carry the L2 evict_last policy (see forward.cu)
-  int walk_back = 0;                 // tc_gemm.cu: walk the token tiles from the last to the first (same result; see forward.cu)
+  int walk_back = 0;                 // tc_gemm.cu / tc_conv3.cu: walk the tiles from the last to the first (same result; forward.cu)
   SideJob side;                      // honoured by tc_conv3.cu only (the caller checks conv3_tc_supported first)
   // conv_last in one pass (tc_conv3.cu, FeatLast; hat_arch.py:858): y = (acc + bias) / img_range + mean written straight
   // to the NCHW image (nchw_dt F32 / BF16), or, nchw_dt = HATB200_U8, tensor2img of it (img_util.py:38-95: the value as

@@ -72,6 +72,7 @@ struct C3Params {
   int rot;                       // start tap rotated per CTA (HATB200_C3_ROT=0 disables)
   int shuf_r;                    // > 1: pixel-shuffle store (columns pre-permuted to (i, j, c))
   int lean;                      // MMA issue through the unrolled c3_issue_tiles (grp == 3, kblocks 1 or 3, no tap rotation)
+  int rev;                       // walk the tiles from the last to the first (Epilogue::walk_back)
   int main_ctas;                 // CTAs that walk tiles; blockIdx.x >= main_ctas runs ep.side (side_jobs.cuh) and exits
   int probe;                     // engineering (HATB200_C3_PROBE=1, with tracing): time 64 back-to-back MMAs before the tile loop
 };
@@ -143,10 +144,13 @@ __device__ __noinline__ void c3_issue_tiles(const C3Issue a) {
   }
 }
 
-__device__ __forceinline__ void tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
+// the t-th tile of the walk (backwards when p.rev: Epilogue::walk_back); returns the tile's index in image order
+__device__ __forceinline__ int tile_coords(const C3Params& p, int t, int& x0, int& y0, int& b) {
+  if (p.rev) t = p.tiles - 1 - t;
   const int tx = t % p.tiles_x, ty = (t / p.tiles_x) % p.tiles_y;
   b = t / (p.tiles_x * p.tiles_y);
   x0 = tx * C3_TW; y0 = ty * C3_TH;
+  return t;
 }
 
 }  // namespace
@@ -488,14 +492,14 @@ conv3_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int t = t_first; t < p.tiles; t += t_step, i++) {
       if ((i & 1) != g) continue;
       Tile4D ts;
-      tile_coords(p, t, ts.x0, ts.y0, ts.b);
+      const int te = tile_coords(p, t, ts.x0, ts.y0, ts.b);
       ts.r = p.shuf_r; ts.H = p.H;
       RowInfo ri;
       ri.b = ts.b;
       ri.py = ts.y0 + ws.row / C3_TW; ri.px = ts.x0 + ws.row % C3_TW;
       ri.m = (ts.b * p.H + ri.py) * p.W + ri.px;
       ri.nchunk = p.tiles_x * p.tiles_y;
-      ri.chunk = t - ts.b * ri.nchunk;
+      ri.chunk = te - ts.b * ri.nchunk;
       ri.trow = tmem_base + (uint32_t)g * p.acc_stride + ((uint32_t)(ws.quarter * 32) << 16);
       const bool tr = ws.wg_tid == 0 && i < 4;
       if (tr) C3_TRACE(16 + 4 * i);
@@ -728,6 +732,7 @@ int launch_conv3_tc(const ConvArgs& a, const bf16* w, int Npad, int Kpad, const 
     HB_TRY(map4(&tmOT, false, (const bf16*)ep.out_t + ep.out_t_coff, width, ep.out_t_pitch, w16, C3_TW, 4));
   }
   if (ep.ln_out) HB_TRY(map4(&tmLN, false, ep.ln_out, ep.ln_pitch, ep.ln_pitch, w16, C3_TW, 4));
+  p.rev = ep.walk_back ? 1 : 0;
   p.trace = gemm_trace_arm(st);
   p.rot = getenv("HATB200_C3_ROT") ? atoi(getenv("HATB200_C3_ROT")) : 1;
   if (p.lean) p.rot = 0;         // the unrolled issuer walks the taps in order
