@@ -461,6 +461,7 @@ struct Fwd {
     HB_TRY(dbg("attention"));
     {  // proj + shortcut, norm2
       Epilogue ep; ep.resid = x; ep.resid_pitch = d.C; ep.out_f32 = x; ep.out_f32_pitch = d.C;
+      ep.pin_stream = pin_stream();
       set_ln(ep, &o.n2, w.XN2, 0);
       if (use_attn_tc) HB_TRY(conv("ocab_proj", o.proj_tc, w.G, hp, 0, d.H, d.W, ep));
       else HB_TRY(conv("ocab_proj", o.proj, w.G, d.Cp, 0, d.H, d.W, ep));
@@ -469,6 +470,7 @@ struct Fwd {
       Epilogue ep; ep.act = ACT_GELU; ep.out_t = w.H1; ep.out_t_pitch = d.hp2; ep.out_t_zero_to = d.hp2;
       HB_TRY(conv("ocab_mlp0", o.mlp0, w.XN2, d.Cp, 0, d.H, d.W, ep));
       Epilogue e2; e2.resid = x; e2.resid_pitch = d.C; e2.out_f32 = x; e2.out_f32_pitch = d.C;
+      e2.pin_stream = pin_stream();
       if (want_copy) { e2.out_t = w.XN2; e2.out_t_pitch = d.Cp; e2.out_t_zero_to = d.Cp; }
       HB_TRY(conv("ocab_mlp2", o.mlp2, w.H1, d.hp2, 0, d.H, d.W, e2));
     }
