@@ -80,51 +80,79 @@ int launch_layernorm(const float* x, int M, int C, const float* gamma, const flo
 // address (one broadcast transaction), reused by the 32 tokens.  0.3 loads per FMA instead of 0.5 with all 27 inputs
 // re-read by each of a token's 45 threads (B200: 131 us for 65 536 tokens x 180 channels before).
 constexpr int CF_G = 5;                // float4 groups per thread (20 channels)
-template <typename T>
-__global__ void __launch_bounds__(256) conv_first_kernel(const T* __restrict__ x, int B, int IC, int H, int W,
+// Round 2: a BLOCK owns 32 consecutive tokens and all their channels (one warp per 20-channel group), parks the result
+// in shared memory and writes the 32 x C floats -- one contiguous piece of the token tensor -- with fully coalesced
+// 16-byte stores.  Storing from the accumulators scattered every float4 over 32 different 720-byte rows (78 us per
+// forward in the ncu launch list for 47 MB of output).
+// ICT / CT: in_chans / embed_dim known at compile time (0 = run time).  With both, the 9 * IC inputs of a token load up
+// front and every weight read is ld.shared at an immediate offset with no bounds test: 41 M -> 14 M warp instructions
+// (the run-time form spent two thirds of its issue slots on index arithmetic and the `c < C` tests).
+template <typename T, int ICT, int CT>
+__global__ void __launch_bounds__(512) conv_first_kernel(const T* __restrict__ x, int B, int ICr, int H, int W,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
-                                                         int C, float4 mean, float range, float* __restrict__ out) {
-  const int groups = (C + CF_G * 4 - 1) / (CF_G * 4);
+                                                         int Cr, float4 mean, float range, float* __restrict__ out) {
+  const int C = CT > 0 ? CT : Cr;
+  constexpr bool FULL = CT > 0 && CT % (CF_G * 4) == 0;     // every warp's 20-channel group is complete
+  extern __shared__ __align__(16) float cf_tile[];       // [32 tokens][C], then the weights [9 * IC][C]
+  const int IC = ICT > 0 ? ICT : ICr;
+  float* cf_w = cf_tile + 32 * C;
+  // weights in shared memory: every FMA quad reads a warp-uniform float4, and LDS broadcasts at one per clock where the
+  // same read through L1 (round 1) made the kernel load-issue bound (83 us for 318 MFMA)
+  for (int i = threadIdx.x; i < 9 * IC * C / 4; i += blockDim.x)
+    reinterpret_cast<float4*>(cf_w)[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
+  __syncthreads();
   const size_t M = (size_t)B * H * W;
   const int lane = threadIdx.x & 31;
-  const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;     // warp index: (token block, group)
-  const int grp = (int)(wid % groups);
-  const size_t m = (wid / groups) * 32 + lane;
-  if (m >= M) return;
+  const int grp = threadIdx.x >> 5;                      // 20-channel group of this warp
+  const size_t m0 = (size_t)blockIdx.x * 32;
+  const size_t m = m0 + lane;
   const int c0 = grp * CF_G * 4;
-  const int px = (int)(m % W);
-  const int py = (int)((m / W) % H);
-  const int b = (int)(m / ((size_t)W * H));
-  const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
-  float4 acc[CF_G];
+  if (m < M) {
+    const int px = (int)(m % W);
+    const int py = (int)((m / W) % H);
+    const int b = (int)(m / ((size_t)W * H));
+    const float mean_a[4] = {mean.x, mean.y, mean.z, mean.w};
+    float4 acc[CF_G];
 #pragma unroll
-  for (int q = 0; q < CF_G; q++)
-    acc[q] = (bias && c0 + 4 * q < C) ? __ldg(reinterpret_cast<const float4*>(bias + c0 + 4 * q)) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const T* xb = x + (size_t)b * IC * H * W;
+    for (int q = 0; q < CF_G; q++)
+      acc[q] = (bias && (FULL || c0 + 4 * q < C)) ? __ldg(reinterpret_cast<const float4*>(bias + c0 + 4 * q)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const T* xb = x + (size_t)b * IC * H * W;
+    auto fma_tap = [&](int t, float v) {                  // t = (ky * 3 + kx) * IC + i
+      const float* wr = cf_w + t * C + c0;
 #pragma unroll
-  for (int ky = 0; ky < 3; ky++) {
-    const int yy = py + ky - 1;
-#pragma unroll
-    for (int kx = 0; kx < 3; kx++) {
-      const int xx = px + kx - 1;
-      const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
-      for (int i = 0; i < IC; i++) {
-        // zero padding applies to the NORMALISED image (hat_arch.py:849-853): a pad pixel contributes nothing
-        const float v = in ? (to_f(xb[((size_t)i * H + yy) * W + xx]) - mean_a[i]) * range : 0.f;
-        const float* wr = w + ((ky * 3 + kx) * IC + i) * C + c0;
-#pragma unroll
-        for (int q = 0; q < CF_G; q++) {
-          if (c0 + 4 * q >= C) break;
-          const float4 wv = __ldg(reinterpret_cast<const float4*>(wr + 4 * q));
-          acc[q].x = fmaf(v, wv.x, acc[q].x); acc[q].y = fmaf(v, wv.y, acc[q].y);
-          acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
-        }
+      for (int q = 0; q < CF_G; q++) {
+        if (!FULL && c0 + 4 * q >= C) break;
+        const float4 wv = *reinterpret_cast<const float4*>(wr + 4 * q);
+        acc[q].x = fmaf(v, wv.x, acc[q].x); acc[q].y = fmaf(v, wv.y, acc[q].y);
+        acc[q].z = fmaf(v, wv.z, acc[q].z); acc[q].w = fmaf(v, wv.w, acc[q].w);
       }
-    }
-  }
+    };
+    // zero padding applies to the NORMALISED image (hat_arch.py:849-853): a pad pixel contributes nothing
+    auto input = [&](int ky, int kx, int i) {
+      const int yy = py + ky - 1, xx = px + kx - 1;
+      const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      return in ? (to_f(xb[((size_t)i * H + yy) * W + xx]) - mean_a[i]) * range : 0.f;
+    };
+    if (ICT > 0) {
+      float v[9 * (ICT > 0 ? ICT : 1)];                   // all loads in flight before the first FMA needs one
 #pragma unroll
-  for (int q = 0; q < CF_G; q++)
-    if (c0 + 4 * q < C) *reinterpret_cast<float4*>(out + m * C + c0 + 4 * q) = acc[q];
+      for (int t = 0; t < 9 * ICT; t++) v[t] = input(t / (3 * ICT), (t / ICT) % 3, t % ICT);
+#pragma unroll
+      for (int t = 0; t < 9 * ICT; t++) fma_tap(t, v[t]);
+    } else {
+      for (int ky = 0; ky < 3; ky++)
+        for (int kx = 0; kx < 3; kx++)
+          for (int i = 0; i < IC; i++) fma_tap((ky * 3 + kx) * IC + i, input(ky, kx, i));
+    }
+#pragma unroll
+    for (int q = 0; q < CF_G; q++)
+      if (FULL || c0 + 4 * q < C) *reinterpret_cast<float4*>(cf_tile + (size_t)lane * C + c0 + 4 * q) = acc[q];
+  }
+  __syncthreads();
+  const size_t rows = M - m0 < 32 ? M - m0 : 32;
+  const size_t n4 = rows * C / 4;                        // the block's rows are one contiguous piece of `out`
+  float4* dst = reinterpret_cast<float4*>(out + m0 * C);
+  for (size_t i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = reinterpret_cast<const float4*>(cf_tile)[i];
 }
 
 // generic channel count (C % 4 != 0): one thread per (token, channel)
@@ -161,16 +189,23 @@ int launch_conv_first(const void* x, int x_dt, int B, int IC, int H, int W, cons
                       const float* mean, float range, float* out, cudaStream_t st) {
   HB_REQUIRE(IC >= 1 && IC <= 4, HATB200_EUNSUPPORTED, "conv_first: in_chans=%d not in 1..4", IC);
   float4 m4 = make_float4(mean[0], mean[1], mean[2], mean[3]);
-  const bool v4 = C % 4 == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)out & 15) == 0 && (!bias || ((uintptr_t)bias & 15) == 0);
-  // vector kernel: one warp per (32 tokens, 20-channel group); scalar kernel: one thread per (token, channel)
+  // vector kernel: one block per 32 tokens, one warp per 20-channel group; scalar kernel: one thread per (token, channel)
   const size_t M = (size_t)B * H * W;
-  size_t total = v4 ? ((M + 31) / 32) * (size_t)((C + CF_G * 4 - 1) / (CF_G * 4)) * 32 : M * C;
+  const int groups = (C + CF_G * 4 - 1) / (CF_G * 4);
+  const bool v4 = C % 4 == 0 && groups <= 16 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)out & 15) == 0 &&
+                  (!bias || ((uintptr_t)bias & 15) == 0);
   HB_DISPATCH_T(x_dt, T, {
-    if (v4)
-      conv_first_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
-                                                                           range, out);
+    if (v4 && IC == 3 && C == 180)
+      conv_first_kernel<T, 3, 180><<<(unsigned)((M + 31) / 32), groups * 32, (size_t)(32 + 9 * IC) * C * sizeof(float), st>>>(
+          (const T*)x, B, IC, H, W, w, bias, C, m4, range, out);
+    else if (v4 && IC == 3)
+      conv_first_kernel<T, 3, 0><<<(unsigned)((M + 31) / 32), groups * 32, (size_t)(32 + 9 * IC) * C * sizeof(float), st>>>(
+          (const T*)x, B, IC, H, W, w, bias, C, m4, range, out);
+    else if (v4)
+      conv_first_kernel<T, 0, 0><<<(unsigned)((M + 31) / 32), groups * 32, (size_t)(32 + 9 * IC) * C * sizeof(float), st>>>(
+          (const T*)x, B, IC, H, W, w, bias, C, m4, range, out);
     else
-      conv_first_kernel1<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
+      conv_first_kernel1<T><<<(unsigned)((M * C + 255) / 256), 256, 0, st>>>((const T*)x, B, IC, H, W, w, bias, C, m4,
                                                                             range, out);
   });
   HB_CHECK_LAUNCH();
