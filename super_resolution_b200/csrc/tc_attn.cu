@@ -99,6 +99,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __shared__ __align__(8) uint64_t s_full[2][2], s_empty[2][2];
   __shared__ __align__(8) uint64_t p_full[2][2], pv_done[2][2];
   __shared__ uint32_t tmem_slot;
+  __shared__ unsigned long long uoff[2];     // per Q stage: element offset of the unit's (window origin, head) in `out`
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sm_q = smem;                                  // [2][Q 16 KB | bias 6 KB]
@@ -144,6 +145,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         const int qb = ui & 1;
         mbar_wait_relaxed(&q_empty[qb], (((uint32_t)ui >> 1) & 1u) ^ 1u);
         uint8_t* qs = sm_q + qb * QST_BYTES;
+        // the softmax warps need the unit only for their output address: one offset through shared memory instead of
+        // four integer divisions per thread and unit (published by the arrive below)
+        uoff[qb] = (((unsigned long long)b * p.H + wy * WS) * p.W + wx * WS) * (unsigned long long)p.out_pitch + head * DP;
         mbar_arrive_expect_tx(&q_full[qb], Q_BYTES + BIAS_BYTES);
         tma_load_4d(qs, &tmQ, &q_full[qb], head * DP, 0, wx * (WS / 2), b * p.H + wy * WS);          // even columns
         tma_load_4d(qs + Q_BYTES / 2, &tmQ, &q_full[qb], head * DP, 1, wx * (WS / 2), b * p.H + wy * WS);   // odd columns
@@ -255,11 +259,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #define AT_T(i) do { if (tr) { const long long c1 = clock64(); tc[i] += c1 - c0; c0 = c1; } } while (0)
     if (tr) c0 = clock64();
     int ui = 0;
+    const size_t my_off = ((size_t)qy * p.W + qx) * p.out_pitch;     // this thread's query inside the window
     for (int u = blockIdx.x; u < p.units; u += gridDim.x, ui++) {
-      const int head = u % p.heads, win = u / p.heads;
-      const int b = win / wins, wr = win % wins, wy = wr / p.nwx, wx = wr % p.nwx;
       const int qb = ui & 1;
       mbar_wait(&q_full[qb], ((uint32_t)ui >> 1) & 1u);
+      const unsigned long long unit_off = uoff[qb];
       AT_T(0);
       // bias(q, k) = table[(ky - qy + 15) * BP + kx - qx + 15]: this thread's (qy, qx) goes into the base address.
       // 15 - qx is even for warpgroup 1 (aligned pairs of table A) and odd for warpgroup 0, which reads the copy
@@ -396,7 +400,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mbar_arrive(&q_empty[qb]);        // bias tables of this stage consumed
       // O of this unit is complete once PV(5) has landed; it is picked up after chunk 0 of the next unit (`flush`)
       pend = true; pend_ui = ui; pend_l = l2.x + l2.y;
-      pend_row = p.out + (((size_t)b * p.H + wy * WS + qy) * p.W + wx * WS + qx) * p.out_pitch + head * DP;
+      pend_row = p.out + unit_off + my_off;
     }
     if (pend) flush();
     AT_T(7);
