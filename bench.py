@@ -59,7 +59,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.idx), "-lms", "100"],
+                                          "-i", str(self.idx), "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -70,11 +70,22 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
+    def mark(self):
+        """Start of the timed region: only samples taken from here on count (the sampler itself is started before the
+        warm-up, nvidia-smi needs 0.1-1 s to come up -- longer with eight ranks starting one each)."""
+        self.first = len(self.lines)
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.12)
+        time.sleep(0.03)
         self.proc.terminate()
+        window = "timed region"
+        if len(self.lines) > getattr(self, "first", 0):
+            self.lines = self.lines[getattr(self, "first", 0):]
+        else:                                   # the region was shorter than the sampler's first answer: warm-up samples
+            window = "warm-up (same workload) + timed region"
+        self.window = window
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ln in self.lines:
@@ -91,7 +102,7 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": self.window}
 
 
 def dist_env():
@@ -320,6 +331,8 @@ def run_ours(args):
     out_px = BATCH * (LR * 4) ** 2                           # delivered HR pixels per rank per step
     W, K = max(3, args.warmup), args.steps
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    clocks = ClockSampler(local)
+    clocks.start()                                           # comes up during the warm-up; windowed by mark() below
     for _ in range(W):
         y = net(x)
     torch.cuda.synchronize()
@@ -330,10 +343,9 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-resident throughput: K steps, CUDA events per step, L2 flushed between steps ----
-    clocks = ClockSampler(local)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     barrier()
-    clocks.start()
+    clocks.mark()
     for e0, e1 in ev:
         flush.zero_()
         e0.record()
